@@ -1,0 +1,209 @@
+"""ctypes binding of libibp_b200.so (the C ABI declared in include/ibp.h).
+
+There is no Python or CPU implementation behind these calls: if the shared library has not been built, or no CUDA
+device is visible, everything here raises — loudly — instead of falling back.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libibp_b200.so")
+
+NUM_PARTS, NUM_LIMBS, NUM_LAYERS = 18, 30, 50
+IBP_OK = 0
+ERR_NAMES = {-1: "IBP_ERR_SHAPE", -2: "IBP_ERR_PART", -3: "IBP_ERR_CAPACITY", -4: "IBP_ERR_CUDA", -5: "IBP_ERR_ARG",
+             -6: "IBP_ERR_NO_DEVICE"}
+IBP_F32, IBP_F16 = 0, 1
+LIMB_FULLRES_HWC, LIMB_FEAT_PLANAR = 0, 1
+PEAKS_CROSS_REFINE, PEAKS_BOX_CENTROID = 0, 1
+ST_PEAK_OVERFLOW, ST_CAND_OVERFLOW, ST_BODY_OVERFLOW, ST_HUMAN_OVERFLOW = 0x1, 0x2, 0x4, 0x8
+ST_TIE_EMULATED, ST_TIE_UNDEFINED = 0x10, 0x20
+
+
+class IbpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("%s (%d): %s" % (ERR_NAMES.get(code, "IBP_ERR"), code, msg))
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("limb_sample_thresh", C.c_float), ("step_ratio", C.c_float), ("min_parts", C.c_int32),
+                ("min_human_score", C.c_float), ("max_steps", C.c_int32), ("len_rate", C.c_int32),
+                ("merge_tolerance", C.c_float), ("weight_limb", C.c_float), ("weight_a", C.c_float),
+                ("weight_b", C.c_float), ("peak_thresh", C.c_float), ("upsample", C.c_int32),
+                ("refine_window", C.c_int32)]
+
+
+class Limits(C.Structure):
+    _fields_ = [("max_batch", C.c_int32), ("max_peaks_per_part", C.c_int32), ("max_candidates_per_limb", C.c_int32),
+                ("max_bodies", C.c_int32), ("max_humans", C.c_int32), ("max_feat_h", C.c_int32),
+                ("max_feat_w", C.c_int32)]
+
+
+class BatchView(C.Structure):
+    _fields_ = [("batch", C.c_int32), ("peak_stride", C.c_int32), ("human_stride", C.c_int32),
+                ("n_peaks", C.POINTER(C.c_int32)), ("part_count", C.POINTER(C.c_int32)), ("peaks", C.c_void_p),
+                ("n_humans", C.POINTER(C.c_int32)), ("humans", C.c_void_p), ("status", C.POINTER(C.c_uint32))]
+
+
+PEAK_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "<f4"), ("part", "<i4")])
+HUMAN_DTYPE = np.dtype([("peak_id", "<i4", (NUM_PARTS,)), ("score", "<f4"), ("total", "<f4"), ("count", "<i4"),
+                        ("reach", "<f4")])
+assert PEAK_DTYPE.itemsize == 16 and HUMAN_DTYPE.itemsize == 88
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises if it is missing (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("libibp_b200.so is not built: run `python improved-body-parts_b200/build.py` "
+                           "(or __graft_entry__.build()). There is no CPU fallback for this path.")
+    L = C.CDLL(LIB_PATH)
+    fp, vp, ip = C.POINTER(C.c_float), C.c_void_p, C.c_int
+    L.ibp_process_paf.restype = ip
+    L.ibp_process_paf.argtypes = [ip, ip, ip, vp, ip, ip, ip, vp, ip]
+    L.ibp_get_num_humans.restype = ip
+    L.ibp_get_part_peak_id.restype = ip
+    L.ibp_get_part_peak_id.argtypes = [ip, ip]
+    L.ibp_get_score.restype = C.c_float
+    L.ibp_get_score.argtypes = [ip]
+    L.ibp_get_part_x.restype = ip
+    L.ibp_get_part_x.argtypes = [ip]
+    L.ibp_get_part_y.restype = ip
+    L.ibp_get_part_y.argtypes = [ip]
+    L.ibp_get_part_score.restype = C.c_float
+    L.ibp_get_part_score.argtypes = [ip]
+    L.ibp_get_status.restype = C.c_uint32
+    L.ibp_default_params.argtypes = [C.POINTER(Params)]
+    L.ibp_default_limits.argtypes = [C.POINTER(Limits)]
+    L.ibp_create.restype = ip
+    L.ibp_create.argtypes = [C.POINTER(vp), ip, C.POINTER(Params), C.POINTER(Limits)]
+    L.ibp_destroy.argtypes = [vp]
+    L.ibp_last_error.restype = C.c_char_p
+    L.ibp_device_count.restype = ip
+    L.ibp_fuse_flip.restype = ip
+    L.ibp_fuse_flip.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
+    L.ibp_upsample_limbs.restype = ip
+    L.ibp_upsample_limbs.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
+    L.ibp_find_peaks.restype = ip
+    L.ibp_find_peaks.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp]
+    L.ibp_set_peaks.restype = ip
+    L.ibp_set_peaks.argtypes = [vp, ip, vp, ip, ip]
+    L.ibp_assign.restype = ip
+    L.ibp_assign.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp]
+    L.ibp_postprocess_batch.restype = ip
+    L.ibp_postprocess_batch.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp]
+    L.ibp_fetch.restype = ip
+    L.ibp_fetch.argtypes = [vp, ip, C.POINTER(BatchView), vp]
+    L.ibp_launch_count.restype = C.c_int64
+    L.ibp_launch_count.argtypes = [vp]
+    _lib = L
+    return L
+
+
+EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp_get_score", "ibp_get_part_x",
+           "ibp_get_part_y", "ibp_get_part_score", "ibp_get_status", "ibp_default_params", "ibp_default_limits",
+           "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_upsample_limbs",
+           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_launch_count"]
+
+
+def check(rc):
+    if rc != IBP_OK:
+        raise IbpError(rc, lib().ibp_last_error().decode("utf-8", "replace"))
+
+
+def default_params():
+    p = Params()
+    lib().ibp_default_params(C.byref(p))
+    return p
+
+
+def default_limits():
+    l = Limits()
+    lib().ibp_default_limits(C.byref(l))
+    return l
+
+
+class BatchResult:
+    """Host copy of one ibp_fetch: plain numpy, detached from the handle's pinned buffers."""
+
+    def __init__(self, view):
+        B = view.batch
+        self.batch = B
+        self.n_peaks = np.ctypeslib.as_array(view.n_peaks, (B,)).copy()
+        self.part_count = np.ctypeslib.as_array(view.part_count, (B, NUM_PARTS)).copy()
+        self.n_humans = np.ctypeslib.as_array(view.n_humans, (B,)).copy()
+        self.status = np.ctypeslib.as_array(view.status, (B,)).copy()
+        pk = (C.c_char * (B * view.peak_stride * PEAK_DTYPE.itemsize)).from_address(view.peaks)
+        hm = (C.c_char * (B * view.human_stride * HUMAN_DTYPE.itemsize)).from_address(view.humans)
+        peaks = np.frombuffer(pk, dtype=PEAK_DTYPE).reshape(B, view.peak_stride)
+        humans = np.frombuffer(hm, dtype=HUMAN_DTYPE).reshape(B, view.human_stride)
+        self.peaks = [peaks[b, :self.n_peaks[b]].copy() for b in range(B)]
+        self.humans = [humans[b, :self.n_humans[b]].copy() for b in range(B)]
+
+
+class Handle:
+    """Owner of one ibp_handle (device buffers + pinned result buffers) on one GPU."""
+
+    def __init__(self, device=0, params=None, limits=None, **limit_overrides):
+        L = lib()
+        if L.ibp_device_count() <= 0:
+            raise IbpError(-6, "no CUDA device visible: this library has no CPU path")
+        self.params = params or default_params()
+        self.limits = limits or default_limits()
+        for k, v in limit_overrides.items():
+            if not hasattr(self.limits, k):
+                raise TypeError("unknown limit %r" % k)
+            setattr(self.limits, k, v)
+        self._h = C.c_void_p()
+        check(L.ibp_create(C.byref(self._h), int(device), C.byref(self.params), C.byref(self.limits)))
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().ibp_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launches(self):
+        return int(lib().ibp_launch_count(self._h))
+
+    # ---- raw stage calls on device pointers (ints) ----
+    def fuse_flip(self, net_out_ptr, dtype, batch, fh, fw, fused_ptr, flip_avg=True, stream=0):
+        check(lib().ibp_fuse_flip(self._h, net_out_ptr, dtype, batch, fh, fw, int(bool(flip_avg)), fused_ptr, stream))
+
+    def upsample_limbs(self, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream=0):
+        check(lib().ibp_upsample_limbs(self._h, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream))
+
+    def find_peaks(self, maps_ptr, chan_stride, first_chan, batch, fh, fw, flavour=PEAKS_CROSS_REFINE, stream=0):
+        check(lib().ibp_find_peaks(self._h, maps_ptr, chan_stride, first_chan, batch, fh, fw, flavour, stream))
+
+    def set_peaks(self, image, joint_list):
+        a = np.ascontiguousarray(joint_list, dtype=np.float32).reshape(-1, 5)
+        check(lib().ibp_set_peaks(self._h, image, a.ctypes.data, a.shape[0], 5))
+
+    def assign(self, limb_ptr, mode, batch, dim0, dim1, dim2, min_img_size, stream=0):
+        check(lib().ibp_assign(self._h, limb_ptr, mode, batch, dim0, dim1, dim2, int(min_img_size), stream))
+
+    def postprocess_batch(self, net_out_ptr, on_host, dtype, batch, fh, fw, min_img_size, stream=0):
+        check(lib().ibp_postprocess_batch(self._h, net_out_ptr, int(bool(on_host)), dtype, batch, fh, fw,
+                                          int(min_img_size), stream))
+
+    def fetch(self, batch, stream=0, raise_on_overflow=True):
+        view = BatchView()
+        rc = lib().ibp_fetch(self._h, batch, C.byref(view), stream)
+        if rc != IBP_OK and (raise_on_overflow or rc != -3):
+            check(rc)
+        return BatchResult(view)

@@ -1,0 +1,39 @@
+"""In-tree build of libibp_b200.so (sm_100a only).  `python improved-body-parts_b200/build.py [--force]`.
+
+One translation unit (csrc/ibp_capi.cu includes the kernel headers), compiled with -fmad=false: the reference's
+numbers come from code without FMA contraction, and bit-exact parity needs the same roundings."""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libibp_b200.so")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
+         "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr"]
+
+
+def sources():
+    return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)) + \
+        [os.path.join(os.path.dirname(HERE), "include", "ibp.h")]
+
+
+def build(force=False, verbose=False):
+    srcs = sources()
+    if not force and os.path.exists(LIB) and all(os.path.getmtime(s) <= os.path.getmtime(LIB) for s in srcs):
+        return LIB
+    cmd = [NVCC] + FLAGS + [os.path.join(CSRC, "ibp_capi.cu"), "-o", LIB]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("nvcc failed")
+    if verbose:
+        print(res.stdout + res.stderr)
+    with open(os.path.join(HERE, "csrc", "..", "ptxas_info.txt"), "w") as f:
+        f.write(res.stdout + res.stderr)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose=True))

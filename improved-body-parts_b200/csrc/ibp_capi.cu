@@ -1,0 +1,625 @@
+// C ABI of libibp_b200.so (declared in include/ibp.h): handle management, launch wrappers, the legacy
+// seven-call protocol of the reference's pafprocess module, and the batched pipeline.
+// Host-side only: buffers, launch geometry, error reporting.  No compute happens on the CPU.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ibp_device.cuh"
+#include "k_fuse.cuh"
+#include "k_group.cuh"
+#include "k_limbs.cuh"
+#include "k_peaks.cuh"
+#include "k_upsample.cuh"
+
+using namespace ibp;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e__ = (call);                                                                         \
+        if (e__ != cudaSuccess) return fail(IBP_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+constexpr size_t kMaxDynSmem = 227 * 1024;
+constexpr size_t kPeakBandBytes = 64 * 1024;
+constexpr size_t kLimbPlaneMaxBytes = 96 * 1024;
+
+template <typename T>
+void free_dev(T *&p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+template <typename T>
+void free_host(T *&p) {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+}
+
+}  // namespace
+
+struct ibp_handle {
+    int device = 0;
+    ibp_params P;
+    ibp_limits L;
+    int line_stride = 0;
+    // device
+    DevPeak *d_peaks = nullptr;
+    float *d_subpix = nullptr;
+    int *d_part_count = nullptr;
+    DevLink *d_links = nullptr;
+    int *d_link_count = nullptr;
+    ibp_peak *d_line = nullptr;
+    int *d_n_peaks = nullptr;
+    ibp_human *d_humans = nullptr;
+    int *d_n_humans = nullptr;
+    uint32_t *d_status = nullptr;
+    float *d_fused = nullptr;
+    size_t fused_floats = 0;
+    void *d_stage = nullptr;  // host input staging / legacy limb map
+    size_t stage_bytes = 0;
+    // pinned host mirrors
+    int *h_n_peaks = nullptr;
+    int *h_part_count = nullptr;
+    ibp_peak *h_line = nullptr;
+    int *h_n_humans = nullptr;
+    ibp_human *h_humans = nullptr;
+    uint32_t *h_status = nullptr;
+    DevPeak *h_peaks_stage = nullptr;  // one image worth of per-part lists for ibp_set_peaks
+    int64_t launches = 0;
+};
+
+namespace {
+
+int ensure_stage(ibp_handle *h, size_t bytes) {
+    if (h->stage_bytes >= bytes) return IBP_OK;
+    free_dev(h->d_stage);
+    h->stage_bytes = 0;
+    CU(cudaMalloc(&h->d_stage, bytes));
+    h->stage_bytes = bytes;
+    return IBP_OK;
+}
+int ensure_fused(ibp_handle *h, size_t floats) {
+    if (h->fused_floats >= floats) return IBP_OK;
+    free_dev(h->d_fused);
+    h->fused_floats = 0;
+    CU(cudaMalloc(&h->d_fused, floats * sizeof(float)));
+    h->fused_floats = floats;
+    return IBP_OK;
+}
+
+void destroy_buffers(ibp_handle *h) {
+    free_dev(h->d_peaks);
+    free_dev(h->d_subpix);
+    free_dev(h->d_part_count);
+    free_dev(h->d_links);
+    free_dev(h->d_link_count);
+    free_dev(h->d_line);
+    free_dev(h->d_n_peaks);
+    free_dev(h->d_humans);
+    free_dev(h->d_n_humans);
+    free_dev(h->d_status);
+    free_dev(h->d_fused);
+    free_dev(h->d_stage);
+    free_host(h->h_n_peaks);
+    free_host(h->h_part_count);
+    free_host(h->h_line);
+    free_host(h->h_n_humans);
+    free_host(h->h_humans);
+    free_host(h->h_status);
+    free_host(h->h_peaks_stage);
+}
+
+size_t limb_smem_bytes(const ibp_handle *h, size_t plane_bytes) {
+    size_t region0 = std::max(plane_bytes, (size_t)h->L.max_candidates_per_limb * 8);
+    region0 = (region0 + 15) & ~(size_t)15;
+    return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2);
+}
+size_t group_smem_bytes(const ibp_handle *h) { return (size_t)h->L.max_bodies * (kParts * 8 + 12); }
+
+int validate_limits(const ibp_limits &l) {
+    if (l.max_batch < 1 || l.max_peaks_per_part < 1 || l.max_peaks_per_part > 32767 || l.max_candidates_per_limb < 32 ||
+        (l.max_candidates_per_limb & (l.max_candidates_per_limb - 1)) != 0 || l.max_bodies < 1 || l.max_humans < 1 ||
+        l.max_feat_h < 1 || l.max_feat_w < 1)
+        return fail(IBP_ERR_ARG, "ibp_limits out of range (max_candidates_per_limb must be a power of two >= 32)");
+    return IBP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void ibp_default_params(ibp_params *p) {
+    if (!p) return;
+    p->limb_sample_thresh = 0.1f;
+    p->step_ratio = 0.8f;
+    p->min_parts = 2;
+    p->min_human_score = 0.45f;
+    p->max_steps = 20;
+    p->len_rate = 16;
+    p->merge_tolerance = 0.7f;
+    p->weight_limb = 0.5f;
+    p->weight_a = 0.25f;
+    p->weight_b = 0.25f;
+    p->peak_thresh = 0.1f;
+    p->upsample = 4;
+    p->refine_window = 2;
+}
+
+void ibp_default_limits(ibp_limits *l) {
+    if (!l) return;
+    l->max_batch = 64;
+    l->max_peaks_per_part = 128;
+    l->max_candidates_per_limb = 2048;
+    l->max_bodies = 512;
+    l->max_humans = 128;
+    l->max_feat_h = 128;
+    l->max_feat_w = 128;
+}
+
+const char *ibp_last_error(void) { return g_err.c_str(); }
+
+int ibp_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+void ibp_destroy(ibp_handle *h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    destroy_buffers(h);
+    delete h;
+}
+
+int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp_limits *limits) {
+    if (!out) return fail(IBP_ERR_ARG, "ibp_create: out is NULL");
+    *out = nullptr;
+    int ndev = ibp_device_count();
+    if (ndev <= 0) return fail(IBP_ERR_NO_DEVICE, "no CUDA device visible: libibp_b200 has no CPU path");
+    if (device < 0 || device >= ndev) return fail(IBP_ERR_ARG, "device %d out of range [0,%d)", device, ndev);
+    ibp_handle *h = new ibp_handle();
+    h->device = device;
+    if (params) h->P = *params; else ibp_default_params(&h->P);
+    if (limits) h->L = *limits; else ibp_default_limits(&h->L);
+    int rc = validate_limits(h->L);
+    if (rc != IBP_OK) {
+        delete h;
+        return rc;
+    }
+    if (h->P.upsample < 1 || h->P.refine_window < 1 || h->P.refine_window > 8 || h->P.max_steps < 2) {
+        delete h;
+        return fail(IBP_ERR_ARG, "ibp_params out of range");
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        delete h;
+        return fail(IBP_ERR_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    }
+    const size_t B = h->L.max_batch, cap = h->L.max_peaks_per_part;
+    h->line_stride = (int)(cap * kParts);
+    auto alloc = [&]() -> int {
+        CU(cudaMalloc(&h->d_peaks, B * kParts * cap * sizeof(DevPeak)));
+        CU(cudaMalloc(&h->d_subpix, B * kParts * cap * 2 * sizeof(float)));
+        CU(cudaMalloc(&h->d_part_count, B * kParts * sizeof(int)));
+        CU(cudaMalloc(&h->d_links, B * kLimbs * cap * sizeof(DevLink)));
+        CU(cudaMalloc(&h->d_link_count, B * kLimbs * sizeof(int)));
+        CU(cudaMalloc(&h->d_line, B * h->line_stride * sizeof(ibp_peak)));
+        CU(cudaMalloc(&h->d_n_peaks, B * sizeof(int)));
+        CU(cudaMalloc(&h->d_humans, B * h->L.max_humans * sizeof(ibp_human)));
+        CU(cudaMalloc(&h->d_n_humans, B * sizeof(int)));
+        CU(cudaMalloc(&h->d_status, B * sizeof(uint32_t)));
+        CU(cudaMemset(h->d_part_count, 0, B * kParts * sizeof(int)));
+        CU(cudaMemset(h->d_link_count, 0, B * kLimbs * sizeof(int)));
+        CU(cudaMemset(h->d_n_peaks, 0, B * sizeof(int)));
+        CU(cudaMemset(h->d_n_humans, 0, B * sizeof(int)));
+        CU(cudaMemset(h->d_status, 0, B * sizeof(uint32_t)));
+        CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
+        CU(cudaMallocHost(&h->h_part_count, B * kParts * sizeof(int)));
+        CU(cudaMallocHost(&h->h_line, B * h->line_stride * sizeof(ibp_peak)));
+        CU(cudaMallocHost(&h->h_n_humans, B * sizeof(int)));
+        CU(cudaMallocHost(&h->h_humans, B * h->L.max_humans * sizeof(ibp_human)));
+        CU(cudaMallocHost(&h->h_status, B * sizeof(uint32_t)));
+        CU(cudaMallocHost(&h->h_peaks_stage, kParts * cap * sizeof(DevPeak)));
+        memset(h->h_n_peaks, 0, B * sizeof(int));
+        memset(h->h_n_humans, 0, B * sizeof(int));
+        memset(h->h_status, 0, B * sizeof(uint32_t));
+        // opt in to large dynamic shared memory once
+        CU(cudaFuncSetAttribute(peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        if (limb_smem_bytes(h, 0) > kMaxDynSmem)
+            return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_smem_bytes(h, 0), kMaxDynSmem);
+        if (group_smem_bytes(h) > kMaxDynSmem)
+            return fail(IBP_ERR_ARG, "max_bodies=%d needs %zu B of shared memory (max %zu)", h->L.max_bodies, group_smem_bytes(h), kMaxDynSmem);
+        return IBP_OK;
+    };
+    rc = alloc();
+    if (rc != IBP_OK) {
+        std::string keep = g_err;
+        destroy_buffers(h);
+        delete h;
+        g_err = keep;
+        return rc;
+    }
+    *out = h;
+    return IBP_OK;
+}
+
+int64_t ibp_launch_count(const ibp_handle *h) { return h ? h->launches : 0; }
+
+// ------------------------------------------------------------------------------------------------ K1
+int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int fh, int fw, int flip_avg, float *fused, void *stream) {
+    if (!h || !net_out || !fused) return fail(IBP_ERR_ARG, "ibp_fuse_flip: null argument");
+    if (batch < 1 || fh < 1 || fw < 1) return fail(IBP_ERR_SHAPE, "ibp_fuse_flip: bad shape (%d,%d,%d)", batch, fh, fw);
+    if (dtype != IBP_F32 && dtype != IBP_F16) return fail(IBP_ERR_ARG, "ibp_fuse_flip: dtype %d", dtype);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t hw = (size_t)fh * fw;
+    const bool aligned = (((uintptr_t)net_out) & 15) == 0 && (((uintptr_t)fused) & 15) == 0;
+    if (dtype == IBP_F32 && aligned && fw % 4 == 0) {
+        const int hw4 = (int)(hw / 4);
+        dim3 grid((hw4 + 255) / 256, kLayers, batch);
+        fuse_flip_f32_vec4<<<grid, 256, 0, st>>>((const float *)net_out, fused, hw4, fw / 4, flip_avg);
+    } else if (dtype == IBP_F16 && aligned && fw % 8 == 0) {
+        const int hw8 = (int)(hw / 8);
+        dim3 grid((hw8 + 255) / 256, kLayers, batch);
+        fuse_flip_f16_vec8<<<grid, 256, 0, st>>>((const __half *)net_out, fused, hw8, fw / 8, flip_avg);
+    } else {
+        dim3 grid((unsigned)std::min<size_t>((hw + 255) / 256, 65535), kLayers, batch);
+        if (dtype == IBP_F32)
+            fuse_flip_scalar<float><<<grid, 256, 0, st>>>((const float *)net_out, fused, fh, fw, flip_avg);
+        else
+            fuse_flip_scalar<__half><<<grid, 256, 0, st>>>((const __half *)net_out, fused, fh, fw, flip_avg);
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ A4
+int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int batch, int fh, int fw, int up, float *out_hwc, void *stream) {
+    if (!h || !fused || !out_hwc) return fail(IBP_ERR_ARG, "ibp_upsample_limbs: null argument");
+    if (batch < 1 || fh < 1 || fw < 1 || up < 1 || chan_stride < kLimbs) return fail(IBP_ERR_SHAPE, "ibp_upsample_limbs: bad shape");
+    CU(cudaSetDevice(h->device));
+    UpArgs a;
+    a.src = fused;
+    a.chan_stride = chan_stride;
+    a.h = fh;
+    a.w = fw;
+    a.up = up;
+    a.dst = out_hwc;
+    const int Wo = fw * up, Ho = fh * up;
+    dim3 grid((Wo + kUpTileX - 1) / kUpTileX, (Ho + up - 1) / up, batch);
+    const size_t smem = (size_t)kLimbs * kUpMaxRows * (kUpTileX / up + 6) * sizeof(float);
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_upsample_limbs: up=%d not supported", up);
+    upsample_limbs_kernel<<<grid, kUpThreads, smem, (cudaStream_t)stream>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K2
+int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw, int flavour, void *stream) {
+    if (!h || !maps) return fail(IBP_ERR_ARG, "ibp_find_peaks: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_find_peaks: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (fh < 1 || fw < 1 || fw > 32767 || fh > 32767 || first_chan < 0 || first_chan + kParts > chan_stride)
+        return fail(IBP_ERR_SHAPE, "ibp_find_peaks: bad shape");
+    if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID) return fail(IBP_ERR_ARG, "ibp_find_peaks: flavour %d", flavour);
+    if (flavour == IBP_PEAKS_BOX_CENTROID && h->P.refine_window != 2)
+        return fail(IBP_ERR_ARG, "ibp_find_peaks: the centroid flavour supports offset_radius == 2 only");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    PeakArgs a;
+    a.maps = maps;
+    a.chan_stride = chan_stride;
+    a.first_chan = first_chan;
+    a.h = fh;
+    a.w = fw;
+    a.halo = std::max(h->P.refine_window, 1);
+    int rows_buf = (int)(kPeakBandBytes / ((size_t)fw * 4));
+    rows_buf = std::max(rows_buf, 2 * a.halo + 1);
+    if (rows_buf >= fh) {
+        a.rows_buf = fh;
+        a.rows_per_band = fh;
+    } else {
+        a.rows_buf = rows_buf;
+        a.rows_per_band = rows_buf - 2 * a.halo;
+    }
+    a.up = h->P.upsample;
+    a.win = h->P.refine_window;
+    a.thr = h->P.peak_thresh;
+    a.cap = h->L.max_peaks_per_part;
+    a.flavour = flavour;
+    a.peaks = h->d_peaks;
+    a.subpix = h->d_subpix;
+    a.part_count = h->d_part_count;
+    a.status = h->d_status;
+    const int side = 2 * a.win + 1;
+    size_t smem = (((size_t)a.rows_buf * fw * 4) + 15) & ~(size_t)15;
+    smem += (((size_t)(a.rows_per_band * fw + 31) / 32) * 4 + 7) & ~(size_t)7;
+    smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
+    smem += (size_t)a.cap * sizeof(short2);
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_find_peaks: row of %d floats does not fit shared memory", fw);
+    CU(cudaMemsetAsync(h->d_status, 0, (size_t)batch * sizeof(uint32_t), st));
+    peaks_kernel<<<dim3(kParts, batch), kPeakThreads, smem, st>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    pack_peaks_kernel<<<batch, 128, 0, st>>>(h->d_peaks, h->d_part_count, a.cap, h->d_line, h->line_stride, h->d_n_peaks);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride) {
+    if (!h || (n > 0 && !host_peaks)) return fail(IBP_ERR_ARG, "ibp_set_peaks: null argument");
+    if (image < 0 || image >= h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_set_peaks: image %d out of range", image);
+    if (n < 0 || row_stride < 5) return fail(IBP_ERR_SHAPE, "ibp_set_peaks: need rows of >= 5 floats [x,y,score,id,part]");
+    CU(cudaSetDevice(h->device));
+    const int cap = h->L.max_peaks_per_part;
+    int counts[kParts] = {0};
+    // pafprocess.cpp:29-41: bucket by part in arrival order; id = arrival index; x,y truncated to int
+    for (int i = 0; i < n; i++) {
+        const float *r = host_peaks + (size_t)i * row_stride;
+        const int part = (int)r[4];
+        if (part < 0 || part >= kParts) return fail(IBP_ERR_PART, "joint %d has part id %d outside [0,18)", i, part);
+        if (counts[part] >= cap) return fail(IBP_ERR_CAPACITY, "more than %d peaks of part %d (ibp_limits.max_peaks_per_part)", cap, part);
+        DevPeak p;
+        p.x = (int)r[0];
+        p.y = (int)r[1];
+        p.score = r[2];
+        p.id = i;
+        h->h_peaks_stage[(size_t)part * cap + counts[part]++] = p;
+    }
+    // pafprocess.cpp:43-48: part-major concatenation, indexed later BY PEAK ID (identical to arrival order only when
+    // the caller sorted the list by part, as evaluate.py:99-103 does)
+    ibp_peak *line = h->h_line + (size_t)image * h->line_stride;
+    int pos = 0;
+    for (int p = 0; p < kParts; p++)
+        for (int k = 0; k < counts[p]; k++) {
+            const DevPeak &s = h->h_peaks_stage[(size_t)p * cap + k];
+            line[pos].x = s.x;
+            line[pos].y = s.y;
+            line[pos].score = s.score;
+            line[pos].part = p;
+            pos++;
+        }
+    h->h_n_peaks[image] = n;
+    memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
+    CU(cudaMemcpy(h->d_peaks + (size_t)image * kParts * cap, h->h_peaks_stage, (size_t)kParts * cap * sizeof(DevPeak), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_part_count + (size_t)image * kParts, counts, sizeof(counts), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_line + (size_t)image * h->line_stride, line, (size_t)std::max(n, 1) * sizeof(ibp_peak), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_n_peaks + image, &n, sizeof(int), cudaMemcpyHostToDevice));
+    CU(cudaMemset(h->d_status + image, 0, sizeof(uint32_t)));
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K3 + K4
+int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int dim0, int dim1, int dim2, int min_img_size, void *stream) {
+    if (!h || !limb_src) return fail(IBP_ERR_ARG, "ibp_assign: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_assign: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (dim0 < 1 || dim1 < 1 || dim2 < kLimbs) return fail(IBP_ERR_SHAPE, "ibp_assign: bad shape (%d,%d,%d)", dim0, dim1, dim2);
+    if (mode != IBP_LIMB_FULLRES_HWC && mode != IBP_LIMB_FEAT_PLANAR) return fail(IBP_ERR_ARG, "ibp_assign: mode %d", mode);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    LimbArgs a;
+    a.peaks = h->d_peaks;
+    a.part_count = h->d_part_count;
+    a.cap = h->L.max_peaks_per_part;
+    a.src = limb_src;
+    a.mode = mode;
+    a.up = h->P.upsample;
+    size_t plane_bytes = 0;
+    if (mode == IBP_LIMB_FULLRES_HWC) {
+        a.H = dim0;
+        a.W = dim1;
+        a.C = dim2;
+        a.h = a.w = 1;
+        a.stage_plane = 0;
+        a.image_stride = (size_t)dim0 * dim1 * dim2;
+    } else {
+        a.h = dim0;
+        a.w = dim1;
+        a.H = dim0 * a.up;
+        a.W = dim1 * a.up;
+        a.C = dim2;
+        a.image_stride = (size_t)dim2 * dim0 * dim1;
+        plane_bytes = (size_t)dim0 * dim1 * 4;
+        a.stage_plane = (plane_bytes <= kLimbPlaneMaxBytes && limb_smem_bytes(h, plane_bytes) <= kMaxDynSmem) ? 1 : 0;
+        if (!a.stage_plane) plane_bytes = 0;
+    }
+    a.min_img_size = min_img_size;
+    a.thr = h->P.limb_sample_thresh;
+    a.step_ratio = h->P.step_ratio;
+    a.w_limb = h->P.weight_limb;
+    a.w_a = h->P.weight_a;
+    a.w_b = h->P.weight_b;
+    a.max_steps = h->P.max_steps;
+    a.cand_cap = h->L.max_candidates_per_limb;
+    a.links = h->d_links;
+    a.link_count = h->d_link_count;
+    a.status = h->d_status;
+    limbs_kernel<<<dim3(kLimbs, batch), kLimbThreads, limb_smem_bytes(h, plane_bytes), st>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+
+    GroupArgs g;
+    g.links = h->d_links;
+    g.link_count = h->d_link_count;
+    g.cap = a.cap;
+    g.line = h->d_line;
+    g.line_stride = h->line_stride;
+    g.max_bodies = h->L.max_bodies;
+    g.max_humans = h->L.max_humans;
+    g.len_rate = h->P.len_rate;
+    g.merge_tol = h->P.merge_tolerance;
+    g.min_parts = h->P.min_parts;
+    g.min_score = h->P.min_human_score;
+    g.humans = h->d_humans;
+    g.n_humans = h->d_n_humans;
+    g.status = h->d_status;
+    group_kernel<<<batch, 32, group_smem_bytes(h), st>>>(g);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ pipeline
+int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw, int min_img_size, void *stream) {
+    if (!h || !net_out) return fail(IBP_ERR_ARG, "ibp_postprocess_batch: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_postprocess_batch: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (dtype != IBP_F32 && dtype != IBP_F16) return fail(IBP_ERR_ARG, "ibp_postprocess_batch: dtype %d", dtype);
+    if (fh < 1 || fw < 1) return fail(IBP_ERR_SHAPE, "ibp_postprocess_batch: bad shape");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t elems = (size_t)batch * 2 * kLayers * fh * fw;
+    const void *dev_in = net_out;
+    if (on_host) {
+        const size_t bytes = elems * (dtype == IBP_F16 ? 2 : 4);
+        int rc = ensure_stage(h, bytes);
+        if (rc != IBP_OK) return rc;
+        CU(cudaMemcpyAsync(h->d_stage, net_out, bytes, cudaMemcpyHostToDevice, st));
+        dev_in = h->d_stage;
+    }
+    int rc = ensure_fused(h, (size_t)batch * kLayers * fh * fw);
+    if (rc != IBP_OK) return rc;
+    rc = ibp_fuse_flip(h, dev_in, dtype, batch, fh, fw, 1, h->d_fused, stream);
+    if (rc != IBP_OK) return rc;
+    rc = ibp_find_peaks(h, h->d_fused, kLayers, kLimbs, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, stream);
+    if (rc != IBP_OK) return rc;
+    return ibp_assign(h, h->d_fused, IBP_LIMB_FEAT_PLANAR, batch, fh, fw, kLayers, min_img_size, stream);
+}
+
+int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
+    if (!h || !view) return fail(IBP_ERR_ARG, "ibp_fetch: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_fetch: batch %d exceeds limit %d", batch, h->L.max_batch);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t B = batch;
+    CU(cudaMemcpyAsync(h->h_n_peaks, h->d_n_peaks, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_part_count, h->d_part_count, B * kParts * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_line, h->d_line, B * h->line_stride * sizeof(ibp_peak), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_n_humans, h->d_n_humans, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_humans, h->d_humans, B * h->L.max_humans * sizeof(ibp_human), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_status, h->d_status, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    view->batch = batch;
+    view->peak_stride = h->line_stride;
+    view->human_stride = h->L.max_humans;
+    view->n_peaks = h->h_n_peaks;
+    view->part_count = h->h_part_count;
+    view->peaks = h->h_line;
+    view->n_humans = h->h_n_humans;
+    view->humans = h->h_humans;
+    view->status = h->h_status;
+    uint32_t any = 0;
+    for (int b = 0; b < batch; b++) any |= h->h_status[b];
+    if (any & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
+        return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", any);
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ legacy protocol
+namespace {
+ibp_handle *g_legacy = nullptr;
+ibp_batch_view g_view;
+bool g_view_valid = false;
+uint32_t g_legacy_status = 0;
+}  // namespace
+
+int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, int f3, const float *pafmap, int min_img_size) {
+    g_view_valid = false;
+    if (!peaks || !pafmap) return fail(IBP_ERR_ARG, "process_paf: null array");
+    if (p1 < 0 || p2 < 0 || p3 < 5 || f1 < 1 || f2 < 1 || f3 < kLimbs)
+        return fail(IBP_ERR_SHAPE, "process_paf: peaks must be (p1,p2,>=5) and pafmap (H,W,>=30); got (%d,%d,%d) (%d,%d,%d)", p1, p2, p3, f1, f2, f3);
+    const int n = p1 * p2;
+    // capacity: grow the process-global handle when a part has more peaks than it can hold
+    int counts[kParts] = {0};
+    for (int i = 0; i < n; i++) {
+        const int part = (int)peaks[(size_t)i * p3 + 4];
+        if (part < 0 || part >= kParts) return fail(IBP_ERR_PART, "joint %d has part id %d outside [0,18)", i, part);
+        counts[part]++;
+    }
+    int need = 128;
+    for (int p = 0; p < kParts; p++)
+        while (need < counts[p]) need <<= 1;
+    if (!g_legacy || g_legacy->L.max_peaks_per_part < need) {
+        if (g_legacy) ibp_destroy(g_legacy);
+        g_legacy = nullptr;
+        ibp_limits l;
+        ibp_default_limits(&l);
+        l.max_batch = 1;
+        l.max_peaks_per_part = need;
+        l.max_candidates_per_limb = 4096;
+        l.max_bodies = 1024;
+        l.max_humans = 1024;
+        const char *dev = getenv("IBP_DEVICE");
+        int rc = ibp_create(&g_legacy, dev ? atoi(dev) : 0, nullptr, &l);
+        if (rc != IBP_OK) return rc;
+    }
+    ibp_handle *h = g_legacy;
+    int rc = ibp_set_peaks(h, 0, peaks, n, p3);
+    if (rc != IBP_OK) return rc;
+    const size_t bytes = (size_t)f1 * f2 * f3 * sizeof(float);
+    rc = ensure_stage(h, bytes);
+    if (rc != IBP_OK) return rc;
+    CU(cudaMemcpy(h->d_stage, pafmap, bytes, cudaMemcpyHostToDevice));
+    rc = ibp_assign(h, (const float *)h->d_stage, IBP_LIMB_FULLRES_HWC, 1, f1, f2, f3, min_img_size, nullptr);
+    if (rc != IBP_OK) return rc;
+    // results: humans + status only; the peak list is already on the host (ibp_set_peaks filled h_line)
+    CU(cudaMemcpyAsync(h->h_n_humans, h->d_n_humans, sizeof(int), cudaMemcpyDeviceToHost, 0));
+    CU(cudaMemcpyAsync(h->h_humans, h->d_humans, (size_t)h->L.max_humans * sizeof(ibp_human), cudaMemcpyDeviceToHost, 0));
+    CU(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, 0));
+    CU(cudaStreamSynchronize(0));
+    g_view.batch = 1;
+    g_view.peak_stride = h->line_stride;
+    g_view.human_stride = h->L.max_humans;
+    g_view.n_peaks = h->h_n_peaks;
+    g_view.part_count = h->h_part_count;
+    g_view.peaks = h->h_line;
+    g_view.n_humans = h->h_n_humans;
+    g_view.humans = h->h_humans;
+    g_view.status = h->h_status;
+    g_view_valid = true;
+    g_legacy_status = h->h_status[0];
+    if (g_legacy_status & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
+        return fail(IBP_ERR_CAPACITY, "process_paf: device buffer overflow (status 0x%x)", g_legacy_status);
+    return IBP_OK;  // the reference returns 0 (pafprocess.cpp:284)
+}
+
+int ibp_get_num_humans(void) { return g_view_valid ? g_view.n_humans[0] : 0; }
+int ibp_get_part_peak_id(int skeleton_id, int part_id) {
+    if (!g_view_valid || skeleton_id < 0 || skeleton_id >= g_view.n_humans[0] || part_id < 0 || part_id >= kParts) return -1;
+    return g_view.humans[skeleton_id].peak_id[part_id];
+}
+float ibp_get_score(int skeleton_id) {
+    if (!g_view_valid || skeleton_id < 0 || skeleton_id >= g_view.n_humans[0]) return 0.0f;
+    return g_view.humans[skeleton_id].score;
+}
+int ibp_get_part_x(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n_peaks[0]) ? g_view.peaks[cid].x : 0; }
+int ibp_get_part_y(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n_peaks[0]) ? g_view.peaks[cid].y : 0; }
+float ibp_get_part_score(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n_peaks[0]) ? g_view.peaks[cid].score : 0.0f; }
+uint32_t ibp_get_status(void) { return g_legacy_status; }
+
+}  // extern "C"

@@ -1,0 +1,156 @@
+// Device-side building blocks shared by the kernels: constant tables, exact-order float helpers, the OpenCV-order
+// bicubic taps, and the 1-D bulk (TMA) global->shared copy with its mbarrier.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/ibp.h"
+
+namespace ibp {
+
+constexpr int kParts = IBP_NUM_PARTS;
+constexpr int kLimbs = IBP_NUM_LIMBS;
+constexpr int kLayers = IBP_NUM_LAYERS;
+
+struct DevPeak {  // 16 B — reference Peak, pafprocess.h:29-34
+    int x, y;
+    float score;
+    int id;
+};
+struct DevLink {  // 16 B — the fields of Connection (pafprocess.h:60-67) that grouping reads
+    int id_a, id_b;
+    float limb;
+    float len;
+};
+
+// limb end points: pafprocess.h:20-27 COCOPAIRS == config/config.py:114-121
+__constant__ int c_limb_a[kLimbs] = {1, 1, 1, 1, 1, 0, 0, 14, 15, 1, 2, 3, 1, 5, 6, 1, 8, 9, 1, 11, 12, 0, 0, 2, 8, 5, 11, 16, 17, 8};
+__constant__ int c_limb_b[kLimbs] = {0, 14, 15, 16, 17, 14, 15, 16, 17, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 2, 5, 8, 12, 11, 9, 2, 5, 11};
+// channel read from the flipped image for output channel c: config/config.py:150-152 (flip_paf_ord, then
+// 30 + flip_heat_ord)
+__constant__ int c_flip_src[kLayers] = {0, 2, 1, 4, 3, 6, 5, 8, 7, 12, 13, 14, 9, 10, 11, 18, 19, 20, 15, 16, 17, 22, 21, 25, 26, 23, 24, 28, 27, 29,
+                                        30, 31, 35, 36, 37, 32, 33, 34, 41, 42, 43, 38, 39, 40, 45, 44, 47, 46, 48, 49};
+
+// ---------------------------------------------------------------------------------------------------------------
+// OpenCV cubic taps (cv2.resize INTER_CUBIC, A = -0.75).  The library is compiled with -fmad=false, and the
+// intrinsics below pin the evaluation order on top of that: the reference's numbers come from code without FMA
+// contraction (OpenCV baseline SSE3; pafprocess built by distutils without -march).
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cubic_weights(float t, float *w) {
+    const float A = -0.75f;
+    const float t1 = __fadd_rn(t, 1.0f);
+    const float u = __fsub_rn(1.0f, t);
+    // coeffs[0] = ((A*(x+1) - 5*A)*(x+1) + 8*A)*(x+1) - 4*A
+    w[0] = __fsub_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fsub_rn(__fmul_rn(A, t1), 5.0f * A), t1), 8.0f * A), t1), 4.0f * A);
+    // coeffs[1] = ((A+2)*x - (A+3))*x*x + 1
+    w[1] = __fadd_rn(__fmul_rn(__fmul_rn(__fsub_rn(__fmul_rn(A + 2.0f, t), A + 3.0f), t), t), 1.0f);
+    // coeffs[2] = ((A+2)*(1-x) - (A+3))*(1-x)*(1-x) + 1
+    w[2] = __fadd_rn(__fmul_rn(__fmul_rn(__fsub_rn(__fmul_rn(A + 2.0f, u), A + 3.0f), u), u), 1.0f);
+    // coeffs[3] = 1 - coeffs[0] - coeffs[1] - coeffs[2]
+    w[3] = __fsub_rn(__fsub_rn(__fsub_rn(1.0f, w[0]), w[1]), w[2]);
+}
+
+// destination index d of an n_src -> n_src*up axis: first source index (unclamped) and the four weights
+__device__ __forceinline__ int cubic_tap(int d, int up, float *w) {
+    if (up == 4) {
+        // (d+0.5)/4 - 0.5 is exact: floor = (d-2)>>2, fraction = ((d-2)&3)/4 + 1/8
+        const int s = (d - 2) >> 2;
+        const float t = __fadd_rn(__int2float_rn((d - 2) & 3) * 0.25f, 0.125f);
+        cubic_weights(t, w);
+        return s;
+    }
+    const double scale = __ddiv_rn(1.0, (double)up);
+    float f = __double2float_rn(__dsub_rn(__dmul_rn(__dadd_rn((double)d, 0.5), scale), 0.5));
+    const int s = __float2int_rd(f);
+    f = __fsub_rn(f, __int2float_rn(s));
+    cubic_weights(f, w);
+    return s;
+}
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// horizontal 4-tap: ((s0*a0 + s1*a1) + s2*a2) + s3*a3   (OpenCV HResizeCubic)
+__device__ __forceinline__ float hsum4(float s0, float s1, float s2, float s3, const float *a) {
+    return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s0, a[0]), __fmul_rn(s1, a[1])), __fmul_rn(s2, a[2])), __fmul_rn(s3, a[3]));
+}
+// vertical 4-tap: s0*b0 + (s1*b1 + (s2*b2 + s3*b3))   (OpenCV VResizeCubicVec_32f)
+__device__ __forceinline__ float vsum4(float s0, float s1, float s2, float s3, const float *b) {
+    return __fadd_rn(__fmul_rn(s0, b[0]), __fadd_rn(__fmul_rn(s1, b[1]), __fadd_rn(__fmul_rn(s2, b[2]), __fmul_rn(s3, b[3]))));
+}
+
+// value of pixel (X,Y) of cv2.resize(plane(h,w), fx=up, fy=up, INTER_CUBIC); `plane` may be shared or global
+__device__ __forceinline__ float cubic_sample(const float *plane, int h, int w, int up, int X, int Y) {
+    float xw[4], yw[4];
+    const int sx = cubic_tap(X, up, xw);
+    const int sy = cubic_tap(Y, up, yw);
+    const int x0 = clampi(sx - 1, 0, w - 1), x1 = clampi(sx, 0, w - 1), x2 = clampi(sx + 1, 0, w - 1), x3 = clampi(sx + 2, 0, w - 1);
+    float r[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
+        r[k] = hsum4(row[x0], row[x1], row[x2], row[x3], xw);
+    }
+    return vsum4(r[0], r[1], r[2], r[3], yw);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// mbarrier + 1-D bulk copy (TMA engine, SASS UBLKCP): one elected thread moves a contiguous run of rows of a
+// planar map into shared memory; everybody waits on the barrier's phase.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t phase) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(phase)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Cooperative "rows to shared": the bulk engine when source, destination and size are 16-byte aligned (every map
+// the reference pads to a multiple of 64 pixels is), plain coalesced loads otherwise.  Must be called by all
+// threads of the CTA; returns after the data is visible to all of them.  `phase` is the barrier's running parity.
+__device__ __forceinline__ void rows_to_smem(float *dst, const float *src, uint32_t n_floats, uint64_t *bar, uint32_t &phase) {
+    const uint32_t bytes = n_floats * 4u;
+    const bool bulk_ok = ((bytes & 15u) == 0) && ((((uintptr_t)src) & 15u) == 0) && ((smem_u32(dst) & 15u) == 0);
+    if (bulk_ok) {
+        if (threadIdx.x == 0) {
+            // chunks keep each transaction count well inside the mbarrier's tx-count range
+            uint32_t done = 0;
+            mbar_expect_tx(bar, bytes);
+            while (done < bytes) {
+                uint32_t chunk = bytes - done;
+                if (chunk > 65536u) chunk = 65536u;
+                bulk_g2s((char *)dst + done, (const char *)src + done, chunk, bar);
+                done += chunk;
+            }
+        }
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+    } else {
+        for (uint32_t i = threadIdx.x; i < n_floats; i += blockDim.x) dst[i] = __ldg(src + i);
+        __syncthreads();
+    }
+}
+
+}  // namespace ibp

@@ -1,0 +1,189 @@
+// K4b — person grouping: grow / merge partial skeletons limb by limb, then filter.  One warp per image.
+//
+// Reference: utils/pafprocess/pafprocess.cpp:133-282.  The chain is sequential by construction (every connection
+// reads and mutates the table the next one scans, and a merge erases a row so later indices shift), so the
+// parallelism is images across CTAs and, inside a step, lanes over the skeleton scan (32 rows per ballot), over the
+// 18 part slots of a merge, and over the columns of the row shift that implements vector::erase.
+// The table lives in shared memory: ids[S][18], limb scores[S][18], total[S], count[S], reach[S].
+#pragma once
+#include "ibp_device.cuh"
+
+namespace ibp {
+
+struct GroupArgs {
+    const DevLink *links;    // (batch, 30, cap)
+    const int *link_count;   // (batch, 30)
+    int cap;
+    const ibp_peak *line;    // (batch, line_stride): part-major peak list indexed by peak id (pafprocess.cpp:43-48)
+    int line_stride;
+    int max_bodies;
+    int max_humans;
+    int len_rate;
+    float merge_tol;
+    int min_parts;
+    float min_score;
+    ibp_human *humans;       // (batch, max_humans)
+    int *n_humans;           // (batch)
+    uint32_t *status;        // (batch)
+};
+
+__global__ void __launch_bounds__(32) group_kernel(GroupArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int img = blockIdx.x, lane = threadIdx.x;
+    const int S = a.max_bodies;
+    int *ids = reinterpret_cast<int *>(smem_raw);                 // [S][18]
+    float *sc = reinterpret_cast<float *>(ids + (size_t)S * kParts);  // [S][18]
+    float *total = sc + (size_t)S * kParts;                       // [S]
+    int *count = reinterpret_cast<int *>(total + S);              // [S]
+    float *reach = reinterpret_cast<float *>(count + S);          // [S]
+    const ibp_peak *line = a.line + (size_t)img * a.line_stride;
+
+    int nb = 0;
+    bool overflow = false;
+    for (int limb = 0; limb < kLimbs; limb++) {
+        const int pa = c_limb_a[limb], pb = c_limb_b[limb];
+        const int nl = a.link_count[img * kLimbs + limb];
+        const DevLink *L = a.links + ((size_t)img * kLimbs + limb) * a.cap;
+        for (int li = 0; li < nl; li++) {
+            const DevLink l = L[li];
+            // :143-150 scan: first two matching rows, total number of matches
+            int hits = 0, first = 0, second = 0;
+            for (int base = 0; base < nb; base += 32) {
+                const int s = base + lane;
+                const bool m = (s < nb) && (ids[s * kParts + pa] == l.id_a || ids[s * kParts + pb] == l.id_b);
+                uint32_t bal = __ballot_sync(0xffffffffu, m);
+                while (bal) {
+                    const int pos = __ffs(bal) - 1;
+                    bal &= bal - 1;
+                    if (hits == 0) first = base + pos;
+                    else if (hits == 1) second = base + pos;
+                    hits++;
+                }
+            }
+            if (hits == 1) {  // :152-180
+                if (lane == 0) {
+                    const int f = first;
+                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(reach[f], __int2float_rn(a.len_rate))));  // :154
+                    const int cur_id = ids[f * kParts + pb];
+                    const float cur_sc = sc[f * kParts + pb];
+                    const float add = __fadd_rn(line[l.id_b].score, l.limb);
+                    if (cur_id == -1 && gate > l.len) {
+                        ids[f * kParts + pb] = l.id_b;
+                        sc[f * kParts + pb] = l.limb;
+                        count[f] += 1;
+                        reach[f] = fmaxf(reach[f], l.len);
+                        total[f] = __fadd_rn(total[f], add);
+                    } else if ((cur_id != l.id_b && cur_sc <= l.limb && gate > l.len) || (cur_id == l.id_b && cur_sc <= l.limb)) {
+                        ids[f * kParts + pb] = l.id_b;
+                        sc[f * kParts + pb] = l.limb;
+                        // :168-169 / :177-178 — subtracts the values just written, then adds them back
+                        total[f] = __fadd_rn(__fsub_rn(total[f], add), add);
+                        reach[f] = fmaxf(reach[f], l.len);
+                    }
+                }
+                __syncwarp();
+            } else if (hits == 2) {  // :182-256
+                const int f = first, g = second;
+                int idm = -1, ido = -1;
+                float scm = 0.f, sco = 0.f;
+                if (lane < kParts) {
+                    idm = ids[f * kParts + lane];
+                    ido = ids[g * kParts + lane];
+                    scm = sc[f * kParts + lane];
+                    sco = sc[g * kParts + lane];
+                }
+                const bool hm = idm > 0, ho = ido > 0;  // :198-199 peak id 0 counts as unassigned
+                const bool overlap = __ballot_sync(0xffffffffu, hm && ho) != 0;
+                if (!overlap) {
+                    // :201-205 running minimum with the 0.0f sentinel, evaluated in part order on every lane
+                    float low_m = 0.0f, low_o = 0.0f;
+                    for (int k = 0; k < kParts; k++) {
+                        const int im = __shfl_sync(0xffffffffu, idm, k), io = __shfl_sync(0xffffffffu, ido, k);
+                        const float sm = __shfl_sync(0xffffffffu, scm, k), so = __shfl_sync(0xffffffffu, sco, k);
+                        if (im > 0) low_m = (low_m == 0.0f) ? sm : (sm < low_m ? sm : low_m);
+                        if (io > 0) low_o = (low_o == 0.0f) ? so : (so < low_o ? so : low_o);
+                    }
+                    const float floor_score = __fmul_rn((low_o < low_m ? low_o : low_m), a.merge_tol);  // :219
+                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(reach[f], __int2float_rn(a.len_rate))));  // :186
+                    if (l.limb >= floor_score || l.len < gate) {  // :220
+                        if (lane < kParts) {  // :222-225
+                            ids[f * kParts + lane] = idm + (ido + 1);
+                            sc[f * kParts + lane] = __fadd_rn(scm, __fadd_rn(sco, 1.0f));
+                        }
+                        if (lane == 0) {  // :226-228
+                            count[f] += count[g];
+                            reach[f] = fmaxf(reach[f], l.len);
+                            total[f] = __fadd_rn(total[f], __fadd_rn(total[g], l.limb));
+                        }
+                        __syncwarp();
+                        // :229 erase row g: every lane shifts its own column down, rows in increasing order
+                        for (int r = g; r < nb - 1; r++) {
+                            if (lane < kParts) {
+                                ids[r * kParts + lane] = ids[(r + 1) * kParts + lane];
+                                sc[r * kParts + lane] = sc[(r + 1) * kParts + lane];
+                            } else if (lane == kParts) {
+                                total[r] = total[r + 1];
+                            } else if (lane == kParts + 1) {
+                                count[r] = count[r + 1];
+                            } else if (lane == kParts + 2) {
+                                reach[r] = reach[r + 1];
+                            }
+                        }
+                        nb--;
+                    }
+                }
+                // overlap: DELETE_SHARED_JOINTS is const false (pafprocess.h:16) => the branch at :231-256 does nothing
+                __syncwarp();
+            } else if (hits == 0) {  // :257-273
+                if (nb < S) {
+                    if (lane < kParts) {
+                        ids[nb * kParts + lane] = (lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1);
+                        sc[nb * kParts + lane] = (lane == pa || lane == pb) ? l.limb : -1.0f;
+                    }
+                    if (lane == 0) {
+                        count[nb] = 2;
+                        reach[nb] = l.len;
+                        total[nb] = __fadd_rn(__fadd_rn(line[l.id_a].score, line[l.id_b].score), l.limb);
+                    }
+                    nb++;
+                } else {
+                    overflow = true;
+                }
+                __syncwarp();
+            }
+            // hits >= 3: the connection is silently dropped
+        }
+    }
+
+    // :277-282 filter (order preserved) + results of the getters (:287-297)
+    int n_out = 0;
+    ibp_human *out = a.humans + (size_t)img * a.max_humans;
+    for (int base = 0; base < nb; base += 32) {
+        const int s = base + lane;
+        bool keep = false;
+        if (s < nb) keep = !(count[s] < a.min_parts || __fdiv_rn(total[s], __int2float_rn(count[s])) < a.min_score);
+        const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+        if (keep) {
+            const int o = n_out + __popc(bal & ((1u << lane) - 1u));
+            if (o < a.max_humans) {
+                ibp_human hmn;
+                for (int k = 0; k < kParts; k++) hmn.peak_id[k] = ids[s * kParts + k];
+                hmn.score = __fdiv_rn(total[s], __int2float_rn(count[s]));
+                hmn.total = total[s];
+                hmn.count = count[s];
+                hmn.reach = reach[s];
+                out[o] = hmn;
+            }
+        }
+        n_out += __popc(bal);
+    }
+    if (lane == 0) {
+        a.n_humans[img] = min(n_out, a.max_humans);
+        uint32_t st = 0;
+        if (overflow) st |= IBP_ST_BODY_OVERFLOW;
+        if (n_out > a.max_humans) st |= IBP_ST_HUMAN_OVERFLOW;
+        if (st) atomicOr(a.status + img, st);
+    }
+}
+
+}  // namespace ibp

@@ -1,0 +1,91 @@
+"""Mirror of the reference's utils/parse_skeletons.py call surface, computed on the GPU through libibp_b200.so.
+Same function names, argument order and return containers; no CPU fallback.
+
+    predict_refactor   parse_skeletons.py:28-103
+    heatmap_nms        parse_skeletons.py:126-176
+    limb_upsample      evaluate.py:77-80 (the cv2.resize between heatmap_nms and process_paf)
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .pipeline import PostProcessor
+
+NUM_KEYPOINTS = 18
+NUM_HEATMAPS = NUM_KEYPOINTS + 2
+NUM_PAFS = 30
+
+_pp = {}
+
+
+def _processor(device=0):
+    if device not in _pp:
+        _pp[device] = PostProcessor(device=device, max_batch=1, max_feat=(1024, 1024))
+    return _pp[device]
+
+
+def pad_right_down_corner(img, stride, pad_value):
+    """utils/util.py:44-65: pad bottom/right to a multiple of `stride` with `pad_value`."""
+    h, w = img.shape[:2]
+    pad = [0, 0, 0 if h % stride == 0 else stride - h % stride, 0 if w % stride == 0 else stride - w % stride]
+    out = np.full((h + pad[2], w + pad[3]) + img.shape[2:], pad_value, dtype=img.dtype)
+    out[:h, :w] = img
+    return out, pad
+
+
+def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, config=None):
+    """-> (heatmaps (h,w,20), pafs (h,w,30)) float32 HWC, like parse_skeletons.py:28-103.  Image preparation stays
+    on the host exactly as in the reference (scale pinned to 1.0, l.36); the flip average runs on the device."""
+    import cv2
+    scale = 1.0  # parse_skeletons.py:36
+    img_h, img_w, _ = image.shape
+    if scale * img_h > 2600 or scale * img_w > 3800:  # l.46-49
+        scale = min(2600 / img_h, 3800 / img_w)
+        print("Input image: '{}' is too big, shrink it!".format(input_image_path))
+    img = cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC)
+    padded, _ = pad_right_down_corner(img, model_cfg['max_downsample'], model_cfg['padValue'])
+    x = np.float32(padded / 255)
+    batch = np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0)  # l.69-72
+    pp = _processor()
+    with torch.no_grad():
+        out = model(torch.from_numpy(batch).to(pp.device))
+    if isinstance(out, (list, tuple)):
+        out = out[-1][0]  # last stack, scale 0 (l.80)
+    fused = pp.fuse_flip(out[None, ...], flip_avg)[0]  # (50,h,w)
+    hwc = fused.permute(1, 2, 0).contiguous().cpu().numpy()
+    return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
+
+
+def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
+    """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176)."""
+    if not bool_refine_center:
+        raise NotImplementedError("bool_refine_center=False is not on the reference's path (evaluate.py:76)")
+    pp = _processor()
+    up = int(upsample_factor)
+    if pp.handle.params.upsample != up:
+        pp.handle.close()
+        p = _lib.default_params()
+        p.upsample = up
+        pp.handle = _lib.Handle(pp.device.index or 0, params=p, max_batch=1, max_feat_h=1024, max_feat_w=1024)
+    maps = torch.from_numpy(np.ascontiguousarray(heatmaps[:, :, :NUM_KEYPOINTS], dtype=np.float32))
+    maps = maps.to(pp.device).permute(2, 0, 1).contiguous()[None, ...]
+    pp.find_peaks(maps, 0)
+    res = pp.fetch(1)
+    peaks = res.peaks[0]
+    out, pos = [], 0
+    for part in range(NUM_KEYPOINTS):
+        n = int(res.part_count[0, part])
+        rows = np.zeros((n, 4), dtype=np.float32)
+        sel = peaks[pos:pos + n]
+        rows[:, 0], rows[:, 1], rows[:, 2] = sel["x"], sel["y"], sel["score"]
+        rows[:, 3] = np.arange(pos, pos + n)
+        out.append(rows)
+        pos += n
+    return out
+
+
+def limb_upsample(pafs, upsample_factor=4):
+    """evaluate.py:77-80: cv2.resize(pafs, None, fx=stride, fy=stride, INTER_CUBIC) on (h,w,30) -> (H,W,30)."""
+    pp = _processor()
+    t = torch.from_numpy(np.ascontiguousarray(pafs, dtype=np.float32)).to(pp.device).permute(2, 0, 1).contiguous()
+    return pp.upsample_limbs(t[None, ...], int(upsample_factor))[0].cpu().numpy()

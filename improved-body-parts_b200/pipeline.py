@@ -1,0 +1,153 @@
+"""Batched, device-resident post-processing: everything evaluate.py:75-129 does after the model call, for B images
+per launch set, plus the multi-GPU sharding helpers (images shard, no collective on the data path).
+
+PyTorch is used for device memory, streams and (optionally) torch.distributed rendezvous only.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .common import humans_from_result
+from .config import ORDER_COCO
+
+_DTYPES = {torch.float32: _lib.IBP_F32, torch.float16: _lib.IBP_F16}
+
+
+def _stream_ptr(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class PostProcessor:
+    """One instance per GPU (and per stream / thread).  `net_out` is what `NetworkEval` returns for the last stack at
+    scale 0 on the batch [img, flip(img)] (models/posenet.py:184-202, parse_skeletons.py:76-80): (B, 2, 50, h, w)."""
+
+    def __init__(self, device=0, max_batch=64, max_feat=(128, 128), **limit_overrides):
+        if not torch.cuda.is_available():
+            raise _lib.IbpError(-6, "no CUDA device: improved-body-parts_b200 has no CPU fallback")
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        self.handle = _lib.Handle(self.device.index or 0, max_batch=max_batch, max_feat_h=max_feat[0],
+                                  max_feat_w=max_feat[1], **limit_overrides)
+        self.max_batch = max_batch
+
+    # ---- full pipeline -------------------------------------------------------------------------------------
+    def enqueue(self, net_out, min_img_size):
+        """Launch the pipeline on the current stream.  net_out: CUDA tensor, pinned/pageable CPU tensor or numpy."""
+        if isinstance(net_out, np.ndarray):
+            net_out = torch.from_numpy(net_out)
+        if net_out.dim() != 5 or net_out.shape[1] != 2 or net_out.shape[2] != _lib.NUM_LAYERS:
+            raise ValueError("net_out must be (B, 2, 50, h, w), got %s" % (tuple(net_out.shape),))
+        if net_out.dtype not in _DTYPES:
+            raise TypeError("net_out dtype must be float32 or float16")
+        net_out = net_out.contiguous()
+        B, _, _, h, w = net_out.shape
+        on_host = not net_out.is_cuda
+        with torch.cuda.device(self.device):
+            self.handle.postprocess_batch(net_out.data_ptr(), on_host, _DTYPES[net_out.dtype], B, h, w, min_img_size,
+                                          _stream_ptr(self.device))
+        self._keep = net_out  # keep the source alive until fetch
+        return B
+
+    def fetch(self, batch, raise_on_overflow=True):
+        with torch.cuda.device(self.device):
+            res = self.handle.fetch(batch, _stream_ptr(self.device), raise_on_overflow)
+        self._keep = None
+        return res
+
+    def __call__(self, net_out, min_img_size):
+        return self.fetch(self.enqueue(net_out, min_img_size))
+
+    # ---- stages on tensors (used by the parse_skeletons mirror and by tests) ---------------------------------
+    def fuse_flip(self, net_out, flip_avg=True):
+        """(B,2,50,h,w) CUDA tensor -> (B,50,h,w) float32 CUDA tensor (K1)."""
+        net_out = net_out.to(self.device).contiguous()
+        B, _, _, h, w = net_out.shape
+        fused = torch.empty((B, _lib.NUM_LAYERS, h, w), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.handle.fuse_flip(net_out.data_ptr(), _DTYPES[net_out.dtype], B, h, w, fused.data_ptr(), flip_avg,
+                                  _stream_ptr(self.device))
+        return fused
+
+    def upsample_limbs(self, fused, up=4):
+        """(B,C>=30,h,w) planar -> (B, h*up, w*up, 30) HWC float32 (A4, evaluate.py:77-80)."""
+        fused = fused.to(self.device, torch.float32).contiguous()
+        B, Cs, h, w = fused.shape
+        out = torch.empty((B, h * up, w * up, _lib.NUM_LIMBS), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.handle.upsample_limbs(fused.data_ptr(), Cs, B, h, w, up, out.data_ptr(), _stream_ptr(self.device))
+        return out
+
+    def find_peaks(self, maps, first_chan, flavour=_lib.PEAKS_CROSS_REFINE):
+        """maps (B,C,h,w) planar float32 CUDA tensor; peaks stay on the device for assign()/fetch()."""
+        maps = maps.to(self.device, torch.float32).contiguous()
+        B, Cs, h, w = maps.shape
+        with torch.cuda.device(self.device):
+            self.handle.find_peaks(maps.data_ptr(), Cs, first_chan, B, h, w, flavour, _stream_ptr(self.device))
+        self._keep = maps
+        return B
+
+    def assign_feat(self, limb_planes, min_img_size):
+        """limb_planes (B,C>=30,h,w) planar feature-resolution maps, bicubic evaluated at the samples."""
+        t = limb_planes.to(self.device, torch.float32).contiguous()
+        B, Cs, h, w = t.shape
+        with torch.cuda.device(self.device):
+            self.handle.assign(t.data_ptr(), _lib.LIMB_FEAT_PLANAR, B, h, w, Cs, min_img_size,
+                               _stream_ptr(self.device))
+        self._keep2 = t
+
+    def assign_fullres(self, pafmap_hwc, min_img_size):
+        """pafmap_hwc (B,H,W,C>=30) float32 CUDA tensor in the reference layout."""
+        t = pafmap_hwc.to(self.device, torch.float32).contiguous()
+        B, H, W, Cc = t.shape
+        with torch.cuda.device(self.device):
+            self.handle.assign(t.data_ptr(), _lib.LIMB_FULLRES_HWC, B, H, W, Cc, min_img_size,
+                               _stream_ptr(self.device))
+        self._keep2 = t
+
+
+# ---- result conversions ------------------------------------------------------------------------------------------
+def to_humans(result):
+    """BatchResult -> list (per image) of [Human] exactly as evaluate.py:111-129 builds them."""
+    return [humans_from_result(result.peaks[b], result.humans[b]) for b in range(result.batch)]
+
+
+def to_coco_rows(result, b):
+    """evaluate.py:182-209 for image b: [(keypoints[17*3] CMU-18 -> COCO-17 via ORDER_COCO, score)]."""
+    rows = []
+    peaks = result.peaks[b]
+    for rec in result.humans[b]:
+        kp = np.zeros((18, 3), dtype=np.float32)
+        for part in range(18):
+            pid = int(rec["peak_id"][part])
+            if pid >= 0:
+                kp[part] = (peaks[pid]["x"], peaks[pid]["y"], 1)
+        rows.append((kp[ORDER_COCO].reshape(-1), float(rec["score"])))
+    return rows
+
+
+# ---- multi-GPU: images shard, no data-path collective ---------------------------------------------
+def shard_indices(n_images, rank, world):
+    """rank r of W takes images[r::W]."""
+    return list(range(rank, n_images, world))
+
+
+def merge_shards(shards, n_images):
+    """shards: list over ranks of [(image_index, payload)] -> list of payloads ordered by image index, independent of
+    the world size."""
+    out = [None] * n_images
+    for part in shards:
+        for idx, payload in part:
+            out[idx] = payload
+    if any(o is None for o in out):
+        raise ValueError("missing image results after merge")
+    return out
+
+
+def gather_results(local, n_images):
+    """Host-side gather of per-image results over torch.distributed (any backend; the payload is a few KB per
+    image, so this is an object gather, not a tensor collective).  Every rank returns the full ordered list."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return merge_shards([local], n_images)
+    buckets = [None] * dist.get_world_size()
+    dist.all_gather_object(buckets, local)
+    return merge_shards(buckets, n_images)

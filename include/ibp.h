@@ -1,0 +1,193 @@
+/* ibp.h — C ABI of the B200-native keypoint-assignment path (network output -> skeletons).
+ *
+ * One shared library, libibp_b200.so, hand-written sm_100a CUDA behind plain-C entry points: pointers and sizes
+ * only, no torch / numpy / C++ types.  Each entry point names the reference interface it replaces
+ * (paths relative to the reference repository sokunmin/Improved-Body-Parts).
+ *
+ * Three groups:
+ *   1. the seven legacy calls of utils/pafprocess/pafprocess.h:70-76 (what SWIG binds today) — host pointers,
+ *      process-global result state, same argument meaning, same getter protocol;
+ *   2. stage entry points on DEVICE pointers (fuse, peaks, limb up-sampling, assignment) for callers that keep
+ *      tensors resident — what utils/parse_skeletons.py's predict_refactor / heatmap_nms and evaluate.py:77-80
+ *      compute on the host today;
+ *   3. the batched pipeline (net output of B images in, packed skeletons out) that bench.py measures.
+ *
+ * There is no CPU fallback: every compute call returns IBP_ERR_NO_DEVICE / IBP_ERR_CUDA when no sm_100 device
+ * can run it.  Nothing aborts; ibp_last_error() gives the message of the last failing call on this thread.
+ */
+#ifndef IBP_B200_H
+#define IBP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IBP_NUM_PARTS 18  /* pafprocess.h:11 NUM_PART; config/config.py:64 */
+#define IBP_NUM_LIMBS 30  /* pafprocess.h:19 COCOPAIRS_SIZE; config/config.py:125 */
+#define IBP_NUM_LAYERS 50 /* config/config.py:128: [0,30) limb, [30,48) keypoint, [48,50) background */
+
+/* return codes (the reference always returns 0 and has undefined behaviour on bad input) */
+#define IBP_OK 0
+#define IBP_ERR_SHAPE (-1)     /* p3 < 5, f3 < 30, non-positive sizes */
+#define IBP_ERR_PART (-2)      /* part id outside [0,18) in the joint list */
+#define IBP_ERR_CAPACITY (-3)  /* a fixed-capacity device buffer overflowed; see ibp_limits and status bits */
+#define IBP_ERR_CUDA (-4)      /* CUDA runtime error, message in ibp_last_error() */
+#define IBP_ERR_ARG (-5)       /* null pointer / bad enum / batch larger than the handle's limit */
+#define IBP_ERR_NO_DEVICE (-6) /* no CUDA device: this library has no CPU path */
+
+/* element type of the network output handed to the fuse / pipeline calls */
+#define IBP_F32 0
+#define IBP_F16 1 /* apex amp O1 output, utils/parse_skeletons.py:75 */
+
+/* where the limb values come from in ibp_assign */
+#define IBP_LIMB_FULLRES_HWC 0 /* (H,W,30) float32 per image, the reference layout (pafprocess.cpp:9 PAF macro) */
+#define IBP_LIMB_FEAT_PLANAR 1 /* (C,h,w) planar feature-resolution maps, bicubic x`up` evaluated at the samples */
+
+/* peak extraction flavours */
+#define IBP_PEAKS_CROSS_REFINE 0 /* heatmap_nms: 4-connected NMS, strict > thr, 5x5 bicubic patch refine
+                                    (utils/parse_skeletons.py:106-176) */
+#define IBP_PEAKS_BOX_CENTROID 1 /* find_peaks: 3x3 NMS, >= thr, 5x5 centroid refine
+                                    (utils/parse_skeletons.py:286-321, utils/util.py:177-213) */
+
+/* per-image status bits (ibp_batch_view.status) */
+#define IBP_ST_PEAK_OVERFLOW 0x1u    /* more peaks of one part than limits.max_peaks_per_part */
+#define IBP_ST_CAND_OVERFLOW 0x2u    /* more accepted pairs on one limb than limits.max_candidates_per_limb */
+#define IBP_ST_BODY_OVERFLOW 0x4u    /* more simultaneous partial skeletons than limits.max_bodies */
+#define IBP_ST_HUMAN_OVERFLOW 0x8u   /* more humans than limits.max_humans */
+#define IBP_ST_TIE_EMULATED 0x10u    /* a limb had > 16 candidates with duplicate sort keys; order taken from the
+                                        libstdc++ introsort emulation (pafprocess.cpp:109) */
+#define IBP_ST_TIE_UNDEFINED 0x20u   /* ...and the reference's std::sort would have read out of bounds there */
+
+/* Constants the reference compiles in (pafprocess.h:6-18) or reads from utils/config:16-27. */
+typedef struct ibp_params {
+    float limb_sample_thresh; /* THRESH_PAF_SCORE 0.1        | thre2 */
+    float step_ratio;         /* THRESH_PAF_STEP_RATIO 0.8   | connect_ration */
+    int32_t min_parts;        /* THRESH_PART_CNT 2 */
+    float min_human_score;    /* THRESH_SKELETON_SCORE 0.45 */
+    int32_t max_steps;        /* STEP_PAF 20                 | mid_num */
+    int32_t len_rate;         /* LIMB_LENGTH_RATE 16         | len_rate */
+    float merge_tolerance;    /* MIN_SCORE_TOLERANCE 0.7     | connection_tole */
+    float weight_limb;        /* PAF_OUT_WEIGHTS[0] 0.5 */
+    float weight_a;           /* PAF_OUT_WEIGHTS[1] 0.25 */
+    float weight_b;           /* PAF_OUT_WEIGHTS[2] 0.25 */
+    float peak_thresh;        /* 0.1: literal at parse_skeletons.py:139 | thre1 for the box/centroid flavour */
+    int32_t upsample;         /* 4: model_cfg['stride'] (evaluate.py:76-80) */
+    int32_t refine_window;    /* 2: win_size at parse_skeletons.py:135 | offset_radius */
+} ibp_params;
+
+/* Fixed capacities of the device-side variable-length outputs. */
+typedef struct ibp_limits {
+    int32_t max_batch;               /* images per call */
+    int32_t max_peaks_per_part;      /* per image and joint type */
+    int32_t max_candidates_per_limb; /* accepted pairs kept for the sort, power of two */
+    int32_t max_bodies;              /* live partial skeletons during grouping */
+    int32_t max_humans;              /* humans reported per image */
+    int32_t max_feat_h, max_feat_w;  /* largest feature map handed to the pipeline */
+} ibp_limits;
+
+typedef struct ibp_peak { /* one row of the joint list (evaluate.py:99-103) after pafprocess.cpp:33-38 */
+    int32_t x, y;         /* truncated to int like the reference's Peak (pafprocess.h:29-34) */
+    float score;
+    int32_t part;
+} ibp_peak;
+
+typedef struct ibp_human { /* one row of the reference's skeleton table (pafprocess.cpp:16, pafprocess.h:36-45) */
+    int32_t peak_id[IBP_NUM_PARTS]; /* get_part_peak_id: id or -1 */
+    float score;                    /* get_score: total / count */
+    float total;                    /* slot 18 .score */
+    int32_t count;                  /* slot 19 .count */
+    float reach;                    /* slot 19 .length */
+} ibp_human;
+
+typedef struct ibp_batch_view { /* host pointers into pinned memory owned by the handle, valid until the next call */
+    int32_t batch;
+    int32_t peak_stride;        /* peaks of image b start at peaks + b*peak_stride */
+    int32_t human_stride;       /* humans of image b start at humans + b*human_stride */
+    const int32_t *n_peaks;     /* [batch] */
+    const int32_t *part_count;  /* [batch][18] peaks per joint type; peaks are stored part-major ("line" order) */
+    const ibp_peak *peaks;      /* [batch][peak_stride], index == peak id */
+    const int32_t *n_humans;    /* [batch] */
+    const ibp_human *humans;    /* [batch][human_stride] */
+    const uint32_t *status;     /* [batch] IBP_ST_* bits */
+} ibp_batch_view;
+
+typedef struct ibp_handle ibp_handle;
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * 1. Legacy protocol — replaces utils/pafprocess/pafprocess.h:70-76 as bound by utils/pafprocess/pafprocess.i:14.
+ *    HOST pointers.  Results live in a process-global handle until the next ibp_process_paf (the reference keeps
+ *    them in two globals, pafprocess.cpp:16-17); not thread-safe, exactly like the reference.
+ * ------------------------------------------------------------------------------------------------------------- */
+/* pafprocess.h:70 process_paf: peaks (p1,p2,p3>=5) rows [x,y,score,id,part]; pafmap (f1=H,f2=W,f3>=30) HWC. */
+int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, int f3, const float *pafmap,
+                    int min_img_size);
+int ibp_get_num_humans(void);                            /* pafprocess.h:71 */
+int ibp_get_part_peak_id(int skeleton_id, int part_id);  /* pafprocess.h:72 */
+float ibp_get_score(int skeleton_id);                    /* pafprocess.h:73 */
+int ibp_get_part_x(int cid);                             /* pafprocess.h:74 */
+int ibp_get_part_y(int cid);                             /* pafprocess.h:75 */
+float ibp_get_part_score(int cid);                       /* pafprocess.h:76 */
+uint32_t ibp_get_status(void);                           /* IBP_ST_* bits of the last legacy call (no counterpart) */
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * Handles, defaults, errors.
+ * ------------------------------------------------------------------------------------------------------------- */
+void ibp_default_params(ibp_params *p);
+void ibp_default_limits(ibp_limits *l);
+int ibp_create(ibp_handle **out, int device, const ibp_params *params /*NULL=defaults*/,
+               const ibp_limits *limits /*NULL=defaults*/);
+void ibp_destroy(ibp_handle *h);
+const char *ibp_last_error(void);
+int ibp_device_count(void); /* 0 when there is no usable CUDA device */
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * 2. Stage entry points.  All pointers are DEVICE pointers on the handle's device unless named host_*; `stream`
+ *    is a cudaStream_t passed as void* (NULL = default stream).  Calls are asynchronous on that stream.
+ * ------------------------------------------------------------------------------------------------------------- */
+/* K1 — flip/channel-permutation average: utils/parse_skeletons.py:80-96 (predict_refactor) and :232-248 (predict).
+ * net_out (batch,2,50,h,w) of `dtype`; fused (batch,50,h,w) float32 planar:
+ *   fused[c] = (net_out[0][c] + mirror_x(net_out[1][perm[c]])) / 2, averaged in `dtype` like numpy does.
+ * flip_avg == 0 copies net_out[:,0] (parse_skeletons.py:94-96). */
+int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int fh, int fw, int flip_avg,
+                  float *fused, void *stream);
+
+/* A4 — limb-map up-sampling: evaluate.py:77-80 / demo_image.py:94-97, cv2.resize(pafs, fx=up, fy=up, INTER_CUBIC).
+ * fused (batch,chan_stride,h,w) planar, limb channels first; out (batch, h*up, w*up, 30) HWC float32. */
+int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int batch, int fh, int fw, int up,
+                       float *out_hwc, void *stream);
+
+/* K2 — peaks: utils/parse_skeletons.py:126-176 heatmap_nms (flavour 0) or :286-321 find_peaks (flavour 1).
+ * maps (batch,chan_stride,h,w) planar float32, keypoint channel j at index first_chan + j.  Peaks are left in the
+ * handle's device buffers (part-major, row-major inside a part, ids = running counter, parse_skeletons.py:172-173)
+ * for ibp_assign / ibp_fetch. */
+int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw,
+                   int flavour, void *stream);
+
+/* Load an explicit joint list instead (legacy path, tests): host_peaks (n,5) rows [x,y,score,id,part] for ONE
+ * image slot `image`; ids are arrival order (pafprocess.cpp:34).  Synchronous host->device copy. */
+int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride);
+
+/* K3+K4 — pair scoring, ordering, greedy connection, grouping, filter: utils/pafprocess/pafprocess.cpp:52-285.
+ * limb_src layout per `mode`; for IBP_LIMB_FULLRES_HWC: (batch,H,W,C>=30) with H=dim0, W=dim1, C=dim2;
+ * for IBP_LIMB_FEAT_PLANAR: (batch,dim2,dim0,dim1) planar with `up` from the handle's params.
+ * min_img_size: the reference passes the image height (evaluate.py:110). */
+int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int dim0, int dim1, int dim2,
+               int min_img_size, void *stream);
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * 3. Batched pipeline: everything evaluate.py:75-129 does after the model call, for `batch` images.
+ *    net_out (batch,2,50,h,w); on_host != 0 means a HOST pointer (pinned or pageable) that is copied in-stream.
+ *    ibp_fetch waits for the stream, copies the packed results to the handle's pinned buffers and fills `view`.
+ * ------------------------------------------------------------------------------------------------------------- */
+int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw,
+                          int min_img_size, void *stream);
+int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream);
+/* number of kernels this library has launched through `h` since creation (bench.py's gpu_launches) */
+int64_t ibp_launch_count(const ibp_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IBP_B200_H */

@@ -1,0 +1,162 @@
+"""TEST INFRASTRUCTURE ONLY — numpy restatement of the Python half of the reference's hot path.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this module.
+The product package never does (it fails loudly without its CUDA library instead).
+
+Parity status: PINNED against the reference's own code run in the build container (tests/golden/make_golden.py
+imports /root/reference/utils/parse_skeletons.py and freezes its outputs; tests/test_oracle_numpy.py replays them),
+with ONE documented library switch: cv2's cubic resize is compared with `cv2.ipp.setUseIPP(False)`.  OpenCV's own
+C++ cubic kernel is reproduced here bit-for-bit; the closed-source IPP kernel that opencv-python substitutes for
+1/3/4-channel images is CPU-dispatch dependent and differs from OpenCV's own code by <= 1.2e-7 abs.
+The 30-channel limb-map resize (evaluate.py:77-80) never goes through IPP and matches cv2 with no switch at all.
+
+Every function cites the reference lines it restates (paths relative to /root/reference/).
+"""
+import numpy as np
+
+f32 = np.float32
+
+NUM_KEYPOINTS = 18  # utils/parse_skeletons.py:17
+NUM_HEATMAPS = 20   # :18
+NUM_PAFS = 30       # :19
+
+# config/config.py:150-152
+FLIP_HEAT_ORD = np.array([0, 1, 5, 6, 7, 2, 3, 4, 11, 12, 13, 8, 9, 10, 15, 14, 17, 16, 18, 19])
+FLIP_PAF_ORD = np.array([0, 2, 1, 4, 3, 6, 5, 8, 7, 12, 13, 14, 9, 10, 11, 18, 19, 20, 15, 16, 17,
+                         22, 21, 25, 26, 23, 24, 28, 27, 29])
+# config/config.py:114-123 == utils/pafprocess/pafprocess.h:20-27
+LIMBS = np.array([[1, 0], [1, 14], [1, 15], [1, 16], [1, 17], [0, 14], [0, 15], [14, 16], [15, 17], [1, 2],
+                  [2, 3], [3, 4], [1, 5], [5, 6], [6, 7], [1, 8], [8, 9], [9, 10], [1, 11], [11, 12],
+                  [12, 13], [0, 2], [0, 5], [2, 8], [8, 12], [5, 11], [11, 9], [16, 2], [17, 5], [8, 11]])
+ORDER_COCO = [0, 15, 14, 17, 16, 5, 2, 6, 3, 7, 4, 11, 8, 12, 9, 13, 10]  # evaluate.py:40
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A0  flip fusion — utils/parse_skeletons.py:80-103
+# ----------------------------------------------------------------------------------------------------------
+def fuse_flip(net_out, flip_avg=True):
+    """net_out (2,50,h,w) in the model's dtype -> heatmaps (h,w,20), pafs (h,w,30), float32 HWC.
+
+    The average runs in the input dtype (fp16 under amp O1, parse_skeletons.py:75) and only the result is cast
+    (l.103)."""
+    out = np.asarray(net_out)
+    blob = out[0].transpose(1, 2, 0)
+    paf, heat = blob[:, :, :NUM_PAFS], blob[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS]
+    if flip_avg:
+        blob_f = out[1].transpose(1, 2, 0)
+        paf_f, heat_f = blob_f[:, :, :NUM_PAFS], blob_f[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS]
+        paf = (paf + paf_f[:, ::-1, :][:, :, FLIP_PAF_ORD]) / 2
+        heat = (heat + heat_f[:, ::-1, :][:, :, FLIP_HEAT_ORD]) / 2
+    return heat.astype(f32), paf.astype(f32)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# OpenCV-native cubic resize, integer up-scaling (cv2.resize(..., fx=up, fy=up, INTER_CUBIC), IPP off)
+# ----------------------------------------------------------------------------------------------------------
+def _cubic_weights(t):
+    """OpenCV interpolateCubic, A = -0.75, float32 arithmetic."""
+    t = f32(t)
+    A = f32(-0.75)
+    one = f32(1)
+    w0 = ((A * (t + one) - f32(5) * A) * (t + one) + f32(8) * A) * (t + one) - f32(4) * A
+    w1 = ((A + f32(2)) * t - (A + f32(3))) * t * t + one
+    w2 = ((A + f32(2)) * (one - t) - (A + f32(3))) * (one - t) * (one - t) + one
+    w3 = one - w0 - w1 - w2
+    return np.array([w0, w1, w2, w3], dtype=f32)
+
+
+def _cubic_taps(n_src, n_dst, scale):
+    """per destination index: 4 clamped source indices and 4 float32 weights (OpenCV resize.cpp, cubic branch:
+    fx = (float)((dx+0.5)*scale - 0.5); sx = floor(fx); fx -= sx; replicate border)."""
+    idx = np.empty((n_dst, 4), dtype=np.int64)
+    wts = np.empty((n_dst, 4), dtype=f32)
+    for d in range(n_dst):
+        fx = f32((d + 0.5) * scale - 0.5)
+        sx = int(np.floor(fx))
+        wts[d] = _cubic_weights(f32(fx - f32(sx)))
+        idx[d] = np.clip(np.arange(sx - 1, sx + 3), 0, n_src - 1)
+    return idx, wts
+
+
+def cubic_upsample(src, up):
+    """Bit-exact restatement of cv2.resize(src, None, fx=up, fy=up, interpolation=cv2.INTER_CUBIC) for float32
+    input on OpenCV's own code path.  Horizontal pass: ((s0*a0 + s1*a1) + s2*a2) + s3*a3 (HResizeCubic).  Vertical
+    pass: s0*b0 + (s1*b1 + (s2*b2 + s3*b3)) (VResizeCubicVec_32f; the 4-lane vector loop covers the whole row
+    because the destination row length is a multiple of `up` = 4)."""
+    s = np.asarray(src, dtype=f32)
+    squeeze = s.ndim == 2
+    if squeeze:
+        s = s[:, :, None]
+    h, w, _ = s.shape
+    up = int(up)
+    xi, xw = _cubic_taps(w, w * up, 1.0 / up)
+    yi, yw = _cubic_taps(h, h * up, 1.0 / up)
+    p = [s[:, xi[:, k], :] * xw[:, k][None, :, None] for k in range(4)]
+    rows = ((p[0] + p[1]) + p[2]) + p[3]
+    q = [rows[yi[:, k], :, :] * yw[:, k][:, None, None] for k in range(4)]
+    out = q[0] + (q[1] + (q[2] + q[3]))
+    if (w * up * s.shape[2]) % 4:
+        raise NotImplementedError("row length not a multiple of 4: OpenCV's scalar tail uses another order")
+    return out[:, :, 0] if squeeze else out
+
+
+def limb_upsample(pafs, up=4):
+    """A4 — evaluate.py:77-80 / demo_image.py:94-97."""
+    return cubic_upsample(pafs, up)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A2  cross-footprint NMS — utils/parse_skeletons.py:106-119
+# ----------------------------------------------------------------------------------------------------------
+def cross_nms(img, thr=0.1):
+    """maximum_filter(img, footprint=cross) == img, AND img > thr (strict, float32 compare).  scipy's default
+    border 'reflect' repeats the edge pixel, so out-of-image neighbours never beat the centre.  Returns (n,2)
+    int64 [x, y] in row-major (y, then x) order — the order of np.nonzero."""
+    a = np.asarray(img)
+    big = np.pad(a, 1, mode="edge")
+    c = big[1:-1, 1:-1]
+    keep = (c >= big[:-2, 1:-1]) & (c >= big[2:, 1:-1]) & (c >= big[1:-1, :-2]) & (c >= big[1:-1, 2:])
+    keep &= a > a.dtype.type(thr)
+    ys, xs = np.nonzero(keep)
+    return np.stack([xs, ys], axis=1).astype(np.int64)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A3  per-peak patch refinement — utils/parse_skeletons.py:122-176
+# ----------------------------------------------------------------------------------------------------------
+def heatmap_nms(heatmaps, upsample_factor=4, bool_refine_center=True):
+    """heatmaps (h,w,>=18) float32 -> list of 18 arrays (n,4) float32 [x, y, score, id]."""
+    up = int(upsample_factor)
+    win = 2
+    out = []
+    total = 0
+    h, w = heatmaps.shape[:2]
+    for joint in range(NUM_KEYPOINTS):
+        m = np.ascontiguousarray(heatmaps[:, :, joint], dtype=f32)
+        coords = cross_nms(m, 0.1)  # literal 0.1 at :139
+        peaks = np.zeros((len(coords), 4), dtype=f32)
+        for i, (px, py) in enumerate(coords):
+            if bool_refine_center:
+                x0, y0 = max(0, px - win), max(0, py - win)
+                x1, y1 = min(w - 1, px + win), min(h - 1, py + win)
+                patch_up = cubic_upsample(m[y0:y1 + 1, x0:x1 + 1], up)  # border = replicate of the PATCH
+                flat = int(np.argmax(patch_up))  # first maximum in row-major order
+                ry, rx = divmod(flat, patch_up.shape[1])
+                # :159-172 reduces to integer arithmetic: (p+0.5)*up-0.5 + (r - ((p-p0+0.5)*up-0.5)) = p0*up + r
+                peaks[i] = (f32(x0 * up + rx), f32(y0 * up + ry), patch_up[ry, rx], total)
+            else:
+                peaks[i] = ((f32(px) + f32(0.5)) * up - f32(0.5), (f32(py) + f32(0.5)) * up - f32(0.5),
+                            m[py, px], total)
+            total += 1
+        out.append(peaks)
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A5  joint list — evaluate.py:99-108
+# ----------------------------------------------------------------------------------------------------------
+def joint_list(all_peaks):
+    rows = [tuple(p) + (t,) for t, peaks in enumerate(all_peaks) for p in peaks]
+    if not rows:
+        return np.zeros((0, 5), dtype=f32)
+    return np.array(rows).astype(f32)
