@@ -38,7 +38,7 @@ int fail(int code, const char *fmt, ...) {
         if (e__ != cudaSuccess) return fail(IBP_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
     } while (0)
 
-constexpr size_t kMaxDynSmem = 227 * 1024;
+constexpr size_t kMaxDynSmem = 220 * 1024;  // opt-in dynamic shared memory we ask for (device max 227 KB minus static use)
 constexpr size_t kPeakBandBytes = 64 * 1024;
 constexpr size_t kLimbPlaneMaxBytes = 96 * 1024;
 

@@ -1,0 +1,105 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for coordinates, ids and assignments; scores compared exactly as well (the tolerance of north_star is
+1e-4 relative, the expectation is 0 ulp)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SEEDS = [(11, 1), (12, 4), (13, 10), (14, 25), (15, 50)]
+
+
+@pytest.fixture(scope="module")
+def pp():
+    from improved_body_parts_b200.pipeline import PostProcessor
+    return PostProcessor(device=0, max_batch=8, max_bodies=1024, max_humans=256, max_candidates_per_limb=4096)
+
+
+def _oracle_image(oracle, out):
+    from oracle import np_oracle as O
+    heat, paf = O.fuse_flip(out)
+    peaks = O.heatmap_nms(heat, 4)
+    jl = O.joint_list(peaks)
+    oracle.process_paf_feat(jl[None], np.ascontiguousarray(paf.transpose(2, 0, 1)), 4, 512)
+    return heat, paf, peaks, jl, oracle.humans()
+
+
+def test_fuse_flip_exact(pp):
+    import torch
+    from improved_body_parts_b200 import synth
+    from oracle import np_oracle as O
+    out, _ = synth.make_network_output(21, 6)
+    fused = pp.fuse_flip(torch.from_numpy(out[None]).cuda())[0].cpu().numpy()
+    heat, paf = O.fuse_flip(out)
+    assert np.array_equal(fused[:30].transpose(1, 2, 0), paf)
+    assert np.array_equal(fused[30:50].transpose(1, 2, 0), heat)
+    # fp16 network output (amp O1): the average is taken in half precision like numpy does
+    out16 = out.astype(np.float16)
+    fused16 = pp.fuse_flip(torch.from_numpy(out16[None]).cuda())[0].cpu().numpy()
+    heat16, paf16 = O.fuse_flip(out16)
+    assert np.array_equal(fused16[:30].transpose(1, 2, 0), paf16)
+    assert np.array_equal(fused16[30:50].transpose(1, 2, 0), heat16)
+
+
+@pytest.mark.parametrize("seed,people", SEEDS)
+def test_peaks_exact(pp, oracle, seed, people):
+    import torch
+    from improved_body_parts_b200 import synth
+    out, _ = synth.make_network_output(seed, people)
+    heat, paf, peaks, jl, _ = _oracle_image(oracle, out)
+    maps = torch.from_numpy(np.ascontiguousarray(heat[:, :, :18].transpose(2, 0, 1))[None]).cuda()
+    pp.find_peaks(maps, 0)
+    res = pp.fetch(1)
+    assert res.n_peaks[0] == jl.shape[0]
+    assert np.array_equal(res.part_count[0], [len(p) for p in peaks])
+    got = res.peaks[0]
+    assert np.array_equal(got["x"], jl[:, 0].astype(np.int32))
+    assert np.array_equal(got["y"], jl[:, 1].astype(np.int32))
+    assert np.array_equal(got["score"], jl[:, 2])
+    assert np.array_equal(got["part"], jl[:, 4].astype(np.int32))
+
+
+@pytest.mark.parametrize("seed,people", SEEDS)
+def test_pipeline_exact(pp, oracle, seed, people):
+    from improved_body_parts_b200 import synth
+    out, _ = synth.make_network_output(seed, people)
+    _, _, _, jl, humans = _oracle_image(oracle, out)
+    res = pp(out[None], 512)
+    assert res.n_humans[0] == len(humans)
+    for rec, (ids, score) in zip(res.humans[0], humans):
+        assert np.array_equal(rec["peak_id"], ids)
+        assert rec["score"] == score
+    assert res.status[0] & 0xF == 0
+
+
+@pytest.mark.parametrize("seed,people", SEEDS[:4])
+def test_legacy_process_paf_exact(oracle, seed, people):
+    """The seven-call protocol with HOST arrays in the reference layout (evaluate.py:106-129)."""
+    from improved_body_parts_b200 import pafprocess, synth
+    from oracle import np_oracle as O
+    out, _ = synth.make_network_output(seed, people)
+    heat, paf = O.fuse_flip(out)
+    jl = O.joint_list(O.heatmap_nms(heat, 4))[None]
+    up = O.limb_upsample(paf, 4)
+    oracle.process_paf(jl, up, 512)
+    assert pafprocess.process_paf(jl, up, 512) == 0
+    assert pafprocess.get_num_humans() == oracle.get_num_humans()
+    for h in range(oracle.get_num_humans()):
+        for part in range(18):
+            assert pafprocess.get_part_peak_id(h, part) == oracle.get_part_peak_id(h, part)
+        assert np.float32(pafprocess.get_score(h)) == np.float32(oracle.get_score(h))
+    for cid in range(jl.shape[1]):
+        assert pafprocess.get_part_x(cid) == oracle.get_part_x(cid)
+        assert pafprocess.get_part_y(cid) == oracle.get_part_y(cid)
+        assert np.float32(pafprocess.get_part_score(cid)) == np.float32(oracle.get_part_score(cid))
+
+
+def test_upsample_limbs_exact(pp):
+    import torch
+    from improved_body_parts_b200 import synth
+    from oracle import np_oracle as O
+    out, _ = synth.make_network_output(31, 8)
+    _, paf = O.fuse_flip(out)
+    t = torch.from_numpy(np.ascontiguousarray(paf.transpose(2, 0, 1))[None]).cuda()
+    got = pp.upsample_limbs(t, 4)[0].cpu().numpy()
+    assert np.array_equal(got, O.limb_upsample(paf, 4))
