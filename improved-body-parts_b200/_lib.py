@@ -103,6 +103,10 @@ def lib():
     L.ibp_fetch.argtypes = [vp, ip, C.POINTER(BatchView), vp]
     L.ibp_launch_count.restype = C.c_int64
     L.ibp_launch_count.argtypes = [vp]
+    L.ibp_set_profiling.restype = ip
+    L.ibp_set_profiling.argtypes = [vp, ip]
+    L.ibp_get_stage_ms.restype = ip
+    L.ibp_get_stage_ms.argtypes = [vp, fp]
     _lib = L
     return L
 
@@ -110,7 +114,9 @@ def lib():
 EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp_get_score", "ibp_get_part_x",
            "ibp_get_part_y", "ibp_get_part_score", "ibp_get_status", "ibp_default_params", "ibp_default_limits",
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_upsample_limbs",
-           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_launch_count"]
+           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_launch_count", "ibp_set_profiling",
+           "ibp_get_stage_ms"]
+STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
 
 def check(rc):
@@ -179,6 +185,15 @@ class Handle:
     @property
     def launches(self):
         return int(lib().ibp_launch_count(self._h))
+
+    def set_profiling(self, on=True):
+        check(lib().ibp_set_profiling(self._h, int(bool(on))))
+
+    def stage_ms(self):
+        """{stage: ms} of the kernels of the last call, from CUDA events on the launching stream."""
+        buf = (C.c_float * len(STAGES))()
+        check(lib().ibp_get_stage_ms(self._h, buf))
+        return {n: float(buf[i]) for i, n in enumerate(STAGES) if buf[i] >= 0}
 
     # ---- raw stage calls on device pointers (ints) ----
     def fuse_flip(self, net_out_ptr, dtype, batch, fh, fw, fused_ptr, flip_avg=True, stream=0):

@@ -84,6 +84,10 @@ struct ibp_handle {
     uint32_t *h_status = nullptr;
     DevPeak *h_peaks_stage = nullptr;  // one image worth of per-part lists for ibp_set_peaks
     int64_t launches = 0;
+    // optional per-kernel timing with events recorded on the launching stream (ibp_set_profiling)
+    int profiling = 0;
+    cudaEvent_t ev[2 * IBP_NUM_STAGES] = {nullptr};
+    int ev_used[IBP_NUM_STAGES] = {0};
 };
 
 namespace {
@@ -125,6 +129,11 @@ void destroy_buffers(ibp_handle *h) {
     free_host(h->h_humans);
     free_host(h->h_status);
     free_host(h->h_peaks_stage);
+    for (int i = 0; i < 2 * IBP_NUM_STAGES; i++)
+        if (h->ev[i]) {
+            cudaEventDestroy(h->ev[i]);
+            h->ev[i] = nullptr;
+        }
 }
 
 size_t limb_smem_bytes(const ibp_handle *h, size_t plane_bytes) {
@@ -142,9 +151,47 @@ int validate_limits(const ibp_limits &l) {
     return IBP_OK;
 }
 
+struct StageTimer {
+    ibp_handle *h;
+    int stage;
+    cudaStream_t st;
+    StageTimer(ibp_handle *h_, int stage_, cudaStream_t st_) : h(h_), stage(stage_), st(st_) {
+        if (h->profiling) cudaEventRecord(h->ev[2 * stage], st);
+    }
+    ~StageTimer() {
+        if (h->profiling) {
+            cudaEventRecord(h->ev[2 * stage + 1], st);
+            h->ev_used[stage] = 1;
+        }
+    }
+};
+
 }  // namespace
 
 extern "C" {
+
+int ibp_set_profiling(ibp_handle *h, int on) {
+    if (!h) return fail(IBP_ERR_ARG, "ibp_set_profiling: null handle");
+    CU(cudaSetDevice(h->device));
+    if (on && !h->ev[0])
+        for (int i = 0; i < 2 * IBP_NUM_STAGES; i++) CU(cudaEventCreate(&h->ev[i]));
+    h->profiling = on ? 1 : 0;
+    for (int i = 0; i < IBP_NUM_STAGES; i++) h->ev_used[i] = 0;
+    return IBP_OK;
+}
+
+int ibp_get_stage_ms(ibp_handle *h, float *ms) {
+    if (!h || !ms) return fail(IBP_ERR_ARG, "ibp_get_stage_ms: null argument");
+    CU(cudaSetDevice(h->device));
+    for (int i = 0; i < IBP_NUM_STAGES; i++) {
+        ms[i] = -1.0f;
+        if (h->profiling && h->ev_used[i]) {
+            CU(cudaEventSynchronize(h->ev[2 * i + 1]));
+            CU(cudaEventElapsedTime(&ms[i], h->ev[2 * i], h->ev[2 * i + 1]));
+        }
+    }
+    return IBP_OK;
+}
 
 void ibp_default_params(ibp_params *p) {
     if (!p) return;
@@ -281,13 +328,16 @@ int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int 
     if (dtype == IBP_F32 && aligned && fw % 4 == 0) {
         const int hw4 = (int)(hw / 4);
         dim3 grid((hw4 + 255) / 256, kLayers, batch);
+        StageTimer t(h, IBP_STAGE_FUSE, st);
         fuse_flip_f32_vec4<<<grid, 256, 0, st>>>((const float *)net_out, fused, hw4, fw / 4, flip_avg);
     } else if (dtype == IBP_F16 && aligned && fw % 8 == 0) {
         const int hw8 = (int)(hw / 8);
         dim3 grid((hw8 + 255) / 256, kLayers, batch);
+        StageTimer t(h, IBP_STAGE_FUSE, st);
         fuse_flip_f16_vec8<<<grid, 256, 0, st>>>((const __half *)net_out, fused, hw8, fw / 8, flip_avg);
     } else {
         dim3 grid((unsigned)std::min<size_t>((hw + 255) / 256, 65535), kLayers, batch);
+        StageTimer t(h, IBP_STAGE_FUSE, st);
         if (dtype == IBP_F32)
             fuse_flip_scalar<float><<<grid, 256, 0, st>>>((const float *)net_out, fused, fh, fw, flip_avg);
         else
@@ -314,6 +364,7 @@ int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int b
     dim3 grid((Wo + kUpTileX - 1) / kUpTileX, (Ho + up - 1) / up, batch);
     const size_t smem = (size_t)kLimbs * kUpMaxRows * (kUpTileX / up + 6) * sizeof(float);
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_upsample_limbs: up=%d not supported", up);
+    StageTimer t(h, IBP_STAGE_UPSAMPLE, (cudaStream_t)stream);
     upsample_limbs_kernel<<<grid, kUpThreads, smem, (cudaStream_t)stream>>>(a);
     h->launches++;
     CU(cudaGetLastError());
@@ -363,10 +414,16 @@ int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_
     smem += (size_t)a.cap * sizeof(short2);
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_find_peaks: row of %d floats does not fit shared memory", fw);
     CU(cudaMemsetAsync(h->d_status, 0, (size_t)batch * sizeof(uint32_t), st));
-    peaks_kernel<<<dim3(kParts, batch), kPeakThreads, smem, st>>>(a);
+    {
+        StageTimer t(h, IBP_STAGE_PEAKS, st);
+        peaks_kernel<<<dim3(kParts, batch), kPeakThreads, smem, st>>>(a);
+    }
     h->launches++;
     CU(cudaGetLastError());
-    pack_peaks_kernel<<<batch, 128, 0, st>>>(h->d_peaks, h->d_part_count, a.cap, h->d_line, h->line_stride, h->d_n_peaks);
+    {
+        StageTimer t(h, IBP_STAGE_PACK, st);
+        pack_peaks_kernel<<<batch, 128, 0, st>>>(h->d_peaks, h->d_part_count, a.cap, h->d_line, h->line_stride, h->d_n_peaks);
+    }
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;
@@ -460,7 +517,10 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
     a.links = h->d_links;
     a.link_count = h->d_link_count;
     a.status = h->d_status;
-    limbs_kernel<<<dim3(kLimbs, batch), kLimbThreads, limb_smem_bytes(h, plane_bytes), st>>>(a);
+    {
+        StageTimer t(h, IBP_STAGE_LIMBS, st);
+        limbs_kernel<<<dim3(kLimbs, batch), kLimbThreads, limb_smem_bytes(h, plane_bytes), st>>>(a);
+    }
     h->launches++;
     CU(cudaGetLastError());
 
@@ -479,7 +539,10 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
     g.humans = h->d_humans;
     g.n_humans = h->d_n_humans;
     g.status = h->d_status;
-    group_kernel<<<batch, 32, group_smem_bytes(h), st>>>(g);
+    {
+        StageTimer t(h, IBP_STAGE_GROUP, st);
+        group_kernel<<<batch, 32, group_smem_bytes(h), st>>>(g);
+    }
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;

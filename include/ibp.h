@@ -187,6 +187,19 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream);
 /* number of kernels this library has launched through `h` since creation (bench.py's gpu_launches) */
 int64_t ibp_launch_count(const ibp_handle *h);
 
+
+/* Per-kernel device times, measured with CUDA events recorded on the launching stream around each kernel of the
+ * last call(s).  Stage indices below; ms[i] < 0 when the stage did not run.  ibp_get_stage_ms waits for the events. */
+#define IBP_STAGE_FUSE 0
+#define IBP_STAGE_PEAKS 1
+#define IBP_STAGE_PACK 2
+#define IBP_STAGE_LIMBS 3
+#define IBP_STAGE_GROUP 4
+#define IBP_STAGE_UPSAMPLE 5
+#define IBP_NUM_STAGES 6
+int ibp_set_profiling(ibp_handle *h, int on);
+int ibp_get_stage_ms(ibp_handle *h, float *ms /* [IBP_NUM_STAGES] */);
+
 #ifdef __cplusplus
 }
 #endif

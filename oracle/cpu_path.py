@@ -1,0 +1,119 @@
+"""TEST INFRASTRUCTURE ONLY — the reference's CPU post-processing route, timed as the baseline.
+
+`postprocess_image` performs, for one image, exactly what evaluate.py:75-129 runs after the model call with
+`--run_refactor --run_cpp`: flip average (parse_skeletons.py:80-103), heatmap_nms with scipy's maximum_filter and one
+cv2.resize per peak (parse_skeletons.py:106-176), cv2.resize of the limb maps x4 (evaluate.py:77-80), joint-list
+packing (evaluate.py:99-108), process_paf and the getter loop (evaluate.py:110-129).
+
+/root/reference does not exist on the GPU box, so the Python half is this restatement issuing the SAME library
+calls (scipy.ndimage.maximum_filter, cv2.resize INTER_CUBIC) and the C++ half is the UNMODIFIED reference
+pafprocess.cpp prebuilt into oracle/_ref/libpafprocess_ref.so when available (else the C++ oracle port).
+bench.py (cpu_baseline leg and --impl reference) is the only caller besides tests.
+"""
+import os
+
+import numpy as np
+
+from . import np_oracle as O
+
+_state = {}
+
+
+def _cpp():
+    if "cpp" not in _state:
+        from .cpu_lib import Oracle, Reference, reference_available
+        if reference_available():
+            _state["cpp"], _state["kind"] = Reference(), "reference"
+        else:
+            _state["cpp"], _state["kind"] = Oracle(), "port"
+    return _state["cpp"]
+
+
+def cpp_kind():
+    _cpp()
+    return _state["kind"]
+
+
+def heatmap_nms_cv2(heatmaps, up=4):
+    """parse_skeletons.py:126-176 with the reference's own library calls."""
+    import cv2
+    from scipy.ndimage import generate_binary_structure, maximum_filter
+    cross = generate_binary_structure(2, 1)
+    out, total = [], 0
+    for joint in range(O.NUM_KEYPOINTS):
+        m = heatmaps[:, :, joint]
+        binary = (maximum_filter(m, footprint=cross) == m) * (m > 0.1)
+        coords = np.array(np.nonzero(binary)[::-1]).T
+        peaks = np.zeros((len(coords), 4), dtype=np.float32)
+        for i, peak in enumerate(coords):
+            x0, y0 = np.maximum(0, peak - 2)
+            x1, y1 = np.minimum(np.array(m.T.shape) - 1, peak + 2)
+            patch = m[y0:y1 + 1, x0:x1 + 1]
+            big = cv2.resize(patch, None, fx=up, fy=up, interpolation=cv2.INTER_CUBIC)
+            loc = np.unravel_index(big.argmax(), big.shape)
+            center = (np.array(peak[::-1] - [y0, x0], dtype=np.float32) + 0.5) * up - 0.5
+            refined = loc - center
+            xy = (np.array(coords[i], dtype=np.float32) + 0.5) * up - 0.5 + refined[::-1]
+            peaks[i, :] = (xy[0], xy[1], big[loc], total)
+            total += 1
+        out.append(peaks)
+    return out
+
+
+def postprocess_image(net_out, img_h=512, up=4):
+    """net_out (2,50,h,w) -> [(keypoints {part: (x,y,score)}, human score)]"""
+    import cv2
+    heat, paf = O.fuse_flip(net_out)
+    all_peaks = heatmap_nms_cv2(heat, up)
+    paf_up = cv2.resize(paf, None, fx=up, fy=up, interpolation=cv2.INTER_CUBIC)
+    jl = O.joint_list(all_peaks)
+    humans = []
+    if jl.shape[0] > 0:
+        cpp = _cpp()
+        cpp.process_paf(jl[None], paf_up, img_h)
+        for h in range(cpp.get_num_humans()):
+            parts = {}
+            for part in range(18):
+                pid = cpp.get_part_peak_id(h, part)
+                if pid < 0:
+                    continue
+                parts[part] = (cpp.get_part_x(pid), cpp.get_part_y(pid), cpp.get_part_score(pid))
+            if parts:
+                humans.append((parts, cpp.get_score(h)))
+    return humans
+
+
+_shared = {}  # the sample is inherited by forked workers instead of being pickled to them
+
+
+def _worker(args):
+    import cv2
+    cv2.setNumThreads(1)
+    idx, img_h = args
+    batch = _shared["batch"]
+    return [len(postprocess_image(batch[i], img_h)) for i in idx]
+
+
+def time_batch(batch, img_h=512, procs=None, repeat=1):
+    """Seconds to post-process `batch` (n,2,50,h,w) once on `procs` host processes (default: all cores), images
+    sharded evenly; returns (seconds, procs)."""
+    import multiprocessing as mp
+    import time
+    procs = procs or os.cpu_count() or 1
+    n = batch.shape[0]
+    procs = max(1, min(procs, n))
+    _shared["batch"] = batch
+    if procs == 1:
+        t0 = time.perf_counter()
+        for _ in range(repeat):
+            _worker((list(range(n)), img_h))
+        return (time.perf_counter() - t0) / repeat, 1
+    ctx = mp.get_context("fork")
+    shards = [(list(range(r, n, procs)), img_h) for r in range(procs)]
+    with ctx.Pool(procs) as pool:
+        pool.map(_worker, [([0], img_h)] * procs, chunksize=1)  # warm the workers (imports, page-in)
+        t0 = time.perf_counter()
+        for _ in range(repeat):
+            pool.map(_worker, shards, chunksize=1)
+        dt = (time.perf_counter() - t0) / repeat
+    return dt, procs
