@@ -11,7 +11,6 @@
 
 #include "ibp_device.cuh"
 #include "k_fuse.cuh"
-#include "k_group.cuh"
 #include "k_limbs.cuh"
 #include "k_peaks.cuh"
 #include "k_upsample.cuh"
@@ -39,8 +38,18 @@ int fail(int code, const char *fmt, ...) {
     } while (0)
 
 constexpr size_t kMaxDynSmem = 220 * 1024;  // opt-in dynamic shared memory we ask for (device max 227 KB minus static use)
-constexpr size_t kPeakBandBytes = 64 * 1024;
+constexpr size_t kPeakBandTarget = 16 * 1024;  // owned rows of one band (the CTA also stages 2*halo rows around them)
 constexpr size_t kLimbPlaneMaxBytes = 96 * 1024;
+
+size_t peak_band_target() {
+    static size_t v = 0;
+    if (!v) {
+        const char *e = getenv("IBP_PEAK_BAND_BYTES");  // tuning knob for experiments
+        v = e ? (size_t)atol(e) : kPeakBandTarget;
+        if (v < 1024) v = 1024;
+    }
+    return v;
+}
 
 template <typename T>
 void free_dev(T *&p) {
@@ -71,6 +80,12 @@ struct ibp_handle {
     ibp_human *d_humans = nullptr;
     int *d_n_humans = nullptr;
     uint32_t *d_status = nullptr;
+    // scratch of the banded peak kernel and the two ticket counters (last CTA of an image packs / groups)
+    DevPeak *d_band_peaks = nullptr;
+    float *d_band_subpix = nullptr;
+    int *d_band_count = nullptr;
+    int band_slots = 0;  // nbands the scratch was sized for
+    unsigned *d_ticket = nullptr;  // [2][max_batch]
     float *d_fused = nullptr;
     size_t fused_floats = 0;
     void *d_stage = nullptr;  // host input staging / legacy limb map
@@ -100,6 +115,19 @@ int ensure_stage(ibp_handle *h, size_t bytes) {
     h->stage_bytes = bytes;
     return IBP_OK;
 }
+int ensure_bands(ibp_handle *h, int nbands) {
+    if (h->band_slots >= nbands) return IBP_OK;
+    free_dev(h->d_band_peaks);
+    free_dev(h->d_band_subpix);
+    free_dev(h->d_band_count);
+    h->band_slots = 0;
+    const size_t n = (size_t)h->L.max_batch * kParts * nbands;
+    CU(cudaMalloc(&h->d_band_peaks, n * h->L.max_peaks_per_part * sizeof(DevPeak)));
+    CU(cudaMalloc(&h->d_band_subpix, n * h->L.max_peaks_per_part * 2 * sizeof(float)));
+    CU(cudaMalloc(&h->d_band_count, n * sizeof(int)));
+    h->band_slots = nbands;
+    return IBP_OK;
+}
 int ensure_fused(ibp_handle *h, size_t floats) {
     if (h->fused_floats >= floats) return IBP_OK;
     free_dev(h->d_fused);
@@ -122,6 +150,10 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_status);
     free_dev(h->d_fused);
     free_dev(h->d_stage);
+    free_dev(h->d_band_peaks);
+    free_dev(h->d_band_subpix);
+    free_dev(h->d_band_count);
+    free_dev(h->d_ticket);
     free_host(h->h_n_peaks);
     free_host(h->h_part_count);
     free_host(h->h_line);
@@ -136,12 +168,19 @@ void destroy_buffers(ibp_handle *h) {
         }
 }
 
-size_t limb_smem_bytes(const ibp_handle *h, size_t plane_bytes) {
+// shared memory of the limb phase (layout in k_limbs.cuh) ...
+size_t limb_phase_bytes(const ibp_handle *h, size_t plane_bytes) {
     size_t region0 = std::max(plane_bytes, (size_t)h->L.max_candidates_per_limb * 8);
     region0 = (region0 + 15) & ~(size_t)15;
-    return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2);
+    return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2) +
+           (size_t)kPairChunk * (sizeof(PairGeo) + (size_t)h->P.max_steps * 4);
 }
-size_t group_smem_bytes(const ibp_handle *h) { return (size_t)h->L.max_bodies * (kParts * 8 + 12); }
+// ... and of the grouping phase that the last CTA of an image runs in the same allocation (k_group.cuh): the
+// skeleton table plus room for at least 256 staged connections
+size_t group_phase_bytes(const ibp_handle *h) { return (((size_t)h->L.max_bodies * kBodyBytes + 15) & ~(size_t)15) + 128 + 256 * sizeof(DevLink); }
+size_t limb_smem_bytes(const ibp_handle *h, size_t plane_bytes) {
+    return (std::max(limb_phase_bytes(h, plane_bytes), group_phase_bytes(h)) + 15) & ~(size_t)15;
+}
 
 int validate_limits(const ibp_limits &l) {
     if (l.max_batch < 1 || l.max_peaks_per_part < 1 || l.max_peaks_per_part > 32767 || l.max_candidates_per_limb < 32 ||
@@ -214,8 +253,8 @@ void ibp_default_limits(ibp_limits *l) {
     if (!l) return;
     l->max_batch = 64;
     l->max_peaks_per_part = 128;
-    l->max_candidates_per_limb = 2048;
-    l->max_bodies = 512;
+    l->max_candidates_per_limb = 1024;
+    l->max_bodies = 256;
     l->max_humans = 128;
     l->max_feat_h = 128;
     l->max_feat_w = 128;
@@ -281,6 +320,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMemset(h->d_n_peaks, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_n_humans, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_status, 0, B * sizeof(uint32_t)));
+        CU(cudaMalloc(&h->d_ticket, 2 * B * sizeof(unsigned)));
+        CU(cudaMemset(h->d_ticket, 0, 2 * B * sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
         CU(cudaMallocHost(&h->h_part_count, B * kParts * sizeof(int)));
         CU(cudaMallocHost(&h->h_line, B * h->line_stride * sizeof(ibp_peak)));
@@ -292,14 +333,15 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         memset(h->h_n_humans, 0, B * sizeof(int));
         memset(h->h_status, 0, B * sizeof(uint32_t));
         // opt in to large dynamic shared memory once
-        CU(cudaFuncSetAttribute(peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        if (limb_smem_bytes(h, 0) > kMaxDynSmem)
-            return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_smem_bytes(h, 0), kMaxDynSmem);
-        if (group_smem_bytes(h) > kMaxDynSmem)
-            return fail(IBP_ERR_ARG, "max_bodies=%d needs %zu B of shared memory (max %zu)", h->L.max_bodies, group_smem_bytes(h), kMaxDynSmem);
+        if (limb_phase_bytes(h, 0) > kMaxDynSmem)
+            return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_phase_bytes(h, 0), kMaxDynSmem);
+        if (group_phase_bytes(h) > kMaxDynSmem)
+            return fail(IBP_ERR_ARG, "max_bodies=%d needs %zu B of shared memory (max %zu)", h->L.max_bodies, group_phase_bytes(h), kMaxDynSmem);
         return IBP_OK;
     };
     rc = alloc();
@@ -372,61 +414,76 @@ int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int b
 }
 
 // ------------------------------------------------------------------------------------------------ K2
-int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw, int flavour, void *stream) {
-    if (!h || !maps) return fail(IBP_ERR_ARG, "ibp_find_peaks: null argument");
-    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_find_peaks: batch %d exceeds limit %d", batch, h->L.max_batch);
-    if (fh < 1 || fw < 1 || fw > 32767 || fh > 32767 || first_chan < 0 || first_chan + kParts > chan_stride)
-        return fail(IBP_ERR_SHAPE, "ibp_find_peaks: bad shape");
-    if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID) return fail(IBP_ERR_ARG, "ibp_find_peaks: flavour %d", flavour);
+namespace {
+// src: element (img, chan, y, x) at src + img*image_stride + (chan*fh + y)*fw + x; keypoint j in channel chan0 + j;
+// twin_base >= 0: average with the mirrored plane twin_base + 30 + flip_heat_ord[j] of the same image on the way in
+int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride, int chan0, int twin_base, int batch, int fh, int fw,
+                 int flavour, cudaStream_t st) {
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "find_peaks: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (fh < 1 || fw < 1 || fw > 32767 || fh > 32767) return fail(IBP_ERR_SHAPE, "find_peaks: bad shape");
+    if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID) return fail(IBP_ERR_ARG, "find_peaks: flavour %d", flavour);
     if (flavour == IBP_PEAKS_BOX_CENTROID && h->P.refine_window != 2)
-        return fail(IBP_ERR_ARG, "ibp_find_peaks: the centroid flavour supports offset_radius == 2 only");
-    CU(cudaSetDevice(h->device));
-    cudaStream_t st = (cudaStream_t)stream;
+        return fail(IBP_ERR_ARG, "find_peaks: the centroid flavour supports offset_radius == 2 only");
     PeakArgs a;
-    a.maps = maps;
-    a.chan_stride = chan_stride;
-    a.first_chan = first_chan;
+    a.src = src;
+    a.dtype = dtype;
+    a.image_stride = image_stride;
+    a.chan0 = chan0;
+    a.twin_base = twin_base;
     a.h = fh;
     a.w = fw;
     a.halo = std::max(h->P.refine_window, 1);
-    int rows_buf = (int)(kPeakBandBytes / ((size_t)fw * 4));
-    rows_buf = std::max(rows_buf, 2 * a.halo + 1);
-    if (rows_buf >= fh) {
-        a.rows_buf = fh;
-        a.rows_per_band = fh;
-    } else {
-        a.rows_buf = rows_buf;
-        a.rows_per_band = rows_buf - 2 * a.halo;
-    }
+    int rows_target = std::max<int>(4 * a.halo, (int)(peak_band_target() / ((size_t)fw * 4)));
+    int nbands = (fh + rows_target - 1) / rows_target;
+    a.rows_per_band = (fh + nbands - 1) / nbands;
+    a.nbands = (fh + a.rows_per_band - 1) / a.rows_per_band;
+    const int rows_buf = std::min(a.rows_per_band + 2 * a.halo, fh);
+    size_t band_bytes = std::max((size_t)rows_buf * fw * 4, (size_t)(kParts * a.nbands + 1) * 4);
+    band_bytes = (band_bytes + 15) & ~(size_t)15;
+    a.band_bytes = (int)band_bytes;
     a.up = h->P.upsample;
     a.win = h->P.refine_window;
     a.thr = h->P.peak_thresh;
     a.cap = h->L.max_peaks_per_part;
     a.flavour = flavour;
+    int rc = ensure_bands(h, a.nbands);
+    if (rc != IBP_OK) return rc;
+    a.band_peaks = h->d_band_peaks;
+    a.band_subpix = (flavour == IBP_PEAKS_BOX_CENTROID) ? h->d_band_subpix : nullptr;
+    a.band_count = h->d_band_count;
+    a.ticket = h->d_ticket;
     a.peaks = h->d_peaks;
     a.subpix = h->d_subpix;
     a.part_count = h->d_part_count;
+    a.line = h->d_line;
+    a.line_stride = h->line_stride;
+    a.n_peaks = h->d_n_peaks;
     a.status = h->d_status;
     const int side = 2 * a.win + 1;
-    size_t smem = (((size_t)a.rows_buf * fw * 4) + 15) & ~(size_t)15;
-    smem += (((size_t)(a.rows_per_band * fw + 31) / 32) * 4 + 7) & ~(size_t)7;
+    size_t smem = band_bytes;
     smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
-    smem += (size_t)a.cap * sizeof(short2);
-    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_find_peaks: row of %d floats does not fit shared memory", fw);
+    smem += (size_t)a.cap * 8;
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "find_peaks: rows of %d floats do not fit shared memory", fw);
     CU(cudaMemsetAsync(h->d_status, 0, (size_t)batch * sizeof(uint32_t), st));
     {
         StageTimer t(h, IBP_STAGE_PEAKS, st);
-        peaks_kernel<<<dim3(kParts, batch), kPeakThreads, smem, st>>>(a);
-    }
-    h->launches++;
-    CU(cudaGetLastError());
-    {
-        StageTimer t(h, IBP_STAGE_PACK, st);
-        pack_peaks_kernel<<<batch, 128, 0, st>>>(h->d_peaks, h->d_part_count, a.cap, h->d_line, h->line_stride, h->d_n_peaks);
+        const dim3 grid(a.nbands, kParts, batch);
+        if (dtype == IBP_F16)
+            peaks_kernel<__half><<<grid, kPeakThreads, smem, st>>>(a);
+        else
+            peaks_kernel<float><<<grid, kPeakThreads, smem, st>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;
+}
+}  // namespace
+
+int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw, int flavour, void *stream) {
+    if (!h || !maps) return fail(IBP_ERR_ARG, "ibp_find_peaks: null argument");
+    if (fh < 1 || fw < 1 || first_chan < 0 || first_chan + kParts > chan_stride) return fail(IBP_ERR_SHAPE, "ibp_find_peaks: bad shape");
+    CU(cudaSetDevice(h->device));
+    return launch_peaks(h, maps, IBP_F32, (size_t)chan_stride * fh * fw, first_chan, -1, batch, fh, fw, flavour, (cudaStream_t)stream);
 }
 
 int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride) {
@@ -473,19 +530,21 @@ int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int 
 }
 
 // ------------------------------------------------------------------------------------------------ K3 + K4
-int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int dim0, int dim1, int dim2, int min_img_size, void *stream) {
-    if (!h || !limb_src) return fail(IBP_ERR_ARG, "ibp_assign: null argument");
-    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_assign: batch %d exceeds limit %d", batch, h->L.max_batch);
-    if (dim0 < 1 || dim1 < 1 || dim2 < kLimbs) return fail(IBP_ERR_SHAPE, "ibp_assign: bad shape (%d,%d,%d)", dim0, dim1, dim2);
-    if (mode != IBP_LIMB_FULLRES_HWC && mode != IBP_LIMB_FEAT_PLANAR) return fail(IBP_ERR_ARG, "ibp_assign: mode %d", mode);
-    CU(cudaSetDevice(h->device));
-    cudaStream_t st = (cudaStream_t)stream;
+namespace {
+int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int twin_base, size_t image_stride, int batch, int dim0, int dim1,
+                 int dim2, int min_img_size, cudaStream_t st) {
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "assign: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (dim0 < 1 || dim1 < 1 || dim2 < kLimbs) return fail(IBP_ERR_SHAPE, "assign: bad shape (%d,%d,%d)", dim0, dim1, dim2);
+    if (mode != IBP_LIMB_FULLRES_HWC && mode != IBP_LIMB_FEAT_PLANAR) return fail(IBP_ERR_ARG, "assign: mode %d", mode);
     LimbArgs a;
     a.peaks = h->d_peaks;
     a.part_count = h->d_part_count;
     a.cap = h->L.max_peaks_per_part;
     a.src = limb_src;
+    a.dtype = dtype;
     a.mode = mode;
+    a.twin_base = twin_base;
+    a.image_stride = image_stride;
     a.up = h->P.upsample;
     size_t plane_bytes = 0;
     if (mode == IBP_LIMB_FULLRES_HWC) {
@@ -494,17 +553,19 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
         a.C = dim2;
         a.h = a.w = 1;
         a.stage_plane = 0;
-        a.image_stride = (size_t)dim0 * dim1 * dim2;
     } else {
         a.h = dim0;
         a.w = dim1;
         a.H = dim0 * a.up;
         a.W = dim1 * a.up;
         a.C = dim2;
-        a.image_stride = (size_t)dim2 * dim0 * dim1;
         plane_bytes = (size_t)dim0 * dim1 * 4;
         a.stage_plane = (plane_bytes <= kLimbPlaneMaxBytes && limb_smem_bytes(h, plane_bytes) <= kMaxDynSmem) ? 1 : 0;
-        if (!a.stage_plane) plane_bytes = 0;
+        if (!a.stage_plane) {
+            if (dtype != IBP_F32 || twin_base >= 0)
+                return fail(IBP_ERR_SHAPE, "assign: a %dx%d limb plane does not fit shared memory; fuse to float32 first (ibp_fuse_flip)", dim0, dim1);
+            plane_bytes = 0;
+        }
     }
     a.min_img_size = min_img_size;
     a.thr = h->P.limb_sample_thresh;
@@ -514,22 +575,18 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
     a.w_b = h->P.weight_b;
     a.max_steps = h->P.max_steps;
     a.cand_cap = h->L.max_candidates_per_limb;
+    a.line = h->d_line;
+    a.line_stride = h->line_stride;
     a.links = h->d_links;
     a.link_count = h->d_link_count;
     a.status = h->d_status;
-    {
-        StageTimer t(h, IBP_STAGE_LIMBS, st);
-        limbs_kernel<<<dim3(kLimbs, batch), kLimbThreads, limb_smem_bytes(h, plane_bytes), st>>>(a);
-    }
-    h->launches++;
-    CU(cudaGetLastError());
-
-    GroupArgs g;
+    a.ticket = h->d_ticket + h->L.max_batch;
+    const size_t smem = limb_smem_bytes(h, plane_bytes);
+    a.smem_bytes = (int)smem;
+    GroupArgs &g = a.group;
     g.links = h->d_links;
     g.link_count = h->d_link_count;
     g.cap = a.cap;
-    g.line = h->d_line;
-    g.line_stride = h->line_stride;
     g.max_bodies = h->L.max_bodies;
     g.max_humans = h->L.max_humans;
     g.len_rate = h->P.len_rate;
@@ -540,12 +597,24 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
     g.n_humans = h->d_n_humans;
     g.status = h->d_status;
     {
-        StageTimer t(h, IBP_STAGE_GROUP, st);
-        group_kernel<<<batch, 32, group_smem_bytes(h), st>>>(g);
+        StageTimer t(h, IBP_STAGE_LIMBS, st);
+        const dim3 grid(kLimbs, batch);
+        if (dtype == IBP_F16)
+            limbs_kernel<__half><<<grid, kLimbThreads, smem, st>>>(a);
+        else
+            limbs_kernel<float><<<grid, kLimbThreads, smem, st>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;
+}
+}  // namespace
+
+int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int dim0, int dim1, int dim2, int min_img_size, void *stream) {
+    if (!h || !limb_src) return fail(IBP_ERR_ARG, "ibp_assign: null argument");
+    CU(cudaSetDevice(h->device));
+    const size_t image_stride = (size_t)dim0 * dim1 * (size_t)std::max(dim2, 0);
+    return launch_limbs(h, limb_src, IBP_F32, mode, -1, image_stride, batch, dim0, dim1, dim2, min_img_size, (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------------ pipeline
@@ -556,7 +625,8 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
     if (fh < 1 || fw < 1) return fail(IBP_ERR_SHAPE, "ibp_postprocess_batch: bad shape");
     CU(cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t elems = (size_t)batch * 2 * kLayers * fh * fw;
+    const size_t image_stride = (size_t)2 * kLayers * fh * fw;
+    const size_t elems = (size_t)batch * image_stride;
     const void *dev_in = net_out;
     if (on_host) {
         const size_t bytes = elems * (dtype == IBP_F16 ? 2 : 4);
@@ -565,6 +635,16 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
         CU(cudaMemcpyAsync(h->d_stage, net_out, bytes, cudaMemcpyHostToDevice, st));
         dev_in = h->d_stage;
     }
+    const size_t plane_bytes = (size_t)fh * fw * 4;
+    const bool direct = plane_bytes <= kLimbPlaneMaxBytes && limb_smem_bytes(h, plane_bytes) <= kMaxDynSmem;
+    if (direct) {
+        // two kernels, the network output is read once and nothing intermediate is written: the flip average
+        // happens while each keypoint band / limb plane is staged in shared memory
+        int rc = launch_peaks(h, dev_in, dtype, image_stride, kLimbs, kLayers, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, st);
+        if (rc != IBP_OK) return rc;
+        return launch_limbs(h, dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st);
+    }
+    // limb planes too large for shared memory: materialise the fused float32 maps, sample them through L2
     int rc = ensure_fused(h, (size_t)batch * kLayers * fh * fw);
     if (rc != IBP_OK) return rc;
     rc = ibp_fuse_flip(h, dev_in, dtype, batch, fh, fw, 1, h->d_fused, stream);

@@ -18,10 +18,11 @@ struct DevPeak {  // 16 B — reference Peak, pafprocess.h:29-34
     float score;
     int id;
 };
-struct DevLink {  // 16 B — the fields of Connection (pafprocess.h:60-67) that grouping reads
-    int id_a, id_b;
+struct DevLink {  // 24 B — the fields of Connection (pafprocess.h:60-67) that grouping reads, plus the two peak scores
+    int id_a, id_b;   // the grouping step would otherwise fetch through peak_infos_line (pafprocess.cpp:261-262)
     float limb;
     float len;
+    float score_a, score_b;
 };
 
 // limb end points: pafprocess.h:20-27 COCOPAIRS == config/config.py:114-121
@@ -70,6 +71,13 @@ __device__ __forceinline__ int cubic_tap(int d, int up, float *w) {
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
 
+// For up == 4 the four weights depend only on the phase (d-2)&3 (fractions 1/8, 3/8, 5/8, 7/8): a 4x4 table in
+// shared memory, filled with the very same cubic_weights() evaluation so that table and on-the-fly values are the
+// same bits.  Call from all threads; the caller synchronises before the first use.
+__device__ __forceinline__ void cubic_tab4_init(float (*tab)[4]) {
+    if (threadIdx.x < 4) cubic_weights(__fadd_rn(__int2float_rn(threadIdx.x) * 0.25f, 0.125f), tab[threadIdx.x]);
+}
+
 // horizontal 4-tap: ((s0*a0 + s1*a1) + s2*a2) + s3*a3   (OpenCV HResizeCubic)
 __device__ __forceinline__ float hsum4(float s0, float s1, float s2, float s3, const float *a) {
     return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(s0, a[0]), __fmul_rn(s1, a[1])), __fmul_rn(s2, a[2])), __fmul_rn(s3, a[3]));
@@ -84,6 +92,20 @@ __device__ __forceinline__ float cubic_sample(const float *plane, int h, int w, 
     float xw[4], yw[4];
     const int sx = cubic_tap(X, up, xw);
     const int sy = cubic_tap(Y, up, yw);
+    const int x0 = clampi(sx - 1, 0, w - 1), x1 = clampi(sx, 0, w - 1), x2 = clampi(sx + 1, 0, w - 1), x3 = clampi(sx + 2, 0, w - 1);
+    float r[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
+        r[k] = hsum4(row[x0], row[x1], row[x2], row[x3], xw);
+    }
+    return vsum4(r[0], r[1], r[2], r[3], yw);
+}
+
+// same value through the phase table (up == 4 only)
+__device__ __forceinline__ float cubic_sample4(const float *plane, int h, int w, const float (*tab)[4], int X, int Y) {
+    const int sx = (X - 2) >> 2, sy = (Y - 2) >> 2;
+    const float *xw = tab[(X - 2) & 3], *yw = tab[(Y - 2) & 3];
     const int x0 = clampi(sx - 1, 0, w - 1), x1 = clampi(sx, 0, w - 1), x2 = clampi(sx + 1, 0, w - 1), x3 = clampi(sx + 2, 0, w - 1);
     float r[4];
 #pragma unroll
@@ -151,6 +173,82 @@ __device__ __forceinline__ void rows_to_smem(float *dst, const float *src, uint3
         for (uint32_t i = threadIdx.x; i < n_floats; i += blockDim.x) dst[i] = __ldg(src + i);
         __syncthreads();
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Flip / channel-permutation average fused into the staging load (utils/parse_skeletons.py:91-93):
+//     dst[r][x] = (up[row0+r][x] + twin[row0+r][w-1-x]) / 2      averaged in the element type T like numpy does.
+// 128-bit loads of the upright run and of the mirrored run (reversed in registers), four independent pairs in
+// flight per thread, 128-bit shared stores.  Falls back to scalar loads for widths / alignments that do not
+// vectorise.  `twin == nullptr` copies (through the bulk-copy engine when T is float and everything is aligned).
+// Must be called by all threads; returns after the rows are visible to the whole CTA.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float avg_like_numpy(float a, float b) { return __fmul_rn(__fadd_rn(a, b), 0.5f); }
+__device__ __forceinline__ float avg_like_numpy(__half a, __half b) {
+    // numpy float16: each ufunc rounds to half — (a+b) -> half, then /2 -> half
+    const __half s = __float2half_rn(__fadd_rn(__half2float(a), __half2float(b)));
+    return __half2float(__float2half_rn(__fmul_rn(__half2float(s), 0.5f)));
+}
+__device__ __forceinline__ float to_f32(float a) { return a; }
+__device__ __forceinline__ float to_f32(__half a) { return __half2float(a); }
+
+template <typename T>
+__device__ __forceinline__ void stage_rows_fused(float *dst, const T *up, const T *twin, int row0, int nrows, int w, uint64_t *bar,
+                                                 uint32_t &phase) {
+    constexpr int V = 16 / (int)sizeof(T);  // elements per 128-bit load
+    const T *up0 = up + (size_t)row0 * w;
+    if (twin == nullptr && sizeof(T) == 4) {
+        rows_to_smem(dst, reinterpret_cast<const float *>(up0), (uint32_t)(nrows * w), bar, phase);
+        return;
+    }
+    const bool vec_ok = (w % V == 0) && ((((uintptr_t)up) & 15u) == 0) && (twin == nullptr || (((uintptr_t)twin) & 15u) == 0) &&
+                        ((smem_u32(dst) & 15u) == 0);
+    if (vec_ok) {
+        const int wv = w / V, nvec = nrows * wv, T_ = blockDim.x;
+        const uint4 *u4 = reinterpret_cast<const uint4 *>(up0);
+        const uint4 *t4 = twin ? reinterpret_cast<const uint4 *>(twin + (size_t)row0 * w) : nullptr;
+        float4 *d4 = reinterpret_cast<float4 *>(dst);
+        constexpr int U = 4;
+        for (int base = threadIdx.x; base < nvec; base += U * T_) {
+            uint4 a[U], m[U];
+#pragma unroll
+            for (int k = 0; k < U; k++) {
+                const int i = base + k * T_;
+                if (i < nvec) {
+                    a[k] = __ldcs(u4 + i);
+                    if (t4) {
+                        const int r = i / wv, c = i - r * wv;
+                        m[k] = __ldcs(t4 + r * wv + (wv - 1 - c));
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < U; k++) {
+                const int i = base + k * T_;
+                if (i < nvec) {
+                    const T *av = reinterpret_cast<const T *>(&a[k]);
+                    const T *mv = reinterpret_cast<const T *>(&m[k]);
+                    float o[V];
+#pragma unroll
+                    for (int q = 0; q < V; q++) o[q] = t4 ? avg_like_numpy(av[q], mv[V - 1 - q]) : to_f32(av[q]);
+#pragma unroll
+                    for (int q = 0; q < V / 4; q++) d4[(size_t)i * (V / 4) + q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+                }
+            }
+        }
+    } else {
+        const int n = nrows * w;
+        const T *tw0 = twin ? twin + (size_t)row0 * w : nullptr;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            if (tw0) {
+                const int r = i / w, c = i - r * w;
+                dst[i] = avg_like_numpy(up0[i], tw0[r * w + (w - 1 - c)]);
+            } else {
+                dst[i] = to_f32(up0[i]);
+            }
+        }
+    }
+    __syncthreads();
 }
 
 }  // namespace ibp

@@ -4,7 +4,12 @@
 // reads and mutates the table the next one scans, and a merge erases a row so later indices shift), so the
 // parallelism is images across CTAs and, inside a step, lanes over the skeleton scan (32 rows per ballot), over the
 // 18 part slots of a merge, and over the columns of the row shift that implements vector::erase.
-// The table lives in shared memory: ids[S][18], limb scores[S][18], total[S], count[S], reach[S].
+//
+// It runs as the tail of the limb kernel: the last of an image's 30 limb CTAs to finish (ticket counter) calls
+// group_image() with the CTA's whole dynamic shared memory.  The connections of all 30 limbs are first copied into
+// shared memory in one coalesced sweep (each carries its two peak scores, so the chain never touches global memory:
+// a dependent global load per connection was what bounded the stand-alone kernel), then warp 0 walks the chain on the
+// table ids[S][18], limb scores[S][18], total[S], count[S], reach[S].
 #pragma once
 #include "ibp_device.cuh"
 
@@ -14,8 +19,6 @@ struct GroupArgs {
     const DevLink *links;    // (batch, 30, cap)
     const int *link_count;   // (batch, 30)
     int cap;
-    const ibp_peak *line;    // (batch, line_stride): part-major peak list indexed by peak id (pafprocess.cpp:43-48)
-    int line_stride;
     int max_bodies;
     int max_humans;
     int len_rate;
@@ -27,25 +30,64 @@ struct GroupArgs {
     uint32_t *status;        // (batch)
 };
 
-__global__ void __launch_bounds__(32) group_kernel(GroupArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int img = blockIdx.x, lane = threadIdx.x;
+constexpr size_t kBodyBytes = kParts * 8 + 12;  // shared bytes per row of the skeleton table
+
+// All threads of the CTA call this; `smem` / `smem_bytes` is the CTA's dynamic shared memory (free for re-use).
+__device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigned char *smem, size_t smem_bytes) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = a.max_bodies;
-    int *ids = reinterpret_cast<int *>(smem_raw);                 // [S][18]
+    int *ids = reinterpret_cast<int *>(smem);                         // [S][18]
     float *sc = reinterpret_cast<float *>(ids + (size_t)S * kParts);  // [S][18]
-    float *total = sc + (size_t)S * kParts;                       // [S]
-    int *count = reinterpret_cast<int *>(total + S);              // [S]
-    float *reach = reinterpret_cast<float *>(count + S);          // [S]
-    const ibp_peak *line = a.line + (size_t)img * a.line_stride;
+    float *total = sc + (size_t)S * kParts;                           // [S]
+    int *count = reinterpret_cast<int *>(total + S);                  // [S]
+    float *reach = reinterpret_cast<float *>(count + S);              // [S]
+    size_t off = ((size_t)S * kBodyBytes + 15) & ~(size_t)15;
+    int *loff = reinterpret_cast<int *>(smem + off);                  // [31] start of each limb's run in `slinks`
+    off += 32 * sizeof(int);
+    DevLink *slinks = reinterpret_cast<DevLink *>(smem + off);
+    const int slots = (int)((smem_bytes - off) / sizeof(DevLink));
+
+    // ---- stage the connections (written by other CTAs: read through L2) ----
+    if (tid == 0) {
+        int acc = 0;
+        for (int l = 0; l < kLimbs; l++) {
+            loff[l] = acc;
+            acc += __ldcg(a.link_count + img * kLimbs + l);
+        }
+        loff[kLimbs] = acc;
+    }
+    __syncthreads();
+    for (int l = warp; l < kLimbs; l += (int)(blockDim.x >> 5)) {
+        const int n = loff[l + 1] - loff[l];
+        const float2 *src = reinterpret_cast<const float2 *>(a.links + ((size_t)img * kLimbs + l) * a.cap);
+        float2 *dst = reinterpret_cast<float2 *>(slinks + loff[l]);
+        const int fit = max(0, min(n, slots - loff[l]));
+        for (int i = lane; i < fit * 3; i += 32) dst[i] = __ldcg(src + i);  // 24-byte records as three float2
+    }
+    __syncthreads();
+    if (warp != 0) return;
 
     int nb = 0;
     bool overflow = false;
     for (int limb = 0; limb < kLimbs; limb++) {
         const int pa = c_limb_a[limb], pb = c_limb_b[limb];
-        const int nl = a.link_count[img * kLimbs + limb];
-        const DevLink *L = a.links + ((size_t)img * kLimbs + limb) * a.cap;
+        const int base_slot = loff[limb];
+        const int nl = loff[limb + 1] - base_slot;
+        const DevLink *G = a.links + ((size_t)img * kLimbs + limb) * a.cap;
         for (int li = 0; li < nl; li++) {
-            const DevLink l = L[li];
+            DevLink l;
+            if (base_slot + li < slots) {
+                l = slinks[base_slot + li];
+            } else {  // more connections than the shared run holds: read the rest through L2
+                const float2 *g2 = reinterpret_cast<const float2 *>(G + li);
+                const float2 q0 = __ldcg(g2), q1 = __ldcg(g2 + 1), q2 = __ldcg(g2 + 2);
+                l.id_a = __float_as_int(q0.x);
+                l.id_b = __float_as_int(q0.y);
+                l.limb = q1.x;
+                l.len = q1.y;
+                l.score_a = q2.x;
+                l.score_b = q2.y;
+            }
             // :143-150 scan: first two matching rows, total number of matches
             int hits = 0, first = 0, second = 0;
             for (int base = 0; base < nb; base += 32) {
@@ -66,7 +108,7 @@ __global__ void __launch_bounds__(32) group_kernel(GroupArgs a) {
                     const float gate = __int2float_rn(__float2int_rz(__fmul_rn(reach[f], __int2float_rn(a.len_rate))));  // :154
                     const int cur_id = ids[f * kParts + pb];
                     const float cur_sc = sc[f * kParts + pb];
-                    const float add = __fadd_rn(line[l.id_b].score, l.limb);
+                    const float add = __fadd_rn(l.score_b, l.limb);
                     if (cur_id == -1 && gate > l.len) {
                         ids[f * kParts + pb] = l.id_b;
                         sc[f * kParts + pb] = l.limb;
@@ -143,7 +185,7 @@ __global__ void __launch_bounds__(32) group_kernel(GroupArgs a) {
                     if (lane == 0) {
                         count[nb] = 2;
                         reach[nb] = l.len;
-                        total[nb] = __fadd_rn(__fadd_rn(line[l.id_a].score, line[l.id_b].score), l.limb);
+                        total[nb] = __fadd_rn(__fadd_rn(l.score_a, l.score_b), l.limb);
                     }
                     nb++;
                 } else {

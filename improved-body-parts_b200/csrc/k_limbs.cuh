@@ -1,16 +1,24 @@
-// K3 + K4a — limb scoring of every candidate pair, ordering, greedy connection.  One CTA per (image, limb).
+// K3 + K4 — limb scoring of every candidate pair, ordering, greedy connection (one CTA per image and limb), then
+// person grouping by the last CTA of each image.
 //
 // Reference: utils/pafprocess/pafprocess.cpp:52-130 with get_paf_scores (:311-327), round2int (:329-331) and
-// comp_candidate (:333-335).  The arithmetic below reproduces the reference's mix of int, float and double step
-// by step; every float operation is an explicit round-to-nearest intrinsic so that no
-// FMA contraction can creep in (the reference build has none).
+// comp_candidate (:333-335); grouping :133-282 (k_group.cuh).  The arithmetic below reproduces the reference's mix
+// of int, float and double step by step; every float operation is an explicit
+// round-to-nearest intrinsic so that no FMA contraction can creep in (the reference build has none).
 //
-// Limb values come from one of two sources:
+// Limb values come from one of three sources:
 //   IBP_LIMB_FULLRES_HWC  the caller's (H,W,C) map, nearest-pixel lookup exactly like the PAF macro (:9, :322);
-//   IBP_LIMB_FEAT_PLANAR  the feature-resolution plane of this limb staged in shared memory by the bulk-copy engine
-//                         (h*w*4 bytes, one contiguous run); each sample evaluates OpenCV's bicubic x`up` at that
+//   IBP_LIMB_FEAT_PLANAR  the feature-resolution plane of this limb staged in shared memory (h*w*4 bytes, one
+//                         contiguous run, bulk-copy engine); each sample evaluates OpenCV's bicubic x`up` at that
 //                         pixel, which equals indexing cv2.resize(pafs, fx=up, fy=up, INTER_CUBIC) (evaluate.py:77-80)
-//                         bit for bit without ever writing the 31 MB up-sampled map.
+//                         bit for bit without ever writing the 31 MB up-sampled map;
+//   ... with twin_base >= 0  the same, staged straight from the raw network output: the upright plane and the
+//                         mirrored, channel-permuted plane of the flipped image are averaged on the way into shared
+//                         memory (utils/parse_skeletons.py:91-92), so the fused limb maps never exist in HBM.
+//
+// Scoring is split so that all 256 threads stay busy whatever the number of pairs: per chunk of kPairChunk pairs,
+// (0) one thread per pair derives the step geometry, (1) one thread per (pair, sample) evaluates the limb value,
+// (2) one thread per pair adds its samples in order (the reference's sequential fp32 sum) and applies the criteria.
 //
 // Ordering: candidates are compacted in (a-major, b-minor) pair order, then sorted by a bitonic network on
 // (score descending, candidate index descending).  That equals libstdc++'s std::sort with the reference's non-strict
@@ -19,6 +27,7 @@
 // stl_sort_emul.h (status bit IBP_ST_TIE_EMULATED; IBP_ST_TIE_UNDEFINED when the real sort would have left the array).
 #pragma once
 #include "ibp_device.cuh"
+#include "k_group.cuh"
 #include "stl_sort_emul.h"
 
 namespace ibp {
@@ -27,9 +36,11 @@ struct LimbArgs {
     const DevPeak *peaks;   // (batch, 18, cap)
     const int *part_count;  // (batch, 18)
     int cap;
-    const float *src;       // limb values, see mode
+    const void *src;        // limb values, see mode
+    int dtype;              // element type of src (IBP_F16 only with IBP_LIMB_FEAT_PLANAR)
     int mode;
-    size_t image_stride;    // floats between images in src
+    size_t image_stride;    // elements between images in src
+    int twin_base;          // IBP_LIMB_FEAT_PLANAR: channel offset of the flipped image's block, or -1
     int H, W, C;            // mode 0: full-resolution dims and channel count (stride); sample clamp bounds
     int h, w;               // mode 1: feature dims
     int up;
@@ -38,12 +49,18 @@ struct LimbArgs {
     float thr, step_ratio, w_limb, w_a, w_b;
     int max_steps;
     int cand_cap;           // power of two
+    const ibp_peak *line;   // (batch, line_stride) part-major peak list, indexed BY PEAK ID like peak_infos_line
+    int line_stride;
     DevLink *links;         // (batch, 30, cap)
     int *link_count;        // (batch, 30)
     uint32_t *status;       // (batch)
+    unsigned *ticket;       // (batch) zero on entry, left zero on exit
+    int smem_bytes;         // dynamic shared memory of the launch
+    GroupArgs group;
 };
 
 constexpr int kLimbThreads = 256;
+constexpr int kPairChunk = 128;  // pairs scored per round
 
 __device__ __forceinline__ uint32_t float_orderable(float f) {
     const uint32_t u = __float_as_uint(f);
@@ -53,6 +70,7 @@ __device__ __forceinline__ uint32_t float_orderable_inv(uint32_t k) { return (k 
 
 struct Sampler {
     const float *base;  // mode 0: image base; mode 1: plane base (shared or global)
+    const float (*tab4)[4];
     int mode, limb;
     int H, W, C, h, w, up;
     __device__ __forceinline__ float at(int px, int py) const {
@@ -63,6 +81,7 @@ struct Sampler {
         }
         px = clampi(px, 0, w * up - 1);
         py = clampi(py, 0, h * up - 1);
+        if (up == 4) return cubic_sample4(base, h, w, tab4, px, py);
         return cubic_sample(base, h, w, up, px, py);
     }
 };
@@ -72,36 +91,12 @@ __device__ __forceinline__ float limb_length(const DevPeak &A, const DevPeak &B)
     return __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));        // :70
 }
 
-// pafprocess.cpp:66-104 for one pair.  Returns true when both criteria hold.
-__device__ __forceinline__ bool score_pair(const DevPeak &A, const DevPeak &B, const Sampler &s, const LimbArgs &a, float &limb_score,
-                                           float &rank) {
-    const float len = limb_length(A, B);
-    if ((double)len < 1e-12) return false;                                                     // :71
-    const int steps = min(__double2int_rz(__dadd_rn((double)__fadd_rn(len, 1.0f), 0.5)), a.max_steps);  // :73
-    const float denom = __int2float_rn(steps - 1);
-    const float sx = __fdiv_rn(__int2float_rn(B.x - A.x), denom);  // :315
-    const float sy = __fdiv_rn(__int2float_rn(B.y - A.y), denom);  // :316
-    const float ax = __int2float_rn(A.x), ay = __int2float_rn(A.y);
-    float sum = 0.0f;
-    int above = 0;
-    for (int i = 0; i < steps; i++) {
-        const float fi = __int2float_rn(i);
-        const int px = __double2int_rz(__dadd_rn((double)__fadd_rn(ax, __fmul_rn(fi, sx)), 0.5));  // :319, :329-331
-        const int py = __double2int_rz(__dadd_rn((double)__fadd_rn(ay, __fmul_rn(fi, sy)), 0.5));  // :320
-        const float v = s.at(px, py);
-        sum = __fadd_rn(sum, v);  // :85
-        above += (v > a.thr);     // :87
-    }
-    // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
-    const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
-    const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
-    limb_score = __double2float_rn(__dadd_rn((double)__fdiv_rn(sum, __int2float_rn(steps)), pen));
-    const float need = __fmul_rn(__int2float_rn(steps), a.step_ratio);  // :91
-    if (!(__int2float_rn(above) > need && limb_score > 0.0f)) return false;  // :93
-    rank = __fadd_rn(__fadd_rn(__fmul_rn(a.w_limb, limb_score), __fmul_rn(a.w_a, A.score)), __fmul_rn(a.w_b, B.score));  // :94-96
-    return true;
-}
+struct PairGeo {  // step geometry of one pair (pafprocess.cpp:66-73, :311-316)
+    float ax, ay, sx, sy;
+    int steps;  // 0: skipped (zero length)
+};
 
+template <typename T>
 __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int limb = blockIdx.x, img = blockIdx.y;
@@ -109,10 +104,6 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     const int pa = c_limb_a[limb], pb = c_limb_b[limb];
     const int nA = a.part_count[img * kParts + pa], nB = a.part_count[img * kParts + pb];
     int *link_count = a.link_count + img * kLimbs + limb;
-    if (nA == 0 || nB == 0) {  // no pair => no candidate => no connection (covers the both-empty skip at :57)
-        if (tid == 0) *link_count = 0;
-        return;
-    }
 
     // ---- carve shared memory ----
     // region 0: limb plane while scoring (mode 1, staged), re-used for the introsort emulation array afterwards
@@ -135,173 +126,258 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     off += (size_t)a.cap * sizeof(DevPeak);
     DevPeak *sB = reinterpret_cast<DevPeak *>(smem_raw + off);
     off += (size_t)a.cap * sizeof(DevPeak);
+    PairGeo *geo = reinterpret_cast<PairGeo *>(smem_raw + off);  // [kPairChunk]
+    off += (size_t)kPairChunk * sizeof(PairGeo);
+    float *vals = reinterpret_cast<float *>(smem_raw + off);     // [kPairChunk][max_steps]
+    off += (size_t)kPairChunk * a.max_steps * 4;
     unsigned char *used_a = smem_raw + off;
     off += (size_t)a.cap;
     unsigned char *used_b = smem_raw + off;
     __shared__ uint64_t bar;
     __shared__ int wcnt[kLimbThreads / 32];
-    __shared__ int s_flag;
+    __shared__ int s_last;
+    __shared__ float tab4[4][4];
 
-    if (tid == 0) {
-        mbar_init(&bar, 1);
-        fence_barrier_init();
-        s_flag = 0;
-    }
-    const DevPeak *gA = a.peaks + ((size_t)img * kParts + pa) * a.cap;
-    const DevPeak *gB = a.peaks + ((size_t)img * kParts + pb) * a.cap;
-    for (int i = tid; i < nA; i += kLimbThreads) {
-        sA[i] = gA[i];
-        used_a[i] = 0;
-    }
-    for (int i = tid; i < nB; i += kLimbThreads) {
-        sB[i] = gB[i];
-        used_b[i] = 0;
-    }
-    __syncthreads();
-
-    Sampler smp;
-    smp.mode = a.mode;
-    smp.limb = limb;
-    smp.H = a.H;
-    smp.W = a.W;
-    smp.C = a.C;
-    smp.h = a.h;
-    smp.w = a.w;
-    smp.up = a.up;
-    if (a.mode == IBP_LIMB_FEAT_PLANAR) {
-        const float *gplane = a.src + (size_t)img * a.image_stride + (size_t)limb * a.h * a.w;
-        if (a.stage_plane) {
-            uint32_t phase = 0;
-            rows_to_smem(plane_s, gplane, (uint32_t)(a.h * a.w), &bar, phase);
-            smp.base = plane_s;
-        } else {
-            smp.base = gplane;
+    int n_links = 0;  // meaningful on thread 0 only
+    // no pair => no candidate => no connection (covers the both-empty skip at :57)
+    if (nA > 0 && nB > 0) {
+        if (tid == 0) {
+            mbar_init(&bar, 1);
+            fence_barrier_init();
         }
-    } else {
-        smp.base = a.src + (size_t)img * a.image_stride;
-    }
-
-    // ---- score all pairs; compact the accepted ones in pair order ----
-    const int npairs = nA * nB;
-    int ncand = 0;
-    for (int base = 0; base < npairs; base += kLimbThreads) {
-        const int p = base + tid;
-        bool ok = false;
-        float ls = 0.f, rk = 0.f;
-        int ia = 0, ib = 0;
-        if (p < npairs) {
-            ia = p / nB;
-            ib = p - ia * nB;
-            ok = score_pair(sA[ia], sB[ib], smp, a, ls, rk);
+        cubic_tab4_init(tab4);
+        const DevPeak *gA = a.peaks + ((size_t)img * kParts + pa) * a.cap;
+        const DevPeak *gB = a.peaks + ((size_t)img * kParts + pb) * a.cap;
+        for (int i = tid; i < nA; i += kLimbThreads) {
+            sA[i] = gA[i];
+            used_a[i] = 0;
         }
-        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
-        if (lane == 0) wcnt[warp] = __popc(bal);
+        for (int i = tid; i < nB; i += kLimbThreads) {
+            sB[i] = gB[i];
+            used_b[i] = 0;
+        }
         __syncthreads();
-        int woff = 0, tot = 0;
-#pragma unroll
-        for (int i = 0; i < kLimbThreads / 32; i++) {
-            const int t = wcnt[i];
-            if (i < warp) woff += t;
-            tot += t;
-        }
-        if (ok) {
-            const int idx = ncand + woff + __popc(bal & ((1u << lane) - 1u));
-            if (idx < a.cand_cap) {
-                keys[idx] = ((uint64_t)float_orderable(rk) << 32) | (uint32_t)idx;
-                cand_limb[idx] = ls;
-                cand_pair[idx] = ((uint32_t)ia << 16) | (uint32_t)ib;
+
+        Sampler smp;
+        smp.mode = a.mode;
+        smp.limb = limb;
+        smp.H = a.H;
+        smp.W = a.W;
+        smp.C = a.C;
+        smp.h = a.h;
+        smp.w = a.w;
+        smp.up = a.up;
+        smp.tab4 = tab4;
+        if (a.mode == IBP_LIMB_FEAT_PLANAR) {
+            const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
+            const size_t hw = (size_t)a.h * a.w;
+            const T *gplane = base + (size_t)limb * hw;
+            const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[limb]) * hw : nullptr;
+            if (a.stage_plane) {
+                uint32_t phase = 0;
+                stage_rows_fused<T>(plane_s, gplane, twin, 0, a.h, a.w, &bar, phase);
+                smp.base = plane_s;
+            } else {
+                smp.base = reinterpret_cast<const float *>(gplane);  // host side guarantees float + no twin here
             }
+        } else {
+            smp.base = reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride;
         }
-        ncand += tot;
-        __syncthreads();
-    }
-    if (ncand > a.cand_cap) {
-        if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
-        ncand = a.cand_cap;
-    }
-    if (ncand == 0) {
-        if (tid == 0) *link_count = 0;
-        return;
-    }
 
-    // ---- order: bitonic network, descending on (score, index) ----
-    int np2 = 1;
-    while (np2 < ncand) np2 <<= 1;
-    for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
-    __syncthreads();
-    for (int k = 2; k <= np2; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < np2; i += kLimbThreads) {
-                const int l = i ^ j;
-                if (l > i) {
-                    const uint64_t x = keys[i], y = keys[l];
-                    const bool desc = ((i & k) == 0);
-                    if (desc ? (x < y) : (x > y)) {
-                        keys[i] = y;
-                        keys[l] = x;
-                    }
+        // ---- score all pairs; compact the accepted ones in pair order ----
+        const int npairs = nA * nB;
+        int ncand = 0;
+        for (int base = 0; base < npairs; base += kPairChunk) {
+            const int chunk = min(kPairChunk, npairs - base);
+            // (0) geometry, one thread per pair
+            if (tid < chunk) {
+                const int p = base + tid;
+                const int ia = p / nB, ib = p - ia * nB;
+                const DevPeak A = sA[ia], B = sB[ib];
+                const float len = limb_length(A, B);
+                PairGeo g;
+                g.steps = 0;
+                g.ax = __int2float_rn(A.x);
+                g.ay = __int2float_rn(A.y);
+                g.sx = g.sy = 0.f;
+                if (!((double)len < 1e-12)) {                                                                       // :71
+                    g.steps = min(__double2int_rz(__dadd_rn((double)__fadd_rn(len, 1.0f), 0.5)), a.max_steps);  // :73
+                    const float denom = __int2float_rn(g.steps - 1);
+                    g.sx = __fdiv_rn(__int2float_rn(B.x - A.x), denom);  // :315
+                    g.sy = __fdiv_rn(__int2float_rn(B.y - A.y), denom);  // :316
+                }
+                geo[tid] = g;
+            }
+            __syncthreads();
+            // (1) samples, one thread per (pair, step)
+            for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
+                const int q = it / a.max_steps, i = it - q * a.max_steps;
+                const PairGeo g = geo[q];
+                if (i < g.steps) {
+                    const float fi = __int2float_rn(i);
+                    const int px = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ax, __fmul_rn(fi, g.sx)), 0.5));  // :319, :329-331
+                    const int py = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ay, __fmul_rn(fi, g.sy)), 0.5));  // :320
+                    vals[it] = smp.at(px, py);
                 }
             }
             __syncthreads();
-        }
-    }
-    // duplicate keys?
-    bool dup = false;
-    for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
-    const bool emulate = __syncthreads_or(dup && ncand > 16);
-    if (emulate) {
-        // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
-        for (int i = tid; i < ncand; i += kLimbThreads) {
-            const uint64_t kv = keys[i];
-            const uint32_t idx = (uint32_t)kv;
-            emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
-        }
-        __syncthreads();
-        if (tid == 0) {
-            const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
-            atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
-        }
-        __syncthreads();
-    }
-    const uint64_t *order = emulate ? emu : keys;
-
-    // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order ----
-    if (warp == 0) {
-        const int max_links = min(nA, nB);
-        DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
-        int nl = 0;
-        for (int base = 0; base < ncand && nl < max_links; base += 32) {
-            const int i = base + lane;
-            bool valid = i < ncand;
-            int ia = 0, ib = 0, cidx = 0;
-            if (valid) {
-                cidx = (int)(uint32_t)order[i];
-                const uint32_t pr = cand_pair[cidx];
-                ia = (int)(pr >> 16);
-                ib = (int)(pr & 0xffffu);
-            }
-            while (nl < max_links) {
-                const bool free_now = valid && !used_a[ia] && !used_b[ib];
-                const uint32_t bal = __ballot_sync(0xffffffffu, free_now);
-                if (bal == 0) break;
-                const int leader = __ffs(bal) - 1;
-                if (lane == leader) {
-                    used_a[ia] = 1;
-                    used_b[ib] = 1;
-                    DevLink l;
-                    l.id_a = sA[ia].id;
-                    l.id_b = sB[ib].id;
-                    l.limb = cand_limb[cidx];
-                    l.len = limb_length(sA[ia], sB[ib]);
-                    out[nl] = l;
-                    valid = false;
+            // (2) criteria, one thread per pair
+            bool ok = false;
+            float ls = 0.f, rk = 0.f;
+            int ia = 0, ib = 0;
+            if (tid < chunk) {
+                const PairGeo g = geo[tid];
+                if (g.steps > 0) {
+                    const int p = base + tid;
+                    ia = p / nB;
+                    ib = p - ia * nB;
+                    const DevPeak A = sA[ia], B = sB[ib];
+                    const float len = limb_length(A, B);
+                    const float *v = vals + tid * a.max_steps;
+                    float sum = 0.0f;
+                    int above = 0;
+                    for (int i = 0; i < g.steps; i++) {
+                        sum = __fadd_rn(sum, v[i]);   // :85
+                        above += (v[i] > a.thr);      // :87
+                    }
+                    // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
+                    const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
+                    const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
+                    ls = __double2float_rn(__dadd_rn((double)__fdiv_rn(sum, __int2float_rn(g.steps)), pen));
+                    const float need = __fmul_rn(__int2float_rn(g.steps), a.step_ratio);  // :91
+                    if (__int2float_rn(above) > need && ls > 0.0f) {                      // :93
+                        ok = true;
+                        rk = __fadd_rn(__fadd_rn(__fmul_rn(a.w_limb, ls), __fmul_rn(a.w_a, A.score)), __fmul_rn(a.w_b, B.score));  // :94-96
+                    }
                 }
-                nl++;
-                __syncwarp();
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) wcnt[warp] = __popc(bal);
+            __syncthreads();
+            int woff = 0, tot = 0;
+#pragma unroll
+            for (int i = 0; i < kLimbThreads / 32; i++) {
+                const int t = wcnt[i];
+                if (i < warp) woff += t;
+                tot += t;
+            }
+            if (ok) {
+                const int idx = ncand + woff + __popc(bal & ((1u << lane) - 1u));
+                if (idx < a.cand_cap) {
+                    keys[idx] = ((uint64_t)float_orderable(rk) << 32) | (uint32_t)idx;
+                    cand_limb[idx] = ls;
+                    cand_pair[idx] = ((uint32_t)ia << 16) | (uint32_t)ib;
+                }
+            }
+            ncand += tot;
+            __syncthreads();
+        }
+        if (ncand > a.cand_cap) {
+            if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
+            ncand = a.cand_cap;
+        }
+
+        if (ncand > 0) {
+            // ---- order: bitonic network, descending on (score, index) ----
+            int np2 = 1;
+            while (np2 < ncand) np2 <<= 1;
+            for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
+            __syncthreads();
+            for (int k = 2; k <= np2; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < np2; i += kLimbThreads) {
+                        const int l = i ^ j;
+                        if (l > i) {
+                            const uint64_t x = keys[i], y = keys[l];
+                            const bool desc = ((i & k) == 0);
+                            if (desc ? (x < y) : (x > y)) {
+                                keys[i] = y;
+                                keys[l] = x;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+            // duplicate keys?
+            bool dup = false;
+            for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
+            const bool emulate = __syncthreads_or(dup && ncand > 16);
+            if (emulate) {
+                // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
+                for (int i = tid; i < ncand; i += kLimbThreads) {
+                    const uint64_t kv = keys[i];
+                    const uint32_t idx = (uint32_t)kv;
+                    emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
+                }
+                __syncthreads();
+                if (tid == 0) {
+                    const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
+                    atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
+                }
+                __syncthreads();
+            }
+            const uint64_t *order = emulate ? emu : keys;
+
+            // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order ----
+            if (warp == 0) {
+                const int max_links = min(nA, nB);
+                DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
+                int nl = 0;
+                for (int base = 0; base < ncand && nl < max_links; base += 32) {
+                    const int i = base + lane;
+                    bool valid = i < ncand;
+                    int ia = 0, ib = 0, cidx = 0;
+                    if (valid) {
+                        cidx = (int)(uint32_t)order[i];
+                        const uint32_t pr = cand_pair[cidx];
+                        ia = (int)(pr >> 16);
+                        ib = (int)(pr & 0xffffu);
+                    }
+                    while (nl < max_links) {
+                        const bool free_now = valid && !used_a[ia] && !used_b[ib];
+                        const uint32_t bal = __ballot_sync(0xffffffffu, free_now);
+                        if (bal == 0) break;
+                        const int leader = __ffs(bal) - 1;
+                        if (lane == leader) {
+                            used_a[ia] = 1;
+                            used_b[ib] = 1;
+                            DevLink l;
+                            l.id_a = sA[ia].id;
+                            l.id_b = sB[ib].id;
+                            l.limb = cand_limb[cidx];
+                            l.len = limb_length(sA[ia], sB[ib]);
+                            // pafprocess.cpp:160,261-262 look the peak scores up as peak_infos_line[peak_id]: the
+                            // part-major list indexed by ARRIVAL id — the same peak only when the caller's joint
+                            // list is sorted by part (evaluate.py:99-103 does that); keep the quirk
+                            const ibp_peak *line = a.line + (size_t)img * a.line_stride;
+                            l.score_a = line[min(l.id_a, a.line_stride - 1)].score;
+                            l.score_b = line[min(l.id_b, a.line_stride - 1)].score;
+                            out[nl] = l;
+                            valid = false;
+                        }
+                        nl++;
+                        __syncwarp();
+                    }
+                }
+                n_links = nl;
             }
         }
-        if (lane == 0) *link_count = nl;
     }
+    if (tid == 0) *link_count = n_links;
+
+    // ---- the last CTA of this image groups its connections into people ----
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned t = atomicAdd(a.ticket + img, 1u);
+        s_last = (t == (unsigned)kLimbs - 1);
+        if (s_last) a.ticket[img] = 0;  // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    group_image(a.group, img, smem_raw, (size_t)a.smem_bytes);
 }
 
 }  // namespace ibp

@@ -1,4 +1,4 @@
-// K2 — keypoint peaks: non-maximum suppression, in-order compaction into per-part candidate lists, sub-pixel refine.
+// K2 — keypoint peaks: (flip average) -> non-maximum suppression -> ordered candidate lists -> sub-pixel refine.
 //
 // Flavour IBP_PEAKS_CROSS_REFINE restates heatmap_nms (utils/parse_skeletons.py:126-176):
 //   * find_peaks_refactor (l.106-119): maximum_filter with the 4-connected cross footprint == value, AND value > 0.1
@@ -12,33 +12,46 @@
 // `heat * keep` product non-zero) and util.refine_centroid (utils/util.py:188-213, float64 moments with numpy's
 // summation order); see centroid_refine below.
 //
-// One CTA per (image, part).  The plane is streamed through shared memory in bands of whole rows (+2 halo rows)
-// by the bulk-copy engine — a band of a planar map is one contiguous run of bytes — so HBM sees each value once
-// (algorithmic bytes: 18*h*w*4 per image) and the 5-point / 9-point stencil and the 5x5 patches
-// are served from shared memory.  Ordered compaction: one ballot word per 32 pixels, a block scan over the
-// pop-counts, then every thread emits the set bits of its words — list order equals np.nonzero order.
+// Grid (bands, 18 parts, images).  A CTA owns a band of whole rows of one keypoint plane (+`halo` rows either side),
+// stages it in shared memory — averaging the upright plane with the mirrored, channel-permuted plane of the flipped
+// image on the way in when the source is the raw network output (utils/parse_skeletons.py:91-93), so the fused map
+// is never written to HBM — and runs the stencil and the 5x5 patches from shared memory.  HBM sees every input value
+// once: 18*h*w*sizeof(T) per image, twice that with the flip twin.
+// Peaks are rare (a few per plane): threads that find one append its pixel index to a shared list, the list is
+// rank-sorted (row-major == np.nonzero order), refined one warp per peak and written to a band-local list.
+// The last CTA of an image to finish (ticket counter) concatenates the band lists in (part, band) order, assigns the
+// running ids across parts (parse_skeletons.py:172-173) and writes the part-major "line" array
+// (pafprocess.cpp:43-48) that grouping and the results index by peak id.
 #pragma once
 #include "ibp_device.cuh"
 
 namespace ibp {
 
 struct PeakArgs {
-    const float *maps;   // (batch, chan_stride, h, w)
-    int chan_stride;
-    int first_chan;
+    const void *src;      // planes: element (img, chan, y, x) at src + img*image_stride + chan*h*w + y*w + x
+    int dtype;            // IBP_F32 / IBP_F16
+    size_t image_stride;  // elements between images
+    int chan0;            // channel of keypoint 0 in the upright block
+    int twin_base;        // channel offset of the flipped image's block (50 for the network output), or -1: no flip
     int h, w;
-    int rows_per_band;   // owned rows per band
-    int rows_buf;        // rows that fit the shared buffer (>= rows_per_band + 2*halo, or h)
-    int halo;
-    int up;              // up-sampling factor of the refine step
-    int win;             // patch half-size / centroid radius
+    int rows_per_band, nbands, halo;
+    int band_bytes;       // shared bytes reserved for the band (>= rows*w*4 and >= (18*nbands+1)*4, multiple of 16)
+    int up;               // up-sampling factor of the refine step
+    int win;              // patch half-size / centroid radius
     float thr;
-    int cap;             // max peaks per (image, part)
+    int cap;              // max peaks per (image, part); also per band
     int flavour;
-    DevPeak *peaks;      // (batch, 18, cap)
-    float *subpix;       // (batch, 18, cap, 2) float x,y for the centroid flavour (may be null)
-    int *part_count;     // (batch, 18)
-    uint32_t *status;    // (batch)
+    DevPeak *band_peaks;  // (batch, 18, nbands, cap) scratch
+    float *band_subpix;   // (batch, 18, nbands, cap, 2) scratch, centroid flavour
+    int *band_count;      // (batch, 18, nbands) scratch
+    unsigned *ticket;     // (batch) zero on entry, left zero on exit
+    DevPeak *peaks;       // (batch, 18, cap)
+    float *subpix;        // (batch, 18, cap, 2)
+    int *part_count;      // (batch, 18)
+    ibp_peak *line;       // (batch, line_stride)
+    int line_stride;
+    int *n_peaks;         // (batch)
+    uint32_t *status;     // (batch)
 };
 
 constexpr int kPeakThreads = 256;
@@ -51,6 +64,7 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int *warp_tot, int &t
         const int n = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += n;
     }
+    __syncthreads();  // warp_tot may still be read from a previous call
     if (lane == 31) warp_tot[warp] = incl;
     __syncthreads();
     int base = 0, tot = 0;
@@ -83,246 +97,321 @@ __device__ __forceinline__ double np_pairwise_sum_f64(const double *a, int n) {
     return res;
 }
 
+template <typename T>
 __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int part = blockIdx.x, img = blockIdx.y;
+    const int bandi = blockIdx.x, part = blockIdx.y, img = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int nwarps = kPeakThreads / 32;
+    constexpr int nwarps = kPeakThreads / 32;
     const int w = a.w, h = a.h;
+
+    const int r0 = bandi * a.rows_per_band, r1 = min(r0 + a.rows_per_band, h);
+    const int l0 = max(r0 - a.halo, 0), l1 = min(r1 + a.halo, h);
 
     // carve shared memory
     float *band = reinterpret_cast<float *>(smem_raw);
-    size_t off = (size_t)a.rows_buf * w * sizeof(float);
-    off = (off + 15) & ~(size_t)15;
-    uint32_t *words = reinterpret_cast<uint32_t *>(smem_raw + off);
-    const int words_max = (a.rows_per_band * w + 31) / 32;
-    off += (size_t)words_max * 4;
-    off = (off + 7) & ~(size_t)7;
+    size_t off = (size_t)a.band_bytes;
     const int side = 2 * a.win + 1;
-    float *hbuf_all = reinterpret_cast<float *>(smem_raw + off);  // per warp: side * side*up floats
     const int hbuf_per_warp = side * side * a.up;
-    off += (size_t)nwarps * hbuf_per_warp * 4;
-    off = (off + 7) & ~(size_t)7;
-    short2 *pk = reinterpret_cast<short2 *>(smem_raw + off);      // [cap]
+    float *hbuf_all = reinterpret_cast<float *>(smem_raw + off);  // per warp: side rows x side*up columns
+    off += ((size_t)nwarps * hbuf_per_warp * 4 + 7) & ~(size_t)7;
+    int *found = reinterpret_cast<int *>(smem_raw + off);         // [cap] unordered pixel indices
+    off += (size_t)a.cap * 4;
+    int *sorted = reinterpret_cast<int *>(smem_raw + off);        // [cap] row-major order
     __shared__ uint64_t bar;
-    __shared__ int warp_tot[kPeakThreads / 32];
+    __shared__ int warp_tot[nwarps];
+    __shared__ int s_found;
+    __shared__ int s_last;
+    __shared__ float tab4[4][4];
 
     if (tid == 0) {
         mbar_init(&bar, 1);
         fence_barrier_init();
+        s_found = 0;
     }
+    cubic_tab4_init(tab4);
     __syncthreads();
     uint32_t phase = 0;
 
-    const float *plane = a.maps + ((size_t)img * a.chan_stride + a.first_chan + part) * (size_t)h * w;
-    DevPeak *out = a.peaks + ((size_t)img * kParts + part) * a.cap;
-    int n_total = 0;  // peaks found so far (may exceed cap)
-
-    for (int r0 = 0; r0 < h; r0 += a.rows_per_band) {
-        const int r1 = min(r0 + a.rows_per_band, h);
-        const int l0 = max(r0 - a.halo, 0), l1 = min(r1 + a.halo, h);
-        __syncthreads();  // everybody is done with the previous band
-        rows_to_smem(band, plane + (size_t)l0 * w, (uint32_t)(l1 - l0) * w, &bar, phase);
+    {
+        const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
+        const size_t hw = (size_t)h * w;
+        const T *up = base + (size_t)(a.chan0 + part) * hw;
+        // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
+        const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[kLimbs + part]) * hw : nullptr;
+        stage_rows_fused<T>(band, up, twin, l0, l1 - l0, w, &bar, phase);
+    }
 #define BAND(y, x) band[((y)-l0) * w + (x)]
-        const int npix = (r1 - r0) * w;
-        const int npix32 = (npix + 31) & ~31;
-        for (int i = tid; i < npix32; i += kPeakThreads) {
-            bool keep = false;
-            if (i < npix) {
-                const int yy = i / w;
-                const int x = i - yy * w;
-                const int y = r0 + yy;
-                const float v = BAND(y, x);
-                if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
-                    keep = v > a.thr;
-                    if (keep) {
-                        if (y > 0) keep = keep && (v >= BAND(y - 1, x));
-                        if (y < h - 1) keep = keep && (v >= BAND(y + 1, x));
-                        if (x > 0) keep = keep && (v >= BAND(y, x - 1));
-                        if (x < w - 1) keep = keep && (v >= BAND(y, x + 1));
-                    }
-                } else {
-                    // util.py:181-185: hmax == heat, heat >= thre, and heat*keep != 0
-                    keep = (v >= a.thr) && (v != 0.0f);
-                    if (keep) {
-                        const int ya = max(y - 1, 0), yb = min(y + 1, h - 1), xa = max(x - 1, 0), xb = min(x + 1, w - 1);
-                        for (int q = ya; q <= yb; q++)
-                            for (int p = xa; p <= xb; p++) keep = keep && (v >= BAND(q, p));
-                    }
-                }
-            }
-            const uint32_t bal = __ballot_sync(0xffffffffu, keep);
-            if (lane == 0) words[i >> 5] = bal;
-        }
-        __syncthreads();
-        // scan the pop-counts
-        const int nwords = npix32 >> 5;
-        const int wpt = (nwords + kPeakThreads - 1) / kPeakThreads;
-        const int w_begin = min(tid * wpt, nwords), w_end = min(w_begin + wpt, nwords);
-        int cnt = 0;
-        for (int q = w_begin; q < w_end; q++) cnt += __popc(words[q]);
-        int band_total;
-        int pos = n_total + block_exclusive_scan(cnt, warp_tot, band_total);
-        for (int q = w_begin; q < w_end; q++) {
-            uint32_t bits = words[q];
-            while (bits) {
-                const int bit = __ffs(bits) - 1;
-                bits &= bits - 1;
-                const int i = (q << 5) + bit;
-                const int yy = i / w;
-                if (pos < a.cap) pk[pos] = make_short2((short)(i - yy * w), (short)(r0 + yy));
-                pos++;
-            }
-        }
-        __syncthreads();
-        const int k_begin = min(n_total, a.cap), k_end = min(n_total + band_total, a.cap);
-        n_total += band_total;
 
-        // refine the peaks of this band, one warp per peak
-        float *hbuf = hbuf_all + warp * hbuf_per_warp;
-        for (int k = k_begin + warp; k < k_end; k += nwarps) {
-            const int px = pk[k].x, py = pk[k].y;
-            if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
-                const int x0 = max(px - a.win, 0), x1 = min(px + a.win, w - 1);
-                const int y0 = max(py - a.win, 0), y1 = min(py + a.win, h - 1);
-                const int pw = x1 - x0 + 1, ph = y1 - y0 + 1;
-                const int W4 = pw * a.up, H4 = ph * a.up;
-                // horizontal pass: ph rows x W4 columns
-                for (int idx = lane; idx < ph * W4; idx += 32) {
-                    const int r = idx / W4, X = idx - r * W4;
-                    float xw[4];
-                    const int sx = cubic_tap(X, a.up, xw);
-                    const int c0 = x0 + clampi(sx - 1, 0, pw - 1), c1 = x0 + clampi(sx, 0, pw - 1);
-                    const int c2 = x0 + clampi(sx + 1, 0, pw - 1), c3 = x0 + clampi(sx + 2, 0, pw - 1);
-                    const int y = y0 + r;
-                    hbuf[r * W4 + X] = hsum4(BAND(y, c0), BAND(y, c1), BAND(y, c2), BAND(y, c3), xw);
-                }
-                __syncwarp();
-                float best = -INFINITY;
-                int best_idx = 0x7fffffff;
-                for (int idx = lane; idx < H4 * W4; idx += 32) {
-                    const int Y = idx / W4, X = idx - Y * W4;
-                    float yw[4];
-                    const int sy = cubic_tap(Y, a.up, yw);
-                    const int q0 = clampi(sy - 1, 0, ph - 1), q1 = clampi(sy, 0, ph - 1);
-                    const int q2 = clampi(sy + 1, 0, ph - 1), q3 = clampi(sy + 2, 0, ph - 1);
-                    const float v = vsum4(hbuf[q0 * W4 + X], hbuf[q1 * W4 + X], hbuf[q2 * W4 + X], hbuf[q3 * W4 + X], yw);
-                    if (v > best) {
-                        best = v;
-                        best_idx = idx;
-                    }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
-                    const int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
-                    if (ov > best || (ov == best && oi < best_idx)) {
-                        best = ov;
-                        best_idx = oi;
-                    }
-                }
-                if (lane == 0) {
-                    if (best_idx == 0x7fffffff) best_idx = 0;
-                    DevPeak p;
-                    p.x = x0 * a.up + best_idx % W4;
-                    p.y = y0 * a.up + best_idx / W4;
-                    p.score = best;
-                    p.id = k;
-                    out[k] = p;
-                }
-                __syncwarp();
-            } else {
-                // util.refine_centroid (util.py:188-213), radius = win
-                if (lane == 0) {
-                    const int rad = a.win;
-                    float fx, fy, sc;
-                    if (py + rad + 1 > h || py - rad < 0 || px + rad + 1 > w || px - rad < 0) {
-                        fx = (float)px;
-                        fy = (float)py;
-                        sc = BAND(py, px);
-                    } else {
-                        // score_box is a float32 view; box*grid promotes to float64 (grid is int64) and the 25
-                        // products form a fresh contiguous array summed pairwise in float64; box.sum() reduces the
-                        // strided float32 view row by row (inner runs of 2*rad+1 < 8 values, left to right, then
-                        // accumulated across rows); box.mean() = that float32 sum / 25 in float32.
-                        double prod_r[25 * 1], prod_c[25 * 1];
-                        const int sidec = 2 * rad + 1;
-                        float total = 0.0f;
-                        int n = 0;
-                        for (int q = -rad; q <= rad; q++) {
-                            float rowsum = 0.0f;
-                            for (int p = -rad; p <= rad; p++) {
-                                const float v = BAND(py + q, px + p);
-                                if (n < 25) {
-                                    prod_r[n] = __dmul_rn((double)v, (double)q);  // x_grid = ROW offset (l.207 quirk)
-                                    prod_c[n] = __dmul_rn((double)v, (double)p);  // y_grid = column offset
-                                }
-                                n++;
-                                rowsum = __fadd_rn(rowsum, v);
-                            }
-                            total = (q == -rad) ? rowsum : __fadd_rn(total, rowsum);
-                        }
-                        const int cntp = min(n, 25);
-                        const double denom = (double)total;
-                        const double offx = __ddiv_rn(np_pairwise_sum_f64(prod_r, cntp), denom);
-                        const double offy = __ddiv_rn(np_pairwise_sum_f64(prod_c, cntp), denom);
-                        fx = __double2float_rn(__dadd_rn((double)px, offx));
-                        fy = __double2float_rn(__dadd_rn((double)py, offy));
-                        sc = __fdiv_rn(total, (float)(sidec * sidec));
-                    }
-                    DevPeak p;
-                    p.x = (int)fx;  // truncated like the C++ route would (pafprocess.cpp:35-36)
-                    p.y = (int)fy;
-                    p.score = sc;
-                    p.id = k;
-                    out[k] = p;
-                    if (a.subpix) {
-                        float *sp = a.subpix + (((size_t)img * kParts + part) * a.cap + k) * 2;
-                        sp[0] = fx;
-                        sp[1] = fy;
-                    }
-                }
-                __syncwarp();
+    // ---- non-maximum suppression over the owned rows ----
+    auto test_pixel = [&](int y, int x, float v) {
+        bool keep;
+        if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
+            keep = v > a.thr;
+            if (keep) {
+                if (y > 0) keep = keep && (v >= BAND(y - 1, x));
+                if (y < h - 1) keep = keep && (v >= BAND(y + 1, x));
+                if (x > 0) keep = keep && (v >= BAND(y, x - 1));
+                if (x < w - 1) keep = keep && (v >= BAND(y, x + 1));
+            }
+        } else {
+            // util.py:181-185: hmax == heat, heat >= thre, and heat*keep != 0
+            keep = (v >= a.thr) && (v != 0.0f);
+            if (keep) {
+                const int ya = max(y - 1, 0), yb = min(y + 1, h - 1), xa = max(x - 1, 0), xb = min(x + 1, w - 1);
+                for (int q = ya; q <= yb; q++)
+                    for (int p = xa; p <= xb; p++) keep = keep && (v >= BAND(q, p));
             }
         }
-#undef BAND
-    }
-    if (tid == 0) {
-        a.part_count[img * kParts + part] = min(n_total, a.cap);
-        if (n_total > a.cap) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
-    }
-}
-
-// After the per-part lists exist: running ids across parts (parse_skeletons.py:172-173) and the part-major "line"
-// array (pafprocess.cpp:43-48) that results and grouping index by peak id.  One CTA per image.
-__global__ void __launch_bounds__(128) pack_peaks_kernel(DevPeak *peaks, const int *part_count, int cap, ibp_peak *line, int line_stride,
-                                                         int *n_peaks) {
-    const int img = blockIdx.x;
-    __shared__ int offs[kParts + 1];
-    if (threadIdx.x == 0) {
-        int acc = 0;
-        for (int p = 0; p < kParts; p++) {
-            offs[p] = acc;
-            acc += part_count[img * kParts + p];
+        if (keep) {
+            const int slot = atomicAdd(&s_found, 1);
+            if (slot < a.cap) found[slot] = y * w + x;
         }
-        offs[kParts] = acc;
-        n_peaks[img] = min(acc, line_stride);
+    };
+    const int npix = (r1 - r0) * w;
+    const float *own = &BAND(r0, 0);
+    const float gate = a.thr;  // both flavours need v >= thr at least
+    if ((w & 3) == 0) {
+        const float4 *own4 = reinterpret_cast<const float4 *>(own);
+        for (int i4 = tid; i4 < (npix >> 2); i4 += kPeakThreads) {
+            const float4 v = own4[i4];
+            // cheap reject: nothing at or above the threshold in these four pixels
+            if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= gate) {
+                const int i = i4 << 2;
+                const int yy = i / w, x = i - yy * w, y = r0 + yy;
+                test_pixel(y, x, v.x);
+                test_pixel(y, x + 1, v.y);
+                test_pixel(y, x + 2, v.z);
+                test_pixel(y, x + 3, v.w);
+            }
+        }
+    } else {
+        for (int i = tid; i < npix; i += kPeakThreads) {
+            const float v = own[i];
+            if (v >= gate) {
+                const int yy = i / w;
+                test_pixel(r0 + yy, i - yy * w, v);
+            }
+        }
     }
     __syncthreads();
-    for (int p = 0; p < kParts; p++) {
-        const int n = part_count[img * kParts + p];
-        DevPeak *src = peaks + ((size_t)img * kParts + p) * cap;
-        for (int k = threadIdx.x; k < n; k += blockDim.x) {
-            const int id = offs[p] + k;
-            src[k].id = id;
-            if (id < line_stride) {
-                ibp_peak o;
-                o.x = src[k].x;
-                o.y = src[k].y;
-                o.score = src[k].score;
-                o.part = p;
-                line[(size_t)img * line_stride + id] = o;
+    const int n_raw = s_found;
+    const int n = min(n_raw, a.cap);
+    // rank sort: pixel indices are distinct
+    for (int i = tid; i < n; i += kPeakThreads) {
+        const int mine = found[i];
+        int rank = 0;
+        for (int j = 0; j < n; j++) rank += (found[j] < mine);
+        sorted[rank] = mine;
+    }
+    __syncthreads();
+
+    // ---- refine, one warp per peak ----
+    const size_t slot_base = (((size_t)img * kParts + part) * a.nbands + bandi) * a.cap;
+    DevPeak *out = a.band_peaks + slot_base;
+    float *hbuf = hbuf_all + warp * hbuf_per_warp;
+    for (int k = warp; k < n; k += nwarps) {
+        const int pix = sorted[k];
+        const int py = pix / w, px = pix - py * w;
+        if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
+            const int x0 = max(px - a.win, 0), x1 = min(px + a.win, w - 1);
+            const int y0 = max(py - a.win, 0), y1 = min(py + a.win, h - 1);
+            const int pw = x1 - x0 + 1, ph = y1 - y0 + 1;
+            const int W4 = pw * a.up, H4 = ph * a.up;
+            // horizontal pass: ph rows x W4 columns
+            for (int idx = lane; idx < ph * W4; idx += 32) {
+                const int r = idx / W4, X = idx - r * W4;
+                float xw_[4];
+                const float *xw;
+                int sx;
+                if (a.up == 4) {
+                    sx = (X - 2) >> 2;
+                    xw = tab4[(X - 2) & 3];
+                } else {
+                    sx = cubic_tap(X, a.up, xw_);
+                    xw = xw_;
+                }
+                const int c0 = x0 + clampi(sx - 1, 0, pw - 1), c1 = x0 + clampi(sx, 0, pw - 1);
+                const int c2 = x0 + clampi(sx + 1, 0, pw - 1), c3 = x0 + clampi(sx + 2, 0, pw - 1);
+                const int y = y0 + r;
+                hbuf[r * W4 + X] = hsum4(BAND(y, c0), BAND(y, c1), BAND(y, c2), BAND(y, c3), xw);
             }
+            __syncwarp();
+            float best = -INFINITY;
+            int best_idx = 0x7fffffff;
+            for (int idx = lane; idx < H4 * W4; idx += 32) {
+                const int Y = idx / W4, X = idx - Y * W4;
+                float yw_[4];
+                const float *yw;
+                int sy;
+                if (a.up == 4) {
+                    sy = (Y - 2) >> 2;
+                    yw = tab4[(Y - 2) & 3];
+                } else {
+                    sy = cubic_tap(Y, a.up, yw_);
+                    yw = yw_;
+                }
+                const int q0 = clampi(sy - 1, 0, ph - 1), q1 = clampi(sy, 0, ph - 1);
+                const int q2 = clampi(sy + 1, 0, ph - 1), q3 = clampi(sy + 2, 0, ph - 1);
+                const float v = vsum4(hbuf[q0 * W4 + X], hbuf[q1 * W4 + X], hbuf[q2 * W4 + X], hbuf[q3 * W4 + X], yw);
+                if (v > best) {
+                    best = v;
+                    best_idx = idx;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+                if (ov > best || (ov == best && oi < best_idx)) {
+                    best = ov;
+                    best_idx = oi;
+                }
+            }
+            if (lane == 0) {
+                if (best_idx == 0x7fffffff) best_idx = 0;
+                DevPeak p;
+                p.x = x0 * a.up + best_idx % W4;
+                p.y = y0 * a.up + best_idx / W4;
+                p.score = best;
+                p.id = k;
+                out[k] = p;
+            }
+            __syncwarp();
+        } else {
+            // util.refine_centroid (util.py:188-213), radius = win
+            if (lane == 0) {
+                const int rad = a.win;
+                float fx, fy, sc;
+                if (py + rad + 1 > h || py - rad < 0 || px + rad + 1 > w || px - rad < 0) {
+                    fx = (float)px;
+                    fy = (float)py;
+                    sc = BAND(py, px);
+                } else {
+                    // score_box is a float32 view; box*grid promotes to float64 (grid is int64) and the 25
+                    // products form a fresh contiguous array summed pairwise in float64; box.sum() reduces the
+                    // strided float32 view row by row (inner runs of 2*rad+1 < 8 values, left to right, then
+                    // accumulated across rows); box.mean() = that float32 sum / 25 in float32.
+                    double prod_r[25 * 1], prod_c[25 * 1];
+                    const int sidec = 2 * rad + 1;
+                    float total = 0.0f;
+                    int cnt = 0;
+                    for (int q = -rad; q <= rad; q++) {
+                        float rowsum = 0.0f;
+                        for (int p = -rad; p <= rad; p++) {
+                            const float v = BAND(py + q, px + p);
+                            if (cnt < 25) {
+                                prod_r[cnt] = __dmul_rn((double)v, (double)q);  // x_grid = ROW offset (l.207 quirk)
+                                prod_c[cnt] = __dmul_rn((double)v, (double)p);  // y_grid = column offset
+                            }
+                            cnt++;
+                            rowsum = __fadd_rn(rowsum, v);
+                        }
+                        total = (q == -rad) ? rowsum : __fadd_rn(total, rowsum);
+                    }
+                    const int cntp = min(cnt, 25);
+                    const double denom = (double)total;
+                    const double offx = __ddiv_rn(np_pairwise_sum_f64(prod_r, cntp), denom);
+                    const double offy = __ddiv_rn(np_pairwise_sum_f64(prod_c, cntp), denom);
+                    fx = __double2float_rn(__dadd_rn((double)px, offx));
+                    fy = __double2float_rn(__dadd_rn((double)py, offy));
+                    sc = __fdiv_rn(total, (float)(sidec * sidec));
+                }
+                DevPeak p;
+                p.x = (int)fx;  // truncated like the C++ route would (pafprocess.cpp:35-36)
+                p.y = (int)fy;
+                p.score = sc;
+                p.id = k;
+                out[k] = p;
+                if (a.band_subpix) {
+                    float *sp = a.band_subpix + (slot_base + k) * 2;
+                    sp[0] = fx;
+                    sp[1] = fy;
+                }
+            }
+            __syncwarp();
+        }
+    }
+#undef BAND
+    if (tid == 0) {
+        a.band_count[((size_t)img * kParts + part) * a.nbands + bandi] = n;
+        if (n_raw > a.cap) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
+    }
+
+    // ---- last CTA of this image packs ----
+    __threadfence();
+    __syncthreads();
+    const unsigned ctas_per_image = (unsigned)a.nbands * kParts;
+    if (tid == 0) {
+        const unsigned t = atomicAdd(a.ticket + img, 1u);
+        s_last = (t == ctas_per_image - 1);
+        if (s_last) a.ticket[img] = 0;  // ready for the next launch
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    // exclusive scan of the band counts in (part, band) order; re-use the band buffer (>= 18*nbands+1 ints by launch)
+    int *offs = reinterpret_cast<int *>(smem_raw);
+    const int items = kParts * a.nbands;
+    const int *bc = a.band_count + (size_t)img * items;
+    const int per = (items + kPeakThreads - 1) / kPeakThreads;
+    const int i_begin = min(tid * per, items), i_end = min(i_begin + per, items);
+    int mine = 0;
+    for (int i = i_begin; i < i_end; i++) mine += __ldcg(bc + i);
+    int total;
+    int run = block_exclusive_scan(mine, warp_tot, total);
+    for (int i = i_begin; i < i_end; i++) {
+        offs[i] = run;
+        run += __ldcg(bc + i);
+    }
+    if (tid == 0) offs[items] = total;
+    __syncthreads();
+    // per-part counts, clamped to the per-part capacity
+    bool over = false;
+    if (tid < kParts) {
+        const int c = offs[(tid + 1) * a.nbands] - offs[tid * a.nbands];
+        over = c > a.cap;
+        a.part_count[img * kParts + tid] = min(c, a.cap);
+    }
+    if (__syncthreads_or(over)) {
+        // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
+        if (tid == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
+    }
+    if (tid == 0) a.n_peaks[img] = min(total, a.line_stride);
+    for (int j = tid; j < total; j += kPeakThreads) {
+        // item holding global position j: last i with offs[i] <= j
+        int lo = 0, hi = items - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (offs[mid] <= j) lo = mid; else hi = mid - 1;
+        }
+        const int p = lo / a.nbands;
+        const int k_in_band = j - offs[lo];
+        const int k_in_part = j - offs[p * a.nbands];
+        const size_t srci = ((size_t)img * items + lo) * a.cap + k_in_band;
+        const int4 raw = __ldcg(reinterpret_cast<const int4 *>(a.band_peaks + srci));
+        DevPeak pk;
+        pk.x = raw.x;
+        pk.y = raw.y;
+        pk.score = __int_as_float(raw.z);
+        pk.id = j;
+        if (k_in_part < a.cap) {
+            const size_t dsti = ((size_t)img * kParts + p) * a.cap + k_in_part;
+            a.peaks[dsti] = pk;
+            if (a.band_subpix && a.subpix) {
+                const float2 sp = __ldcg(reinterpret_cast<const float2 *>(a.band_subpix + srci * 2));
+                a.subpix[dsti * 2] = sp.x;
+                a.subpix[dsti * 2 + 1] = sp.y;
+            }
+        }
+        if (j < a.line_stride) {
+            ibp_peak o;
+            o.x = pk.x;
+            o.y = pk.y;
+            o.score = pk.score;
+            o.part = p;
+            a.line[(size_t)img * a.line_stride + j] = o;
         }
     }
 }
