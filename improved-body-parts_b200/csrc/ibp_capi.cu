@@ -173,7 +173,7 @@ size_t limb_phase_bytes(const ibp_handle *h, size_t plane_bytes) {
     size_t region0 = std::max(plane_bytes, (size_t)h->L.max_candidates_per_limb * 8);
     region0 = (region0 + 15) & ~(size_t)15;
     return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2) +
-           (size_t)kPairChunk * (sizeof(PairGeo) + (size_t)h->P.max_steps * 4);
+           (size_t)kPairChunk * (sizeof(PairGeo) + (size_t)h->P.max_steps * 4) + 16;
 }
 // ... and of the grouping phase that the last CTA of an image runs in the same allocation (k_group.cuh): the
 // skeleton table plus room for at least 256 staged connections
@@ -463,7 +463,13 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     size_t smem = band_bytes;
     smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
     smem += (size_t)a.cap * 8;
+    smem = (smem + 15) & ~(size_t)15;
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "find_peaks: rows of %d floats do not fit shared memory", fw);
+    a.ring_bytes = 0;
+    if (twin_base >= 0 && dtype == IBP_F32 && fw % 4 == 0 && smem + band_bytes <= kMaxDynSmem) {
+        a.ring_bytes = (int)band_bytes;  // second band buffer: the twin rows land here by bulk copy
+        smem += band_bytes;
+    }
     CU(cudaMemsetAsync(h->d_status, 0, (size_t)batch * sizeof(uint32_t), st));
     {
         StageTimer t(h, IBP_STAGE_PEAKS, st);
@@ -583,6 +589,10 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     a.ticket = h->d_ticket + h->L.max_batch;
     const size_t smem = limb_smem_bytes(h, plane_bytes);
     a.smem_bytes = (int)smem;
+    {
+        const char *dbg = getenv("IBP_DEBUG");
+        a.debug = dbg ? atoi(dbg) : 0;
+    }
     GroupArgs &g = a.group;
     g.links = h->d_links;
     g.link_count = h->d_link_count;

@@ -251,4 +251,77 @@ __device__ __forceinline__ void stage_rows_fused(float *dst, const T *up, const 
     __syncthreads();
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The same flip average as a bulk-copy (TMA) pipeline, float32 sources only.  The upright rows go straight to their
+// final place in shared memory; the twin rows stream through a ring of NS slots of `slot_rows` rows each and are
+// folded into the upright rows (mirrored) as they land, so up to nrows + NS*slot_rows rows are in flight per CTA
+// without holding a single register.  bars[0] tracks the upright copy, bars[1..NS] the ring slots.
+// flip_tma_ok() says whether the shapes/alignments allow it; flip_tma_issue() is called by ONE thread as early as
+// possible; flip_tma_finish() by all threads, and returns once dst holds the fused rows for everybody.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool flip_tma_ok(const float *dst, const float *up, const float *twin, const float *ring, int w, int slot_rows) {
+    return twin != nullptr && (w & 3) == 0 && slot_rows >= 1 && ((((uintptr_t)up) | ((uintptr_t)twin)) & 15u) == 0 &&
+           ((smem_u32(dst) | smem_u32(ring)) & 15u) == 0;
+}
+__device__ __forceinline__ void bulk_rows(float *dst, const float *src, uint32_t bytes, uint64_t *bar) {
+    mbar_expect_tx(bar, bytes);
+    uint32_t done = 0;
+    while (done < bytes) {
+        uint32_t chunk = bytes - done;
+        if (chunk > 65536u) chunk = 65536u;
+        bulk_g2s((char *)dst + done, (const char *)src + done, chunk, bar);
+        done += chunk;
+    }
+}
+template <int NS>
+__device__ __forceinline__ void flip_tma_issue(float *dst, const float *up, const float *twin, int row0, int nrows, int w, float *ring,
+                                               int slot_rows, uint64_t *bars) {
+    bulk_rows(dst, up + (size_t)row0 * w, (uint32_t)nrows * w * 4u, &bars[0]);
+    for (int s = 0; s < NS; s++) {
+        const int first = s * slot_rows;
+        if (first < nrows) {
+            const int rows = min(slot_rows, nrows - first);
+            bulk_rows(ring + (size_t)s * slot_rows * w, twin + (size_t)(row0 + first) * w, (uint32_t)rows * w * 4u, &bars[1 + s]);
+        }
+    }
+}
+template <int NS>
+__device__ __forceinline__ void flip_tma_finish(float *dst, const float *twin, int row0, int nrows, int w, float *ring, int slot_rows,
+                                                uint64_t *bars) {
+    const int wv = w >> 2;
+    const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
+    const int nchunks = (nrows + slot_rows - 1) / slot_rows;
+    mbar_wait(&bars[0], 0);
+    float4 *d4 = reinterpret_cast<float4 *>(dst);
+    for (int c = 0; c < nchunks; c++) {
+        const int s = c % NS;
+        mbar_wait(&bars[1 + s], (uint32_t)((c / NS) & 1));
+        const int first = c * slot_rows;
+        const int rows = min(slot_rows, nrows - first);
+        const float4 *r4 = reinterpret_cast<const float4 *>(ring + (size_t)s * slot_rows * w);
+        float4 *o4 = d4 + (size_t)first * wv;
+        for (int i = threadIdx.x; i < rows * wv; i += blockDim.x) {
+            const int r = (shift >= 0) ? (i >> shift) : (i / wv);
+            const int col = i - r * wv;
+            float4 a = o4[i];
+            const float4 m = r4[r * wv + (wv - 1 - col)];
+            a.x = avg_like_numpy(a.x, m.w);
+            a.y = avg_like_numpy(a.y, m.z);
+            a.z = avg_like_numpy(a.z, m.y);
+            a.w = avg_like_numpy(a.w, m.x);
+            o4[i] = a;
+        }
+        if (c + NS < nchunks) {
+            __syncthreads();  // everybody has read slot s
+            if (threadIdx.x == 0) {
+                fence_proxy_async();  // order those generic-proxy reads before the async-proxy refill
+                const int nfirst = (c + NS) * slot_rows;
+                const int nrows2 = min(slot_rows, nrows - nfirst);
+                bulk_rows(ring + (size_t)s * slot_rows * w, twin + (size_t)(row0 + nfirst) * w, (uint32_t)nrows2 * w * 4u, &bars[1 + s]);
+            }
+        }
+    }
+    __syncthreads();
+}
+
 }  // namespace ibp

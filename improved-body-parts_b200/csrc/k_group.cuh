@@ -74,7 +74,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
         const int base_slot = loff[limb];
         const int nl = loff[limb + 1] - base_slot;
         const DevLink *G = a.links + ((size_t)img * kLimbs + limb) * a.cap;
-        for (int li = 0; li < nl; li++) {
+        auto fetch = [&](int li) -> DevLink {
             DevLink l;
             if (base_slot + li < slots) {
                 l = slinks[base_slot + li];
@@ -88,39 +88,63 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                 l.score_a = q2.x;
                 l.score_b = q2.y;
             }
-            // :143-150 scan: first two matching rows, total number of matches
+            return l;
+        };
+        DevLink nxt;
+        if (nl > 0) nxt = fetch(0);
+        for (int li = 0; li < nl; li++) {
+            const DevLink l = nxt;
+            if (li + 1 < nl) nxt = fetch(li + 1);  // off the dependent chain
+            // :143-150 scan: first two matching rows, total number of matches.  Every lane also reads the fields of
+            // its row that the one-match case needs, so that case continues from registers (one shuffle) instead of
+            // a second round of dependent shared-memory loads.
             int hits = 0, first = 0, second = 0;
+            int f_idb = -1;
+            float f_scb = 0.f, f_reach = 0.f, f_total = 0.f;
             for (int base = 0; base < nb; base += 32) {
                 const int s = base + lane;
-                const bool m = (s < nb) && (ids[s * kParts + pa] == l.id_a || ids[s * kParts + pb] == l.id_b);
-                uint32_t bal = __ballot_sync(0xffffffffu, m);
-                while (bal) {
-                    const int pos = __ffs(bal) - 1;
-                    bal &= bal - 1;
-                    if (hits == 0) first = base + pos;
-                    else if (hits == 1) second = base + pos;
-                    hits++;
+                const bool valid = s < nb;
+                const int ia = valid ? ids[s * kParts + pa] : -2;
+                const int ibv = valid ? ids[s * kParts + pb] : -2;
+                const float scb = valid ? sc[s * kParts + pb] : 0.f;
+                const float rch = valid ? reach[s] : 0.f;
+                const float tot = valid ? total[s] : 0.f;
+                const uint32_t bal = __ballot_sync(0xffffffffu, valid && (ia == l.id_a || ibv == l.id_b));
+                if (bal) {
+                    const int p0 = __ffs(bal) - 1;
+                    if (hits == 0) {
+                        first = base + p0;
+                        f_idb = __shfl_sync(0xffffffffu, ibv, p0);
+                        f_scb = __shfl_sync(0xffffffffu, scb, p0);
+                        f_reach = __shfl_sync(0xffffffffu, rch, p0);
+                        f_total = __shfl_sync(0xffffffffu, tot, p0);
+                        const uint32_t rest = bal & (bal - 1);
+                        if (rest) second = base + __ffs(rest) - 1;
+                    } else if (hits == 1) {
+                        second = base + p0;
+                    }
+                    hits += __popc(bal);
                 }
             }
             if (hits == 1) {  // :152-180
                 if (lane == 0) {
                     const int f = first;
-                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(reach[f], __int2float_rn(a.len_rate))));  // :154
-                    const int cur_id = ids[f * kParts + pb];
-                    const float cur_sc = sc[f * kParts + pb];
+                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(f_reach, __int2float_rn(a.len_rate))));  // :154
+                    const int cur_id = f_idb;
+                    const float cur_sc = f_scb;
                     const float add = __fadd_rn(l.score_b, l.limb);
                     if (cur_id == -1 && gate > l.len) {
                         ids[f * kParts + pb] = l.id_b;
                         sc[f * kParts + pb] = l.limb;
                         count[f] += 1;
-                        reach[f] = fmaxf(reach[f], l.len);
-                        total[f] = __fadd_rn(total[f], add);
+                        reach[f] = fmaxf(f_reach, l.len);
+                        total[f] = __fadd_rn(f_total, add);
                     } else if ((cur_id != l.id_b && cur_sc <= l.limb && gate > l.len) || (cur_id == l.id_b && cur_sc <= l.limb)) {
                         ids[f * kParts + pb] = l.id_b;
                         sc[f * kParts + pb] = l.limb;
                         // :168-169 / :177-178 — subtracts the values just written, then adds them back
-                        total[f] = __fadd_rn(__fsub_rn(total[f], add), add);
-                        reach[f] = fmaxf(reach[f], l.len);
+                        total[f] = __fadd_rn(__fsub_rn(f_total, add), add);
+                        reach[f] = fmaxf(f_reach, l.len);
                     }
                 }
                 __syncwarp();

@@ -56,11 +56,14 @@ struct LimbArgs {
     uint32_t *status;       // (batch)
     unsigned *ticket;       // (batch) zero on entry, left zero on exit
     int smem_bytes;         // dynamic shared memory of the launch
+    int debug;              // experiments only (IBP_DEBUG): 1 = skip grouping, 2 = skip scoring
     GroupArgs group;
 };
 
 constexpr int kLimbThreads = 256;
 constexpr int kPairChunk = 128;  // pairs scored per round
+constexpr int kLimbRing = 4;      // slots of the twin-plane ring while staging
+constexpr int kRankSortMax = 512; // up to this many candidates are ordered by a rank sort, more by a bitonic network
 
 __device__ __forceinline__ uint32_t float_orderable(float f) {
     const uint32_t u = __float_as_uint(f);
@@ -116,24 +119,29 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         off = (off + 15) & ~(size_t)15;
     }
     uint64_t *emu = reinterpret_cast<uint64_t *>(smem_raw);
+    DevPeak *sA = reinterpret_cast<DevPeak *>(smem_raw + off);
+    off += (size_t)a.cap * sizeof(DevPeak);
+    DevPeak *sB = reinterpret_cast<DevPeak *>(smem_raw + off);
+    off += (size_t)a.cap * sizeof(DevPeak);
+    unsigned char *used_a = smem_raw + off;
+    off += (size_t)a.cap;
+    unsigned char *used_b = smem_raw + off;
+    off += (size_t)a.cap;
+    off = (off + 15) & ~(size_t)15;
+    // everything from here on is idle while the plane is staged: the twin ring borrows it
+    const size_t ring_off = off;
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw + off);
     off += (size_t)a.cand_cap * 8;
     float *cand_limb = reinterpret_cast<float *>(smem_raw + off);
     off += (size_t)a.cand_cap * 4;
     uint32_t *cand_pair = reinterpret_cast<uint32_t *>(smem_raw + off);
     off += (size_t)a.cand_cap * 4;
-    DevPeak *sA = reinterpret_cast<DevPeak *>(smem_raw + off);
-    off += (size_t)a.cap * sizeof(DevPeak);
-    DevPeak *sB = reinterpret_cast<DevPeak *>(smem_raw + off);
-    off += (size_t)a.cap * sizeof(DevPeak);
     PairGeo *geo = reinterpret_cast<PairGeo *>(smem_raw + off);  // [kPairChunk]
     off += (size_t)kPairChunk * sizeof(PairGeo);
     float *vals = reinterpret_cast<float *>(smem_raw + off);     // [kPairChunk][max_steps]
     off += (size_t)kPairChunk * a.max_steps * 4;
-    unsigned char *used_a = smem_raw + off;
-    off += (size_t)a.cap;
-    unsigned char *used_b = smem_raw + off;
-    __shared__ uint64_t bar;
+    const int ring_bytes = (int)((off - ring_off) & ~(size_t)15);
+    __shared__ uint64_t bars[1 + kLimbRing];
     __shared__ int wcnt[kLimbThreads / 32];
     __shared__ int s_last;
     __shared__ float tab4[4][4];
@@ -141,9 +149,28 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     int n_links = 0;  // meaningful on thread 0 only
     // no pair => no candidate => no connection (covers the both-empty skip at :57)
     if (nA > 0 && nB > 0) {
+        // source planes of this limb (feature-resolution modes)
+        const T *gplane = nullptr, *twin = nullptr;
+        if (a.mode == IBP_LIMB_FEAT_PLANAR) {
+            const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
+            const size_t hw = (size_t)a.h * a.w;
+            gplane = base + (size_t)limb * hw;
+            // flipped image: channel flip_paf_ord[limb] of its block (config/config.py:150-152)
+            twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[limb]) * hw : nullptr;
+        }
+        // twin rows stream through a ring that borrows the candidate/geometry/sample scratch (idle until scoring)
+        float *ring = reinterpret_cast<float *>(smem_raw + ring_off);
+        const int slot_rows = (a.mode == IBP_LIMB_FEAT_PLANAR) ? min(a.h, (ring_bytes / kLimbRing) / (a.w * 4)) : 0;
+        bool tma_flip = false;
+        if (sizeof(T) == 4 && a.mode == IBP_LIMB_FEAT_PLANAR && a.stage_plane)
+            tma_flip = flip_tma_ok(plane_s, reinterpret_cast<const float *>(gplane), reinterpret_cast<const float *>(twin), ring, a.w, slot_rows);
         if (tid == 0) {
-            mbar_init(&bar, 1);
+            for (int i = 0; i <= kLimbRing; i++) mbar_init(&bars[i], 1);
             fence_barrier_init();
+            // start the copies before anything else so that they overlap the candidate-list loads below
+            if (tma_flip)
+                flip_tma_issue<kLimbRing>(plane_s, reinterpret_cast<const float *>(gplane), reinterpret_cast<const float *>(twin), 0, a.h, a.w, ring,
+                               slot_rows, bars);
         }
         cubic_tab4_init(tab4);
         const DevPeak *gA = a.peaks + ((size_t)img * kParts + pa) * a.cap;
@@ -169,13 +196,13 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         smp.up = a.up;
         smp.tab4 = tab4;
         if (a.mode == IBP_LIMB_FEAT_PLANAR) {
-            const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
-            const size_t hw = (size_t)a.h * a.w;
-            const T *gplane = base + (size_t)limb * hw;
-            const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[limb]) * hw : nullptr;
             if (a.stage_plane) {
-                uint32_t phase = 0;
-                stage_rows_fused<T>(plane_s, gplane, twin, 0, a.h, a.w, &bar, phase);
+                if (tma_flip) {
+                    flip_tma_finish<kLimbRing>(plane_s, reinterpret_cast<const float *>(twin), 0, a.h, a.w, ring, slot_rows, bars);
+                } else {
+                    uint32_t phase = 0;
+                    stage_rows_fused<T>(plane_s, gplane, twin, 0, a.h, a.w, &bars[0], phase);
+                }
                 smp.base = plane_s;
             } else {
                 smp.base = reinterpret_cast<const float *>(gplane);  // host side guarantees float + no twin here
@@ -185,7 +212,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         }
 
         // ---- score all pairs; compact the accepted ones in pair order ----
-        const int npairs = nA * nB;
+        const int npairs = (a.debug & 2) ? 0 : nA * nB;
         int ncand = 0;
         for (int base = 0; base < npairs; base += kPairChunk) {
             const int chunk = min(kPairChunk, npairs - base);
@@ -278,25 +305,47 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         }
 
         if (ncand > 0) {
-            // ---- order: bitonic network, descending on (score, index) ----
-            int np2 = 1;
-            while (np2 < ncand) np2 <<= 1;
-            for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
-            __syncthreads();
-            for (int k = 2; k <= np2; k <<= 1) {
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < np2; i += kLimbThreads) {
-                        const int l = i ^ j;
-                        if (l > i) {
-                            const uint64_t x = keys[i], y = keys[l];
-                            const bool desc = ((i & k) == 0);
-                            if (desc ? (x < y) : (x > y)) {
-                                keys[i] = y;
-                                keys[l] = x;
+            // ---- order: descending on (score, index); keys are distinct because they carry the index ----
+            if (ncand <= kRankSortMax) {
+                // rank sort: one pass, two barriers — the common case (a handful of candidates per limb)
+                uint64_t mine[kRankSortMax / kLimbThreads];
+                int rank[kRankSortMax / kLimbThreads];
+#pragma unroll
+                for (int q = 0; q < kRankSortMax / kLimbThreads; q++) {
+                    const int i = tid + q * kLimbThreads;
+                    mine[q] = (i < ncand) ? keys[i] : 0;
+                    rank[q] = 0;
+                }
+                for (int j = 0; j < ncand; j++) {
+                    const uint64_t kj = keys[j];
+#pragma unroll
+                    for (int q = 0; q < kRankSortMax / kLimbThreads; q++) rank[q] += (kj > mine[q]);
+                }
+                __syncthreads();
+#pragma unroll
+                for (int q = 0; q < kRankSortMax / kLimbThreads; q++)
+                    if (tid + q * kLimbThreads < ncand) keys[rank[q]] = mine[q];
+                __syncthreads();
+            } else {
+                int np2 = 1;
+                while (np2 < ncand) np2 <<= 1;
+                for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
+                __syncthreads();
+                for (int k = 2; k <= np2; k <<= 1) {
+                    for (int j = k >> 1; j > 0; j >>= 1) {
+                        for (int i = tid; i < np2; i += kLimbThreads) {
+                            const int l = i ^ j;
+                            if (l > i) {
+                                const uint64_t x = keys[i], y = keys[l];
+                                const bool desc = ((i & k) == 0);
+                                if (desc ? (x < y) : (x > y)) {
+                                    keys[i] = y;
+                                    keys[l] = x;
+                                }
                             }
                         }
+                        __syncthreads();
                     }
-                    __syncthreads();
                 }
             }
             // duplicate keys?
@@ -367,7 +416,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     if (tid == 0) *link_count = n_links;
 
     // ---- the last CTA of this image groups its connections into people ----
-    __threadfence();
+    if (warp == 0) __threadfence();  // only warp 0 wrote connections / the count
     __syncthreads();
     if (tid == 0) {
         const unsigned t = atomicAdd(a.ticket + img, 1u);
@@ -377,6 +426,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     __syncthreads();
     if (!s_last) return;
     __threadfence();
+    if (a.debug & 1) return;
     group_image(a.group, img, smem_raw, (size_t)a.smem_bytes);
 }
 

@@ -36,6 +36,7 @@ struct PeakArgs {
     int h, w;
     int rows_per_band, nbands, halo;
     int band_bytes;       // shared bytes reserved for the band (>= rows*w*4 and >= (18*nbands+1)*4, multiple of 16)
+    int ring_bytes;       // shared bytes after the lists for the twin band (bulk-copy flip pipeline), 0: none
     int up;               // up-sampling factor of the refine step
     int win;              // patch half-size / centroid radius
     float thr;
@@ -118,20 +119,14 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     int *found = reinterpret_cast<int *>(smem_raw + off);         // [cap] unordered pixel indices
     off += (size_t)a.cap * 4;
     int *sorted = reinterpret_cast<int *>(smem_raw + off);        // [cap] row-major order
-    __shared__ uint64_t bar;
+    off += (size_t)a.cap * 4;
+    off = (off + 15) & ~(size_t)15;
+    float *ring = reinterpret_cast<float *>(smem_raw + off);      // twin band while staging (ring_bytes)
+    __shared__ uint64_t bars[2];
     __shared__ int warp_tot[nwarps];
     __shared__ int s_found;
     __shared__ int s_last;
     __shared__ float tab4[4][4];
-
-    if (tid == 0) {
-        mbar_init(&bar, 1);
-        fence_barrier_init();
-        s_found = 0;
-    }
-    cubic_tab4_init(tab4);
-    __syncthreads();
-    uint32_t phase = 0;
 
     {
         const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
@@ -139,7 +134,27 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
         const T *up = base + (size_t)(a.chan0 + part) * hw;
         // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
         const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[kLimbs + part]) * hw : nullptr;
-        stage_rows_fused<T>(band, up, twin, l0, l1 - l0, w, &bar, phase);
+        const int nrows = l1 - l0;
+        // float32 + twin: both bands by the bulk-copy engine, the twin into its own buffer (one ring slot holds it all)
+        const int slot_rows = (a.ring_bytes >= nrows * w * 4) ? nrows : 0;
+        bool tma_flip = false;
+        if (sizeof(T) == 4) tma_flip = flip_tma_ok(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), ring, w, slot_rows);
+        if (tid == 0) {
+            mbar_init(&bars[0], 1);
+            mbar_init(&bars[1], 1);
+            fence_barrier_init();
+            s_found = 0;
+            if (tma_flip)
+                flip_tma_issue<1>(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
+        }
+        cubic_tab4_init(tab4);
+        __syncthreads();
+        if (tma_flip) {
+            flip_tma_finish<1>(band, reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
+        } else {
+            uint32_t phase = 0;
+            stage_rows_fused<T>(band, up, twin, l0, nrows, w, &bars[0], phase);
+        }
     }
 #define BAND(y, x) band[((y)-l0) * w + (x)]
 
@@ -239,6 +254,22 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
             __syncwarp();
             float best = -INFINITY;
             int best_idx = 0x7fffffff;
+            if (W4 <= 32 && a.up == 4) {
+                // lane = column: the four taps and weights of a row are the same for every lane, no index division
+                if (lane < W4) {
+                    for (int Y = 0; Y < H4; Y++) {
+                        const int sy = (Y - 2) >> 2;
+                        const float *yw = tab4[(Y - 2) & 3];
+                        const int q0 = clampi(sy - 1, 0, ph - 1), q1 = clampi(sy, 0, ph - 1);
+                        const int q2 = clampi(sy + 1, 0, ph - 1), q3 = clampi(sy + 2, 0, ph - 1);
+                        const float v = vsum4(hbuf[q0 * W4 + lane], hbuf[q1 * W4 + lane], hbuf[q2 * W4 + lane], hbuf[q3 * W4 + lane], yw);
+                        if (v > best) {
+                            best = v;
+                            best_idx = Y * W4 + lane;
+                        }
+                    }
+                }
+            } else
             for (int idx = lane; idx < H4 * W4; idx += 32) {
                 const int Y = idx / W4, X = idx - Y * W4;
                 float yw_[4];
@@ -339,7 +370,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     }
 
     // ---- last CTA of this image packs ----
-    __threadfence();
+    if (lane == 0 && (warp < n || tid == 0)) __threadfence();  // the lanes that wrote peaks / the count
     __syncthreads();
     const unsigned ctas_per_image = (unsigned)a.nbands * kParts;
     if (tid == 0) {
