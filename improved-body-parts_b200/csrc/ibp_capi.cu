@@ -85,7 +85,10 @@ struct ibp_handle {
     float *d_band_subpix = nullptr;
     int *d_band_count = nullptr;
     int band_slots = 0;  // nbands the scratch was sized for
-    unsigned *d_ticket = nullptr;  // [2][max_batch]
+    unsigned *d_ticket = nullptr;  // [2][max_batch] + 1
+    int *d_order = nullptr;        // [max_batch] images by descending peak count (written by the peak kernel)
+    int order_batch = 0;           // batch size d_order is valid for (0: not valid)
+    unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
     float *d_fused = nullptr;
     size_t fused_floats = 0;
     void *d_stage = nullptr;  // host input staging / legacy limb map
@@ -154,6 +157,8 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_band_subpix);
     free_dev(h->d_band_count);
     free_dev(h->d_ticket);
+    free_dev(h->d_timeline);
+    free_dev(h->d_order);
     free_host(h->h_n_peaks);
     free_host(h->h_part_count);
     free_host(h->h_line);
@@ -177,14 +182,14 @@ size_t limb_phase_bytes(const ibp_handle *h, size_t plane_bytes) {
 }
 // ... and of the grouping phase that the last CTA of an image runs in the same allocation (k_group.cuh): the
 // skeleton table plus room for at least 256 staged connections
-size_t group_phase_bytes(const ibp_handle *h) { return (((size_t)h->L.max_bodies * kBodyBytes + 15) & ~(size_t)15) + 128 + 256 * sizeof(DevLink); }
+size_t group_phase_bytes(const ibp_handle *h) { return (size_t)h->L.max_bodies * kBodyBytes + 128 + 256 * sizeof(DevLink); }
 size_t limb_smem_bytes(const ibp_handle *h, size_t plane_bytes) {
     return (std::max(limb_phase_bytes(h, plane_bytes), group_phase_bytes(h)) + 15) & ~(size_t)15;
 }
 
 int validate_limits(const ibp_limits &l) {
     if (l.max_batch < 1 || l.max_peaks_per_part < 1 || l.max_peaks_per_part > 32767 || l.max_candidates_per_limb < 32 ||
-        (l.max_candidates_per_limb & (l.max_candidates_per_limb - 1)) != 0 || l.max_bodies < 1 || l.max_humans < 1 ||
+        (l.max_candidates_per_limb & (l.max_candidates_per_limb - 1)) != 0 || l.max_bodies < 32 || l.max_humans < 1 ||
         l.max_feat_h < 1 || l.max_feat_w < 1)
         return fail(IBP_ERR_ARG, "ibp_limits out of range (max_candidates_per_limb must be a power of two >= 32)");
     return IBP_OK;
@@ -320,8 +325,9 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMemset(h->d_n_peaks, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_n_humans, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_status, 0, B * sizeof(uint32_t)));
-        CU(cudaMalloc(&h->d_ticket, 2 * B * sizeof(unsigned)));
-        CU(cudaMemset(h->d_ticket, 0, 2 * B * sizeof(unsigned)));
+        CU(cudaMalloc(&h->d_ticket, (2 * B + 1) * sizeof(unsigned)));
+        CU(cudaMemset(h->d_ticket, 0, (2 * B + 1) * sizeof(unsigned)));
+        CU(cudaMalloc(&h->d_order, B * sizeof(int)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
         CU(cudaMallocHost(&h->h_part_count, B * kParts * sizeof(int)));
         CU(cudaMallocHost(&h->h_line, B * h->line_stride * sizeof(ibp_peak)));
@@ -459,6 +465,10 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.line_stride = h->line_stride;
     a.n_peaks = h->d_n_peaks;
     a.status = h->d_status;
+    a.batch_ticket = h->d_ticket + 2 * h->L.max_batch;
+    a.order = h->d_order;
+    a.batch = batch;
+    h->order_batch = batch;
     const int side = 2 * a.win + 1;
     size_t smem = band_bytes;
     smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
@@ -526,6 +536,7 @@ int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int 
             pos++;
         }
     h->h_n_peaks[image] = n;
+    h->order_batch = 0;  // the peak kernel's image order no longer describes the lists
     memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
     CU(cudaMemcpy(h->d_peaks + (size_t)image * kParts * cap, h->h_peaks_stage, (size_t)kParts * cap * sizeof(DevPeak), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(h->d_part_count + (size_t)image * kParts, counts, sizeof(counts), cudaMemcpyHostToDevice));
@@ -587,11 +598,18 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     a.link_count = h->d_link_count;
     a.status = h->d_status;
     a.ticket = h->d_ticket + h->L.max_batch;
+    a.order = (h->order_batch == batch) ? h->d_order : nullptr;
     const size_t smem = limb_smem_bytes(h, plane_bytes);
     a.smem_bytes = (int)smem;
     {
         const char *dbg = getenv("IBP_DEBUG");
         a.debug = dbg ? atoi(dbg) : 0;
+        a.timeline = nullptr;
+        if (a.debug & 8) {  // experiments only: per-CTA %globaltimer stamps, dumped by ibp_fetch
+            if (!h->d_timeline) CU(cudaMalloc(&h->d_timeline, (size_t)h->L.max_batch * 31 * 4 * sizeof(unsigned long long)));
+            CU(cudaMemsetAsync(h->d_timeline, 0, (size_t)h->L.max_batch * 31 * 4 * sizeof(unsigned long long), st));
+            a.timeline = h->d_timeline;
+        }
     }
     GroupArgs &g = a.group;
     g.links = h->d_links;
@@ -677,6 +695,15 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
     CU(cudaMemcpyAsync(h->h_humans, h->d_humans, B * h->L.max_humans * sizeof(ibp_human), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(h->h_status, h->d_status, B * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    if (h->d_timeline) {
+        std::vector<unsigned long long> tl((size_t)batch * 31 * 4);
+        CU(cudaMemcpy(tl.data(), h->d_timeline, tl.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        const char *path = getenv("IBP_TIMELINE");
+        if (FILE *f = fopen(path ? path : "ibp_timeline.bin", "wb")) {
+            fwrite(tl.data(), sizeof(unsigned long long), tl.size(), f);
+            fclose(f);
+        }
+    }
     view->batch = batch;
     view->peak_stride = h->line_stride;
     view->human_stride = h->L.max_humans;

@@ -18,11 +18,13 @@ struct DevPeak {  // 16 B — reference Peak, pafprocess.h:29-34
     float score;
     int id;
 };
-struct DevLink {  // 24 B — the fields of Connection (pafprocess.h:60-67) that grouping reads, plus the two peak scores
-    int id_a, id_b;   // the grouping step would otherwise fetch through peak_infos_line (pafprocess.cpp:261-262)
+struct __align__(16) DevLink {  // 32 B — the fields of Connection (pafprocess.h:60-67) that grouping reads, plus ...
+    int id_a, id_b;
     float limb;
     float len;
-    float score_a, score_b;
+    float score_a, score_b;  // ... the two peak scores grouping would fetch through peak_infos_line (pafprocess.cpp:160, :261-262)
+    float gate;              // ... and (float)(int)(len * LIMB_LENGTH_RATE), the connection's share of the :154 / :186 test
+    float pad;
 };
 
 // limb end points: pafprocess.h:20-27 COCOPAIRS == config/config.py:114-121

@@ -1,15 +1,25 @@
 // K4b — person grouping: grow / merge partial skeletons limb by limb, then filter.  One warp per image.
 //
 // Reference: utils/pafprocess/pafprocess.cpp:133-282.  The chain is sequential by construction (every connection
-// reads and mutates the table the next one scans, and a merge erases a row so later indices shift), so the
-// parallelism is images across CTAs and, inside a step, lanes over the skeleton scan (32 rows per ballot), over the
-// 18 part slots of a merge, and over the columns of the row shift that implements vector::erase.
+// reads and mutates the table the next one scans), so the parallelism is images across CTAs and, inside a step,
+// lanes over the skeleton scan (32 rows per ballot) and over the 18 part slots of a merge.  What is left is a
+// latency chain of one warp, so the code is organised around the number of dependent steps per connection:
 //
-// It runs as the tail of the limb kernel: the last of an image's 30 limb CTAs to finish (ticket counter) calls
-// group_image() with the CTA's whole dynamic shared memory.  The connections of all 30 limbs are first copied into
-// shared memory in one coalesced sweep (each carries its two peak scores, so the chain never touches global memory:
-// a dependent global load per connection was what bounded the stand-alone kernel), then warp 0 walks the chain on the
-// table ids[S][18], limb scores[S][18], total[S], count[S], reach[S].
+//   * It runs as the tail of the limb kernel: the last of an image's 30 limb CTAs to finish (ticket counter) calls
+//     group_image() with the CTA's whole dynamic shared memory.  The connections of all 30 limbs are first copied into
+//     shared memory in one coalesced sweep; each carries its two peak scores and its length gate, so the chain never
+//     touches global memory (a dependent global load per connection bounded the first version of this step).
+//   * Row layout: slot[S][18] = {peak id, limb score} pairs (one 64-bit load gives both), row[S] = {total, gate,
+//     reach, count} (one 128-bit load).  Every lane loads the three values of ITS row during the scan; the lane that
+//     owns the single matching row then updates it from its own registers — no second round of loads, no shuffles.
+//   * The reference's `(int)(length * 16) > conn.length` test (:154, :186) needs a float->int->float round trip on
+//     the chain.  x -> (float)(int)(x*16) is monotonic and a row's length is the running maximum of connection
+//     lengths, so gate(row) = max over its connections of gate(connection): the limb kernel computes the latter once
+//     per connection and the row keeps the running maximum — the same bits, no conversion on the chain.
+//   * vector::erase (:229) shifts every later row down, which only matters through the ORDER of the rows (the scan
+//     keeps the first two matches, the output keeps row order).  Rows here are never moved: an erased row gets ids
+//     that match nothing and count -1 (so the final filter drops it); surviving rows keep their relative order.
+//     max_bodies therefore bounds the number of rows ever created, not the number alive at one time.
 #pragma once
 #include "ibp_device.cuh"
 
@@ -30,39 +40,46 @@ struct GroupArgs {
     uint32_t *status;        // (batch)
 };
 
-constexpr size_t kBodyBytes = kParts * 8 + 12;  // shared bytes per row of the skeleton table
+constexpr size_t kBodyBytes = kParts * 8 + 16;  // shared bytes per row of the skeleton table
+constexpr int kDeadId = -3;                      // id in every slot of an erased row: equals no peak id, not -1
+
+// pafprocess.cpp:154 / :186  min_len = (int)(length * LIMB_LENGTH_RATE), later compared with a float
+__device__ __forceinline__ float length_gate(float len, int len_rate) {
+    return __int2float_rn(__float2int_rz(__fmul_rn(len, __int2float_rn(len_rate))));
+}
 
 // All threads of the CTA call this; `smem` / `smem_bytes` is the CTA's dynamic shared memory (free for re-use).
 __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigned char *smem, size_t smem_bytes) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = a.max_bodies;
-    int *ids = reinterpret_cast<int *>(smem);                         // [S][18]
-    float *sc = reinterpret_cast<float *>(ids + (size_t)S * kParts);  // [S][18]
-    float *total = sc + (size_t)S * kParts;                           // [S]
-    int *count = reinterpret_cast<int *>(total + S);                  // [S]
-    float *reach = reinterpret_cast<float *>(count + S);              // [S]
-    size_t off = ((size_t)S * kBodyBytes + 15) & ~(size_t)15;
-    int *loff = reinterpret_cast<int *>(smem + off);                  // [31] start of each limb's run in `slinks`
+    float4 *row = reinterpret_cast<float4 *>(smem);                       // [S] {total, gate, reach, count bits}
+    int2 *slot = reinterpret_cast<int2 *>(smem + (size_t)S * 16);         // [S][18] {id, limb score bits}
+    size_t off = (size_t)S * kBodyBytes;
+    int *loff = reinterpret_cast<int *>(smem + off);                      // [31] start of each limb's run in `slinks`
     off += 32 * sizeof(int);
     DevLink *slinks = reinterpret_cast<DevLink *>(smem + off);
     const int slots = (int)((smem_bytes - off) / sizeof(DevLink));
 
     // ---- stage the connections (written by other CTAs: read through L2) ----
-    if (tid == 0) {
-        int acc = 0;
-        for (int l = 0; l < kLimbs; l++) {
-            loff[l] = acc;
-            acc += __ldcg(a.link_count + img * kLimbs + l);
+    if (tid < 32) {
+        const int n = (tid < kLimbs) ? __ldcg(a.link_count + img * kLimbs + tid) : 0;
+        int incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
         }
-        loff[kLimbs] = acc;
+        loff[tid] = incl - n;  // loff[30] = total, loff[31] unused
     }
+    // the first 32 rows can be scanned without a bounds test: give them ids that match nothing
+    for (int i = tid; i < 32 * kParts; i += (int)blockDim.x) slot[i] = make_int2(kDeadId, 0);
     __syncthreads();
     for (int l = warp; l < kLimbs; l += (int)(blockDim.x >> 5)) {
         const int n = loff[l + 1] - loff[l];
-        const float2 *src = reinterpret_cast<const float2 *>(a.links + ((size_t)img * kLimbs + l) * a.cap);
-        float2 *dst = reinterpret_cast<float2 *>(slinks + loff[l]);
+        const float4 *src = reinterpret_cast<const float4 *>(a.links + ((size_t)img * kLimbs + l) * a.cap);
+        float4 *dst = reinterpret_cast<float4 *>(slinks + loff[l]);
         const int fit = max(0, min(n, slots - loff[l]));
-        for (int i = lane; i < fit * 3; i += 32) dst[i] = __ldcg(src + i);  // 24-byte records as three float2
+        for (int i = lane; i < fit * 2; i += 32) dst[i] = __ldcg(src + i);  // 32-byte records as two float4
     }
     __syncthreads();
     if (warp != 0) return;
@@ -75,89 +92,97 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
         const int nl = loff[limb + 1] - base_slot;
         const DevLink *G = a.links + ((size_t)img * kLimbs + limb) * a.cap;
         auto fetch = [&](int li) -> DevLink {
-            DevLink l;
+            union {
+                float4 q[2];
+                DevLink l;
+            } u;
             if (base_slot + li < slots) {
-                l = slinks[base_slot + li];
+                const float4 *p = reinterpret_cast<const float4 *>(slinks + base_slot + li);
+                u.q[0] = p[0];
+                u.q[1] = p[1];
             } else {  // more connections than the shared run holds: read the rest through L2
-                const float2 *g2 = reinterpret_cast<const float2 *>(G + li);
-                const float2 q0 = __ldcg(g2), q1 = __ldcg(g2 + 1), q2 = __ldcg(g2 + 2);
-                l.id_a = __float_as_int(q0.x);
-                l.id_b = __float_as_int(q0.y);
-                l.limb = q1.x;
-                l.len = q1.y;
-                l.score_a = q2.x;
-                l.score_b = q2.y;
+                const float4 *p = reinterpret_cast<const float4 *>(G + li);
+                u.q[0] = __ldcg(p);
+                u.q[1] = __ldcg(p + 1);
             }
-            return l;
+            return u.l;
         };
         DevLink nxt;
         if (nl > 0) nxt = fetch(0);
         for (int li = 0; li < nl; li++) {
             const DevLink l = nxt;
             if (li + 1 < nl) nxt = fetch(li + 1);  // off the dependent chain
-            // :143-150 scan: first two matching rows, total number of matches.  Every lane also reads the fields of
-            // its row that the one-match case needs, so that case continues from registers (one shuffle) instead of
-            // a second round of dependent shared-memory loads.
+            // :143-150 scan: first two matching rows, total number of matches
             int hits = 0, first = 0, second = 0;
-            int f_idb = -1;
-            float f_scb = 0.f, f_reach = 0.f, f_total = 0.f;
-            for (int base = 0; base < nb; base += 32) {
-                const int s = base + lane;
-                const bool valid = s < nb;
-                const int ia = valid ? ids[s * kParts + pa] : -2;
-                const int ibv = valid ? ids[s * kParts + pb] : -2;
-                const float scb = valid ? sc[s * kParts + pb] : 0.f;
-                const float rch = valid ? reach[s] : 0.f;
-                const float tot = valid ? total[s] : 0.f;
-                const uint32_t bal = __ballot_sync(0xffffffffu, valid && (ia == l.id_a || ibv == l.id_b));
-                if (bal) {
-                    const int p0 = __ffs(bal) - 1;
-                    if (hits == 0) {
-                        first = base + p0;
-                        f_idb = __shfl_sync(0xffffffffu, ibv, p0);
-                        f_scb = __shfl_sync(0xffffffffu, scb, p0);
-                        f_reach = __shfl_sync(0xffffffffu, rch, p0);
-                        f_total = __shfl_sync(0xffffffffu, tot, p0);
-                        const uint32_t rest = bal & (bal - 1);
-                        if (rest) second = base + __ffs(rest) - 1;
-                    } else if (hits == 1) {
-                        second = base + p0;
+            int2 my_pb;
+            float4 my_row;
+            if (nb <= 32) {
+                // one row per lane; rows >= nb still hold the never-matching initial ids, so no bounds test
+                const int ia = slot[lane * kParts + pa].x;
+                my_pb = slot[lane * kParts + pb];
+                my_row = row[lane];
+                const uint32_t bal = __ballot_sync(0xffffffffu, ia == l.id_a || my_pb.x == l.id_b);
+                hits = __popc(bal);
+                first = __ffs(bal) - 1;
+                second = __ffs(bal & (bal - 1)) - 1;
+            } else {
+                my_pb = make_int2(-1, 0);
+                my_row = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int base = 0; base < nb; base += 32) {
+                    const int s = base + lane;
+                    int ia = kDeadId;
+                    int2 pbv = make_int2(kDeadId, 0);
+                    float4 rw = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (s < nb) {
+                        ia = slot[s * kParts + pa].x;
+                        pbv = slot[s * kParts + pb];
+                        rw = row[s];
                     }
-                    hits += __popc(bal);
+                    const uint32_t bal = __ballot_sync(0xffffffffu, ia == l.id_a || pbv.x == l.id_b);
+                    if (bal) {
+                        const int p0 = __ffs(bal) - 1;
+                        if (hits == 0) {
+                            first = base + p0;
+                            my_pb = pbv;  // the owner lane of row `first` keeps that row's values
+                            my_row = rw;
+                            const uint32_t rest = bal & (bal - 1);
+                            if (rest) second = base + __ffs(rest) - 1;
+                        } else if (hits == 1) {
+                            second = base + p0;
+                        }
+                        hits += __popc(bal);
+                    }
                 }
             }
-            if (hits == 1) {  // :152-180
-                if (lane == 0) {
-                    const int f = first;
-                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(f_reach, __int2float_rn(a.len_rate))));  // :154
-                    const int cur_id = f_idb;
-                    const float cur_sc = f_scb;
-                    const float add = __fadd_rn(l.score_b, l.limb);
-                    if (cur_id == -1 && gate > l.len) {
-                        ids[f * kParts + pb] = l.id_b;
-                        sc[f * kParts + pb] = l.limb;
-                        count[f] += 1;
-                        reach[f] = fmaxf(f_reach, l.len);
-                        total[f] = __fadd_rn(f_total, add);
-                    } else if ((cur_id != l.id_b && cur_sc <= l.limb && gate > l.len) || (cur_id == l.id_b && cur_sc <= l.limb)) {
-                        ids[f * kParts + pb] = l.id_b;
-                        sc[f * kParts + pb] = l.limb;
-                        // :168-169 / :177-178 — subtracts the values just written, then adds them back
-                        total[f] = __fadd_rn(__fsub_rn(f_total, add), add);
-                        reach[f] = fmaxf(f_reach, l.len);
-                    }
+            if (hits == 1) {  // :152-180, on the lane that owns the row, from the values it loaded during the scan
+                const int f = first;
+                const float gate = my_row.y;  // :154
+                const int cur_id = my_pb.x;
+                const float cur_sc = __int_as_float(my_pb.y);
+                const float add = __fadd_rn(l.score_b, l.limb);
+                const bool grow = (cur_id == -1) & (gate > l.len);
+                const bool swap = !grow & (cur_sc <= l.limb) & ((cur_id == l.id_b) | ((cur_id != l.id_b) & (gate > l.len)));
+                if ((lane == (f & 31)) & (grow | swap)) {
+                    slot[f * kParts + pb] = make_int2(l.id_b, __float_as_int(l.limb));
+                    float4 nr;
+                    // swap (:168-169 / :177-178) subtracts the values just written, then adds them back
+                    nr.x = grow ? __fadd_rn(my_row.x, add) : __fadd_rn(__fsub_rn(my_row.x, add), add);
+                    nr.y = fmaxf(gate, l.gate);
+                    nr.z = fmaxf(my_row.z, l.len);
+                    nr.w = __int_as_float(__float_as_int(my_row.w) + (grow ? 1 : 0));
+                    row[f] = nr;
                 }
                 __syncwarp();
             } else if (hits == 2) {  // :182-256
                 const int f = first, g = second;
-                int idm = -1, ido = -1;
-                float scm = 0.f, sco = 0.f;
+                int2 vm = make_int2(-1, 0), vo = make_int2(-1, 0);
                 if (lane < kParts) {
-                    idm = ids[f * kParts + lane];
-                    ido = ids[g * kParts + lane];
-                    scm = sc[f * kParts + lane];
-                    sco = sc[g * kParts + lane];
+                    vm = slot[f * kParts + lane];
+                    vo = slot[g * kParts + lane];
                 }
+                const float4 rf = row[f], rg = row[g];
+                const int idm = vm.x, ido = vo.x;
+                const float scm = __int_as_float(vm.y), sco = __int_as_float(vo.y);
                 const bool hm = idm > 0, ho = ido > 0;  // :198-199 peak id 0 counts as unassigned
                 const bool overlap = __ballot_sync(0xffffffffu, hm && ho) != 0;
                 if (!overlap) {
@@ -170,32 +195,21 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                         if (io > 0) low_o = (low_o == 0.0f) ? so : (so < low_o ? so : low_o);
                     }
                     const float floor_score = __fmul_rn((low_o < low_m ? low_o : low_m), a.merge_tol);  // :219
-                    const float gate = __int2float_rn(__float2int_rz(__fmul_rn(reach[f], __int2float_rn(a.len_rate))));  // :186
-                    if (l.limb >= floor_score || l.len < gate) {  // :220
-                        if (lane < kParts) {  // :222-225
-                            ids[f * kParts + lane] = idm + (ido + 1);
-                            sc[f * kParts + lane] = __fadd_rn(scm, __fadd_rn(sco, 1.0f));
+                    if (l.limb >= floor_score || l.len < rf.y) {  // :220, rf.y = (int)(length*16) of row f (:186)
+                        if (lane < kParts) {
+                            // :222-225 ids and scores are ADDED (+1 undoes the -1 of an empty slot)
+                            slot[f * kParts + lane] = make_int2(idm + (ido + 1), __float_as_int(__fadd_rn(scm, __fadd_rn(sco, 1.0f))));
+                            slot[g * kParts + lane] = make_int2(kDeadId, 0);  // :229 erase
                         }
                         if (lane == 0) {  // :226-228
-                            count[f] += count[g];
-                            reach[f] = fmaxf(reach[f], l.len);
-                            total[f] = __fadd_rn(total[f], __fadd_rn(total[g], l.limb));
+                            float4 nr;
+                            nr.x = __fadd_rn(rf.x, __fadd_rn(rg.x, l.limb));
+                            nr.y = fmaxf(rf.y, l.gate);
+                            nr.z = fmaxf(rf.z, l.len);
+                            nr.w = __int_as_float(__float_as_int(rf.w) + __float_as_int(rg.w));
+                            row[f] = nr;
+                            row[g] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
                         }
-                        __syncwarp();
-                        // :229 erase row g: every lane shifts its own column down, rows in increasing order
-                        for (int r = g; r < nb - 1; r++) {
-                            if (lane < kParts) {
-                                ids[r * kParts + lane] = ids[(r + 1) * kParts + lane];
-                                sc[r * kParts + lane] = sc[(r + 1) * kParts + lane];
-                            } else if (lane == kParts) {
-                                total[r] = total[r + 1];
-                            } else if (lane == kParts + 1) {
-                                count[r] = count[r + 1];
-                            } else if (lane == kParts + 2) {
-                                reach[r] = reach[r + 1];
-                            }
-                        }
-                        nb--;
                     }
                 }
                 // overlap: DELETE_SHARED_JOINTS is const false (pafprocess.h:16) => the branch at :231-256 does nothing
@@ -203,14 +217,12 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
             } else if (hits == 0) {  // :257-273
                 if (nb < S) {
                     if (lane < kParts) {
-                        ids[nb * kParts + lane] = (lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1);
-                        sc[nb * kParts + lane] = (lane == pa || lane == pb) ? l.limb : -1.0f;
+                        const bool end = (lane == pa || lane == pb);
+                        slot[nb * kParts + lane] = make_int2((lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1),
+                                                             __float_as_int(end ? l.limb : -1.0f));
                     }
-                    if (lane == 0) {
-                        count[nb] = 2;
-                        reach[nb] = l.len;
-                        total[nb] = __fadd_rn(__fadd_rn(l.score_a, l.score_b), l.limb);
-                    }
+                    if (lane == 0)
+                        row[nb] = make_float4(__fadd_rn(__fadd_rn(l.score_a, l.score_b), l.limb), l.gate, l.len, __int_as_float(2));
                     nb++;
                 } else {
                     overflow = true;
@@ -221,23 +233,29 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
         }
     }
 
-    // :277-282 filter (order preserved) + results of the getters (:287-297)
+    // :277-282 filter (order preserved; erased rows carry count -1) + results of the getters (:287-297)
     int n_out = 0;
     ibp_human *out = a.humans + (size_t)img * a.max_humans;
     for (int base = 0; base < nb; base += 32) {
         const int s = base + lane;
         bool keep = false;
-        if (s < nb) keep = !(count[s] < a.min_parts || __fdiv_rn(total[s], __int2float_rn(count[s])) < a.min_score);
+        float4 rw = make_float4(0.f, 0.f, 0.f, 0.f);
+        int cnt = -1;
+        if (s < nb) {
+            rw = row[s];
+            cnt = __float_as_int(rw.w);
+            keep = cnt >= 0 && !(cnt < a.min_parts || __fdiv_rn(rw.x, __int2float_rn(cnt)) < a.min_score);
+        }
         const uint32_t bal = __ballot_sync(0xffffffffu, keep);
         if (keep) {
             const int o = n_out + __popc(bal & ((1u << lane) - 1u));
             if (o < a.max_humans) {
                 ibp_human hmn;
-                for (int k = 0; k < kParts; k++) hmn.peak_id[k] = ids[s * kParts + k];
-                hmn.score = __fdiv_rn(total[s], __int2float_rn(count[s]));
-                hmn.total = total[s];
-                hmn.count = count[s];
-                hmn.reach = reach[s];
+                for (int k = 0; k < kParts; k++) hmn.peak_id[k] = slot[s * kParts + k].x;
+                hmn.score = __fdiv_rn(rw.x, __int2float_rn(cnt));
+                hmn.total = rw.x;
+                hmn.count = cnt;
+                hmn.reach = rw.z;
                 out[o] = hmn;
             }
         }

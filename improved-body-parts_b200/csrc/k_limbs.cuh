@@ -57,6 +57,8 @@ struct LimbArgs {
     unsigned *ticket;       // (batch) zero on entry, left zero on exit
     int smem_bytes;         // dynamic shared memory of the launch
     int debug;              // experiments only (IBP_DEBUG): 1 = skip grouping, 2 = skip scoring
+    const int *order;       // (batch) image handled by grid row y, or null: identity
+    unsigned long long *timeline;  // experiments only: (batch, 31, 4) %globaltimer stamps, or null
     GroupArgs group;
 };
 
@@ -102,7 +104,8 @@ struct PairGeo {  // step geometry of one pair (pafprocess.cpp:66-73, :311-316)
 template <typename T>
 __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int limb = blockIdx.x, img = blockIdx.y;
+    const int limb = blockIdx.x;
+    const int img = a.order ? a.order[blockIdx.y] : (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int pa = c_limb_a[limb], pb = c_limb_b[limb];
     const int nA = a.part_count[img * kParts + pa], nB = a.part_count[img * kParts + pb];
@@ -147,6 +150,14 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     __shared__ float tab4[4][4];
 
     int n_links = 0;  // meaningful on thread 0 only
+    auto stamp = [&](int row, int col) {
+        if (a.timeline && tid == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.timeline[((size_t)img * 31 + row) * 4 + col] = t;
+        }
+    };
+    stamp(limb, 0);
     // no pair => no candidate => no connection (covers the both-empty skip at :57)
     if (nA > 0 && nB > 0) {
         // source planes of this limb (feature-resolution modes)
@@ -211,6 +222,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
             smp.base = reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride;
         }
 
+        stamp(limb, 1);
         // ---- score all pairs; compact the accepted ones in pair order ----
         const int npairs = (a.debug & 2) ? 0 : nA * nB;
         int ncand = 0;
@@ -299,6 +311,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
             ncand += tot;
             __syncthreads();
         }
+        stamp(limb, 2);
         if (ncand > a.cand_cap) {
             if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
             ncand = a.cand_cap;
@@ -396,6 +409,8 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
                             l.id_b = sB[ib].id;
                             l.limb = cand_limb[cidx];
                             l.len = limb_length(sA[ia], sB[ib]);
+                            l.gate = length_gate(l.len, a.group.len_rate);
+                            l.pad = 0.f;
                             // pafprocess.cpp:160,261-262 look the peak scores up as peak_infos_line[peak_id]: the
                             // part-major list indexed by ARRIVAL id — the same peak only when the caller's joint
                             // list is sorted by part (evaluate.py:99-103 does that); keep the quirk
@@ -414,6 +429,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         }
     }
     if (tid == 0) *link_count = n_links;
+    stamp(limb, 3);
 
     // ---- the last CTA of this image groups its connections into people ----
     if (warp == 0) __threadfence();  // only warp 0 wrote connections / the count
@@ -427,7 +443,9 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     if (!s_last) return;
     __threadfence();
     if (a.debug & 1) return;
+    stamp(30, 0);
     group_image(a.group, img, smem_raw, (size_t)a.smem_bytes);
+    stamp(30, 1);
 }
 
 }  // namespace ibp

@@ -53,6 +53,9 @@ struct PeakArgs {
     int line_stride;
     int *n_peaks;         // (batch)
     uint32_t *status;     // (batch)
+    unsigned *batch_ticket;  // one counter, zero on entry, left zero on exit
+    int *order;           // (batch) images sorted by descending number of peaks, written by the last CTA of the launch
+    int batch;
 };
 
 constexpr int kPeakThreads = 256;
@@ -444,6 +447,29 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
             o.part = p;
             a.line[(size_t)img * a.line_stride + j] = o;
         }
+    }
+
+    // ---- the last image to be packed ranks the whole batch: heaviest image first ----
+    // The limb kernel walks images in this order so that the longest grouping chains (a sequential tail of one warp
+    // per image) start first and overlap the rest of the batch instead of trailing it.
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned t = atomicAdd(a.batch_ticket, 1u);
+        s_last = (t == (unsigned)a.batch - 1);
+        if (s_last) *a.batch_ticket = 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int b = tid; b < a.batch; b += kPeakThreads) {
+        const int mine_n = __ldcg(a.n_peaks + b);
+        int rank = 0;
+        for (int u = 0; u < a.batch; u++) {
+            const int other = __ldcg(a.n_peaks + u);
+            rank += (other > mine_n) || (other == mine_n && u < b);
+        }
+        a.order[rank] = b;
     }
 }
 

@@ -1,0 +1,34 @@
+#!/usr/bin/env python
+"""Experiments only: run one bench batch with IBP_DEBUG=8 and summarise the per-CTA %globaltimer stamps of the limb
+kernel (start, staged, scored, done per (image, limb); grouping start/end per image)."""
+import os
+import sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+os.environ["IBP_DEBUG"] = "8"
+os.environ["IBP_TIMELINE"] = "/tmp/ibp_timeline.bin"
+import torch
+from improved_body_parts_b200 import synth
+from improved_body_parts_b200.pipeline import PostProcessor
+
+B = 64
+batch = torch.from_numpy(synth.make_batch(2000, B, people=(1, 10))).cuda()
+pp = PostProcessor(device=0, max_batch=B)
+for _ in range(3):
+    res = pp(batch, 512)
+t = np.fromfile("/tmp/ibp_timeline.bin", dtype=np.uint64).reshape(B, 31, 4).astype(np.float64)
+t0 = t[:, :30, 0].min()
+T = (t - t0) / 1000.0
+limb = T[:, :30, :]
+print("limb CTAs: start min/max %.1f %.1f us, end max %.1f" % (limb[:, :, 0].min(), limb[:, :, 0].max(), limb[:, :, 3].max()))
+d = limb[:, :, 3] - limb[:, :, 0]
+print("limb CTA duration mean %.2f max %.2f; stage %.2f score %.2f tail %.2f (means over CTAs with pairs)" % (
+    d.mean(), d.max(), np.nanmean(np.where(t[:, :30, 1] > 0, limb[:, :, 1] - limb[:, :, 0], np.nan)),
+    np.nanmean(np.where(t[:, :30, 2] > 0, limb[:, :, 2] - limb[:, :, 1], np.nan)),
+    np.nanmean(np.where(t[:, :30, 2] > 0, limb[:, :, 3] - limb[:, :, 2], np.nan))))
+g0, g1 = T[:, 30, 0], T[:, 30, 1]
+links = np.array([int(h.shape[0]) for h in res.humans])
+print("group: start min/max %.1f %.1f, end max %.1f, duration mean %.2f max %.2f" % (g0.min(), g0.max(), g1.max(), (g1 - g0).mean(), (g1 - g0).max()))
+order = np.argsort(g1)[-8:]
+for b in order:
+    print("img %2d limb-done %.1f group %.1f..%.1f (%.1f us) peaks %d humans %d" % (b, limb[b, :, 3].max(), g0[b], g1[b], g1[b] - g0[b], res.n_peaks[b], res.n_humans[b]))
