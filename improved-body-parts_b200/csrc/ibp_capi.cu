@@ -89,6 +89,8 @@ struct ibp_handle {
     int *d_order = nullptr;        // [max_batch] images by descending peak count (written by the peak kernel)
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
     unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
+    unsigned long long *d_timeline_pk = nullptr;  // experiments only (IBP_DEBUG & 16)
+    size_t timeline_pk_n = 0;
     float *d_fused = nullptr;
     size_t fused_floats = 0;
     void *d_stage = nullptr;  // host input staging / legacy limb map
@@ -158,6 +160,7 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_band_count);
     free_dev(h->d_ticket);
     free_dev(h->d_timeline);
+    free_dev(h->d_timeline_pk);
     free_dev(h->d_order);
     free_host(h->h_n_peaks);
     free_host(h->h_part_count);
@@ -177,7 +180,7 @@ void destroy_buffers(ibp_handle *h) {
 size_t limb_phase_bytes(const ibp_handle *h, size_t plane_bytes) {
     size_t region0 = std::max(plane_bytes, (size_t)h->L.max_candidates_per_limb * 8);
     region0 = (region0 + 15) & ~(size_t)15;
-    return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2) +
+    return region0 + (size_t)h->L.max_candidates_per_limb * 16 + (size_t)h->L.max_peaks_per_part * (2 * sizeof(DevPeak) + 2 + 8) + 32 +
            (size_t)kPairChunk * (sizeof(PairGeo) + (size_t)h->P.max_steps * 4) + 16;
 }
 // ... and of the grouping phase that the last CTA of an image runs in the same allocation (k_group.cuh): the
@@ -445,6 +448,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.nbands = (fh + a.rows_per_band - 1) / a.rows_per_band;
     const int rows_buf = std::min(a.rows_per_band + 2 * a.halo, fh);
     size_t band_bytes = std::max((size_t)rows_buf * fw * 4, (size_t)(kParts * a.nbands + 1) * 4);
+    band_bytes = std::max(band_bytes, (size_t)batch * 4);
     band_bytes = (band_bytes + 15) & ~(size_t)15;
     a.band_bytes = (int)band_bytes;
     a.up = h->P.upsample;
@@ -469,6 +473,21 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.order = h->d_order;
     a.batch = batch;
     h->order_batch = batch;
+    a.timeline = nullptr;
+    {
+        const char *dbg = getenv("IBP_DEBUG");
+        if (dbg && (atoi(dbg) & 16)) {  // experiments only: per-CTA %globaltimer stamps of the peak kernel
+            const size_t n = (size_t)h->L.max_batch * kParts * a.nbands * 6;
+            if (!h->d_timeline_pk) {
+                CU(cudaMalloc(&h->d_timeline_pk, n * sizeof(unsigned long long)));
+                h->timeline_pk_n = n;
+            }
+            if (h->timeline_pk_n >= n) {
+                CU(cudaMemsetAsync(h->d_timeline_pk, 0, n * sizeof(unsigned long long), st));
+                a.timeline = h->d_timeline_pk;
+            }
+        }
+    }
     const int side = 2 * a.win + 1;
     size_t smem = band_bytes;
     smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
@@ -700,6 +719,15 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
         CU(cudaMemcpy(tl.data(), h->d_timeline, tl.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
         const char *path = getenv("IBP_TIMELINE");
         if (FILE *f = fopen(path ? path : "ibp_timeline.bin", "wb")) {
+            fwrite(tl.data(), sizeof(unsigned long long), tl.size(), f);
+            fclose(f);
+        }
+    }
+    if (h->d_timeline_pk) {
+        std::vector<unsigned long long> tl(h->timeline_pk_n);
+        CU(cudaMemcpy(tl.data(), h->d_timeline_pk, tl.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        const char *path = getenv("IBP_TIMELINE_PK");
+        if (FILE *f = fopen(path ? path : "ibp_timeline_pk.bin", "wb")) {
             fwrite(tl.data(), sizeof(unsigned long long), tl.size(), f);
             fclose(f);
         }

@@ -131,6 +131,11 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     unsigned char *used_b = smem_raw + off;
     off += (size_t)a.cap;
     off = (off + 15) & ~(size_t)15;
+    float *line_a = reinterpret_cast<float *>(smem_raw + off);  // peak_infos_line[id].score of each candidate end
+    off += (size_t)a.cap * 4;
+    float *line_b = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)a.cap * 4;
+    off = (off + 15) & ~(size_t)15;
     // everything from here on is idle while the plane is staged: the twin ring borrows it
     const size_t ring_off = off;
     uint64_t *keys = reinterpret_cast<uint64_t *>(smem_raw + off);
@@ -186,13 +191,21 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         cubic_tab4_init(tab4);
         const DevPeak *gA = a.peaks + ((size_t)img * kParts + pa) * a.cap;
         const DevPeak *gB = a.peaks + ((size_t)img * kParts + pb) * a.cap;
+        // pafprocess.cpp:160,261-262 look the peak scores up as peak_infos_line[peak_id]: the part-major list indexed
+        // by ARRIVAL id — the same peak only when the caller's joint list is sorted by part (evaluate.py:99-103 does
+        // that); keep the quirk, but fetch the values now so that the greedy loop never waits on global memory
+        const ibp_peak *line = a.line + (size_t)img * a.line_stride;
         for (int i = tid; i < nA; i += kLimbThreads) {
-            sA[i] = gA[i];
+            const DevPeak p = gA[i];
+            sA[i] = p;
             used_a[i] = 0;
+            line_a[i] = line[min(max(p.id, 0), a.line_stride - 1)].score;
         }
         for (int i = tid; i < nB; i += kLimbThreads) {
-            sB[i] = gB[i];
+            const DevPeak p = gB[i];
+            sB[i] = p;
             used_b[i] = 0;
+            line_b[i] = line[min(max(p.id, 0), a.line_stride - 1)].score;
         }
         __syncthreads();
 
@@ -411,12 +424,8 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
                             l.len = limb_length(sA[ia], sB[ib]);
                             l.gate = length_gate(l.len, a.group.len_rate);
                             l.pad = 0.f;
-                            // pafprocess.cpp:160,261-262 look the peak scores up as peak_infos_line[peak_id]: the
-                            // part-major list indexed by ARRIVAL id — the same peak only when the caller's joint
-                            // list is sorted by part (evaluate.py:99-103 does that); keep the quirk
-                            const ibp_peak *line = a.line + (size_t)img * a.line_stride;
-                            l.score_a = line[min(l.id_a, a.line_stride - 1)].score;
-                            l.score_b = line[min(l.id_b, a.line_stride - 1)].score;
+                            l.score_a = line_a[ia];
+                            l.score_b = line_b[ib];
                             out[nl] = l;
                             valid = false;
                         }

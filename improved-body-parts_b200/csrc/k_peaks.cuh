@@ -54,6 +54,7 @@ struct PeakArgs {
     int *n_peaks;         // (batch)
     uint32_t *status;     // (batch)
     unsigned *batch_ticket;  // one counter, zero on entry, left zero on exit
+    unsigned long long *timeline;  // experiments only: (batch, 18, nbands, 6) %globaltimer stamps, or null
     int *order;           // (batch) images sorted by descending number of peaks, written by the last CTA of the launch
     int batch;
 };
@@ -112,6 +113,14 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     const int r0 = bandi * a.rows_per_band, r1 = min(r0 + a.rows_per_band, h);
     const int l0 = max(r0 - a.halo, 0), l1 = min(r1 + a.halo, h);
 
+    auto stamp = [&](int col) {
+        if (a.timeline && tid == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.timeline[((((size_t)img * kParts + part) * a.nbands) + bandi) * 6 + col] = t;
+        }
+    };
+    stamp(0);
     // carve shared memory
     float *band = reinterpret_cast<float *>(smem_raw);
     size_t off = (size_t)a.band_bytes;
@@ -126,9 +135,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     off = (off + 15) & ~(size_t)15;
     float *ring = reinterpret_cast<float *>(smem_raw + off);      // twin band while staging (ring_bytes)
     __shared__ uint64_t bars[2];
-    __shared__ int warp_tot[nwarps];
     __shared__ int s_found;
-    __shared__ int s_last;
     __shared__ float tab4[4][4];
 
     {
@@ -160,59 +167,69 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
         }
     }
 #define BAND(y, x) band[((y)-l0) * w + (x)]
+    stamp(1);
 
     // ---- non-maximum suppression over the owned rows ----
-    auto test_pixel = [&](int y, int x, float v) {
-        bool keep;
-        if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
-            keep = v > a.thr;
-            if (keep) {
-                if (y > 0) keep = keep && (v >= BAND(y - 1, x));
-                if (y < h - 1) keep = keep && (v >= BAND(y + 1, x));
-                if (x > 0) keep = keep && (v >= BAND(y, x - 1));
-                if (x < w - 1) keep = keep && (v >= BAND(y, x + 1));
-            }
-        } else {
-            // util.py:181-185: hmax == heat, heat >= thre, and heat*keep != 0
-            keep = (v >= a.thr) && (v != 0.0f);
-            if (keep) {
-                const int ya = max(y - 1, 0), yb = min(y + 1, h - 1), xa = max(x - 1, 0), xb = min(x + 1, w - 1);
-                for (int q = ya; q <= yb; q++)
-                    for (int p = xa; p <= xb; p++) keep = keep && (v >= BAND(q, p));
-            }
-        }
+    // Neighbour rows / columns are clamped to the map, which is what both border rules amount to: scipy's 'reflect'
+    // and torch's reflect-pad of 1 only ever add values that are already inside the 3x3 window of the pixel, so a
+    // clamped (repeated) neighbour changes no comparison.  All neighbour loads are unconditional and independent
+    // (one round of shared-memory latency per group of four pixels instead of one per comparison).
+    const bool cross = (a.flavour == IBP_PEAKS_CROSS_REFINE);
+    auto emit = [&](bool keep, int y, int x) {
         if (keep) {
             const int slot = atomicAdd(&s_found, 1);
             if (slot < a.cap) found[slot] = y * w + x;
         }
     };
+    // centre test: heatmap_nms keeps value > 0.1 (parse_skeletons.py:116); keypoint_heatmap_nms keeps value >= thre and
+    // a non-zero product heat*keep (util.py:184-185)
+    auto centre_ok = [&](float v) { return cross ? (v > a.thr) : ((v >= a.thr) && (v != 0.0f)); };
     const int npix = (r1 - r0) * w;
     const float *own = &BAND(r0, 0);
     const float gate = a.thr;  // both flavours need v >= thr at least
     if ((w & 3) == 0) {
         const float4 *own4 = reinterpret_cast<const float4 *>(own);
+        const int wv = w >> 2;
         for (int i4 = tid; i4 < (npix >> 2); i4 += kPeakThreads) {
             const float4 v = own4[i4];
             // cheap reject: nothing at or above the threshold in these four pixels
             if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= gate) {
-                const int i = i4 << 2;
-                const int yy = i / w, x = i - yy * w, y = r0 + yy;
-                test_pixel(y, x, v.x);
-                test_pixel(y, x + 1, v.y);
-                test_pixel(y, x + 2, v.z);
-                test_pixel(y, x + 3, v.w);
+                const int yy = i4 / wv, x = (i4 - yy * wv) << 2, y = r0 + yy;
+                const int yu = max(y - 1, 0), yd = min(y + 1, h - 1), xl = max(x - 1, 0), xr = min(x + 4, w - 1);
+                const float4 u = *reinterpret_cast<const float4 *>(&BAND(yu, x));
+                const float4 d = *reinterpret_cast<const float4 *>(&BAND(yd, x));
+                const float l = BAND(y, xl), r = BAND(y, xr);
+                bool k0 = centre_ok(v.x) & (v.x >= u.x) & (v.x >= d.x) & (v.x >= l) & (v.x >= v.y);
+                bool k1 = centre_ok(v.y) & (v.y >= u.y) & (v.y >= d.y) & (v.y >= v.x) & (v.y >= v.z);
+                bool k2 = centre_ok(v.z) & (v.z >= u.z) & (v.z >= d.z) & (v.z >= v.y) & (v.z >= v.w);
+                bool k3 = centre_ok(v.w) & (v.w >= u.w) & (v.w >= d.w) & (v.w >= v.z) & (v.w >= r);
+                if (!cross) {  // 3x3 window: the four diagonals as well
+                    const float ul = BAND(yu, xl), ur = BAND(yu, xr), dl = BAND(yd, xl), dr = BAND(yd, xr);
+                    k0 = k0 & (v.x >= ul) & (v.x >= u.y) & (v.x >= dl) & (v.x >= d.y);
+                    k1 = k1 & (v.y >= u.x) & (v.y >= u.z) & (v.y >= d.x) & (v.y >= d.z);
+                    k2 = k2 & (v.z >= u.y) & (v.z >= u.w) & (v.z >= d.y) & (v.z >= d.w);
+                    k3 = k3 & (v.w >= u.z) & (v.w >= ur) & (v.w >= d.z) & (v.w >= dr);
+                }
+                emit(k0, y, x);
+                emit(k1, y, x + 1);
+                emit(k2, y, x + 2);
+                emit(k3, y, x + 3);
             }
         }
     } else {
         for (int i = tid; i < npix; i += kPeakThreads) {
             const float v = own[i];
             if (v >= gate) {
-                const int yy = i / w;
-                test_pixel(r0 + yy, i - yy * w, v);
+                const int yy = i / w, x = i - yy * w, y = r0 + yy;
+                const int yu = max(y - 1, 0), yd = min(y + 1, h - 1), xl = max(x - 1, 0), xr = min(x + 1, w - 1);
+                bool k = centre_ok(v) & (v >= BAND(yu, x)) & (v >= BAND(yd, x)) & (v >= BAND(y, xl)) & (v >= BAND(y, xr));
+                if (!cross) k = k & (v >= BAND(yu, xl)) & (v >= BAND(yu, xr)) & (v >= BAND(yd, xl)) & (v >= BAND(yd, xr));
+                emit(k, y, x);
             }
         }
     }
     __syncthreads();
+    stamp(2);
     const int n_raw = s_found;
     const int n = min(n_raw, a.cap);
     // rank sort: pixel indices are distinct
@@ -231,7 +248,54 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     for (int k = warp; k < n; k += nwarps) {
         const int pix = sorted[k];
         const int py = pix / w, px = pix - py * w;
-        if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
+        if (a.flavour == IBP_PEAKS_CROSS_REFINE && a.up == 4 && a.win == 2 && px >= 2 && px + 2 < w && py >= 2 && py + 2 < h) {
+            // The common case — a full 5x5 patch up-sampled x4 to 20x20 — entirely in registers: lane X < 20 owns
+            // output column X; its five horizontal sums (one per patch row) stay in registers, and the twenty vertical
+            // combinations use compile-time row indices and the 4x4 phase table.  Same operations in the same order
+            // as the generic path below, so the same bits.
+            const int x0 = px - 2, y0 = py - 2;
+            float best = -INFINITY;
+            int best_idx = 0x7fffffff;
+            if (lane < 20) {
+                const int sx = (lane - 2) >> 2;
+                const float *xw = tab4[(lane - 2) & 3];
+                const int c0 = x0 + clampi(sx - 1, 0, 4), c1 = x0 + clampi(sx, 0, 4);
+                const int c2 = x0 + clampi(sx + 1, 0, 4), c3 = x0 + clampi(sx + 2, 0, 4);
+                float hcol[5];
+#pragma unroll
+                for (int r = 0; r < 5; r++) hcol[r] = hsum4(BAND(y0 + r, c0), BAND(y0 + r, c1), BAND(y0 + r, c2), BAND(y0 + r, c3), xw);
+#pragma unroll
+                for (int Y = 0; Y < 20; Y++) {
+                    const int sy = (Y - 2) >> 2;  // compile-time after unrolling
+                    const int q0 = sy - 1 < 0 ? 0 : (sy - 1 > 4 ? 4 : sy - 1), q1 = sy < 0 ? 0 : (sy > 4 ? 4 : sy);
+                    const int q2 = sy + 1 < 0 ? 0 : (sy + 1 > 4 ? 4 : sy + 1), q3 = sy + 2 < 0 ? 0 : (sy + 2 > 4 ? 4 : sy + 2);
+                    const float v = vsum4(hcol[q0], hcol[q1], hcol[q2], hcol[q3], tab4[(Y - 2) & 3]);
+                    if (v > best) {
+                        best = v;
+                        best_idx = Y * 20 + lane;
+                    }
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
+                if (ov > best || (ov == best && oi < best_idx)) {
+                    best = ov;
+                    best_idx = oi;
+                }
+            }
+            if (lane == 0) {
+                if (best_idx == 0x7fffffff) best_idx = 0;
+                DevPeak p;
+                p.x = x0 * 4 + best_idx % 20;
+                p.y = y0 * 4 + best_idx / 20;
+                p.score = best;
+                p.id = k;
+                out[k] = p;
+            }
+            __syncwarp();
+        } else if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
             const int x0 = max(px - a.win, 0), x1 = min(px + a.win, w - 1);
             const int y0 = max(py - a.win, 0), y1 = min(py + a.win, h - 1);
             const int pw = x1 - x0 + 1, ph = y1 - y0 + 1;
@@ -372,48 +436,59 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
         if (n_raw > a.cap) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
     }
 
-    // ---- last CTA of this image packs ----
+    stamp(3);
+    // ---- last CTA of this image packs (warp 0 only; the other warps leave as soon as their writes are out) ----
     if (lane == 0 && (warp < n || tid == 0)) __threadfence();  // the lanes that wrote peaks / the count
-    __syncthreads();
-    const unsigned ctas_per_image = (unsigned)a.nbands * kParts;
-    if (tid == 0) {
-        const unsigned t = atomicAdd(a.ticket + img, 1u);
-        s_last = (t == ctas_per_image - 1);
-        if (s_last) a.ticket[img] = 0;  // ready for the next launch
+    if (warp != 0) {
+        asm volatile("bar.arrive 1, %0;" ::"n"(kPeakThreads) : "memory");
+        return;
     }
-    __syncthreads();
-    if (!s_last) return;
+    asm volatile("bar.sync 1, %0;" ::"n"(kPeakThreads) : "memory");
+    stamp(4);
+    const unsigned ctas_per_image = (unsigned)a.nbands * kParts;
+    int last = 0;
+    if (lane == 0) {
+        const unsigned t = atomicAdd(a.ticket + img, 1u);
+        last = (t == ctas_per_image - 1);
+        if (last) a.ticket[img] = 0;  // ready for the next launch
+    }
+    last = __shfl_sync(0xffffffffu, last, 0);
+    stamp(5);
+    if (!last) return;
     __threadfence();
 
     // exclusive scan of the band counts in (part, band) order; re-use the band buffer (>= 18*nbands+1 ints by launch)
     int *offs = reinterpret_cast<int *>(smem_raw);
     const int items = kParts * a.nbands;
     const int *bc = a.band_count + (size_t)img * items;
-    const int per = (items + kPeakThreads - 1) / kPeakThreads;
-    const int i_begin = min(tid * per, items), i_end = min(i_begin + per, items);
-    int mine = 0;
-    for (int i = i_begin; i < i_end; i++) mine += __ldcg(bc + i);
-    int total;
-    int run = block_exclusive_scan(mine, warp_tot, total);
-    for (int i = i_begin; i < i_end; i++) {
-        offs[i] = run;
-        run += __ldcg(bc + i);
+    int total = 0;
+    for (int base = 0; base < items; base += 32) {
+        const int i = base + lane;
+        const int c = (i < items) ? __ldcg(bc + i) : 0;
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (i < items) offs[i] = total + incl - c;
+        total += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (tid == 0) offs[items] = total;
-    __syncthreads();
+    if (lane == 0) offs[items] = total;
+    __syncwarp();
     // per-part counts, clamped to the per-part capacity
     bool over = false;
-    if (tid < kParts) {
-        const int c = offs[(tid + 1) * a.nbands] - offs[tid * a.nbands];
+    if (lane < kParts) {
+        const int c = offs[(lane + 1) * a.nbands] - offs[lane * a.nbands];
         over = c > a.cap;
-        a.part_count[img * kParts + tid] = min(c, a.cap);
+        a.part_count[img * kParts + lane] = min(c, a.cap);
     }
-    if (__syncthreads_or(over)) {
+    if (__any_sync(0xffffffffu, over)) {
         // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
-        if (tid == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
+        if (lane == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
     }
-    if (tid == 0) a.n_peaks[img] = min(total, a.line_stride);
-    for (int j = tid; j < total; j += kPeakThreads) {
+    if (lane == 0) a.n_peaks[img] = min(total, a.line_stride);
+    for (int j = lane; j < total; j += 32) {
         // item holding global position j: last i with offs[i] <= j
         int lo = 0, hi = items - 1;
         while (lo < hi) {
@@ -453,20 +528,24 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     // The limb kernel walks images in this order so that the longest grouping chains (a sequential tail of one warp
     // per image) start first and overlap the rest of the batch instead of trailing it.
     __threadfence();
-    __syncthreads();
-    if (tid == 0) {
+    __syncwarp();
+    if (lane == 0) {
         const unsigned t = atomicAdd(a.batch_ticket, 1u);
-        s_last = (t == (unsigned)a.batch - 1);
-        if (s_last) *a.batch_ticket = 0;
+        last = (t == (unsigned)a.batch - 1);
+        if (last) *a.batch_ticket = 0;
     }
-    __syncthreads();
-    if (!s_last) return;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
     __threadfence();
-    for (int b = tid; b < a.batch; b += kPeakThreads) {
-        const int mine_n = __ldcg(a.n_peaks + b);
+    // counts into shared memory first (one round of loads), then an all-pairs rank from there
+    int *cnt = reinterpret_cast<int *>(smem_raw);  // band buffer, free again; launch guarantees >= batch ints
+    for (int b = lane; b < a.batch; b += 32) cnt[b] = __ldcg(a.n_peaks + b);
+    __syncwarp();
+    for (int b = lane; b < a.batch; b += 32) {
+        const int mine_n = cnt[b];
         int rank = 0;
         for (int u = 0; u < a.batch; u++) {
-            const int other = __ldcg(a.n_peaks + u);
+            const int other = cnt[u];
             rank += (other > mine_n) || (other == mine_n && u < b);
         }
         a.order[rank] = b;

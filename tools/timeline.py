@@ -5,7 +5,8 @@ import os
 import sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ["IBP_DEBUG"] = "8"
+os.environ["IBP_DEBUG"] = "24"
+os.environ["IBP_TIMELINE_PK"] = "/tmp/ibp_timeline_pk.bin"
 os.environ["IBP_TIMELINE"] = "/tmp/ibp_timeline.bin"
 import torch
 from improved_body_parts_b200 import synth
@@ -32,3 +33,14 @@ print("group: start min/max %.1f %.1f, end max %.1f, duration mean %.2f max %.2f
 order = np.argsort(g1)[-8:]
 for b in order:
     print("img %2d limb-done %.1f group %.1f..%.1f (%.1f us) peaks %d humans %d" % (b, limb[b, :, 3].max(), g0[b], g1[b], g1[b] - g0[b], res.n_peaks[b], res.n_humans[b]))
+
+# ---- peak kernel ----
+p = np.fromfile("/tmp/ibp_timeline_pk.bin", dtype=np.uint64).astype(np.float64)
+p = p.reshape(B, 18, -1, 6)
+p0 = p[..., 0].min()
+P = (p - p0) / 1000.0
+names = ["stage", "nms", "sort+refine", "wait warps", "ticket"]
+print("peak CTAs: start max %.1f, end max %.1f us; duration mean %.2f max %.2f" % (P[..., 0].max(), P[..., 5].max(), (P[..., 5] - P[..., 0]).mean(), (P[..., 5] - P[..., 0]).max()))
+for i, nme in enumerate(names):
+    d = P[..., i + 1] - P[..., i]
+    print("  %-12s mean %.2f  p90 %.2f  max %.2f" % (nme, d.mean(), np.percentile(d, 90), d.max()))
