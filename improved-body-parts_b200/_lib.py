@@ -101,6 +101,8 @@ def lib():
     L.ibp_postprocess_batch.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp]
     L.ibp_fetch.restype = ip
     L.ibp_fetch.argtypes = [vp, ip, C.POINTER(BatchView), vp]
+    L.ibp_fetch_subpix.restype = ip
+    L.ibp_fetch_subpix.argtypes = [vp, ip, vp, ip, vp]
     L.ibp_launch_count.restype = C.c_int64
     L.ibp_launch_count.argtypes = [vp]
     L.ibp_set_profiling.restype = ip
@@ -114,7 +116,7 @@ def lib():
 EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp_get_score", "ibp_get_part_x",
            "ibp_get_part_y", "ibp_get_part_score", "ibp_get_status", "ibp_default_params", "ibp_default_limits",
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_upsample_limbs",
-           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_launch_count", "ibp_set_profiling",
+           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_launch_count", "ibp_set_profiling",
            "ibp_get_stage_ms"]
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
@@ -215,6 +217,14 @@ class Handle:
     def postprocess_batch(self, net_out_ptr, on_host, dtype, batch, fh, fw, min_img_size, stream=0):
         check(lib().ibp_postprocess_batch(self._h, net_out_ptr, int(bool(on_host)), dtype, batch, fh, fw,
                                           int(min_img_size), stream))
+
+    def fetch_subpix(self, image, n, stream=0):
+        """(n,2) float64 sub-pixel x, y of image `image` in peak-id order (centroid flavour), after fetch()."""
+        out = np.zeros((max(int(n), 1), 2), dtype=np.float64)
+        rc = lib().ibp_fetch_subpix(self._h, int(image), out.ctypes.data, out.shape[0], stream)
+        if rc < 0:
+            check(rc)
+        return out[:rc]
 
     def fetch(self, batch, stream=0, raise_on_overflow=True):
         view = BatchView()

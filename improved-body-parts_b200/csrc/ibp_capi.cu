@@ -71,7 +71,7 @@ struct ibp_handle {
     int line_stride = 0;
     // device
     DevPeak *d_peaks = nullptr;
-    float *d_subpix = nullptr;
+    double *d_subpix = nullptr;
     int *d_part_count = nullptr;
     DevLink *d_links = nullptr;
     int *d_link_count = nullptr;
@@ -82,7 +82,7 @@ struct ibp_handle {
     uint32_t *d_status = nullptr;
     // scratch of the banded peak kernel and the two ticket counters (last CTA of an image packs / groups)
     DevPeak *d_band_peaks = nullptr;
-    float *d_band_subpix = nullptr;
+    double *d_band_subpix = nullptr;
     int *d_band_count = nullptr;
     int band_slots = 0;  // nbands the scratch was sized for
     unsigned *d_ticket = nullptr;  // [2][max_batch] + 1
@@ -128,7 +128,7 @@ int ensure_bands(ibp_handle *h, int nbands) {
     h->band_slots = 0;
     const size_t n = (size_t)h->L.max_batch * kParts * nbands;
     CU(cudaMalloc(&h->d_band_peaks, n * h->L.max_peaks_per_part * sizeof(DevPeak)));
-    CU(cudaMalloc(&h->d_band_subpix, n * h->L.max_peaks_per_part * 2 * sizeof(float)));
+    CU(cudaMalloc(&h->d_band_subpix, n * h->L.max_peaks_per_part * 2 * sizeof(double)));
     CU(cudaMalloc(&h->d_band_count, n * sizeof(int)));
     h->band_slots = nbands;
     return IBP_OK;
@@ -314,7 +314,7 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
     h->line_stride = (int)(cap * kParts);
     auto alloc = [&]() -> int {
         CU(cudaMalloc(&h->d_peaks, B * kParts * cap * sizeof(DevPeak)));
-        CU(cudaMalloc(&h->d_subpix, B * kParts * cap * 2 * sizeof(float)));
+        CU(cudaMalloc(&h->d_subpix, B * kParts * cap * 2 * sizeof(double)));
         CU(cudaMalloc(&h->d_part_count, B * kParts * sizeof(int)));
         CU(cudaMalloc(&h->d_links, B * kLimbs * cap * sizeof(DevLink)));
         CU(cudaMalloc(&h->d_link_count, B * kLimbs * sizeof(int)));
@@ -746,6 +746,28 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
     if (any & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
         return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", any);
     return IBP_OK;
+}
+
+int ibp_fetch_subpix(ibp_handle *h, int image, double *host_xy, int capacity, void *stream) {
+    if (!h || !host_xy) return fail(IBP_ERR_ARG, "ibp_fetch_subpix: null argument");
+    if (image < 0 || image >= h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_fetch_subpix: image %d out of range", image);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cap = h->L.max_peaks_per_part;
+    std::vector<double> tmp(kParts * cap * 2);
+    CU(cudaMemcpyAsync(tmp.data(), h->d_subpix + (size_t)image * kParts * cap * 2, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    // per-part lists -> id order (running counter across parts), using the counts of the last ibp_fetch
+    int pos = 0;
+    for (int p = 0; p < kParts; p++) {
+        const int n = h->h_part_count[(size_t)image * kParts + p];
+        for (int k = 0; k < n; k++, pos++) {
+            if (pos >= capacity) return fail(IBP_ERR_CAPACITY, "ibp_fetch_subpix: more than %d peaks", capacity);
+            host_xy[2 * pos] = tmp[((size_t)p * cap + k) * 2];
+            host_xy[2 * pos + 1] = tmp[((size_t)p * cap + k) * 2 + 1];
+        }
+    }
+    return pos;
 }
 
 // ------------------------------------------------------------------------------------------------ legacy protocol

@@ -43,11 +43,11 @@ struct PeakArgs {
     int cap;              // max peaks per (image, part); also per band
     int flavour;
     DevPeak *band_peaks;  // (batch, 18, nbands, cap) scratch
-    float *band_subpix;   // (batch, 18, nbands, cap, 2) scratch, centroid flavour
+    double *band_subpix;  // (batch, 18, nbands, cap, 2) scratch, centroid flavour: float64 x, y like the reference
     int *band_count;      // (batch, 18, nbands) scratch
     unsigned *ticket;     // (batch) zero on entry, left zero on exit
     DevPeak *peaks;       // (batch, 18, cap)
-    float *subpix;        // (batch, 18, cap, 2)
+    double *subpix;       // (batch, 18, cap, 2)
     int *part_count;      // (batch, 18)
     ibp_peak *line;       // (batch, line_stride)
     int line_stride;
@@ -380,39 +380,45 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
             // util.refine_centroid (util.py:188-213), radius = win
             if (lane == 0) {
                 const int rad = a.win;
-                float fx, fy, sc;
+                double fx, fy;
+                float sc;
                 if (py + rad + 1 > h || py - rad < 0 || px + rad + 1 > w || px - rad < 0) {
-                    fx = (float)px;
-                    fy = (float)py;
+                    fx = (double)px;
+                    fy = (double)py;
                     sc = BAND(py, px);
                 } else {
-                    // score_box is a float32 view; box*grid promotes to float64 (grid is int64) and the 25
-                    // products form a fresh contiguous array summed pairwise in float64; box.sum() reduces the
-                    // strided float32 view row by row (inner runs of 2*rad+1 < 8 values, left to right, then
-                    // accumulated across rows); box.mean() = that float32 sum / 25 in float32.
+                    // box*grid promotes to float64 (grid is int64): 25 products summed by numpy's pairwise scheme in
+                    // float64; box.sum() is the same pairwise scheme over the 25 float32 values in row-major order
+                    // (measured against numpy: the strided 5x5 view is reduced as one flat run, not row by row);
+                    // box.mean() = that float32 sum / 25 in float32.
                     double prod_r[25 * 1], prod_c[25 * 1];
+                    float vals[25];
                     const int sidec = 2 * rad + 1;
-                    float total = 0.0f;
                     int cnt = 0;
                     for (int q = -rad; q <= rad; q++) {
-                        float rowsum = 0.0f;
                         for (int p = -rad; p <= rad; p++) {
                             const float v = BAND(py + q, px + p);
                             if (cnt < 25) {
+                                vals[cnt] = v;
                                 prod_r[cnt] = __dmul_rn((double)v, (double)q);  // x_grid = ROW offset (l.207 quirk)
                                 prod_c[cnt] = __dmul_rn((double)v, (double)p);  // y_grid = column offset
                             }
                             cnt++;
-                            rowsum = __fadd_rn(rowsum, v);
                         }
-                        total = (q == -rad) ? rowsum : __fadd_rn(total, rowsum);
                     }
+                    float racc[8];
+                    for (int k = 0; k < 8; k++) racc[k] = vals[k];
+                    for (int i = 8; i < 24; i += 8)
+                        for (int k = 0; k < 8; k++) racc[k] = __fadd_rn(racc[k], vals[i + k]);
+                    float total = __fadd_rn(__fadd_rn(__fadd_rn(racc[0], racc[1]), __fadd_rn(racc[2], racc[3])),
+                                            __fadd_rn(__fadd_rn(racc[4], racc[5]), __fadd_rn(racc[6], racc[7])));
+                    total = __fadd_rn(total, vals[24]);
                     const int cntp = min(cnt, 25);
                     const double denom = (double)total;
                     const double offx = __ddiv_rn(np_pairwise_sum_f64(prod_r, cntp), denom);
                     const double offy = __ddiv_rn(np_pairwise_sum_f64(prod_c, cntp), denom);
-                    fx = __double2float_rn(__dadd_rn((double)px, offx));
-                    fy = __double2float_rn(__dadd_rn((double)py, offy));
+                    fx = __dadd_rn((double)px, offx);  // x_c + offset_x in float64 (util.py:210)
+                    fy = __dadd_rn((double)py, offy);
                     sc = __fdiv_rn(total, (float)(sidec * sidec));
                 }
                 DevPeak p;
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
                 p.id = k;
                 out[k] = p;
                 if (a.band_subpix) {
-                    float *sp = a.band_subpix + (slot_base + k) * 2;
+                    double *sp = a.band_subpix + (slot_base + k) * 2;
                     sp[0] = fx;
                     sp[1] = fy;
                 }
@@ -509,7 +515,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
             const size_t dsti = ((size_t)img * kParts + p) * a.cap + k_in_part;
             a.peaks[dsti] = pk;
             if (a.band_subpix && a.subpix) {
-                const float2 sp = __ldcg(reinterpret_cast<const float2 *>(a.band_subpix + srci * 2));
+                const double2 sp = __ldcg(reinterpret_cast<const double2 *>(a.band_subpix + srci * 2));
                 a.subpix[dsti * 2] = sp.x;
                 a.subpix[dsti * 2 + 1] = sp.y;
             }

@@ -3,6 +3,7 @@ Same function names, argument order and return containers; no C
 
     predict_refactor   parse_skeletons.py:28-103
     heatmap_nms        parse_skeletons.py:126-176
+    find_peaks         parse_skeletons.py:286-321 (original route: 3x3 NMS + centroid refinement, utils/util.py:177-213)
     limb_upsample      evaluate.py:77-80 (the cv2.resize between heatmap_nms and process_paf)
 """
 import numpy as np
@@ -18,10 +19,20 @@ NUM_PAFS = 30
 _pp = {}
 
 
-def _processor(device=0):
-    if device not in _pp:
-        _pp[device] = PostProcessor(device=device, max_batch=1, max_feat=(1024, 1024))
-    return _pp[device]
+def _processor(device=0, upsample=4, peak_thresh=0.1, refine_window=2):
+    """One single-image PostProcessor per (device, peak parameters): the constants live in the handle."""
+    key = (device, int(upsample), float(peak_thresh), int(refine_window))
+    if key not in _pp:
+        p = _lib.default_params()
+        p.upsample, p.peak_thresh, p.refine_window = key[1], key[2], key[3]
+        pp = PostProcessor.__new__(PostProcessor)
+        if not torch.cuda.is_available():
+            raise _lib.IbpError(-6, "no CUDA device: improved-body-parts_b200 has no CPU fallback")
+        pp.device = torch.device("cuda", device)
+        pp.handle = _lib.Handle(device, params=p, max_batch=1, max_feat_h=4096, max_feat_w=4096)
+        pp.max_batch = 1
+        _pp[key] = pp
+    return _pp[key]
 
 
 def pad_right_down_corner(img, stride, pad_value):
@@ -60,13 +71,7 @@ def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
     """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176)."""
     if not bool_refine_center:
         raise NotImplementedError("bool_refine_center=False is not on the reference's path (evaluate.py:76)")
-    pp = _processor()
-    up = int(upsample_factor)
-    if pp.handle.params.upsample != up:
-        pp.handle.close()
-        p = _lib.default_params()
-        p.upsample = up
-        pp.handle = _lib.Handle(pp.device.index or 0, params=p, max_batch=1, max_feat_h=1024, max_feat_w=1024)
+    pp = _processor(upsample=int(upsample_factor))
     maps = torch.from_numpy(np.ascontiguousarray(heatmaps[:, :, :NUM_KEYPOINTS], dtype=np.float32))
     maps = maps.to(pp.device).permute(2, 0, 1).contiguous()[None, ...]
     pp.find_peaks(maps, 0)
@@ -89,3 +94,31 @@ def limb_upsample(pafs, upsample_factor=4):
     pp = _processor()
     t = torch.from_numpy(np.ascontiguousarray(pafs, dtype=np.float32)).to(pp.device).permute(2, 0, 1).contiguous()
     return pp.upsample_limbs(t[None, ...], int(upsample_factor))[0].cpu().numpy()
+
+
+def find_peaks(heatmap_avg, test_cfg):
+    """heatmap_avg (H,W,>=18) -> list of 18 lists of (x, y, score, id) like parse_skeletons.py:286-321: 3x3 NMS with
+    `value >= thre1` (utils/util.py:177-185), 5x5 centroid refinement in float64 (utils/util.py:188-213; border peaks
+    keep their integer position and raw value), running ids across joint types."""
+    pp = _processor(peak_thresh=test_cfg['thre1'], refine_window=test_cfg['offset_radius'])
+    hm = np.asarray(heatmap_avg).astype(np.float32)  # l.291
+    maps = torch.from_numpy(np.ascontiguousarray(hm[:, :, :NUM_KEYPOINTS].transpose(2, 0, 1))).to(pp.device)[None, ...]
+    pp.find_peaks(maps, 0, flavour=_lib.PEAKS_BOX_CENTROID)
+    res = pp.fetch(1)
+    n = int(res.n_peaks[0])
+    xy = pp.handle.fetch_subpix(0, n)
+    peaks = res.peaks[0]
+    h, w = hm.shape[:2]
+    rad = int(test_cfg['offset_radius'])
+    out, pos = [], 0
+    for part in range(NUM_KEYPOINTS):
+        rows = []
+        for k in range(int(res.part_count[0, part])):
+            x, y = xy[pos]
+            ix, iy = int(x), int(y)
+            border = iy + rad + 1 > h or iy - rad < 0 or ix + rad + 1 > w or ix - rad < 0
+            # util.py:203-204 returns the integer anchor at the border, float64 positions elsewhere
+            rows.append(((ix, iy) if border and x == ix and y == iy else (x, y)) + (peaks[pos]["score"], pos))
+            pos += 1
+        out.append(rows)
+    return out

@@ -184,6 +184,10 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
 int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw,
                           int min_img_size, void *stream);
 int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream);
+/* Sub-pixel coordinates of the IBP_PEAKS_BOX_CENTROID flavour (utils/util.py:188-213 returns float64 x, y): after
+ * ibp_fetch, copies image `image`'s (x, y) pairs in peak-id order into host_xy[capacity][2].  Returns the number of
+ * peaks written (>= 0) or a negative error code. */
+int ibp_fetch_subpix(ibp_handle *h, int image, double *host_xy, int capacity, void *stream);
 /* number of kernels this library has launched through `h` since creation (bench.py's gpu_launches) */
 int64_t ibp_launch_count(const ibp_handle *h);
 

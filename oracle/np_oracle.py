@@ -160,3 +160,62 @@ def joint_list(all_peaks):
     if not rows:
         return np.zeros((0, 5), dtype=f32)
     return np.array(rows).astype(f32)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A12  3x3 NMS of the original route — utils/util.py:177-185 (keypoint_heatmap_nms)
+# ----------------------------------------------------------------------------------------------------------
+def box_nms(heat, thre=0.1):
+    """heat (C,H,W) float32 -> heat * keep, keep = (3x3 max over the reflect-padded map == heat) * (heat >= thre).
+    F.pad(mode='reflect') with pad 1 mirrors WITHOUT repeating the edge, i.e. it adds values that are already inside
+    the 3x3 window, so the windowed maximum equals the maximum over the in-image part of the window."""
+    a = np.asarray(heat, dtype=f32)
+    big = np.pad(a, ((0, 0), (1, 1), (1, 1)), mode="reflect")
+    H, W = a.shape[1:]
+    hmax = np.full_like(a, -np.inf)
+    for dy in range(3):
+        for dx in range(3):
+            hmax = np.maximum(hmax, big[:, dy:dy + H, dx:dx + W])
+    keep = (hmax == a).astype(f32) * (a >= f32(thre)).astype(f32)
+    return a * keep
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A13  centroid refinement and the peak lists of the original route — utils/util.py:188-213,
+#      utils/parse_skeletons.py:286-321 (find_peaks)
+# ----------------------------------------------------------------------------------------------------------
+def refine_centroid(scoremap, anchor, radius):
+    """(x, y, score): border peaks are returned unchanged with the raw value (util.py:203-204); otherwise the float64
+    first moments of the (2r+1)^2 box over its float32 sum — note that np.mgrid puts the ROW offset into x_grid
+    (util.py:207), so x moves by the row moment and y by the column moment — and the box mean as the score."""
+    x_c, y_c = anchor
+    x_min, x_max, y_min, y_max = x_c - radius, x_c + radius + 1, y_c - radius, y_c + radius + 1
+    if y_max > scoremap.shape[0] or y_min < 0 or x_max > scoremap.shape[1] or x_min < 0:
+        return anchor + (scoremap[y_c, x_c],)
+    box = scoremap[y_min:y_max, x_min:x_max]
+    x_grid, y_grid = np.mgrid[-radius:radius + 1, -radius:radius + 1]
+    offset_x = (box * x_grid).sum() / box.sum()
+    offset_y = (box * y_grid).sum() / box.sum()
+    return (x_c + offset_x, y_c + offset_y) + (box.mean(),)
+
+
+def find_peaks(heatmap_avg, thre1=0.1, radius=2):
+    """heatmap_avg (H,W,>=18) -> list of 18 lists of (x, y, score, id); x, y float64 (ints at the border)."""
+    hm = np.asarray(heatmap_avg).astype(f32)  # parse_skeletons.py:291
+    planes = np.ascontiguousarray(hm[:, :, :NUM_KEYPOINTS].transpose(2, 0, 1))
+    filt = box_nms(planes, thre1)
+    out, counter = [], 0
+    for part in range(NUM_KEYPOINTS):
+        map_orig = hm[:, :, part]
+        ys, xs = np.nonzero(filt[part])  # row-major order (parse_skeletons.py:305)
+        refined = [refine_centroid(map_orig, (x, y), radius) for x, y in zip(xs, ys)]
+        out.append([refined[i] + (counter + i,) for i in range(len(refined))])
+        counter += len(refined)
+    return out
+
+
+def peaks_table(all_peaks):
+    """list of 18 lists of (x,y,score,id) -> (N,4) float64 + per-part counts, for comparisons and fixtures."""
+    rows = [tuple(float(v) for v in p) for ps in all_peaks for p in ps]
+    tab = np.array(rows, dtype=np.float64).reshape(-1, 4)
+    return tab, np.array([len(ps) for ps in all_peaks], dtype=np.int64)
