@@ -42,6 +42,10 @@ class Limits(C.Structure):
                 ("max_feat_w", C.c_int32)]
 
 
+class ScaleInput(C.Structure):
+    _fields_ = [("net_out", C.c_void_p), ("fh", C.c_int32), ("fw", C.c_int32), ("sh", C.c_int32), ("sw", C.c_int32)]
+
+
 class BatchView(C.Structure):
     _fields_ = [("batch", C.c_int32), ("peak_stride", C.c_int32), ("human_stride", C.c_int32),
                 ("n_peaks", C.POINTER(C.c_int32)), ("part_count", C.POINTER(C.c_int32)), ("peaks", C.c_void_p),
@@ -89,6 +93,8 @@ def lib():
     L.ibp_device_count.restype = ip
     L.ibp_fuse_flip.restype = ip
     L.ibp_fuse_flip.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
+    L.ibp_fuse_multiscale.restype = ip
+    L.ibp_fuse_multiscale.argtypes = [vp, C.POINTER(ScaleInput), ip, ip, ip, ip, ip, vp, vp, vp]
     L.ibp_upsample_limbs.restype = ip
     L.ibp_upsample_limbs.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
     L.ibp_find_peaks.restype = ip
@@ -115,7 +121,7 @@ def lib():
 
 EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp_get_score", "ibp_get_part_x",
            "ibp_get_part_y", "ibp_get_part_score", "ibp_get_status", "ibp_default_params", "ibp_default_limits",
-           "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_upsample_limbs",
+           "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_fuse_multiscale", "ibp_upsample_limbs",
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_launch_count", "ibp_set_profiling",
            "ibp_get_stage_ms"]
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
@@ -200,6 +206,12 @@ class Handle:
     # ---- raw stage calls on device pointers (ints) ----
     def fuse_flip(self, net_out_ptr, dtype, batch, fh, fw, fused_ptr, flip_avg=True, stream=0):
         check(lib().ibp_fuse_flip(self._h, net_out_ptr, dtype, batch, fh, fw, int(bool(flip_avg)), fused_ptr, stream))
+
+    def fuse_multiscale(self, scales, batch, img_h, img_w, out_ptr, heat32_ptr=None, flip_avg=True, stream=0):
+        """scales: [(net_out_ptr, fh, fw, sh, sw)] per scale of the search."""
+        arr = (ScaleInput * len(scales))(*[ScaleInput(int(p), int(fh), int(fw), int(sh), int(sw)) for p, fh, fw, sh, sw in scales])
+        check(lib().ibp_fuse_multiscale(self._h, arr, len(scales), batch, img_h, img_w, int(bool(flip_avg)), out_ptr,
+                                        heat32_ptr, stream))
 
     def upsample_limbs(self, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream=0):
         check(lib().ibp_upsample_limbs(self._h, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream))

@@ -12,6 +12,7 @@
 #include "ibp_device.cuh"
 #include "k_fuse.cuh"
 #include "k_limbs.cuh"
+#include "k_multiscale.cuh"
 #include "k_peaks.cuh"
 #include "k_upsample.cuh"
 
@@ -347,6 +348,7 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(limbs_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         if (limb_phase_bytes(h, 0) > kMaxDynSmem)
             return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_phase_bytes(h, 0), kMaxDynSmem);
         if (group_phase_bytes(h) > kMaxDynSmem)
@@ -393,6 +395,63 @@ int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int 
             fuse_flip_scalar<float><<<grid, 256, 0, st>>>((const float *)net_out, fused, fh, fw, flip_avg);
         else
             fuse_flip_scalar<__half><<<grid, 256, 0, st>>>((const __half *)net_out, fused, fh, fw, flip_avg);
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K1 multi-scale
+int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w, int flip_avg,
+                        double *out, float *heat32, void *stream) {
+    if (!h || !scales || !out) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: null argument");
+    if (n_scales < 1 || n_scales > kMsMaxScales) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: 1..%d scales, got %d", kMsMaxScales, n_scales);
+    if (batch < 1 || img_h < 1 || img_w < 1) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale: bad shape");
+    if (h->P.upsample != 4) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: supports stride 4 only (params.upsample = %d)", h->P.upsample);
+    CU(cudaSetDevice(h->device));
+    MsArgs a;
+    memset(&a, 0, sizeof(a));
+    a.n_scales = n_scales;
+    a.up = h->P.upsample;
+    a.flip = flip_avg ? 1 : 0;
+    a.H = img_h;
+    a.W = img_w;
+    a.out = out;
+    a.heat32 = heat32;
+    size_t cap_f = 1, cap_t1 = 1, cap_i = 1, cap_t2 = 1;
+    for (int s = 0; s < n_scales; s++) {
+        const ibp_scale_input &in = scales[s];
+        if (!in.net_out || in.fh < 1 || in.fw < 1 || in.sh < 1 || in.sw < 1 || in.sh > in.fh * a.up || in.sw > in.fw * a.up)
+            return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale: scale %d: feature (%d,%d), scaled image (%d,%d)", s, in.fh, in.fw, in.sh, in.sw);
+        MsScale &S = a.sc[s];
+        S.src = in.net_out;
+        S.h = in.fh;
+        S.w = in.fw;
+        S.sh = in.sh;
+        S.sw = in.sw;
+        // cv2.resize with an explicit dsize: inv_scale = (double)dsize / ssize; scale = 1. / inv_scale
+        S.scale_x = 1.0 / ((double)img_w / (double)in.sw);
+        S.scale_y = 1.0 / ((double)img_h / (double)in.sh);
+        // upper bounds of the tile footprints (see the kernel): taps of T destination pixels span <= (T-1)*scale + 6
+        const size_t n_rx = std::min<size_t>(in.sw, (size_t)((kMsTileX - 1) * S.scale_x) + 6);
+        const size_t n_ry = std::min<size_t>(in.sh, (size_t)((kMsTileY - 1) * S.scale_y) + 6);
+        const size_t n_fx = std::min<size_t>(in.fw, n_rx / 4 + 6), n_fy = std::min<size_t>(in.fh, n_ry / 4 + 6);
+        cap_f = std::max(cap_f, n_fy * n_fx);
+        cap_t1 = std::max(cap_t1, n_fy * n_rx);
+        cap_i = std::max(cap_i, n_ry * n_rx);
+        cap_t2 = std::max(cap_t2, n_ry * (size_t)kMsTileX);
+    }
+    a.cap_f = (int)cap_f;
+    a.cap_t1 = (int)cap_t1;
+    a.cap_i = (int)cap_i;
+    a.cap_t2 = (int)cap_t2;
+    const size_t smem = (cap_f + cap_t1 + cap_i + cap_t2) * sizeof(float);
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale: a scale factor this large needs %zu B of shared memory", smem);
+    const dim3 grid((img_w + kMsTileX - 1) / kMsTileX, (img_h + kMsTileY - 1) / kMsTileY, (unsigned)batch * kLayers);
+    if (grid.z > 65535u) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: batch %d too large for one launch (max %d)", batch, 65535 / kLayers);
+    {
+        StageTimer t(h, IBP_STAGE_FUSE, (cudaStream_t)stream);
+        fuse_multiscale_kernel<<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());

@@ -2,6 +2,7 @@
 Same function names, argument order and return containers; no CPU fallback.
 
     predict_refactor   parse_skeletons.py:28-103
+    predict            parse_skeletons.py:180-283 (original route: scale search + flip fusion at image resolution)
     heatmap_nms        parse_skeletons.py:126-176
     find_peaks         parse_skeletons.py:286-321 (original route: 3x3 NMS + centroid refinement, utils/util.py:177-213)
     limb_upsample      evaluate.py:77-80 (the cv2.resize between heatmap_nms and process_paf)
@@ -122,3 +123,40 @@ def find_peaks(heatmap_avg, test_cfg):
             pos += 1
         out.append(rows)
     return out
+
+
+def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, config=None, scale_search=None):
+    """-> (heatmap_avg (H,W,20), paf_avg (H,W,30)) float64 HWC like parse_skeletons.py:180-283.
+
+    The reference computes the scale-search multipliers (l.186) and then pins them to [1.] (l.188); `scale_search=None`
+    does the same.  Pass a list such as test_cfg['scale_search'] to run the multi-scale averaging the reference ships
+    but never reaches.  rotation_search is [0.0] (utils/config:15): the rotation branch (l.215-218, 265-267) is not
+    implemented.  Image preparation per scale stays on the host exactly as in the reference; everything after the
+    model calls (flip average, cubic x stride, crop, cubic resize to the image, average) is one kernel launch."""
+    import cv2
+    img_h, img_w, _ = image.shape
+    if scale_search is None:
+        multiplier = [1.]  # l.188
+    else:
+        multiplier = [x * model_cfg['boxsize'] / img_h for x in scale_search]  # l.186
+    if any(a != 0 for a in test_cfg.get('rotation_search', [0.0])):
+        raise NotImplementedError("rotation_search != 0 is not on the reference's path (utils/config:15)")
+    pp = _processor()
+    outs, sizes = [], []
+    for scale in multiplier:
+        if scale * img_h > 2600 or scale * img_w > 3800:  # l.196-199
+            scale = min(2600 / img_h, 3800 / img_w)
+            print("Input image: '{}' is too big, shrink it!".format(input_image_path))
+        scaled = cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC)
+        padded, _ = pad_right_down_corner(scaled, model_cfg['max_downsample'], model_cfg['padValue'])
+        x = np.float32(padded / 255)
+        batch = np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0)  # l.221-224
+        with torch.no_grad():
+            out = model(torch.from_numpy(batch).to(pp.device))
+        if isinstance(out, (list, tuple)):
+            out = out[-1][0]  # last stack, scale 0 (l.232)
+        outs.append(out.to(pp.device, torch.float32)[None, ...])
+        sizes.append(scaled.shape[:2])
+    fused, _ = pp.fuse_multiscale(outs, sizes, img_h, img_w, flip_avg, want_heat32=False)
+    hwc = fused[0].permute(1, 2, 0).contiguous().cpu().numpy()
+    return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()

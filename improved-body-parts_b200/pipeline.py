@@ -67,6 +67,21 @@ class PostProcessor:
                                   _stream_ptr(self.device))
         return fused
 
+    def fuse_multiscale(self, net_outs, scaled_sizes, img_h, img_w, flip_avg=True, want_heat32=True):
+        """predict()'s fusion (utils/parse_skeletons.py:232-281) for a batch: net_outs = one (B,2,50,h_s,w_s) float32
+        CUDA tensor per scale, scaled_sizes = [(sh,sw)] the scaled image sizes before padding.
+        -> (fused (B,50,img_h,img_w) float64 planar [0,30) limb / [30,50) keypoint, heat32 (B,18,img_h,img_w) or None)."""
+        ts = [t.to(self.device, torch.float32).contiguous() for t in net_outs]
+        B = ts[0].shape[0]
+        out = torch.empty((B, _lib.NUM_LAYERS, img_h, img_w), dtype=torch.float64, device=self.device)
+        heat32 = torch.empty((B, _lib.NUM_PARTS, img_h, img_w), dtype=torch.float32, device=self.device) if want_heat32 else None
+        scales = [(t.data_ptr(), t.shape[3], t.shape[4], sh, sw) for t, (sh, sw) in zip(ts, scaled_sizes)]
+        with torch.cuda.device(self.device):
+            self.handle.fuse_multiscale(scales, B, img_h, img_w, out.data_ptr(), heat32.data_ptr() if want_heat32 else None,
+                                        flip_avg, _stream_ptr(self.device))
+        self._keep_ms = ts
+        return out, heat32
+
     def upsample_limbs(self, fused, up=4):
         """(B,C>=30,h,w) planar -> (B, h*up, w*up, 30) HWC float32 (A4, evaluate.py:77-80)."""
         fused = fused.to(self.device, torch.float32).contiguous()

@@ -143,3 +143,30 @@ def make_batch(base_seed, batch, people=(1, 10), height=512, width=512, stride=4
         n = int(rng.integers(people[0], people[1] + 1))
         outs.append(make_network_output(base_seed + i, n, height, width, stride, noise, scale)[0])
     return np.stack(outs)
+
+
+def multiscale_shapes(img_h, img_w, scale_search=(0.5, 1.0, 1.5, 2.0), boxsize=512, max_downsample=64, stride=4):
+    """Per scale: (multiplier, scaled (h,w), padded (h,w), feature (h,w)) like utils/parse_skeletons.py:186,204-208."""
+    out = []
+    for x in scale_search:
+        m = x * boxsize / img_h
+        sh, sw = int(np.rint(img_h * m)), int(np.rint(img_w * m))
+        ph, pw = -(-sh // max_downsample) * max_downsample, -(-sw // max_downsample) * max_downsample
+        out.append((m, (sh, sw), (ph, pw), (ph // stride, pw // stride)))
+    return out
+
+
+def make_multiscale_output(seed, n_people, img_h=480, img_w=640, scale_search=(0.5, 1.0, 1.5, 2.0), noise=0.01,
+                           scale=(0.35, 0.9)):
+    """One image through the scale search: list over scales of (2, 50, h_s, w_s) float32 = [upright, flip twin],
+    the same people drawn at each scale's padded input size (pad area empty), seeded."""
+    rng = np.random.default_rng(seed)
+    joints = random_people(rng, n_people, img_w, img_h, scale=scale)
+    outs = []
+    for m, _, (ph, pw), _ in multiscale_shapes(img_h, img_w, scale_search):
+        j = joints.copy()
+        j[:, :, :2] *= m
+        clean = render_maps(j, ph, pw, 4)
+        # the flipped input is the mirror of the PADDED image: padding ends up on the left of the twin
+        outs.append(np.stack([add_noise(clean, rng, noise), add_noise(flip_twin(clean), rng, noise)]))
+    return outs, joints

@@ -153,6 +153,20 @@ int ibp_device_count(void); /* 0 when there is no usable CUDA device */
 int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int fh, int fw, int flip_avg,
                   float *fused, void *stream);
 
+/* K1, multi-scale — scale-search / flip fusion at image resolution: utils/parse_skeletons.py:180-283 (predict), what
+ * follows the model calls.  One entry per scale of the search (l.186, l.194): net_out (batch,2,50,fh,fw) float32 is the
+ * network output for the input scaled to (sh,sw) and padded to (fh*4, fw*4) (l.204-208).  Per scale the maps are flip-
+ * averaged, resized x4 (cv2 INTER_CUBIC), cropped to (sh,sw), resized to (img_h,img_w) and added / n_scales (l.232-281).
+ * out (batch,50,img_h,img_w) planar float64: channels [0,30) = paf_avg, [30,50) = heatmap_avg.  heat32 (optional, may be
+ * NULL): (batch,18,img_h,img_w) float32 copy of the keypoint planes, what find_peaks (l.291) works on. */
+typedef struct ibp_scale_input {
+    const float *net_out;
+    int32_t fh, fw;
+    int32_t sh, sw;
+} ibp_scale_input;
+int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w,
+                        int flip_avg, double *out, float *heat32, void *stream);
+
 /* A4 — limb-map up-sampling: evaluate.py:77-80 / demo_image.py:94-97, cv2.resize(pafs, fx=up, fy=up, INTER_CUBIC).
  * fused (batch,chan_stride,h,w) planar, limb channels first; out (batch, h*up, w*up, 30) HWC float32. */
 int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int batch, int fh, int fw, int up,

@@ -219,3 +219,83 @@ def peaks_table(all_peaks):
     rows = [tuple(float(v) for v in p) for ps in all_peaks for p in ps]
     tab = np.array(rows, dtype=np.float64).reshape(-1, 4)
     return tab, np.array([len(ps) for ps in all_peaks], dtype=np.int64)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# OpenCV-native cubic resize, arbitrary destination size (cv2.resize(src, (dw, dh), INTER_CUBIC), IPP off)
+# ----------------------------------------------------------------------------------------------------------
+def _cv_cubic_axis(n_src, n_dst, scale):
+    """OpenCV resize.cpp, cubic branch, one axis: fx = (float)((d+0.5)*scale - 0.5) with `scale` a double;
+    s = cvFloor(fx); fx -= s; four taps s-1..s+2 clamped to the source (replicate border)."""
+    idx = np.empty((n_dst, 4), dtype=np.int64)
+    wts = np.empty((n_dst, 4), dtype=f32)
+    for d in range(n_dst):
+        fx = f32((d + 0.5) * scale - 0.5)
+        s = int(np.floor(fx))
+        wts[d] = _cubic_weights(f32(fx - f32(s)))
+        idx[d] = np.clip(np.arange(s - 1, s + 3), 0, n_src - 1)
+    return idx, wts
+
+
+def cv_resize_cubic(src, dst_h, dst_w, scale_y=None, scale_x=None):
+    """Bit-exact restatement of OpenCV's own float32 cubic resize for an (H,W,C) image to (dst_h, dst_w).
+    scale_* default to what cv2 derives from an explicit dsize: 1. / ((double)dst / src); pass 1./f for the
+    fx=f, fy=f call form.  Horizontal pass: ((s0*a0 + s1*a1) + s2*a2) + s3*a3.  Vertical pass: the 4-lane vector
+    loop (SSE baseline build) gives s0*b0 + (s1*b1 + (s2*b2 + s3*b3)) for the first 4*floor(W*C/4) elements of a
+    row, the scalar tail ((s0*b0 + s1*b1) + s2*b2) + s3*b3 for the rest."""
+    s = np.asarray(src, dtype=f32)
+    squeeze = s.ndim == 2
+    if squeeze:
+        s = s[:, :, None]
+    h, w, c = s.shape
+    if scale_x is None:
+        scale_x = 1.0 / (float(dst_w) / w)
+    if scale_y is None:
+        scale_y = 1.0 / (float(dst_h) / h)
+    xi, xw = _cv_cubic_axis(w, dst_w, scale_x)
+    yi, yw = _cv_cubic_axis(h, dst_h, scale_y)
+    p = [s[:, xi[:, k], :] * xw[:, k][None, :, None] for k in range(4)]
+    rows = ((p[0] + p[1]) + p[2]) + p[3]
+    q = [rows[yi[:, k], :, :] * yw[:, k][:, None, None] for k in range(4)]
+    out = q[0] + (q[1] + (q[2] + q[3]))
+    n_vec = (dst_w * c) // 4 * 4
+    if n_vec != dst_w * c:
+        tail = ((q[0] + q[1]) + q[2]) + q[3]
+        flat, flat_t = out.reshape(dst_h, dst_w * c), tail.reshape(dst_h, dst_w * c)
+        flat[:, n_vec:] = flat_t[:, n_vec:]
+        out = flat.reshape(dst_h, dst_w, c)
+    return out[:, :, 0] if squeeze else out
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A1  multi-scale / flip fusion at image resolution — utils/parse_skeletons.py:180-283 (predict)
+# ----------------------------------------------------------------------------------------------------------
+def scaled_size(img_h, img_w, scale):
+    """Size of cv2.resize(image, (0,0), fx=scale, fy=scale) (l.204): saturate_cast<int>(n*scale) = round half to even."""
+    return int(np.rint(img_h * scale)), int(np.rint(img_w * scale))
+
+
+def padded_size(sh, sw, max_downsample=64):
+    """util.padRightDownCorner (utils/util.py:44-65): pad bottom/right up to a multiple of max_downsample."""
+    return -(-sh // max_downsample) * max_downsample, -(-sw // max_downsample) * max_downsample
+
+
+def predict_fuse(net_outs, img_h, img_w, scales, stride=4, max_downsample=64, flip_avg=True):
+    """Everything predict() does after the model calls.  net_outs[i] = (2,50,padH_i/stride,padW_i/stride) network
+    output for scale scales[i] (the multipliers of l.186).  Returns heatmap_avg (H,W,20), paf_avg (H,W,30) float64."""
+    heatmap_avg = np.zeros((img_h, img_w, NUM_HEATMAPS))
+    paf_avg = np.zeros((img_h, img_w, NUM_PAFS))
+    n = len(scales)  # len(multiplier) * len(rotate_angle), rotation_search = [0.0] (utils/config:15)
+    for out, scale in zip(net_outs, scales):
+        sh, sw = scaled_size(img_h, img_w, scale)
+        pad_h, pad_w = padded_size(sh, sw, max_downsample)
+        assert out.shape[2] * stride == pad_h and out.shape[3] * stride == pad_w, (out.shape, pad_h, pad_w)
+        heat, paf = fuse_flip(out, flip_avg)                                              # l.232-248
+        heat = cv_resize_cubic(heat, pad_h, pad_w, 1.0 / stride, 1.0 / stride)            # l.252-256
+        paf = cv_resize_cubic(paf, pad_h, pad_w, 1.0 / stride, 1.0 / stride)              # l.259-263
+        heat, paf = heat[:sh, :sw, :], paf[:sh, :sw, :]                                   # l.272-273
+        heat = cv_resize_cubic(heat, img_h, img_w)                                        # l.276
+        paf = cv_resize_cubic(paf, img_h, img_w)                                          # l.277
+        heatmap_avg = heatmap_avg + heat / n                                              # l.280 (float32 / int, then + in float64)
+        paf_avg = paf_avg + paf / n                                                       # l.281
+    return heatmap_avg, paf_avg
