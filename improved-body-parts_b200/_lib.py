@@ -42,6 +42,12 @@ class Limits(C.Structure):
                 ("max_feat_w", C.c_int32)]
 
 
+class PyParams(C.Structure):
+    """utils/config:17-27 as Python floats (the Python route computes in float64)."""
+    _fields_ = [("thre2", C.c_double), ("connect_ration", C.c_double), ("mid_num", C.c_int32), ("len_rate", C.c_int32),
+                ("connection_tole", C.c_double), ("min_score", C.c_double), ("min_parts", C.c_int32)]
+
+
 class ScaleInput(C.Structure):
     _fields_ = [("net_out", C.c_void_p), ("fh", C.c_int32), ("fw", C.c_int32), ("sh", C.c_int32), ("sw", C.c_int32)]
 
@@ -109,6 +115,19 @@ def lib():
     L.ibp_fetch.argtypes = [vp, ip, C.POINTER(BatchView), vp]
     L.ibp_fetch_subpix.restype = ip
     L.ibp_fetch_subpix.argtypes = [vp, ip, vp, ip, vp]
+    L.ibp_default_py_params.argtypes = [C.POINTER(PyParams)]
+    L.ibp_set_peaks64.restype = ip
+    L.ibp_set_peaks64.argtypes = [vp, ip, vp, vp, ip]
+    L.ibp_find_connections.restype = ip
+    L.ibp_find_connections.argtypes = [vp, C.POINTER(PyParams), vp, ip, ip, ip, ip, ip, vp]
+    L.ibp_fetch_connections.restype = ip
+    L.ibp_fetch_connections.argtypes = [vp, ip, vp, vp, vp]
+    L.ibp_set_connections.restype = ip
+    L.ibp_set_connections.argtypes = [vp, ip, vp, vp, vp, ip]
+    L.ibp_find_humans.restype = ip
+    L.ibp_find_humans.argtypes = [vp, C.POINTER(PyParams), ip, vp]
+    L.ibp_fetch_people.restype = ip
+    L.ibp_fetch_people.argtypes = [vp, ip, vp, ip, vp]
     L.ibp_launch_count.restype = C.c_int64
     L.ibp_launch_count.argtypes = [vp]
     L.ibp_set_profiling.restype = ip
@@ -122,7 +141,8 @@ def lib():
 EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp_get_score", "ibp_get_part_x",
            "ibp_get_part_y", "ibp_get_part_score", "ibp_get_status", "ibp_default_params", "ibp_default_limits",
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_fuse_multiscale", "ibp_upsample_limbs",
-           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_launch_count", "ibp_set_profiling",
+           "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
+           "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
            "ibp_get_stage_ms"]
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
@@ -135,6 +155,19 @@ def check(rc):
 def default_params():
     p = Params()
     lib().ibp_default_params(C.byref(p))
+    return p
+
+
+def py_params(test_cfg=None):
+    """PyParams from a reference-style test_cfg dict (utils/config_reader.py:53-66); defaults = utils/config."""
+    p = PyParams()
+    lib().ibp_default_py_params(C.byref(p))
+    if test_cfg:
+        p.thre2 = float(test_cfg.get('thre2', p.thre2))
+        p.connect_ration = float(test_cfg.get('connect_ration', p.connect_ration))
+        p.mid_num = int(test_cfg.get('mid_num', p.mid_num))
+        p.len_rate = int(test_cfg.get('len_rate', p.len_rate))
+        p.connection_tole = float(test_cfg.get('connection_tole', p.connection_tole))
     return p
 
 
@@ -237,6 +270,43 @@ class Handle:
         if rc < 0:
             check(rc)
         return out[:rc]
+
+    # ---- Python-semantics route (find_connections / find_humans) ----
+    def set_peaks64(self, image, rows, part):
+        r = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1, 4)
+        t = np.ascontiguousarray(part, dtype=np.int32).reshape(-1)
+        check(lib().ibp_set_peaks64(self._h, int(image), r.ctypes.data, t.ctypes.data, r.shape[0]))
+
+    def find_connections(self, params, paf_ptr, chan_stride, batch, img_h, img_w, img_height, stream=0):
+        check(lib().ibp_find_connections(self._h, C.byref(params), paf_ptr, chan_stride, batch, img_h, img_w,
+                                         int(img_height), stream))
+
+    def fetch_connections(self, image, stream=0):
+        """-> (rows (30, cap, 6) float64, counts (30,) int32)"""
+        cap = self.limits.max_peaks_per_part
+        rows = np.zeros((NUM_LIMBS, cap, 6), dtype=np.float64)
+        counts = np.zeros(NUM_LIMBS, dtype=np.int32)
+        check(lib().ibp_fetch_connections(self._h, int(image), rows.ctypes.data, counts.ctypes.data, stream))
+        return rows, counts
+
+    def set_connections(self, image, rows, counts, cand_score):
+        cap = self.limits.max_peaks_per_part
+        r = np.ascontiguousarray(rows, dtype=np.float64)
+        assert r.shape == (NUM_LIMBS, cap, 6)
+        c = np.ascontiguousarray(counts, dtype=np.int32)
+        s = np.ascontiguousarray(cand_score, dtype=np.float64).reshape(-1)
+        check(lib().ibp_set_connections(self._h, int(image), r.ctypes.data, c.ctypes.data, s.ctypes.data, s.shape[0]))
+
+    def find_humans(self, params, batch, stream=0):
+        check(lib().ibp_find_humans(self._h, C.byref(params), batch, stream))
+
+    def fetch_people(self, image, stream=0):
+        """-> person_to_joint_assoc (n, 20, 2) float64"""
+        out = np.zeros((self.limits.max_humans, 20, 2), dtype=np.float64)
+        n = lib().ibp_fetch_people(self._h, int(image), out.ctypes.data, out.shape[0], stream)
+        if n < 0:
+            check(n)
+        return out[:n].copy()
 
     def fetch(self, batch, stream=0, raise_on_overflow=True):
         view = BatchView()

@@ -14,6 +14,7 @@
 #include "k_limbs.cuh"
 #include "k_multiscale.cuh"
 #include "k_peaks.cuh"
+#include "k_pyroute.cuh"
 #include "k_upsample.cuh"
 
 using namespace ibp;
@@ -87,6 +88,14 @@ struct ibp_handle {
     int *d_band_count = nullptr;
     int band_slots = 0;  // nbands the scratch was sized for
     unsigned *d_ticket = nullptr;  // [2][max_batch] + 1
+    // Python-semantics route (find_connections / find_humans), allocated on first use
+    double *d_score64 = nullptr;      // (B,18,cap) float64 peak scores of ibp_set_peaks64
+    int use_score64 = 0;
+    double *d_py_conn = nullptr;      // (B,30,cap,6)
+    int *d_py_conn_count = nullptr;   // (B,30)
+    double *d_py_cand = nullptr;      // (B,line_stride)
+    double *d_py_people = nullptr;    // (B,max_humans,20,2)
+    int *d_py_n_people = nullptr;     // (B)
     int *d_order = nullptr;        // [max_batch] images by descending peak count (written by the peak kernel)
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
     unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
@@ -134,6 +143,21 @@ int ensure_bands(ibp_handle *h, int nbands) {
     h->band_slots = nbands;
     return IBP_OK;
 }
+int ensure_py(ibp_handle *h) {
+    if (h->d_py_conn) return IBP_OK;
+    const size_t B = h->L.max_batch, cap = h->L.max_peaks_per_part;
+    CU(cudaMalloc(&h->d_score64, B * kParts * cap * sizeof(double)));
+    CU(cudaMalloc(&h->d_py_conn, B * kLimbs * cap * 6 * sizeof(double)));
+    CU(cudaMalloc(&h->d_py_conn_count, B * kLimbs * sizeof(int)));
+    CU(cudaMalloc(&h->d_py_cand, B * h->line_stride * sizeof(double)));
+    CU(cudaMalloc(&h->d_py_people, B * h->L.max_humans * 40 * sizeof(double)));
+    CU(cudaMalloc(&h->d_py_n_people, B * sizeof(int)));
+    CU(cudaMemset(h->d_py_conn_count, 0, B * kLimbs * sizeof(int)));
+    CU(cudaMemset(h->d_py_n_people, 0, B * sizeof(int)));
+    CU(cudaFuncSetAttribute(py_connections_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+    CU(cudaFuncSetAttribute(py_humans_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+    return IBP_OK;
+}
 int ensure_fused(ibp_handle *h, size_t floats) {
     if (h->fused_floats >= floats) return IBP_OK;
     free_dev(h->d_fused);
@@ -163,6 +187,12 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_timeline);
     free_dev(h->d_timeline_pk);
     free_dev(h->d_order);
+    free_dev(h->d_score64);
+    free_dev(h->d_py_conn);
+    free_dev(h->d_py_conn_count);
+    free_dev(h->d_py_cand);
+    free_dev(h->d_py_people);
+    free_dev(h->d_py_n_people);
     free_host(h->h_n_peaks);
     free_host(h->h_part_count);
     free_host(h->h_line);
@@ -532,6 +562,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.order = h->d_order;
     a.batch = batch;
     h->order_batch = batch;
+    h->use_score64 = 0;
     a.timeline = nullptr;
     {
         const char *dbg = getenv("IBP_DEBUG");
@@ -827,6 +858,191 @@ int ibp_fetch_subpix(ibp_handle *h, int image, double *host_xy, int capacity, vo
         }
     }
     return pos;
+}
+
+// ------------------------------------------------------------------------------------------------ Python route
+namespace {
+PyParams to_py(const ibp_py_params *p) {
+    ibp_py_params d;
+    if (!p) {
+        ibp_default_py_params(&d);
+        p = &d;
+    }
+    PyParams q;
+    q.thre2 = p->thre2;
+    q.connect_ration = p->connect_ration;
+    q.mid_num = p->mid_num;
+    q.len_rate = p->len_rate;
+    q.connection_tole = p->connection_tole;
+    q.min_score = p->min_score;
+    q.min_parts = p->min_parts;
+    return q;
+}
+}  // namespace
+
+void ibp_default_py_params(ibp_py_params *p) {
+    if (!p) return;
+    p->thre2 = 0.1;
+    p->connect_ration = 0.8;
+    p->mid_num = 20;
+    p->len_rate = 16;
+    p->connection_tole = 0.7;
+    p->min_score = 0.45;
+    p->min_parts = 2;
+}
+
+int ibp_set_peaks64(ibp_handle *h, int image, const double *rows, const int32_t *part, int n) {
+    if (!h || (n > 0 && (!rows || !part))) return fail(IBP_ERR_ARG, "ibp_set_peaks64: null argument");
+    if (image < 0 || image >= h->L.max_batch || n < 0) return fail(IBP_ERR_ARG, "ibp_set_peaks64: image %d / n %d out of range", image, n);
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_py(h);
+    if (rc != IBP_OK) return rc;
+    const int cap = h->L.max_peaks_per_part;
+    std::vector<DevPeak> pk((size_t)kParts * cap);
+    std::vector<double> xy((size_t)kParts * cap * 2), sc((size_t)kParts * cap);
+    int counts[kParts] = {0};
+    for (int i = 0; i < n; i++) {
+        const int p = part[i];
+        if (p < 0 || p >= kParts) return fail(IBP_ERR_PART, "joint %d has part id %d outside [0,18)", i, p);
+        if (counts[p] >= cap) return fail(IBP_ERR_CAPACITY, "more than %d peaks of part %d (ibp_limits.max_peaks_per_part)", cap, p);
+        const size_t k = (size_t)p * cap + counts[p]++;
+        const double *r = rows + (size_t)i * 4;
+        pk[k].x = (int)r[0];
+        pk[k].y = (int)r[1];
+        pk[k].score = (float)r[2];
+        pk[k].id = (int)r[3];
+        xy[2 * k] = r[0];
+        xy[2 * k + 1] = r[1];
+        sc[k] = r[2];
+    }
+    const size_t off = (size_t)image * kParts * cap;
+    CU(cudaMemcpy(h->d_peaks + off, pk.data(), pk.size() * sizeof(DevPeak), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_subpix + off * 2, xy.data(), xy.size() * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_score64 + off, sc.data(), sc.size() * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_part_count + (size_t)image * kParts, counts, sizeof(counts), cudaMemcpyHostToDevice));
+    CU(cudaMemset(h->d_status + image, 0, sizeof(uint32_t)));
+    memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
+    h->h_n_peaks[image] = n;
+    h->use_score64 = 1;
+    h->order_batch = 0;
+    return IBP_OK;
+}
+
+int ibp_find_connections(ibp_handle *h, const ibp_py_params *params, const double *paf, int chan_stride, int batch, int img_h, int img_w,
+                         int img_height, void *stream) {
+    if (!h || !paf) return fail(IBP_ERR_ARG, "ibp_find_connections: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_find_connections: batch %d exceeds limit %d", batch, h->L.max_batch);
+    if (img_h < 1 || img_w < 1 || chan_stride < kLimbs) return fail(IBP_ERR_SHAPE, "ibp_find_connections: bad shape");
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_py(h);
+    if (rc != IBP_OK) return rc;
+    PyConnArgs a;
+    a.P = to_py(params);
+    if (a.P.mid_num < 1 || a.P.mid_num > kPyMaxSteps) return fail(IBP_ERR_ARG, "ibp_find_connections: mid_num must be in [1,%d]", kPyMaxSteps);
+    a.peaks = h->d_peaks;
+    a.subpix = h->d_subpix;
+    a.score64 = h->use_score64 ? h->d_score64 : nullptr;
+    a.part_count = h->d_part_count;
+    a.cap = h->L.max_peaks_per_part;
+    a.paf = paf;
+    a.paf_chan_stride = chan_stride;
+    a.H = img_h;
+    a.W = img_w;
+    a.img_height = img_height;
+    a.cand_cap = h->L.max_candidates_per_limb;
+    a.conn = h->d_py_conn;
+    a.conn_count = h->d_py_conn_count;
+    a.cand_score = h->d_py_cand;
+    a.line_stride = h->line_stride;
+    a.status = h->d_status;
+    const size_t smem = (size_t)a.cap * (2 * sizeof(PyPeak) + 2) + (size_t)a.cand_cap * (3 * 8 + 4 + 4) + 16;
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_ARG, "ibp_find_connections: limits need %zu B of shared memory", smem);
+    {
+        StageTimer t(h, IBP_STAGE_LIMBS, (cudaStream_t)stream);
+        py_connections_kernel<<<dim3(kLimbs, batch), kPyThreads, smem, (cudaStream_t)stream>>>(a);
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+int ibp_fetch_connections(ibp_handle *h, int image, double *rows, int32_t *counts, void *stream) {
+    if (!h || !rows || !counts) return fail(IBP_ERR_ARG, "ibp_fetch_connections: null argument");
+    if (image < 0 || image >= h->L.max_batch || !h->d_py_conn) return fail(IBP_ERR_ARG, "ibp_fetch_connections: nothing to fetch for image %d", image);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t cap = h->L.max_peaks_per_part;
+    CU(cudaMemcpyAsync(counts, h->d_py_conn_count + (size_t)image * kLimbs, kLimbs * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(rows, h->d_py_conn + (size_t)image * kLimbs * cap * 6, kLimbs * cap * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return IBP_OK;
+}
+
+int ibp_set_connections(ibp_handle *h, int image, const double *rows, const int32_t *counts, const double *cand_score, int n_cand) {
+    if (!h || !rows || !counts || (n_cand > 0 && !cand_score)) return fail(IBP_ERR_ARG, "ibp_set_connections: null argument");
+    if (image < 0 || image >= h->L.max_batch || n_cand < 0) return fail(IBP_ERR_ARG, "ibp_set_connections: image %d out of range", image);
+    if (n_cand > h->line_stride) return fail(IBP_ERR_CAPACITY, "ibp_set_connections: %d joint candidates exceed %d", n_cand, h->line_stride);
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_py(h);
+    if (rc != IBP_OK) return rc;
+    const size_t cap = h->L.max_peaks_per_part;
+    for (int l = 0; l < kLimbs; l++)
+        if (counts[l] < 0 || (size_t)counts[l] > cap) return fail(IBP_ERR_CAPACITY, "ibp_set_connections: limb %d has %d rows (max %zu)", l, counts[l], cap);
+    CU(cudaMemcpy(h->d_py_conn + (size_t)image * kLimbs * cap * 6, rows, kLimbs * cap * 6 * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(h->d_py_conn_count + (size_t)image * kLimbs, counts, kLimbs * sizeof(int), cudaMemcpyHostToDevice));
+    if (n_cand > 0) CU(cudaMemcpy(h->d_py_cand + (size_t)image * h->line_stride, cand_score, (size_t)n_cand * sizeof(double), cudaMemcpyHostToDevice));
+    CU(cudaMemset(h->d_status + image, 0, sizeof(uint32_t)));
+    return IBP_OK;
+}
+
+int ibp_find_humans(ibp_handle *h, const ibp_py_params *params, int batch, void *stream) {
+    if (!h) return fail(IBP_ERR_ARG, "ibp_find_humans: null handle");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_find_humans: batch %d exceeds limit %d", batch, h->L.max_batch);
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_py(h);
+    if (rc != IBP_OK) return rc;
+    PyHumanArgs a;
+    a.conn = h->d_py_conn;
+    a.conn_count = h->d_py_conn_count;
+    a.part_count = h->d_part_count;
+    a.cap = h->L.max_peaks_per_part;
+    a.cand_score = h->d_py_cand;
+    a.line_stride = h->line_stride;
+    a.P = to_py(params);
+    a.max_bodies = h->L.max_bodies;
+    a.max_humans = h->L.max_humans;
+    a.people = h->d_py_people;
+    a.n_people = h->d_py_n_people;
+    a.status = h->d_status;
+    const size_t smem = (size_t)a.max_bodies * 40 * sizeof(double);
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_ARG, "ibp_find_humans: max_bodies=%d needs %zu B of shared memory (max %zu)", a.max_bodies, smem, kMaxDynSmem);
+    {
+        StageTimer t(h, IBP_STAGE_GROUP, (cudaStream_t)stream);
+        py_humans_kernel<<<batch, 32, smem, (cudaStream_t)stream>>>(a);
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+int ibp_fetch_people(ibp_handle *h, int image, double *people, int capacity, void *stream) {
+    if (!h || !people) return fail(IBP_ERR_ARG, "ibp_fetch_people: null argument");
+    if (image < 0 || image >= h->L.max_batch || !h->d_py_people) return fail(IBP_ERR_ARG, "ibp_fetch_people: nothing to fetch for image %d", image);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    uint32_t status = 0;
+    CU(cudaMemcpyAsync(&n, h->d_py_n_people + image, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&status, h->d_status + image, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    if (status & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
+        return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", status);
+    if (n > capacity) return fail(IBP_ERR_CAPACITY, "ibp_fetch_people: %d people, room for %d", n, capacity);
+    if (n > 0) {
+        CU(cudaMemcpyAsync(people, h->d_py_people + (size_t)image * h->L.max_humans * 40, (size_t)n * 40 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    return n;
 }
 
 // ------------------------------------------------------------------------------------------------ legacy protocol

@@ -4,6 +4,8 @@ Same function names, argument order and return containers; no C
     predict_refactor   parse_skeletons.py:28-103
     predict            parse_skeletons.py:180-283 (original route: scale search + flip fusion at image resolution)
     heatmap_nms        parse_skeletons.py:126-176
+    find_connections   parse_skeletons.py:324-410 (Python semantics, float64)
+    find_humans        parse_skeletons.py:413-599 (Python semantics, float64)
     find_peaks         parse_skeletons.py:286-321 (original route: 3x3 NMS + centroid refinement, utils/util.py:177-213)
     limb_upsample      evaluate.py:77-80 (the cv2.resize between heatmap_nms and process_paf)
 """
@@ -160,3 +162,61 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
     fused, _ = pp.fuse_multiscale(outs, sizes, img_h, img_w, flip_avg, want_heat32=False)
     hwc = fused[0].permute(1, 2, 0).contiguous().cpu().numpy()
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
+
+
+def _check_pairs(joint2limb_pairs):
+    from .config import LIMBS
+    if joint2limb_pairs is not None and [tuple(p) for p in joint2limb_pairs] != [tuple(p) for p in LIMBS]:
+        raise ValueError("joint2limb_pairs must be the 30 canonical limbs (config/config.py:114-121)")
+
+
+def find_connections(all_peaks, paf_avg, img_height, test_cfg, joint2limb_pairs=None):
+    """-> (connected_limbs, special_limb) like parse_skeletons.py:324-410: connected_limbs[k] is [] when both joint
+    lists of limb k are empty (k is listed in special_limb), else an (n,6) float64 array of rows
+    [src_peak_id, dst_peak_id, score, i, j, length].  all_peaks: 18 lists of (x, y, score, id); paf_avg (H,W,30)."""
+    _check_pairs(joint2limb_pairs)
+    pp = _processor()
+    rows = np.array([tuple(float(v) for v in p) for ps in all_peaks for p in ps], dtype=np.float64).reshape(-1, 4)
+    part = np.array([t for t, ps in enumerate(all_peaks) for _ in ps], dtype=np.int32)
+    pp.handle.set_peaks64(0, rows, part)
+    paf = torch.from_numpy(np.ascontiguousarray(np.asarray(paf_avg, dtype=np.float64)[:, :, :NUM_PAFS].transpose(2, 0, 1)))
+    paf = paf.to(pp.device)
+    H, W = paf.shape[1:]
+    with torch.cuda.device(pp.device):
+        pp.handle.find_connections(_lib.py_params(test_cfg), paf.data_ptr(), NUM_PAFS, 1, H, W, img_height,
+                                   torch.cuda.current_stream(pp.device).cuda_stream)
+        got, counts = pp.handle.fetch_connections(0, torch.cuda.current_stream(pp.device).cuda_stream)
+    from .config import LIMBS
+    connected, special = [], []
+    for k, (a, b) in enumerate(LIMBS):
+        if len(all_peaks[a]) == 0 and len(all_peaks[b]) == 0:
+            special.append(k)
+            connected.append([])
+        else:
+            connected.append(got[k, :counts[k]].copy())
+    return connected, special
+
+
+def find_humans(connected_limbs, special_limb, joint_list, test_cfg, joint2limb_pairs=None):
+    """-> (person_to_joint_assoc (P,20,2) float64, joint_candidates (N,4)) like parse_skeletons.py:413-599."""
+    _check_pairs(joint2limb_pairs)
+    pp = _processor()
+    cand = np.array([item for sub in joint_list for item in sub])  # l.427
+    cap = pp.handle.limits.max_peaks_per_part
+    rows = np.zeros((NUM_PAFS, cap, 6), dtype=np.float64)
+    counts = np.zeros(NUM_PAFS, dtype=np.int32)
+    for k in range(NUM_PAFS):
+        if k in special_limb or len(connected_limbs[k]) == 0:
+            continue
+        r = np.asarray(connected_limbs[k], dtype=np.float64).reshape(-1, 6)
+        if r.shape[0] > cap:
+            raise _lib.IbpError(-3, "limb %d has %d connections (max %d)" % (k, r.shape[0], cap))
+        rows[k, :r.shape[0]] = r
+        counts[k] = r.shape[0]
+    scores = cand[:, 2].astype(np.float64) if cand.size else np.zeros(0)
+    pp.handle.set_connections(0, rows, counts, scores)
+    with torch.cuda.device(pp.device):
+        st = torch.cuda.current_stream(pp.device).cuda_stream
+        pp.handle.find_humans(_lib.py_params(test_cfg), 1, st)
+        people = pp.handle.fetch_people(0, st)
+    return people, cand

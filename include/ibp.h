@@ -202,6 +202,37 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream);
  * ibp_fetch, copies image `image`'s (x, y) pairs in peak-id order into host_xy[capacity][2].  Returns the number of
  * peaks written (>= 0) or a negative error code. */
 int ibp_fetch_subpix(ibp_handle *h, int image, double *host_xy, int capacity, void *stream);
+/* ---------------------------------------------------------------------------------------------------------------
+ * 4. The reference's PYTHON assignment route in float64 — utils/parse_skeletons.py:324-410 (find_connections) and
+ *    :413-599 (find_humans), what evaluate.py:88-90 runs without --run_cpp and the only grouping of the original
+ *    route (predict + find_peaks).  Peaks come from ibp_find_peaks(IBP_PEAKS_BOX_CENTROID) (device resident) or from
+ *    ibp_set_peaks64.  Parameters are the Python floats of utils/config (the C++ constants are float32).
+ * ------------------------------------------------------------------------------------------------------------- */
+typedef struct ibp_py_params {
+    double thre2;           /* 0.1  utils/config:17 */
+    double connect_ration;  /* 0.8  utils/config:18 */
+    int32_t mid_num;        /* 20   utils/config:20 */
+    int32_t len_rate;       /* 16   utils/config:21 */
+    double connection_tole; /* 0.7  utils/config:22 */
+    double min_score;       /* 0.45 literal at parse_skeletons.py:594 */
+    int32_t min_parts;      /* 2    literal at parse_skeletons.py:594 */
+} ibp_py_params;
+void ibp_default_py_params(ibp_py_params *p);
+/* all_peaks of ONE image as host rows (n,4) [x, y, score, id] float64 with their joint type part[n], in list order. */
+int ibp_set_peaks64(ibp_handle *h, int image, const double *rows, const int32_t *part, int n);
+/* find_connections: paf (batch, chan_stride>=30, img_h, img_w) planar float64 DEVICE pointer (ibp_fuse_multiscale's
+ * `out`); img_height is the reference's third argument (evaluate.py:89). */
+int ibp_find_connections(ibp_handle *h, const ibp_py_params *params, const double *paf, int chan_stride, int batch,
+                         int img_h, int img_w, int img_height, void *stream);
+/* connected_limbs of one image: rows (30, max_peaks_per_part, 6) [src_id, dst_id, score, i, j, length], counts[30]. */
+int ibp_fetch_connections(ibp_handle *h, int image, double *rows, int32_t *counts, void *stream);
+/* explicit connected_limbs + joint_candidates[:, 2] for find_humans (same layout as ibp_fetch_connections). */
+int ibp_set_connections(ibp_handle *h, int image, const double *rows, const int32_t *counts, const double *cand_score,
+                        int n_cand);
+int ibp_find_humans(ibp_handle *h, const ibp_py_params *params, int batch, void *stream);
+/* person_to_joint_assoc of one image: people (n,20,2) float64; returns n (>= 0) or a negative error code. */
+int ibp_fetch_people(ibp_handle *h, int image, double *people, int capacity, void *stream);
+
 /* number of kernels this library has launched through `h` since creation (bench.py's gpu_launches) */
 int64_t ibp_launch_count(const ibp_handle *h);
 

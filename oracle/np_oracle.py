@@ -299,3 +299,101 @@ def predict_fuse(net_outs, img_h, img_w, scales, stride=4, max_downsample=64, fl
         heatmap_avg = heatmap_avg + heat / n                                              # l.280 (float32 / int, then + in float64)
         paf_avg = paf_avg + paf / n                                                       # l.281
     return heatmap_avg, paf_avg
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A14  connections, Python semantics — utils/parse_skeletons.py:324-410 (find_connections)
+# ----------------------------------------------------------------------------------------------------------
+def find_connections(all_peaks, paf_avg, img_height, thre2=0.1, connect_ration=0.8, mid_num_max=20, pairs=LIMBS):
+    """all_peaks: 18 lists of (x, y, score, id); paf_avg (H,W,30).  -> (connected_limbs, special_limb):
+    connected_limbs[k] = [] when both joint lists are empty (k goes to special_limb), else (n,6) float64 rows
+    [src_peak_id, dst_peak_id, score, i, j, length].  Differences from the C++ route: float peak
+    positions, np.linspace + half-to-even rounding of the sample points, float64 arithmetic, stable sort."""
+    connected, special = [], []
+    for k, (pa, pb) in enumerate(pairs):
+        src_list, dst_list = all_peaks[pa], all_peaks[pb]
+        if len(src_list) == 0 and len(dst_list) == 0:           # l.339-341
+            special.append(k)
+            connected.append([])
+            continue
+        plane = paf_avg[:, :, k]
+        cands = []
+        for i, s in enumerate(src_list):
+            s = np.array(s)                                     # mixed tuple -> float64 vector (l.347)
+            for j, d in enumerate(dst_list):
+                d = np.array(d)
+                delta = d[:2] - s[:2]
+                length = np.sqrt(np.sum(delta ** 2))            # l.353
+                n = min(int(round(length + 1)), mid_num_max)    # l.354: Python round = half to even
+                if length == 0.0:                               # l.357
+                    continue
+                xs = np.round(np.linspace(s[0], d[0], num=n)).astype(np.intp)   # l.361
+                ys = np.round(np.linspace(s[1], d[1], num=n)).astype(np.intp)   # l.362
+                vals = plane[ys, xs]
+                score = vals.mean() + min(0.5 * img_height / length - 1, 0)    # l.367
+                if np.count_nonzero(vals > thre2) > n * connect_ration and score > 0:      # l.373-378
+                    cands.append((i, j, score, length, 0.5 * score + 0.25 * s[2] + 0.25 * d[2]))   # l.381
+        cands.sort(key=lambda c: c[4], reverse=True)            # l.391: stable, ties keep pair order
+        limit = min(len(src_list), len(dst_list))
+        rows, used_i, used_j = [], set(), set()
+        for i, j, score, length, _ in cands:                    # l.397-407
+            if i not in used_i and j not in used_j:
+                rows.append([src_list[i][3], dst_list[j][3], score, i, j, length])
+                used_i.add(i)
+                used_j.add(j)
+                if len(rows) >= limit:
+                    break
+        connected.append(np.array(rows, dtype=np.float64).reshape(-1, 6))
+    return connected, special
+
+
+# ----------------------------------------------------------------------------------------------------------
+# A15  people, Python semantics — utils/parse_skeletons.py:413-599 (find_humans)
+# ----------------------------------------------------------------------------------------------------------
+def find_humans(connected_limbs, special_limb, joint_list, len_rate=16, connection_tole=0.7, pairs=LIMBS):
+    """-> (person_to_joint_assoc (P,20,2) float64, joint_candidates (N,4) float64).  Rows: [part] = (peak id, limb
+    score), [18] = (total score, -1), [19] = (count, last limb length).  remove_recon = 0 (utils/config:27)."""
+    cand = np.array([item for sub in joint_list for item in sub])
+    people = []  # list of (20,2) float64 arrays, order = creation order minus deletions
+    for k, (pa, pb) in enumerate(pairs):
+        if k in special_limb:
+            continue
+        for info in connected_limbs[k]:
+            src_id, dst_id, score, length = info[0], info[1], info[2], info[5]
+            hit = [p for p in people if p[pa, 0] == src_id or p[pb, 0] == dst_id][:2]   # l.441-449: third match ignored
+            if len(hit) == 1:
+                p = hit[0]
+                cur_id, cur_sc, reach = p[pb, 0], p[pb, 1], p[19, 1]
+                if int(cur_id) == -1 and reach * len_rate > length:                       # l.458
+                    p[pb] = [dst_id, score]
+                    p[19, 0] += 1
+                    p[19, 1] = max(length, reach)
+                    p[18, 0] += cand[int(dst_id), 2] + score
+                elif (int(cur_id) != int(dst_id) and cur_sc <= score and reach * len_rate > length) or \
+                        (int(cur_id) == int(dst_id) and cur_sc <= score):                 # l.473-475, l.483-484
+                    p[18, 0] -= cand[int(cur_id), 2] + cur_sc
+                    p[pb] = [dst_id, score]
+                    p[19, 1] = max(length, reach)
+                    p[18, 0] += cand[int(dst_id), 2] + score
+            elif len(hit) == 2:
+                p1, p2 = hit
+                m1, m2 = p1[:18, 0] >= 0, p2[:18, 0] >= 0
+                if not np.any(m1 & m2):                                                   # l.506
+                    tol = min(np.min(p1[:18, 1][m1]), np.min(p2[:18, 1][m2]))
+                    if score >= connection_tole * tol and length < p1[19, 1] * len_rate:  # l.511-512
+                        reach = p1[19, 1]
+                        p1[:18] = np.maximum(p1[:18], p2[:18])
+                        p1[19, 0] += p2[19, 0]
+                        p1[19, 1] = max(length, reach)
+                        p1[18, 0] += p2[18, 0] + score
+                        people = [p for p in people if p is not p2]
+            else:                                                                         # l.570-585
+                row = -1 * np.ones((20, 2))
+                row[pa] = [src_id, score]
+                row[pb] = [dst_id, score]
+                row[19] = [2, length]
+                row[18, 0] = sum(cand[[int(src_id), int(dst_id)], 2]) + score
+                people.append(row)
+    keep = [p for p in people if not (p[19, 0] < 2 or p[18, 0] / p[19, 0] < 0.45)]         # l.591-596
+    assoc = np.array(keep, dtype=np.float64).reshape(-1, 20, 2)
+    return assoc, cand
