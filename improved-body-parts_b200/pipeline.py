@@ -82,6 +82,33 @@ class PostProcessor:
         self._keep_ms = ts
         return out, heat32
 
+    def original_route(self, net_outs, scaled_sizes, img_h, img_w, test_cfg=None, flip_avg=True):
+        """The reference's ORIGINAL route for a batch, device resident end to end (evaluate.py:82-90 without flags):
+        predict (scale search + flip fusion at image resolution) -> find_peaks (3x3 NMS, centroid refinement) ->
+        find_connections -> find_humans (Python semantics, float64).  The handle's peak_thresh / refine_window must be
+        the route's thre1 / offset_radius (both equal the defaults).  Returns a list per image of
+        (all_peaks table (N,4) float64 [x,y,score,id], part_count (18,), person_to_joint_assoc (P,20,2) float64)."""
+        fused, heat32 = self.fuse_multiscale(net_outs, scaled_sizes, img_h, img_w, flip_avg, want_heat32=True)
+        B = fused.shape[0]
+        params = _lib.py_params(test_cfg)
+        with torch.cuda.device(self.device):
+            st = _stream_ptr(self.device)
+            self.handle.find_peaks(heat32.data_ptr(), _lib.NUM_PARTS, 0, B, img_h, img_w, _lib.PEAKS_BOX_CENTROID, st)
+            self.handle.find_connections(params, fused.data_ptr(), _lib.NUM_LAYERS, B, img_h, img_w, img_h, st)
+            self.handle.find_humans(params, B, st)
+            res = self.handle.fetch(B, st)
+            out = []
+            for b in range(B):
+                n = int(res.n_peaks[b])
+                xy = self.handle.fetch_subpix(b, n, st)
+                table = np.zeros((n, 4), dtype=np.float64)
+                table[:, :2] = xy
+                table[:, 2] = res.peaks[b]["score"]
+                table[:, 3] = np.arange(n)
+                out.append((table, res.part_count[b].copy(), self.handle.fetch_people(b, st)))
+        self._keep_or = (fused, heat32)
+        return out
+
     def upsample_limbs(self, fused, up=4):
         """(B,C>=30,h,w) planar -> (B, h*up, w*up, 30) HWC float32 (A4, evaluate.py:77-80)."""
         fused = fused.to(self.device, torch.float32).contiguous()

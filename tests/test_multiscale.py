@@ -103,3 +103,28 @@ def test_gpu_predict_mirror_with_canned_model():
         heat, paf = PS.predict(image, model, test_cfg, model_cfg, "synthetic", scale_search=ss)
         want_h, want_p = O.predict_fuse([canned[tuple(s[2])] for s in shapes], img_h, img_w, [s[0] for s in shapes])
         assert np.array_equal(heat, want_h) and np.array_equal(paf, want_p)
+
+
+@pytest.mark.gpu
+def test_gpu_original_route_device_resident():
+    """fuse_multiscale -> find_peaks -> find_connections -> find_humans without leaving the device, against the oracle
+    chain (each link of which is pinned to the reference by its own golden vectors)."""
+    import torch
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    img_h, img_w, ss = 240, 320, (1.0, 2.0)
+    shapes = synth.multiscale_shapes(img_h, img_w, ss)
+    cases = [synth.make_multiscale_output(70 + b, 2 + 3 * b, img_h, img_w, ss)[0] for b in range(3)]
+    pp = PostProcessor(device=0, max_batch=3)
+    ts = [torch.from_numpy(np.stack([c[s] for c in cases])).cuda() for s in range(len(ss))]
+    got = pp.original_route(ts, [s[1] for s in shapes], img_h, img_w)
+    for b, outs in enumerate(cases):
+        heat, paf = O.predict_fuse(outs, img_h, img_w, [s[0] for s in shapes])
+        peaks = O.find_peaks(heat, 0.1, 2)
+        table, counts = O.peaks_table(peaks)
+        cl, sp = O.find_connections(peaks, paf, img_h)
+        assoc, _ = O.find_humans(cl, sp, peaks)
+        assert np.array_equal(got[b][1], counts)
+        assert np.array_equal(got[b][0][:, :2], table[:, :2]) and np.array_equal(got[b][0][:, 2], table[:, 2])
+        assert np.array_equal(got[b][2], assoc)
+        assert assoc.shape[0] >= 1
