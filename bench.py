@@ -33,9 +33,8 @@ UNIT = "images/s"
 SEED = 2000  # 1000 * config_id + image index
 # algorithmic bytes per image at 128x128 fp32 (SURVEY.md §8d / DESIGN.md §5)
 ALGO_BYTES = {
-    "fuse": (2 * 50 + 50) * FEAT * FEAT * 4,   # read both flips, write the fused planes
-    "peaks": 18 * FEAT * FEAT * 4,             # keypoint planes read once
-    "limbs": 30 * FEAT * FEAT * 4,             # limb planes staged once
+    "peaks": 2 * 18 * FEAT * FEAT * 4,         # keypoint planes of the upright and the flipped output, read once
+    "limbs": 2 * 30 * FEAT * FEAT * 4,         # limb planes of the upright and the flipped output, read once
 }
 
 
@@ -47,6 +46,10 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="images in the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="configs1", choices=["configs1", "configs2", "configs3"],
+                    help="configs1 (default, the headline): batch 64 of 128x128x50 maps, refactored + C++ route; "
+                         "configs2: flip + 4-scale fusion to 640x480, original route; configs3: crowd 40-60 people")
+    ap.add_argument("--batch", type=int, default=0, help="images per step and GPU (0 = the workload's default)")
     return ap.parse_args()
 
 
@@ -95,11 +98,11 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_baseline(n_images):
+def cpu_baseline(n_images, wl=None):
     """The reference's CPU route (oracle/cpu_path.py) on a bounded sample of the same workload, all host cores."""
     from improved_body_parts_b200 import synth
     from oracle import cpu_path
-    sample = synth.make_batch(SEED, n_images, people=(1, 10), height=IMG, width=IMG)
+    sample = wl.cpu_sample(n_images) if wl is not None else synth.make_batch(SEED, n_images, people=(1, 10), height=IMG, width=IMG)
     secs, procs = cpu_path.time_batch(sample, IMG)
     return {"value": n_images / secs, "unit": UNIT, "cores": procs,
             "kind": "reference" if cpu_path.cpp_kind() == "reference" else "port",
@@ -135,16 +138,117 @@ def run_reference(args, rank, world):
             "gpu_launches": 0}
 
 
+class Refactored:
+    """configs[1] / configs[3]: B images of 128x128x50 maps with flip twin through the refactored + C++ route
+    (flip fusion -> heatmap_nms peaks -> limb scoring on the fly-upsampled maps -> pafprocess grouping): two kernels."""
+
+    def __init__(self, args, rank, dev, crowd):
+        import torch
+        from improved_body_parts_b200 import synth
+        from improved_body_parts_b200.pipeline import PostProcessor
+        self.batch = args.batch or BATCH
+        self.crowd = crowd
+        people, scale = ((40, 60), (0.2, 0.45)) if crowd else ((1, 10), (0.35, 0.9))
+        self.people = people
+        base = (3 if crowd else 2) * 1000  # SURVEY.md §8(d): 1000 * config_id + image index
+        sets = [synth.make_batch(base + 100000 * rank + 1000 * s, self.batch, people=people, height=IMG, width=IMG, scale=scale)
+                for s in range(2)]
+        self.host_sets = [torch.from_numpy(b).pin_memory() for b in sets]
+        self.dev_sets = [h.to(dev) for h in self.host_sets]
+        lim = dict(max_peaks_per_part=256, max_candidates_per_limb=1024, max_bodies=512, max_humans=256) if crowd else {}
+        self.pp = PostProcessor(device=dev.index, max_batch=self.batch, **lim)
+        self.workload = ("configs[3]: crowd stress, synthetic batch %d, 128x128x50 maps, flip twin, %d-%d people/image"
+                         if crowd else "configs[1]: synthetic batch %d, 512x512 input, stride-4 128x128x50 maps, flip twin, "
+                                       "%d-%d people/image") % (self.batch, people[0], people[1])
+        self.l2 = "2 rotating input sets of %d MB per rank, each larger than the 126 MB L2" % (self.host_sets[0].numel() * 4 // 1000000)
+        self.algo_bytes = dict(ALGO_BYTES)
+        self.route = "refactored + C++ (predict_refactor, heatmap_nms, process_paf)"
+
+    def step_dev(self, s):
+        self.pp.enqueue(self.dev_sets[s % 2], IMG)
+
+    def step_e2e(self, s):
+        self.pp.enqueue(self.host_sets[s % 2], IMG)   # pinned host -> device inside the timed region
+        self.last = self.pp.fetch(self.batch)          # packed skeletons device -> host
+
+    def finish(self):
+        self.last = self.pp.fetch(self.batch)
+
+    def h2d(self):
+        return self.host_sets[0].numel() * self.host_sets[0].element_size()
+
+    def d2h(self):
+        L = self.pp.handle.limits
+        return self.batch * (4 + 18 * 4 + L.max_peaks_per_part * 18 * 16 + 4 + L.max_humans * 88 + 4)
+
+    def humans(self):
+        return int(self.last.n_humans.sum())
+
+    def cpu_sample(self, n):
+        from improved_body_parts_b200 import synth
+        people, scale = ((40, 60), (0.2, 0.45)) if self.crowd else ((1, 10), (0.35, 0.9))
+        return synth.make_batch((3 if self.crowd else 2) * 1000, n, people=people, height=IMG, width=IMG, scale=scale)
+
+
+class MultiScale:
+    """configs[2]: flip + 4-scale fusion up-sampled to the 640x480 image, original route (predict -> find_peaks ->
+    find_connections -> find_humans, Python semantics in float64): four kernels."""
+    H, W, SS = 480, 640, (0.5, 1.0, 1.5, 2.0)
+
+    def __init__(self, args, rank, dev, crowd=False):
+        import torch
+        from improved_body_parts_b200 import synth
+        from improved_body_parts_b200.pipeline import PostProcessor
+        self.batch = args.batch or 32
+        self.shapes = synth.multiscale_shapes(self.H, self.W, self.SS)
+        distinct = min(8, self.batch)
+        imgs = [synth.make_multiscale_output(2000 + 100 * rank + i, 1 + (i * 3) % 12, self.H, self.W, self.SS)[0] for i in range(distinct)]
+        reps = -(-self.batch // distinct)
+        self.host = [torch.from_numpy(np.concatenate([np.stack([im[s] for im in imgs])] * reps)[:self.batch]).pin_memory()
+                     for s in range(len(self.SS))]
+        self.dev = [[h.to(dev) for h in self.host] for _ in range(2)]
+        self.sizes = [s[1] for s in self.shapes]
+        self.pp = PostProcessor(device=dev.index, max_batch=self.batch)
+        self.in_bytes = sum(h.numel() * 4 for h in self.host)
+        self.workload = ("configs[2]: flip + 4-scale fusion (0.5/1/1.5/2 x 512/480: maps 64x96..256x352) up-sampled to 640x480, "
+                         "batch %d (%d distinct images tiled), 1-12 people/image" % (self.batch, distinct))
+        self.l2 = "2 rotating input sets of %d MB per rank plus %d MB of float64 output per step, larger than the 126 MB L2" % (
+            self.in_bytes // 1000000, self.batch * 50 * self.H * self.W * 8 // 1000000)
+        px = self.H * self.W
+        self.algo_bytes = {"fuse": self.in_bytes // self.batch + 50 * px * 8 + 18 * px * 4, "peaks": 18 * px * 4}
+        self.route = "original (predict, find_peaks, find_connections, find_humans)"
+        self.dev_obj = dev
+
+    def step_dev(self, s):
+        self.pp.enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W)
+
+    def step_e2e(self, s):
+        ts = [h.to(self.dev_obj, non_blocking=True) for h in self.host]
+        self.pp.enqueue_original_route(ts, self.sizes, self.H, self.W)
+        self.last = self.pp.fetch_original_route(self.batch)
+
+    def finish(self):
+        self.last = self.pp.fetch_original_route(self.batch)
+
+    def h2d(self):
+        return self.in_bytes
+
+    def d2h(self):
+        return int(sum(t.nbytes + c.nbytes + p.nbytes for t, c, p in self.last))
+
+    def humans(self):
+        return int(sum(p.shape[0] for _, _, p in self.last))
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from improved_body_parts_b200.pipeline import PostProcessor
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    host_sets = [torch.from_numpy(b).pin_memory() for b in make_inputs(rank)]
-    dev_sets = [h.to(dev) for h in host_sets]
-    pp = PostProcessor(device=local_rank, max_batch=BATCH)
+    wl = {"configs1": lambda: Refactored(args, rank, dev, False), "configs3": lambda: Refactored(args, rank, dev, True),
+          "configs2": lambda: MultiScale(args, rank, dev)}[args.workload]()
+    pp, batch = wl.pp, wl.batch
 
     def barrier():
         if world > 1:
@@ -167,37 +271,32 @@ def run_ours(args, rank, world, local_rank):
         return float(ms.item())
 
     # ---- device-resident throughput (`value`) ----
-    def step_dev(s):
-        pp.enqueue(dev_sets[s % len(dev_sets)], IMG)
-
     for s in range(args.warmup):
-        step_dev(s)
-    pp.fetch(BATCH)
+        wl.step_dev(s)
+    wl.finish()
     launches0 = pp.handle.launches
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ms = timed(step_dev, args.steps)
+    ms = timed(wl.step_dev, args.steps)
     launches = pp.handle.launches - launches0
-    last = pp.fetch(BATCH)
+    wl.finish()
 
     # ---- end to end through the public API with HOST buffers (`e2e`) ----
-    def step_e2e(s):
-        pp.enqueue(host_sets[s % len(host_sets)], IMG)   # pinned host -> device inside the timed region
-        pp.fetch(BATCH)                                  # packed skeletons device -> host
     for s in range(min(args.warmup, 3)):
-        step_e2e(s)
-    ms_e2e = timed(step_e2e, args.steps)
+        wl.step_e2e(s)
+    ms_e2e = timed(wl.step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- per-kernel device times for the roofline (events on the launching stream inside the library) ----
     pp.handle.set_profiling(True)
     acc = {}
     for s in range(args.steps):
-        pp.enqueue(dev_sets[s % len(dev_sets)], IMG)
+        wl.step_dev(s)
         for k, v in pp.handle.stage_ms().items():
             acc.setdefault(k, []).append(v)
     pp.handle.set_profiling(False)
+    wl.finish()
     stage_ms = {k: float(np.mean(v)) for k, v in acc.items()}
     if rank != 0:
         return None
@@ -207,29 +306,27 @@ def run_ours(args, rank, world, local_rank):
         peak, peak_src = float(json.load(open(peaks_file))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
-    dominant = max((k for k in stage_ms if k in ALGO_BYTES), key=lambda k: stage_ms[k])
-    achieved = ALGO_BYTES[dominant] * BATCH / (stage_ms[dominant] * 1e-3) / 1e9
-    h2d = host_sets[0].numel() * host_sets[0].element_size()
-    view_bytes = BATCH * (4 + 18 * 4 + pp.handle.limits.max_peaks_per_part * 18 * 16 + 4 +
-                          pp.handle.limits.max_humans * 88 + 4)
-    out = {"metric": METRIC, "value": world * BATCH * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+    algo = wl.algo_bytes
+    dominant = max((k for k in stage_ms if k in algo), key=lambda k: stage_ms[k])
+    achieved = algo[dominant] * batch / (stage_ms[dominant] * 1e-3) / 1e9
+    out = {"metric": METRIC, "value": world * batch * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "global_batch": world * BATCH,
-                      "parallelism": "images sharded, %d rank(s), no collective" % world,
-                      "l2_policy": "2 rotating input sets of 419 MB per rank, each larger than the 126 MB L2"},
-           "e2e": {"value": world * BATCH * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
-                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": view_bytes},
+           "scaling": "weak", "vs_baseline": None, "dtype": "f64" if args.workload == "configs2" else "f32", "data": "synthetic",
+           "config": {"workload": wl.workload, "route": wl.route, "batch_per_gpu": batch, "global_batch": world * batch,
+                      "parallelism": "images sharded, %d rank(s), no collective" % world, "l2_policy": wl.l2},
+           "e2e": {"value": world * batch * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
+                   "h2d_bytes_per_step": wl.h2d(), "d2h_bytes_per_step": wl.d2h()},
            "gpu_launches": int(launches),
            "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                        "algorithmic_bytes_per_launch": ALGO_BYTES[dominant] * BATCH},
+                        "algorithmic_bytes_per_launch": algo[dominant] * batch},
            "stage_ms": stage_ms,
-           "stage_gbs": {k: ALGO_BYTES[k] * BATCH / (stage_ms[k] * 1e-3) / 1e9 for k in stage_ms if k in ALGO_BYTES},
-           "humans_last_batch": int(last.n_humans.sum())}
-    if not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(args.cpu_sample or max(8, 4 * (os.cpu_count() or 1)))
+           "stage_gbs": {k: algo[k] * batch / (stage_ms[k] * 1e-3) / 1e9 for k in stage_ms if k in algo},
+           "whole_step_gbs": sum(algo.values()) * batch / (ms / args.steps * 1e-3) / 1e9,
+           "humans_last_batch": wl.humans()}
+    if not args.no_cpu_baseline and hasattr(wl, "cpu_sample"):
+        out["cpu_baseline"] = cpu_baseline(args.cpu_sample or max(8, 4 * (os.cpu_count() or 1)), wl)
     return out
 
 

@@ -373,10 +373,14 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         memset(h->h_n_humans, 0, B * sizeof(int));
         memset(h->h_status, 0, B * sizeof(uint32_t));
         // opt in to large dynamic shared memory once
-        CU(cudaFuncSetAttribute(peaks_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(peaks_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(limbs_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(limbs_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<float, IBP_PEAKS_CROSS_REFINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<__half, IBP_PEAKS_CROSS_REFINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<float, IBP_PEAKS_BOX_CENTROID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_kernel<__half, IBP_PEAKS_BOX_CENTROID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<float, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<__half, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_kernel<__half, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         if (limb_phase_bytes(h, 0) > kMaxDynSmem)
@@ -593,10 +597,17 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     {
         StageTimer t(h, IBP_STAGE_PEAKS, st);
         const dim3 grid(a.nbands, kParts, batch);
-        if (dtype == IBP_F16)
-            peaks_kernel<__half><<<grid, kPeakThreads, smem, st>>>(a);
-        else
-            peaks_kernel<float><<<grid, kPeakThreads, smem, st>>>(a);
+        if (flavour == IBP_PEAKS_CROSS_REFINE) {
+            if (dtype == IBP_F16)
+                peaks_kernel<__half, IBP_PEAKS_CROSS_REFINE><<<grid, kPeakThreads, smem, st>>>(a);
+            else
+                peaks_kernel<float, IBP_PEAKS_CROSS_REFINE><<<grid, kPeakThreads, smem, st>>>(a);
+        } else {
+            if (dtype == IBP_F16)
+                peaks_kernel<__half, IBP_PEAKS_BOX_CENTROID><<<grid, kPeakThreads, smem, st>>>(a);
+            else
+                peaks_kernel<float, IBP_PEAKS_BOX_CENTROID><<<grid, kPeakThreads, smem, st>>>(a);
+        }
     }
     h->launches++;
     CU(cudaGetLastError());
@@ -736,10 +747,16 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     {
         StageTimer t(h, IBP_STAGE_LIMBS, st);
         const dim3 grid(kLimbs, batch);
-        if (dtype == IBP_F16)
-            limbs_kernel<__half><<<grid, kLimbThreads, smem, st>>>(a);
-        else
-            limbs_kernel<float><<<grid, kLimbThreads, smem, st>>>(a);
+        // a handle sized for crowds (more than 128 peaks per joint type) gets the wider CTA: thousands of pairs per limb
+        // want more warps per plane in flight; the usual image (tens of pairs) is quicker with fewer, cheaper barriers
+        const bool wide = h->L.max_peaks_per_part > 128;
+        if (dtype == IBP_F16) {
+            if (wide) limbs_kernel<__half, 512><<<grid, 512, smem, st>>>(a);
+            else limbs_kernel<__half, 256><<<grid, 256, smem, st>>>(a);
+        } else {
+            if (wide) limbs_kernel<float, 512><<<grid, 512, smem, st>>>(a);
+            else limbs_kernel<float, 256><<<grid, 256, smem, st>>>(a);
+        }
     }
     h->launches++;
     CU(cudaGetLastError());

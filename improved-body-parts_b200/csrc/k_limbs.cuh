@@ -62,8 +62,8 @@ struct LimbArgs {
     GroupArgs group;
 };
 
-constexpr int kLimbThreads = 256;
-constexpr int kPairChunk = 128;  // pairs scored per round
+constexpr int kLimbThreadsMax = 512;  // CTA size is a template parameter: 256 (default) or 512 (handles sized for crowds)
+constexpr int kPairChunk = 128;  // pairs scored per round on the two-phase path
 constexpr int kLimbRing = 4;      // slots of the twin-plane ring while staging
 constexpr int kRankSortMax = 512; // up to this many candidates are ordered by a rank sort, more by a bitonic network
 
@@ -101,7 +101,29 @@ struct PairGeo {  // step geometry of one pair (pafprocess.cpp:66-73, :311-316)
     int steps;  // 0: skipped (zero length)
 };
 
-template <typename T>
+__device__ __forceinline__ PairGeo pair_geometry(const DevPeak &A, const DevPeak &B, int max_steps) {
+    const float len = limb_length(A, B);
+    PairGeo g;
+    g.steps = 0;
+    g.ax = __int2float_rn(A.x);
+    g.ay = __int2float_rn(A.y);
+    g.sx = g.sy = 0.f;
+    if (!((double)len < 1e-12)) {                                                                     // :71
+        g.steps = min(__double2int_rz(__dadd_rn((double)__fadd_rn(len, 1.0f), 0.5)), max_steps);  // :73
+        const float denom = __int2float_rn(g.steps - 1);
+        g.sx = __fdiv_rn(__int2float_rn(B.x - A.x), denom);  // :315
+        g.sy = __fdiv_rn(__int2float_rn(B.y - A.y), denom);  // :316
+    }
+    return g;
+}
+// sample point i of a pair: :319-320 with round2int (:329-331): float multiply, float add, +0.5 in double, truncate
+__device__ __forceinline__ void pair_sample_xy(const PairGeo &g, int i, int &px, int &py) {
+    const float fi = __int2float_rn(i);
+    px = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ax, __fmul_rn(fi, g.sx)), 0.5));
+    py = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ay, __fmul_rn(fi, g.sy)), 0.5));
+}
+
+template <typename T, int kLimbThreads>
 __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int limb = blockIdx.x;
@@ -239,58 +261,58 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         // ---- score all pairs; compact the accepted ones in pair order ----
         const int npairs = (a.debug & 2) ? 0 : nA * nB;
         int ncand = 0;
-        for (int base = 0; base < npairs; base += kPairChunk) {
-            const int chunk = min(kPairChunk, npairs - base);
-            // (0) geometry, one thread per pair
-            if (tid < chunk) {
-                const int p = base + tid;
-                const int ia = p / nB, ib = p - ia * nB;
-                const DevPeak A = sA[ia], B = sB[ib];
-                const float len = limb_length(A, B);
-                PairGeo g;
-                g.steps = 0;
-                g.ax = __int2float_rn(A.x);
-                g.ay = __int2float_rn(A.y);
-                g.sx = g.sy = 0.f;
-                if (!((double)len < 1e-12)) {                                                                       // :71
-                    g.steps = min(__double2int_rz(__dadd_rn((double)__fadd_rn(len, 1.0f), 0.5)), a.max_steps);  // :73
-                    const float denom = __int2float_rn(g.steps - 1);
-                    g.sx = __fdiv_rn(__int2float_rn(B.x - A.x), denom);  // :315
-                    g.sy = __fdiv_rn(__int2float_rn(B.y - A.y), denom);  // :316
+        // Few pairs (the usual image): split every pair's samples over the threads (phases 0-2 below).  Many pairs (a
+        // crowd): one thread per pair does its own samples — enough parallelism already, no staging, fewer barriers.
+        const bool direct = npairs > kLimbThreads;
+        const int chunk_size = direct ? kLimbThreads : kPairChunk;
+        for (int base = 0; base < npairs; base += chunk_size) {
+            const int chunk = min(chunk_size, npairs - base);
+            if (!direct) {
+                // (0) geometry, one thread per pair
+                if (tid < chunk) {
+                    const int p = base + tid;
+                    const int ia = p / nB, ib = p - ia * nB;
+                    geo[tid] = pair_geometry(sA[ia], sB[ib], a.max_steps);
                 }
-                geo[tid] = g;
-            }
-            __syncthreads();
-            // (1) samples, one thread per (pair, step)
-            for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
-                const int q = it / a.max_steps, i = it - q * a.max_steps;
-                const PairGeo g = geo[q];
-                if (i < g.steps) {
-                    const float fi = __int2float_rn(i);
-                    const int px = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ax, __fmul_rn(fi, g.sx)), 0.5));  // :319, :329-331
-                    const int py = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ay, __fmul_rn(fi, g.sy)), 0.5));  // :320
-                    vals[it] = smp.at(px, py);
+                __syncthreads();
+                // (1) samples, one thread per (pair, step)
+                for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
+                    const int q = it / a.max_steps, i = it - q * a.max_steps;
+                    const PairGeo g = geo[q];
+                    if (i < g.steps) {
+                        int px, py;
+                        pair_sample_xy(g, i, px, py);
+                        vals[it] = smp.at(px, py);
+                    }
                 }
+                __syncthreads();
             }
-            __syncthreads();
             // (2) criteria, one thread per pair
             bool ok = false;
             float ls = 0.f, rk = 0.f;
             int ia = 0, ib = 0;
             if (tid < chunk) {
-                const PairGeo g = geo[tid];
+                const int p = base + tid;
+                ia = p / nB;
+                ib = p - ia * nB;
+                const DevPeak A = sA[ia], B = sB[ib];
+                const PairGeo g = direct ? pair_geometry(A, B, a.max_steps) : geo[tid];
                 if (g.steps > 0) {
-                    const int p = base + tid;
-                    ia = p / nB;
-                    ib = p - ia * nB;
-                    const DevPeak A = sA[ia], B = sB[ib];
                     const float len = limb_length(A, B);
                     const float *v = vals + tid * a.max_steps;
                     float sum = 0.0f;
                     int above = 0;
                     for (int i = 0; i < g.steps; i++) {
-                        sum = __fadd_rn(sum, v[i]);   // :85
-                        above += (v[i] > a.thr);      // :87
+                        float vi;
+                        if (direct) {
+                            int px, py;
+                            pair_sample_xy(g, i, px, py);
+                            vi = smp.at(px, py);
+                        } else {
+                            vi = v[i];
+                        }
+                        sum = __fadd_rn(sum, vi);   // :85
+                        above += (vi > a.thr);      // :87
                     }
                     // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
                     const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);

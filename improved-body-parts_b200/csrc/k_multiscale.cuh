@@ -129,33 +129,69 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             }
         }
         __syncthreads();
+        // Stages B-D give every thread ONE column and let it walk rows: the four taps and weights of the column live in
+        // registers, there is no index division in the loops, and a warp reads consecutive columns of a row.
         // ---- B: first resize, horizontal pass: feature rows x intermediate columns ----
-        for (int i = tid; i < n_fy * n_rx; i += kMsThreads) {
-            const int r = i / n_rx, c = i - r * n_rx;
-            const int rx = rx_lo + c;
-            const int sx = (rx - 2) >> 2;
-            const float *w4 = tab4[(rx - 2) & 3];
-            const float *row = F + r * n_fx - fx_lo;
-            T1[i] = hsum4(row[clampi(sx - 1, 0, S.w - 1)], row[clampi(sx, 0, S.w - 1)], row[clampi(sx + 1, 0, S.w - 1)],
-                          row[clampi(sx + 2, 0, S.w - 1)], w4);
+        if (n_rx <= kMsThreads) {
+            const int groups = kMsThreads / n_rx, g = tid / n_rx, c = tid - g * n_rx;
+            if (g < groups) {
+                const int rx = rx_lo + c;
+                const int sx = (rx - 2) >> 2;
+                const float w0 = tab4[(rx - 2) & 3][0], w1 = tab4[(rx - 2) & 3][1], w2 = tab4[(rx - 2) & 3][2], w3 = tab4[(rx - 2) & 3][3];
+                const float wv[4] = {w0, w1, w2, w3};
+                const int i0 = clampi(sx - 1, 0, S.w - 1) - fx_lo, i1 = clampi(sx, 0, S.w - 1) - fx_lo;
+                const int i2 = clampi(sx + 1, 0, S.w - 1) - fx_lo, i3 = clampi(sx + 2, 0, S.w - 1) - fx_lo;
+                for (int r = g; r < n_fy; r += groups) {
+                    const float *row = F + r * n_fx;
+                    T1[r * n_rx + c] = hsum4(row[i0], row[i1], row[i2], row[i3], wv);
+                }
+            }
+        } else {
+            for (int i = tid; i < n_fy * n_rx; i += kMsThreads) {
+                const int r = i / n_rx, c = i - r * n_rx;
+                const int rx = rx_lo + c;
+                const int sx = (rx - 2) >> 2;
+                const float *row = F + r * n_fx - fx_lo;
+                T1[i] = hsum4(row[clampi(sx - 1, 0, S.w - 1)], row[clampi(sx, 0, S.w - 1)], row[clampi(sx + 1, 0, S.w - 1)],
+                              row[clampi(sx + 2, 0, S.w - 1)], tab4[(rx - 2) & 3]);
+            }
         }
         __syncthreads();
         // ---- C: first resize, vertical pass (always the vector formula: padded widths are multiples of 64) ----
-        for (int i = tid; i < n_ry * n_rx; i += kMsThreads) {
-            const int r = i / n_rx, c = i - r * n_rx;
-            const int ry = ry_lo + r;
-            const int sy = (ry - 2) >> 2;
-            const float *w4 = tab4[(ry - 2) & 3];
-            const int q0 = clampi(sy - 1, 0, S.h - 1) - fy_lo, q1 = clampi(sy, 0, S.h - 1) - fy_lo;
-            const int q2 = clampi(sy + 1, 0, S.h - 1) - fy_lo, q3 = clampi(sy + 2, 0, S.h - 1) - fy_lo;
-            I[i] = vsum4(T1[q0 * n_rx + c], T1[q1 * n_rx + c], T1[q2 * n_rx + c], T1[q3 * n_rx + c], w4);
+        if (n_rx <= kMsThreads) {
+            const int groups = kMsThreads / n_rx, g = tid / n_rx, c = tid - g * n_rx;
+            if (g < groups) {
+                for (int r = g; r < n_ry; r += groups) {
+                    const int ry = ry_lo + r;
+                    const int sy = (ry - 2) >> 2;
+                    const int q0 = clampi(sy - 1, 0, S.h - 1) - fy_lo, q1 = clampi(sy, 0, S.h - 1) - fy_lo;
+                    const int q2 = clampi(sy + 1, 0, S.h - 1) - fy_lo, q3 = clampi(sy + 2, 0, S.h - 1) - fy_lo;
+                    I[r * n_rx + c] = vsum4(T1[q0 * n_rx + c], T1[q1 * n_rx + c], T1[q2 * n_rx + c], T1[q3 * n_rx + c], tab4[(ry - 2) & 3]);
+                }
+            }
+        } else {
+            for (int i = tid; i < n_ry * n_rx; i += kMsThreads) {
+                const int r = i / n_rx, c = i - r * n_rx;
+                const int ry = ry_lo + r;
+                const int sy = (ry - 2) >> 2;
+                const int q0 = clampi(sy - 1, 0, S.h - 1) - fy_lo, q1 = clampi(sy, 0, S.h - 1) - fy_lo;
+                const int q2 = clampi(sy + 1, 0, S.h - 1) - fy_lo, q3 = clampi(sy + 2, 0, S.h - 1) - fy_lo;
+                I[i] = vsum4(T1[q0 * n_rx + c], T1[q1 * n_rx + c], T1[q2 * n_rx + c], T1[q3 * n_rx + c], tab4[(ry - 2) & 3]);
+            }
         }
         __syncthreads();
         // ---- D: second resize, horizontal pass: intermediate rows x output columns ----
-        for (int i = tid; i < n_ry * nX; i += kMsThreads) {
-            const int r = i / nX, c = i - r * nX;
-            const float *row = I + r * n_rx - rx_lo;
-            T2[r * kMsTileX + c] = hsum4(row[x_idx[c][0]], row[x_idx[c][1]], row[x_idx[c][2]], row[x_idx[c][3]], x_w[c]);
+        {
+            constexpr int groups = kMsThreads / kMsTileX;
+            const int g = tid / kMsTileX, c = tid % kMsTileX;
+            if (c < nX) {
+                const int i0 = x_idx[c][0] - rx_lo, i1 = x_idx[c][1] - rx_lo, i2 = x_idx[c][2] - rx_lo, i3 = x_idx[c][3] - rx_lo;
+                const float wv[4] = {x_w[c][0], x_w[c][1], x_w[c][2], x_w[c][3]};
+                for (int r = g; r < n_ry; r += groups) {
+                    const float *row = I + r * n_rx;
+                    T2[r * kMsTileX + c] = hsum4(row[i0], row[i1], row[i2], row[i3], wv);
+                }
+            }
         }
         __syncthreads();
         // ---- E: second resize, vertical pass, /n_scales in float32, accumulate in float64 (l.280-281) ----

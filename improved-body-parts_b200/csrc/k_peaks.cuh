@@ -102,8 +102,10 @@ __device__ __forceinline__ double np_pairwise_sum_f64(const double *a, int n) {
     return res;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
+// FLAVOUR is a template parameter so that the heatmap_nms instantiation does not carry the registers of the float64
+// centroid code (and the other way round).
+template <typename T, int FLAVOUR>
+__global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int bandi = blockIdx.x, part = blockIdx.y, img = blockIdx.z;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -174,7 +176,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     // and torch's reflect-pad of 1 only ever add values that are already inside the 3x3 window of the pixel, so a
     // clamped (repeated) neighbour changes no comparison.  All neighbour loads are unconditional and independent
     // (one round of shared-memory latency per group of four pixels instead of one per comparison).
-    const bool cross = (a.flavour == IBP_PEAKS_CROSS_REFINE);
+    const bool cross = (FLAVOUR == IBP_PEAKS_CROSS_REFINE);
     auto emit = [&](bool keep, int y, int x) {
         if (keep) {
             const int slot = atomicAdd(&s_found, 1);
@@ -248,7 +250,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
     for (int k = warp; k < n; k += nwarps) {
         const int pix = sorted[k];
         const int py = pix / w, px = pix - py * w;
-        if (a.flavour == IBP_PEAKS_CROSS_REFINE && a.up == 4 && a.win == 2 && px >= 2 && px + 2 < w && py >= 2 && py + 2 < h) {
+        if (FLAVOUR == IBP_PEAKS_CROSS_REFINE && a.up == 4 && a.win == 2 && px >= 2 && px + 2 < w && py >= 2 && py + 2 < h) {
             // The common case — a full 5x5 patch up-sampled x4 to 20x20 — entirely in registers: lane X < 20 owns
             // output column X; its five horizontal sums (one per patch row) stay in registers, and the twenty vertical
             // combinations use compile-time row indices and the 4x4 phase table.  Same operations in the same order
@@ -295,7 +297,7 @@ __global__ void __launch_bounds__(kPeakThreads) peaks_kernel(PeakArgs a) {
                 out[k] = p;
             }
             __syncwarp();
-        } else if (a.flavour == IBP_PEAKS_CROSS_REFINE) {
+        } else if (FLAVOUR == IBP_PEAKS_CROSS_REFINE) {
             const int x0 = max(px - a.win, 0), x1 = min(px + a.win, w - 1);
             const int y0 = max(py - a.win, 0), y1 = min(py + a.win, h - 1);
             const int pw = x1 - x0 + 1, ph = y1 - y0 + 1;

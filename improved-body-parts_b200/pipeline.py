@@ -88,6 +88,11 @@ class PostProcessor:
         find_connections -> find_humans (Python semantics, float64).  The handle's peak_thresh / refine_window must be
         the route's thre1 / offset_radius (both equal the defaults).  Returns a list per image of
         (all_peaks table (N,4) float64 [x,y,score,id], part_count (18,), person_to_joint_assoc (P,20,2) float64)."""
+        B = self.enqueue_original_route(net_outs, scaled_sizes, img_h, img_w, test_cfg, flip_avg)
+        return self.fetch_original_route(B)
+
+    def enqueue_original_route(self, net_outs, scaled_sizes, img_h, img_w, test_cfg=None, flip_avg=True):
+        """Launch the four kernels of the original route on the current stream; results stay on the device."""
         fused, heat32 = self.fuse_multiscale(net_outs, scaled_sizes, img_h, img_w, flip_avg, want_heat32=True)
         B = fused.shape[0]
         params = _lib.py_params(test_cfg)
@@ -96,6 +101,12 @@ class PostProcessor:
             self.handle.find_peaks(heat32.data_ptr(), _lib.NUM_PARTS, 0, B, img_h, img_w, _lib.PEAKS_BOX_CENTROID, st)
             self.handle.find_connections(params, fused.data_ptr(), _lib.NUM_LAYERS, B, img_h, img_w, img_h, st)
             self.handle.find_humans(params, B, st)
+        self._keep_or = (fused, heat32)
+        return B
+
+    def fetch_original_route(self, B):
+        with torch.cuda.device(self.device):
+            st = _stream_ptr(self.device)
             res = self.handle.fetch(B, st)
             out = []
             for b in range(B):
@@ -106,7 +117,6 @@ class PostProcessor:
                 table[:, 2] = res.peaks[b]["score"]
                 table[:, 3] = np.arange(n)
                 out.append((table, res.part_count[b].copy(), self.handle.fetch_people(b, st)))
-        self._keep_or = (fused, heat32)
         return out
 
     def upsample_limbs(self, fused, up=4):

@@ -13,8 +13,13 @@ from improved_body_parts_b200 import synth
 from improved_body_parts_b200.pipeline import PostProcessor
 
 B = 64
-batch = torch.from_numpy(synth.make_batch(2000, B, people=(1, 10))).cuda()
-pp = PostProcessor(device=0, max_batch=B)
+CROWD = "--crowd" in sys.argv
+if CROWD:
+    batch = torch.from_numpy(synth.make_batch(3000, B, people=(40, 60), scale=(0.2, 0.45))).cuda()
+    pp = PostProcessor(device=0, max_batch=B, max_peaks_per_part=256, max_candidates_per_limb=1024, max_bodies=512, max_humans=256)
+else:
+    batch = torch.from_numpy(synth.make_batch(2000, B, people=(1, 10))).cuda()
+    pp = PostProcessor(device=0, max_batch=B)
 for _ in range(3):
     res = pp(batch, 512)
 t = np.fromfile("/tmp/ibp_timeline.bin", dtype=np.uint64).reshape(B, 31, 4).astype(np.float64)
