@@ -479,7 +479,16 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
     a.cap_t1 = (int)cap_t1;
     a.cap_i = (int)cap_i;
     a.cap_t2 = (int)cap_t2;
-    const size_t smem = (cap_f + cap_t1 + cap_i + cap_t2) * sizeof(float);
+    // the four tiles (16-byte aligned as a whole) + the stage C row table: int4 + int per intermediate row
+    cap_t2 = (cap_t2 + 3) & ~(size_t)3;
+    cap_f = (cap_f + 3) & ~(size_t)3;
+    cap_t1 = (cap_t1 + 3) & ~(size_t)3;
+    cap_i = (cap_i + 3) & ~(size_t)3;
+    a.cap_f = (int)cap_f;
+    a.cap_t1 = (int)cap_t1;
+    a.cap_i = (int)cap_i;
+    a.cap_t2 = (int)cap_t2;
+    const size_t smem = (cap_f + cap_t1 + cap_i + cap_t2) * sizeof(float) + (cap_t2 / kMsTileX) * 20;
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale: a scale factor this large needs %zu B of shared memory", smem);
     const dim3 grid((img_w + kMsTileX - 1) / kMsTileX, (img_h + kMsTileY - 1) / kMsTileY, (unsigned)batch * kLayers);
     if (grid.z > 65535u) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: batch %d too large for one launch (max %d)", batch, 65535 / kLayers);

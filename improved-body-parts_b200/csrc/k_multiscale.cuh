@@ -75,6 +75,8 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     float *T1 = F + a.cap_f;                         // first resize, horizontal   [n_fy][n_rx]
     float *I = T1 + a.cap_t1;                        // first resize, vertical     [n_ry][n_rx] = up_s on the tile's taps
     float *T2 = I + a.cap_i;                         // second resize, horizontal  [n_ry][nX]
+    int4 *row_q = reinterpret_cast<int4 *>(T2 + a.cap_t2);   // [cap_rows] stage C row table (cap_t2 = cap_rows * tile width)
+    int *row_ph = reinterpret_cast<int *>(row_q + a.cap_t2 / kMsTileX);
     __shared__ int x_idx[kMsTileX][4], y_idx[kMsTileY][4];
     __shared__ float x_w[kMsTileX][4], y_w[kMsTileY][4];
     __shared__ float tab4[4][4];
@@ -128,6 +130,14 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
                 F[i] = a.flip ? avg_like_numpy(v, __ldg(twin + (size_t)y * S.w + (S.w - 1 - x))) : v;
             }
         }
+        // per intermediate row: offsets of its four source rows in T1 and its phase (stage C)
+        for (int r = tid; r < n_ry; r += kMsThreads) {
+            const int ry = ry_lo + r;
+            const int sy = (ry - 2) >> 2;
+            row_q[r] = make_int4((clampi(sy - 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy, 0, S.h - 1) - fy_lo) * n_rx,
+                                 (clampi(sy + 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy + 2, 0, S.h - 1) - fy_lo) * n_rx);
+            row_ph[r] = (ry - 2) & 3;
+        }
         __syncthreads();
         // Stages B-D give every thread ONE column and let it walk rows: the four taps and weights of the column live in
         // registers, there is no index division in the loops, and a warp reads consecutive columns of a row.
@@ -158,25 +168,20 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
         }
         __syncthreads();
         // ---- C: first resize, vertical pass (always the vector formula: padded widths are multiples of 64) ----
-        if (n_rx <= kMsThreads) {
-            const int groups = kMsThreads / n_rx, g = tid / n_rx, c = tid - g * n_rx;
-            if (g < groups) {
-                for (int r = g; r < n_ry; r += groups) {
-                    const int ry = ry_lo + r;
-                    const int sy = (ry - 2) >> 2;
-                    const int q0 = clampi(sy - 1, 0, S.h - 1) - fy_lo, q1 = clampi(sy, 0, S.h - 1) - fy_lo;
-                    const int q2 = clampi(sy + 1, 0, S.h - 1) - fy_lo, q3 = clampi(sy + 2, 0, S.h - 1) - fy_lo;
-                    I[r * n_rx + c] = vsum4(T1[q0 * n_rx + c], T1[q1 * n_rx + c], T1[q2 * n_rx + c], T1[q3 * n_rx + c], tab4[(ry - 2) & 3]);
+        // the largest stage: a flat walk over (row, column) that keeps all threads busy, (r, c) advanced without a
+        // division, the four source rows and the phase of a row read from a small table filled before stage B's barrier
+        {
+            const int dr = kMsThreads / n_rx, dc = kMsThreads - dr * n_rx;
+            int r = tid / n_rx, c = tid - r * n_rx;
+            while (r < n_ry) {
+                const int4 q = row_q[r];
+                I[r * n_rx + c] = vsum4(T1[q.x + c], T1[q.y + c], T1[q.z + c], T1[q.w + c], tab4[row_ph[r]]);
+                c += dc;
+                r += dr;
+                if (c >= n_rx) {
+                    c -= n_rx;
+                    r++;
                 }
-            }
-        } else {
-            for (int i = tid; i < n_ry * n_rx; i += kMsThreads) {
-                const int r = i / n_rx, c = i - r * n_rx;
-                const int ry = ry_lo + r;
-                const int sy = (ry - 2) >> 2;
-                const int q0 = clampi(sy - 1, 0, S.h - 1) - fy_lo, q1 = clampi(sy, 0, S.h - 1) - fy_lo;
-                const int q2 = clampi(sy + 1, 0, S.h - 1) - fy_lo, q3 = clampi(sy + 2, 0, S.h - 1) - fy_lo;
-                I[i] = vsum4(T1[q0 * n_rx + c], T1[q1 * n_rx + c], T1[q2 * n_rx + c], T1[q3 * n_rx + c], tab4[(ry - 2) & 3]);
             }
         }
         __syncthreads();
