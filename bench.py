@@ -103,12 +103,13 @@ def cpu_baseline(n_images, wl=None):
     from improved_body_parts_b200 import synth
     from oracle import cpu_path
     sample = wl.cpu_sample(n_images) if wl is not None else synth.make_batch(SEED, n_images, people=(1, 10), height=IMG, width=IMG)
-    secs, procs = cpu_path.time_batch(sample, IMG)
+    passes = 6  # about 10-20 s of CPU work over all cores
+    secs, procs = cpu_path.time_batch(sample, IMG, repeat=passes)
     return {"value": n_images / secs, "unit": UNIT, "cores": procs,
             "kind": "reference" if cpu_path.cpp_kind() == "reference" else "port",
-            "sample": "%d images of the same workload (seed %d..), one pass, %d processes x 1 thread; C++ stage = %s, "
+            "sample": "%d images of the same workload (seed %d..), %d passes after a warm-up, %d processes x 1 thread; C++ stage = %s, "
                       "Python stage = restated scipy.maximum_filter + cv2.resize calls (oracle/cpu_path.py)"
-                      % (n_images, SEED, procs, "unmodified reference pafprocess.cpp (oracle/_ref)"
+                      % (n_images, SEED, passes, procs, "unmodified reference pafprocess.cpp (oracle/_ref)"
                          if cpu_path.cpp_kind() == "reference" else "oracle port")}
 
 
@@ -307,6 +308,12 @@ def run_ours(args, rank, world, local_rank):
     else:
         peak, peak_src = 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
     algo = wl.algo_bytes
+    traffic = None  # dram bytes read + written per launch of the dominant kernel, from the committed ncu --set full capture
+    tfile = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    if os.path.exists(tfile):
+        t = json.load(open(tfile))
+        if t.get("workload") == args.workload and batch == (64 if args.workload != "configs2" else 32):
+            traffic = t["kernels"]
     dominant = max((k for k in stage_ms if k in algo), key=lambda k: stage_ms[k])
     achieved = algo[dominant] * batch / (stage_ms[dominant] * 1e-3) / 1e9
     out = {"metric": METRIC, "value": world * batch * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -319,14 +326,16 @@ def run_ours(args, rank, world, local_rank):
            "gpu_launches": int(launches),
            "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                        "frac": achieved / peak,
+                        "traffic": (traffic[dominant]["dram_bytes_read"] + traffic[dominant]["dram_bytes_write"])
+                        if traffic and dominant in traffic else None, "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": algo[dominant] * batch},
            "stage_ms": stage_ms,
            "stage_gbs": {k: algo[k] * batch / (stage_ms[k] * 1e-3) / 1e9 for k in stage_ms if k in algo},
            "whole_step_gbs": sum(algo.values()) * batch / (ms / args.steps * 1e-3) / 1e9,
            "humans_last_batch": wl.humans()}
     if not args.no_cpu_baseline and hasattr(wl, "cpu_sample"):
-        out["cpu_baseline"] = cpu_baseline(args.cpu_sample or max(8, 4 * (os.cpu_count() or 1)), wl)
+        out["cpu_baseline"] = cpu_baseline(args.cpu_sample or max(8, 8 * (os.cpu_count() or 1)), wl)
     return out
 
 
