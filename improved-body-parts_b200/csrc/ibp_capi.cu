@@ -41,16 +41,19 @@ int fail(int code, const char *fmt, ...) {
 
 constexpr size_t kMaxDynSmem = 220 * 1024;  // opt-in dynamic shared memory we ask for (device max 227 KB minus static use)
 constexpr size_t kPeakBandTarget = 16 * 1024;  // owned rows of one band (the CTA also stages 2*halo rows around them)
+constexpr size_t kPeakBandTargetStream = 24 * 1024;
 constexpr size_t kLimbPlaneMaxBytes = 96 * 1024;
 
-size_t peak_band_target() {
+// bytes of one staged band: the streaming kernel (two buffer sets per CTA, few fat items) likes them larger than the
+// one-CTA-per-band kernel (five CTAs per SM)
+size_t peak_band_target(bool streaming) {
     static size_t v = 0;
     if (!v) {
         const char *e = getenv("IBP_PEAK_BAND_BYTES");  // tuning knob for experiments
-        v = e ? (size_t)atol(e) : kPeakBandTarget;
-        if (v < 1024) v = 1024;
+        v = e ? (size_t)atol(e) : 1;
+        if (e && v < 1024) v = 1024;
     }
-    return v;
+    return v > 1 ? v : (streaming ? kPeakBandTargetStream : kPeakBandTarget);
 }
 
 template <typename T>
@@ -68,6 +71,13 @@ void free_host(T *&p) {
 
 struct ibp_handle {
     int device = 0;
+    int sm_count = 0;
+    // streaming peak kernel: occupancy cached per (instantiation, shared bytes)
+    const void *pk_occ_kern = nullptr;
+    size_t pk_occ_smem = 0;
+    int pk_occ = 0;
+    unsigned *d_pk_work = nullptr;  // work counter of the streaming peak kernel, never reset ...
+    unsigned pk_work_base = 0;      // ... its value before the next launch
     ibp_params P;
     ibp_limits L;
     int line_stride = 0;
@@ -98,6 +108,10 @@ struct ibp_handle {
     int *d_py_n_people = nullptr;     // (B)
     int *d_order = nullptr;        // [max_batch] images by descending peak count (written by the peak kernel)
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
+    int defer_bands = 0;           // > 0: the last peak launch left its band lists unpacked (this many bands per plane)
+    int defer_batch = 0;
+    int *d_partbase = nullptr;     // [max_batch][19] first id of each part + image total (index_bands_kernel)
+    int *d_n_raw = nullptr;        // [max_batch] peaks per image, accumulated by the streaming peak kernel (lives after d_status)
     unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
     unsigned long long *d_timeline_pk = nullptr;  // experiments only (IBP_DEBUG & 16)
     size_t timeline_pk_n = 0;
@@ -187,6 +201,8 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_timeline);
     free_dev(h->d_timeline_pk);
     free_dev(h->d_order);
+    free_dev(h->d_pk_work);
+    free_dev(h->d_partbase);
     free_dev(h->d_score64);
     free_dev(h->d_py_conn);
     free_dev(h->d_py_conn_count);
@@ -353,15 +369,19 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMalloc(&h->d_n_peaks, B * sizeof(int)));
         CU(cudaMalloc(&h->d_humans, B * h->L.max_humans * sizeof(ibp_human)));
         CU(cudaMalloc(&h->d_n_humans, B * sizeof(int)));
-        CU(cudaMalloc(&h->d_status, B * sizeof(uint32_t)));
+        CU(cudaMalloc(&h->d_status, 2 * B * sizeof(uint32_t)));  // status words, then the per-image raw peak counts
+        h->d_n_raw = reinterpret_cast<int *>(h->d_status + B);
         CU(cudaMemset(h->d_part_count, 0, B * kParts * sizeof(int)));
         CU(cudaMemset(h->d_link_count, 0, B * kLimbs * sizeof(int)));
         CU(cudaMemset(h->d_n_peaks, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_n_humans, 0, B * sizeof(int)));
-        CU(cudaMemset(h->d_status, 0, B * sizeof(uint32_t)));
+        CU(cudaMemset(h->d_status, 0, 2 * B * sizeof(uint32_t)));
         CU(cudaMalloc(&h->d_ticket, (2 * B + 1) * sizeof(unsigned)));
         CU(cudaMemset(h->d_ticket, 0, (2 * B + 1) * sizeof(unsigned)));
         CU(cudaMalloc(&h->d_order, B * sizeof(int)));
+        CU(cudaMalloc(&h->d_partbase, B * (kParts + 1) * sizeof(int)));
+        CU(cudaMalloc(&h->d_pk_work, sizeof(unsigned)));
+        CU(cudaMemset(h->d_pk_work, 0, sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
         CU(cudaMallocHost(&h->h_part_count, B * kParts * sizeof(int)));
         CU(cudaMallocHost(&h->h_line, B * h->line_stride * sizeof(ibp_peak)));
@@ -377,6 +397,11 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(peaks_kernel<__half, IBP_PEAKS_CROSS_REFINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_kernel<float, IBP_PEAKS_BOX_CENTROID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_kernel<__half, IBP_PEAKS_BOX_CENTROID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -529,7 +554,8 @@ namespace {
 // src: element (img, chan, y, x) at src + img*image_stride + (chan*fh + y)*fw + x; keypoint j in channel chan0 + j;
 // twin_base >= 0: average with the mirrored plane twin_base + 30 + flip_heat_ord[j] of the same image on the way in
 int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride, int chan0, int twin_base, int batch, int fh, int fw,
-                 int flavour, cudaStream_t st) {
+                 int flavour, cudaStream_t st, bool may_defer = false) {
+    h->defer_bands = 0;
     if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "find_peaks: batch %d exceeds limit %d", batch, h->L.max_batch);
     if (fh < 1 || fw < 1 || fw > 32767 || fh > 32767) return fail(IBP_ERR_SHAPE, "find_peaks: bad shape");
     if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID) return fail(IBP_ERR_ARG, "find_peaks: flavour %d", flavour);
@@ -544,7 +570,9 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.h = fh;
     a.w = fw;
     a.halo = std::max(h->P.refine_window, 1);
-    int rows_target = std::max<int>(4 * a.halo, (int)(peak_band_target() / ((size_t)fw * 4)));
+    static const bool no_stream = getenv("IBP_PEAKS_NO_STREAM") != nullptr;
+    const bool stream_ok = dtype == IBP_F32 && fw % 4 == 0 && ((uintptr_t)src & 15u) == 0 && (image_stride * 4) % 16 == 0 && !no_stream;
+    int rows_target = std::max<int>(4 * a.halo, (int)(peak_band_target(stream_ok) / ((size_t)fw * 4)));
     int nbands = (fh + rows_target - 1) / rows_target;
     a.rows_per_band = (fh + nbands - 1) / nbands;
     a.nbands = (fh + a.rows_per_band - 1) / a.rows_per_band;
@@ -574,6 +602,10 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.batch_ticket = h->d_ticket + 2 * h->L.max_batch;
     a.order = h->d_order;
     a.batch = batch;
+    a.defer_pack = 0;
+    a.n_raw = nullptr;
+    a.work_counter = nullptr;
+    a.work_base = 0;
     h->order_batch = batch;
     h->use_score64 = 0;
     a.timeline = nullptr;
@@ -592,17 +624,84 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
         }
     }
     const int side = 2 * a.win + 1;
-    size_t smem = band_bytes;
-    smem += (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
-    smem += (size_t)a.cap * 8;
-    smem = (smem + 15) & ~(size_t)15;
+    size_t scratch = (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
+    scratch += (size_t)a.cap * 8;
+    scratch = (scratch + 15) & ~(size_t)15;
+    CU(cudaMemsetAsync(h->d_status, 0, (size_t)2 * h->L.max_batch * sizeof(uint32_t), st));  // status + raw counts
+
+    // Streaming kernel: float32 planes whose rows the bulk-copy engine can move (16-byte aligned everywhere).
+    const bool twin = twin_base >= 0;
+    const size_t row_bytes = (size_t)rows_buf * fw * 4;
+    const size_t row_buf = (row_bytes + 15) & ~(size_t)15;
+    const size_t tail_ints = std::max<size_t>((size_t)kParts * a.nbands + 1, (size_t)batch);
+    const size_t smem_stream = 2 * (twin ? 2 : 1) * row_buf + scratch + ((tail_ints * 4 + 15) & ~(size_t)15);
+    if (stream_ok && smem_stream <= kMaxDynSmem) {
+        a.band_bytes = (int)row_buf;
+        a.ring_bytes = 0;
+        const int items = a.nbands * kParts * batch;
+        void (*kern)(PeakArgs) = nullptr;
+        if (flavour == IBP_PEAKS_CROSS_REFINE)
+            kern = twin ? peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true> : peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false>;
+        else
+            kern = twin ? peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, true> : peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, false>;
+        if (h->pk_occ_kern != (const void *)kern || h->pk_occ_smem != smem_stream) {
+            int per_sm = 0;
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kPeakThreads, smem_stream));
+            h->pk_occ_kern = (const void *)kern;
+            h->pk_occ_smem = smem_stream;
+            h->pk_occ = per_sm;
+            const char *dbg = getenv("IBP_DEBUG");
+            if (dbg && (atoi(dbg) & 32))
+                fprintf(stderr, "[ibp] peaks stream: %d bands of %d rows, %zu B shared, %d CTAs/SM x %d SMs, %d items\n", a.nbands,
+                        a.rows_per_band, smem_stream, per_sm, h->sm_count, items);
+        }
+        const int per_sm = h->pk_occ;
+        if (per_sm < 1) return fail(IBP_ERR_SHAPE, "find_peaks: streaming kernel does not fit");
+        const int grid = std::min(items, per_sm * h->sm_count);
+        // straight into the limb kernel: leave the band lists as they are, the limb CTAs gather them (no tickets, no
+        // pack, no fence in this kernel)
+        static const bool no_defer = getenv("IBP_PEAKS_NO_DEFER") != nullptr;
+        a.defer_pack = (may_defer && a.nbands <= kMaxDeferBands && !no_defer) ? 1 : 0;
+        a.n_raw = h->d_n_raw;
+        if (a.defer_pack) {
+            h->defer_bands = a.nbands;
+            h->defer_batch = batch;
+            h->order_batch = 0;
+        }
+        a.work_counter = h->d_pk_work;
+        a.work_base = h->pk_work_base;
+        h->pk_work_base += (unsigned)items;  // (items - grid) claims that succeed + one that fails per CTA
+        StageTimer t(h, IBP_STAGE_PEAKS, st);
+        kern<<<grid, kPeakThreads, smem_stream, st>>>(a);
+        h->launches++;
+        if (a.defer_pack) {
+            IndexArgs ia;
+            ia.band_count = h->d_band_count;
+            ia.n_raw = h->d_n_raw;
+            ia.nbands = a.nbands;
+            ia.batch = batch;
+            ia.cap = a.cap;
+            ia.line_stride = h->line_stride;
+            ia.part_count = h->d_part_count;
+            ia.partbase = h->d_partbase;
+            ia.n_peaks = h->d_n_peaks;
+            ia.order = h->d_order;
+            ia.status = h->d_status;
+            index_bands_kernel<<<batch, 32, 0, st>>>(ia);
+            h->launches++;
+            h->order_batch = batch;
+        }
+        CU(cudaGetLastError());
+        return IBP_OK;
+    }
+
+    size_t smem = band_bytes + scratch;
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "find_peaks: rows of %d floats do not fit shared memory", fw);
     a.ring_bytes = 0;
     if (twin_base >= 0 && dtype == IBP_F32 && fw % 4 == 0 && smem + band_bytes <= kMaxDynSmem) {
         a.ring_bytes = (int)band_bytes;  // second band buffer: the twin rows land here by bulk copy
         smem += band_bytes;
     }
-    CU(cudaMemsetAsync(h->d_status, 0, (size_t)batch * sizeof(uint32_t), st));
     {
         StageTimer t(h, IBP_STAGE_PEAKS, st);
         const dim3 grid(a.nbands, kParts, batch);
@@ -666,6 +765,7 @@ int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int 
         }
     h->h_n_peaks[image] = n;
     h->order_batch = 0;  // the peak kernel's image order no longer describes the lists
+    h->defer_bands = 0;
     memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
     CU(cudaMemcpy(h->d_peaks + (size_t)image * kParts * cap, h->h_peaks_stage, (size_t)kParts * cap * sizeof(DevPeak), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(h->d_part_count + (size_t)image * kParts, counts, sizeof(counts), cudaMemcpyHostToDevice));
@@ -728,6 +828,21 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     a.status = h->d_status;
     a.ticket = h->d_ticket + h->L.max_batch;
     a.order = (h->order_batch == batch) ? h->d_order : nullptr;
+    a.band_peaks = nullptr;
+    a.band_count = nullptr;
+    a.nbands = 0;
+    a.partbase = nullptr;
+    a.batch = batch;
+    a.peaks_out = h->d_peaks;
+    a.line_out = h->d_line;
+    if (h->defer_bands > 0) {
+        if (h->defer_batch != batch) return fail(IBP_ERR_ARG, "assign: %d images, but the pending peak lists are of %d", batch, h->defer_batch);
+        a.band_peaks = h->d_band_peaks;
+        a.band_count = h->d_band_count;
+        a.nbands = h->defer_bands;
+        a.partbase = h->d_partbase;
+        h->defer_bands = 0;
+    }
     const size_t smem = limb_smem_bytes(h, plane_bytes);
     a.smem_bytes = (int)smem;
     {
@@ -803,7 +918,7 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
     if (direct) {
         // two kernels, the network output is read once and nothing intermediate is written: the flip average
         // happens while each keypoint band / limb plane is staged in shared memory
-        int rc = launch_peaks(h, dev_in, dtype, image_stride, kLimbs, kLayers, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, st);
+        int rc = launch_peaks(h, dev_in, dtype, image_stride, kLimbs, kLayers, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, st, /*may_defer=*/true);
         if (rc != IBP_OK) return rc;
         return launch_limbs(h, dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st);
     }
@@ -951,6 +1066,7 @@ int ibp_set_peaks64(ibp_handle *h, int image, const double *rows, const int32_t 
     h->h_n_peaks[image] = n;
     h->use_score64 = 1;
     h->order_batch = 0;
+    h->defer_bands = 0;
     return IBP_OK;
 }
 

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "../../include/ibp.h"
 
 namespace ibp {
@@ -264,6 +266,16 @@ __device__ __forceinline__ void stage_rows_fused(float *dst, const T *up, const 
 __device__ __forceinline__ bool flip_tma_ok(const float *dst, const float *up, const float *twin, const float *ring, int w, int slot_rows) {
     return twin != nullptr && (w & 3) == 0 && slot_rows >= 1 && ((((uintptr_t)up) | ((uintptr_t)twin)) & 15u) == 0 &&
            ((smem_u32(dst) | smem_u32(ring)) & 15u) == 0;
+}
+// copies only; the caller has announced the bytes on `bar` (mbar_expect_tx)
+__device__ __forceinline__ void bulk_chunks(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    uint32_t done = 0;
+    while (done < bytes) {
+        uint32_t chunk = bytes - done;
+        if (chunk > 65536u) chunk = 65536u;
+        bulk_g2s((char *)dst + done, (const char *)src + done, chunk, bar);
+        done += chunk;
+    }
 }
 __device__ __forceinline__ void bulk_rows(float *dst, const float *src, uint32_t bytes, uint64_t *bar) {
     mbar_expect_tx(bar, bytes);

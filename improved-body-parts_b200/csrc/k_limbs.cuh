@@ -58,6 +58,17 @@ struct LimbArgs {
     int smem_bytes;         // dynamic shared memory of the launch
     int debug;              // experiments only (IBP_DEBUG): 1 = skip grouping, 2 = skip scoring
     const int *order;       // (batch) image handled by grid row y, or null: identity
+    // Band-list mode (band_peaks != null): the peak kernel left its per-band lists unpacked and index_bands_kernel
+    // counted them (part_count, partbase, order).  Every CTA gathers the lists of its two joint types from the bands
+    // with their running ids; the CTAs of limbs 0..17 also write the packed per-part arrays the results are fetched
+    // from.
+    const DevPeak *band_peaks;  // (batch, 18, nbands, cap)
+    const int *band_count;      // (batch, 18, nbands)
+    int nbands;
+    const int *partbase;        // (batch, 19) first id of each part, [18] = peaks of the image (index_bands_kernel)
+    int batch;
+    DevPeak *peaks_out;         // (batch, 18, cap)
+    ibp_peak *line_out;         // (batch, line_stride)
     unsigned long long *timeline;  // experiments only: (batch, 31, 4) %globaltimer stamps, or null
     GroupArgs group;
 };
@@ -65,6 +76,7 @@ struct LimbArgs {
 constexpr int kLimbThreadsMax = 512;  // CTA size is a template parameter: 256 (default) or 512 (handles sized for crowds)
 constexpr int kPairChunk = 128;  // pairs scored per round on the two-phase path
 constexpr int kLimbRing = 4;      // slots of the twin-plane ring while staging
+constexpr int kMaxDeferBands = 16; // band-list mode: most bands per plane the limb kernel gathers from
 constexpr int kRankSortMax = 512; // up to this many candidates are ordered by a rank sort, more by a bitonic network
 
 __device__ __forceinline__ uint32_t float_orderable(float f) {
@@ -127,11 +139,31 @@ template <typename T, int kLimbThreads>
 __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int limb = blockIdx.x;
-    const int img = a.order ? a.order[blockIdx.y] : (int)blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int pa = c_limb_a[limb], pb = c_limb_b[limb];
+    const bool from_bands = a.band_peaks != nullptr;
+    __shared__ int s_partbase[kParts + 1];  // band-list mode: first id of each part; [18] = peaks of the image
+    __shared__ int s_bc[kParts * kMaxDeferBands];  // band-list mode: the image's band counts
+    const int img = a.order ? a.order[blockIdx.y] : (int)blockIdx.y;
     const int nA = a.part_count[img * kParts + pa], nB = a.part_count[img * kParts + pb];
+    if (from_bands) {  // published by the barrier that follows the start of the plane copies
+        const int items = kParts * a.nbands;
+        for (int i = tid; i < items; i += kLimbThreads) s_bc[i] = a.band_count[(size_t)img * items + i];
+        if (tid <= kParts) s_partbase[tid] = a.partbase[img * (kParts + 1) + tid];
+    }
     int *link_count = a.link_count + img * kLimbs + limb;
+    // band-list mode: k-th peak of part p (k < its count) = entry (band, k - first of band); copies it with its id
+    auto gather_part = [&](int p, int k, DevPeak &out) {
+        const int *bc = s_bc + p * a.nbands;
+        int bnd = 0, first = 0;
+        for (; bnd + 1 < a.nbands; bnd++) {
+            const int c = bc[bnd];
+            if (k < first + c) break;
+            first += c;
+        }
+        out = a.band_peaks[(((size_t)img * kParts + p) * a.nbands + bnd) * a.cap + (k - first)];
+        out.id = s_partbase[p] + k;
+    };
 
     // ---- carve shared memory ----
     // region 0: limb plane while scoring (mode 1, staged), re-used for the introsort emulation array afterwards
@@ -184,8 +216,32 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
             a.timeline[((size_t)img * 31 + row) * 4 + col] = t;
         }
     };
+    // band-list mode: the CTA of limb l < 18 also writes part l of the packed arrays the results are fetched from
+    // (evaluate.py:99-108 joint list); called while the plane copies are in flight
+    auto pack_part = [&]() {
+        if (!from_bands || limb >= kParts) return;
+        const int c = s_partbase[limb + 1] - s_partbase[limb];
+        const int n = min(c, a.cap);
+        for (int k = tid; k < n; k += kLimbThreads) {
+            DevPeak p;
+            gather_part(limb, k, p);
+            a.peaks_out[((size_t)img * kParts + limb) * a.cap + k] = p;
+            if (p.id < a.line_stride) {
+                ibp_peak o;
+                o.x = p.x;
+                o.y = p.y;
+                o.score = p.score;
+                o.part = limb;
+                a.line_out[(size_t)img * a.line_stride + p.id] = o;
+            }
+        }
+    };
     stamp(limb, 0);
     // no pair => no candidate => no connection (covers the both-empty skip at :57)
+    if (!(nA > 0 && nB > 0) && from_bands) {
+        __syncthreads();
+        pack_part();
+    }
     if (nA > 0 && nB > 0) {
         // source planes of this limb (feature-resolution modes)
         const T *gplane = nullptr, *twin = nullptr;
@@ -217,6 +273,23 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         // by ARRIVAL id — the same peak only when the caller's joint list is sorted by part (evaluate.py:99-103 does
         // that); keep the quirk, but fetch the values now so that the greedy loop never waits on global memory
         const ibp_peak *line = a.line + (size_t)img * a.line_stride;
+        if (from_bands) {
+            __syncthreads();  // s_bc / s_partbase
+            for (int i = tid; i < nA; i += kLimbThreads) {
+                DevPeak p;
+                gather_part(pa, i, p);
+                sA[i] = p;
+                used_a[i] = 0;
+                line_a[i] = p.score;  // ids are arrival order here, so peak_infos_line[id] is the peak itself
+            }
+            for (int i = tid; i < nB; i += kLimbThreads) {
+                DevPeak p;
+                gather_part(pb, i, p);
+                sB[i] = p;
+                used_b[i] = 0;
+                line_b[i] = p.score;
+            }
+        } else {
         for (int i = tid; i < nA; i += kLimbThreads) {
             const DevPeak p = gA[i];
             sA[i] = p;
@@ -229,6 +302,8 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
             used_b[i] = 0;
             line_b[i] = line[min(max(p.id, 0), a.line_stride - 1)].score;
         }
+        }
+        pack_part();
         __syncthreads();
 
         Sampler smp;

@@ -57,6 +57,11 @@ struct PeakArgs {
     unsigned long long *timeline;  // experiments only: (batch, 18, nbands, 6) %globaltimer stamps, or null
     int *order;           // (batch) images sorted by descending number of peaks, written by the last CTA of the launch
     int batch;
+    int defer_pack;          // streaming kernel: 1 = leave the band lists as they are (no tickets, no pack, no order): the
+                             // limb kernel gathers them itself; only n_raw[img] += peaks of the band
+    int *n_raw;              // (batch) zero on entry when defer_pack
+    unsigned *work_counter;  // streaming kernel: items beyond the first gridDim.x are claimed here, ...
+    unsigned work_base;      // ... counter value at launch (it is never reset: a launch adds exactly `items` to it)
 };
 
 constexpr int kPeakThreads = 256;
@@ -101,112 +106,77 @@ __device__ __forceinline__ double np_pairwise_sum_f64(const double *a, int n) {
     for (; i < n; i++) res = __dadd_rn(res, a[i]);
     return res;
 }
-
-// FLAVOUR is a template parameter so that the heatmap_nms instantiation does not carry the registers of the float64
-// centroid code (and the other way round).
-template <typename T, int FLAVOUR>
-__global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int bandi = blockIdx.x, part = blockIdx.y, img = blockIdx.z;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int nwarps = kPeakThreads / 32;
-    const int w = a.w, h = a.h;
-
-    const int r0 = bandi * a.rows_per_band, r1 = min(r0 + a.rows_per_band, h);
-    const int l0 = max(r0 - a.halo, 0), l1 = min(r1 + a.halo, h);
-
-    auto stamp = [&](int col) {
-        if (a.timeline && tid == 0) {
-            unsigned long long t;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-            a.timeline[((((size_t)img * kParts + part) * a.nbands) + bandi) * 6 + col] = t;
-        }
-    };
-    stamp(0);
-    // carve shared memory
-    float *band = reinterpret_cast<float *>(smem_raw);
-    size_t off = (size_t)a.band_bytes;
-    const int side = 2 * a.win + 1;
-    const int hbuf_per_warp = side * side * a.up;
-    float *hbuf_all = reinterpret_cast<float *>(smem_raw + off);  // per warp: side rows x side*up columns
-    off += ((size_t)nwarps * hbuf_per_warp * 4 + 7) & ~(size_t)7;
-    int *found = reinterpret_cast<int *>(smem_raw + off);         // [cap] unordered pixel indices
-    off += (size_t)a.cap * 4;
-    int *sorted = reinterpret_cast<int *>(smem_raw + off);        // [cap] row-major order
-    off += (size_t)a.cap * 4;
-    off = (off + 15) & ~(size_t)15;
-    float *ring = reinterpret_cast<float *>(smem_raw + off);      // twin band while staging (ring_bytes)
-    __shared__ uint64_t bars[2];
-    __shared__ int s_found;
-    __shared__ float tab4[4][4];
-
-    {
-        const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
-        const size_t hw = (size_t)h * w;
-        const T *up = base + (size_t)(a.chan0 + part) * hw;
-        // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
-        const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[kLimbs + part]) * hw : nullptr;
-        const int nrows = l1 - l0;
-        // float32 + twin: both bands by the bulk-copy engine, the twin into its own buffer (one ring slot holds it all)
-        const int slot_rows = (a.ring_bytes >= nrows * w * 4) ? nrows : 0;
-        bool tma_flip = false;
-        if (sizeof(T) == 4) tma_flip = flip_tma_ok(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), ring, w, slot_rows);
-        if (tid == 0) {
-            mbar_init(&bars[0], 1);
-            mbar_init(&bars[1], 1);
-            fence_barrier_init();
-            s_found = 0;
-            if (tma_flip)
-                flip_tma_issue<1>(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
-        }
-        cubic_tab4_init(tab4);
-        __syncthreads();
-        if (tma_flip) {
-            flip_tma_finish<1>(band, reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
-        } else {
-            uint32_t phase = 0;
-            stage_rows_fused<T>(band, up, twin, l0, nrows, w, &bars[0], phase);
-        }
+// ---------------------------------------------------------------------------------------------------------------
+// Views of a staged band.  PlainBand: the fused values are in shared memory.  FlipBand: the upright rows and the
+// flipped image's rows are both in shared memory exactly as they lie in HBM, and the average
+// (utils/parse_skeletons.py:91-93) is taken when a value is read — the scan reads every value once, everything
+// else touches a few pixels around a peak, so the extra pass that would fold one into the other is not needed.
+// ---------------------------------------------------------------------------------------------------------------
+struct PlainBand {
+    const float *p;
+    int l0, w;
+    __device__ __forceinline__ float at(int y, int x) const { return p[(y - l0) * w + x]; }
+    __device__ __forceinline__ float4 at4(int y, int x) const { return *reinterpret_cast<const float4 *>(p + (y - l0) * w + x); }
+};
+struct FlipBand {
+    const float *up, *tw;
+    int l0, w;
+    __device__ __forceinline__ float at(int y, int x) const {
+        const int r = (y - l0) * w;
+        return avg_like_numpy(up[r + x], tw[r + (w - 1 - x)]);
     }
-#define BAND(y, x) band[((y)-l0) * w + (x)]
-    stamp(1);
+    __device__ __forceinline__ float4 at4(int y, int x) const {  // x % 4 == 0, w % 4 == 0
+        const int r = (y - l0) * w;
+        float4 a = *reinterpret_cast<const float4 *>(up + r + x);
+        const float4 m = *reinterpret_cast<const float4 *>(tw + r + (w - 4 - x));
+        a.x = avg_like_numpy(a.x, m.w);
+        a.y = avg_like_numpy(a.y, m.z);
+        a.z = avg_like_numpy(a.z, m.y);
+        a.w = avg_like_numpy(a.w, m.x);
+        return a;
+    }
+};
 
-    // ---- non-maximum suppression over the owned rows ----
-    // Neighbour rows / columns are clamped to the map, which is what both border rules amount to: scipy's 'reflect'
-    // and torch's reflect-pad of 1 only ever add values that are already inside the 3x3 window of the pixel, so a
-    // clamped (repeated) neighbour changes no comparison.  All neighbour loads are unconditional and independent
-    // (one round of shared-memory latency per group of four pixels instead of one per comparison).
-    const bool cross = (FLAVOUR == IBP_PEAKS_CROSS_REFINE);
+// ---- non-maximum suppression over the owned rows [r0, r1) ----
+// Neighbour rows / columns are clamped to the map, which is what both border rules amount to: scipy's 'reflect'
+// and torch's reflect-pad of 1 only ever add values that are already inside the 3x3 window of the pixel, so a
+// clamped (repeated) neighbour changes no comparison.  All neighbour loads are unconditional and independent
+// (one round of shared-memory latency per group of four pixels instead of one per comparison).
+// Threads that find a peak append its pixel index to found[] (unordered; *s_found counts, may exceed cap).
+template <int FLAVOUR, class Acc>
+__device__ __forceinline__ void peaks_scan(const Acc &B, int r0, int r1, int h, int w, float thr, int cap, int *found, int *s_found,
+                                           int tid, int nthr) {
+    constexpr bool cross = (FLAVOUR == IBP_PEAKS_CROSS_REFINE);
     auto emit = [&](bool keep, int y, int x) {
         if (keep) {
-            const int slot = atomicAdd(&s_found, 1);
-            if (slot < a.cap) found[slot] = y * w + x;
+            const int slot = atomicAdd(s_found, 1);
+            if (slot < cap) found[slot] = y * w + x;
         }
     };
     // centre test: heatmap_nms keeps value > 0.1 (parse_skeletons.py:116); keypoint_heatmap_nms keeps value >= thre and
     // a non-zero product heat*keep (util.py:184-185)
-    auto centre_ok = [&](float v) { return cross ? (v > a.thr) : ((v >= a.thr) && (v != 0.0f)); };
-    const int npix = (r1 - r0) * w;
-    const float *own = &BAND(r0, 0);
-    const float gate = a.thr;  // both flavours need v >= thr at least
+    auto centre_ok = [&](float v) { return cross ? (v > thr) : ((v >= thr) && (v != 0.0f)); };
+    const float gate = thr;  // both flavours need v >= thr at least
     if ((w & 3) == 0) {
-        const float4 *own4 = reinterpret_cast<const float4 *>(own);
         const int wv = w >> 2;
-        for (int i4 = tid; i4 < (npix >> 2); i4 += kPeakThreads) {
-            const float4 v = own4[i4];
+        // (row, column group) of this thread's items without a division per item
+        int yy = tid / wv, c = tid - yy * wv;
+        const int dy = nthr / wv, dc = nthr - dy * wv;
+        for (; r0 + yy < r1;) {
+            const int y = r0 + yy, x = c << 2;
+            const float4 v = B.at4(y, x);
             // cheap reject: nothing at or above the threshold in these four pixels
             if (fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)) >= gate) {
-                const int yy = i4 / wv, x = (i4 - yy * wv) << 2, y = r0 + yy;
                 const int yu = max(y - 1, 0), yd = min(y + 1, h - 1), xl = max(x - 1, 0), xr = min(x + 4, w - 1);
-                const float4 u = *reinterpret_cast<const float4 *>(&BAND(yu, x));
-                const float4 d = *reinterpret_cast<const float4 *>(&BAND(yd, x));
-                const float l = BAND(y, xl), r = BAND(y, xr);
+                const float4 u = B.at4(yu, x);
+                const float4 d = B.at4(yd, x);
+                const float l = B.at(y, xl), r = B.at(y, xr);
                 bool k0 = centre_ok(v.x) & (v.x >= u.x) & (v.x >= d.x) & (v.x >= l) & (v.x >= v.y);
                 bool k1 = centre_ok(v.y) & (v.y >= u.y) & (v.y >= d.y) & (v.y >= v.x) & (v.y >= v.z);
                 bool k2 = centre_ok(v.z) & (v.z >= u.z) & (v.z >= d.z) & (v.z >= v.y) & (v.z >= v.w);
                 bool k3 = centre_ok(v.w) & (v.w >= u.w) & (v.w >= d.w) & (v.w >= v.z) & (v.w >= r);
                 if (!cross) {  // 3x3 window: the four diagonals as well
-                    const float ul = BAND(yu, xl), ur = BAND(yu, xr), dl = BAND(yd, xl), dr = BAND(yd, xr);
+                    const float ul = B.at(yu, xl), ur = B.at(yu, xr), dl = B.at(yd, xl), dr = B.at(yd, xr);
                     k0 = k0 & (v.x >= ul) & (v.x >= u.y) & (v.x >= dl) & (v.x >= d.y);
                     k1 = k1 & (v.y >= u.x) & (v.y >= u.z) & (v.y >= d.x) & (v.y >= d.z);
                     k2 = k2 & (v.z >= u.y) & (v.z >= u.w) & (v.z >= d.y) & (v.z >= d.w);
@@ -217,36 +187,34 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
                 emit(k2, y, x + 2);
                 emit(k3, y, x + 3);
             }
+            yy += dy;
+            c += dc;
+            if (c >= wv) {
+                c -= wv;
+                yy++;
+            }
         }
     } else {
-        for (int i = tid; i < npix; i += kPeakThreads) {
-            const float v = own[i];
+        const int npix = (r1 - r0) * w;
+        for (int i = tid; i < npix; i += nthr) {
+            const int yy = i / w, x = i - yy * w, y = r0 + yy;
+            const float v = B.at(y, x);
             if (v >= gate) {
-                const int yy = i / w, x = i - yy * w, y = r0 + yy;
                 const int yu = max(y - 1, 0), yd = min(y + 1, h - 1), xl = max(x - 1, 0), xr = min(x + 1, w - 1);
-                bool k = centre_ok(v) & (v >= BAND(yu, x)) & (v >= BAND(yd, x)) & (v >= BAND(y, xl)) & (v >= BAND(y, xr));
-                if (!cross) k = k & (v >= BAND(yu, xl)) & (v >= BAND(yu, xr)) & (v >= BAND(yd, xl)) & (v >= BAND(yd, xr));
+                bool k = centre_ok(v) & (v >= B.at(yu, x)) & (v >= B.at(yd, x)) & (v >= B.at(y, xl)) & (v >= B.at(y, xr));
+                if (!cross) k = k & (v >= B.at(yu, xl)) & (v >= B.at(yu, xr)) & (v >= B.at(yd, xl)) & (v >= B.at(yd, xr));
                 emit(k, y, x);
             }
         }
     }
-    __syncthreads();
-    stamp(2);
-    const int n_raw = s_found;
-    const int n = min(n_raw, a.cap);
-    // rank sort: pixel indices are distinct
-    for (int i = tid; i < n; i += kPeakThreads) {
-        const int mine = found[i];
-        int rank = 0;
-        for (int j = 0; j < n; j++) rank += (found[j] < mine);
-        sorted[rank] = mine;
-    }
-    __syncthreads();
+}
 
-    // ---- refine, one warp per peak ----
-    const size_t slot_base = (((size_t)img * kParts + part) * a.nbands + bandi) * a.cap;
-    DevPeak *out = a.band_peaks + slot_base;
-    float *hbuf = hbuf_all + warp * hbuf_per_warp;
+// ---- refine, one warp per peak: sorted[0..n) holds the pixel indices in row-major order ----
+template <int FLAVOUR, class Acc>
+__device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, int n, const int *sorted, DevPeak *out, size_t slot_base,
+                                             float *hbuf, const float (*tab4)[4], int warp, int nwarps) {
+    const int lane = threadIdx.x & 31;
+    const int w = a.w, h = a.h;
     for (int k = warp; k < n; k += nwarps) {
         const int pix = sorted[k];
         const int py = pix / w, px = pix - py * w;
@@ -265,7 +233,7 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
                 const int c2 = x0 + clampi(sx + 1, 0, 4), c3 = x0 + clampi(sx + 2, 0, 4);
                 float hcol[5];
 #pragma unroll
-                for (int r = 0; r < 5; r++) hcol[r] = hsum4(BAND(y0 + r, c0), BAND(y0 + r, c1), BAND(y0 + r, c2), BAND(y0 + r, c3), xw);
+                for (int r = 0; r < 5; r++) hcol[r] = hsum4(B.at(y0 + r, c0), B.at(y0 + r, c1), B.at(y0 + r, c2), B.at(y0 + r, c3), xw);
 #pragma unroll
                 for (int Y = 0; Y < 20; Y++) {
                     const int sy = (Y - 2) >> 2;  // compile-time after unrolling
@@ -318,7 +286,7 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
                 const int c0 = x0 + clampi(sx - 1, 0, pw - 1), c1 = x0 + clampi(sx, 0, pw - 1);
                 const int c2 = x0 + clampi(sx + 1, 0, pw - 1), c3 = x0 + clampi(sx + 2, 0, pw - 1);
                 const int y = y0 + r;
-                hbuf[r * W4 + X] = hsum4(BAND(y, c0), BAND(y, c1), BAND(y, c2), BAND(y, c3), xw);
+                hbuf[r * W4 + X] = hsum4(B.at(y, c0), B.at(y, c1), B.at(y, c2), B.at(y, c3), xw);
             }
             __syncwarp();
             float best = -INFINITY;
@@ -387,7 +355,7 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
                 if (py + rad + 1 > h || py - rad < 0 || px + rad + 1 > w || px - rad < 0) {
                     fx = (double)px;
                     fy = (double)py;
-                    sc = BAND(py, px);
+                    sc = B.at(py, px);
                 } else {
                     // box*grid promotes to float64 (grid is int64): 25 products summed by numpy's pairwise scheme in
                     // float64; box.sum() is the same pairwise scheme over the 25 float32 values in row-major order
@@ -399,7 +367,7 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
                     int cnt = 0;
                     for (int q = -rad; q <= rad; q++) {
                         for (int p = -rad; p <= rad; p++) {
-                            const float v = BAND(py + q, px + p);
+                            const float v = B.at(py + q, px + p);
                             if (cnt < 25) {
                                 vals[cnt] = v;
                                 prod_r[cnt] = __dmul_rn((double)v, (double)q);  // x_grid = ROW offset (l.207 quirk)
@@ -438,21 +406,12 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
             __syncwarp();
         }
     }
-#undef BAND
-    if (tid == 0) {
-        a.band_count[((size_t)img * kParts + part) * a.nbands + bandi] = n;
-        if (n_raw > a.cap) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
-    }
+}
 
-    stamp(3);
-    // ---- last CTA of this image packs (warp 0 only; the other warps leave as soon as their writes are out) ----
-    if (lane == 0 && (warp < n || tid == 0)) __threadfence();  // the lanes that wrote peaks / the count
-    if (warp != 0) {
-        asm volatile("bar.arrive 1, %0;" ::"n"(kPeakThreads) : "memory");
-        return;
-    }
-    asm volatile("bar.sync 1, %0;" ::"n"(kPeakThreads) : "memory");
-    stamp(4);
+// ---- the last CTA of an image to finish packs the image; called by warp 0 after the whole CTA's writes are fenced ----
+// scratch: shared memory, >= max(18*nbands + 1, batch) ints.
+__device__ __forceinline__ void peaks_tail(const PeakArgs &a, int img, int *scratch) {
+    const int lane = threadIdx.x & 31;
     const unsigned ctas_per_image = (unsigned)a.nbands * kParts;
     int last = 0;
     if (lane == 0) {
@@ -461,12 +420,11 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
         if (last) a.ticket[img] = 0;  // ready for the next launch
     }
     last = __shfl_sync(0xffffffffu, last, 0);
-    stamp(5);
     if (!last) return;
     __threadfence();
 
     // exclusive scan of the band counts in (part, band) order; re-use the band buffer (>= 18*nbands+1 ints by launch)
-    int *offs = reinterpret_cast<int *>(smem_raw);
+    int *offs = scratch;
     const int items = kParts * a.nbands;
     const int *bc = a.band_count + (size_t)img * items;
     int total = 0;
@@ -546,7 +504,7 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
     if (!last) return;
     __threadfence();
     // counts into shared memory first (one round of loads), then an all-pairs rank from there
-    int *cnt = reinterpret_cast<int *>(smem_raw);  // band buffer, free again; launch guarantees >= batch ints
+    int *cnt = scratch;  // band buffer, free again; launch guarantees >= batch ints
     for (int b = lane; b < a.batch; b += 32) cnt[b] = __ldcg(a.n_peaks + b);
     __syncwarp();
     for (int b = lane; b < a.batch; b += 32) {
@@ -558,6 +516,368 @@ __global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
         }
         a.order[rank] = b;
     }
+}
+
+// Shared-memory carve-up common to both kernels, after the band buffers: per-warp patch buffer, found[], sorted[].
+struct PeakScratch {
+    float *hbuf_all;
+    int hbuf_per_warp;
+    int *found, *sorted;
+    size_t end;
+};
+__device__ __forceinline__ PeakScratch peak_scratch(unsigned char *smem, size_t off, const PeakArgs &a, int nwarps) {
+    PeakScratch s;
+    const int side = 2 * a.win + 1;
+    s.hbuf_per_warp = side * side * a.up;
+    s.hbuf_all = reinterpret_cast<float *>(smem + off);  // per warp: side rows x side*up columns
+    off += ((size_t)nwarps * s.hbuf_per_warp * 4 + 7) & ~(size_t)7;
+    s.found = reinterpret_cast<int *>(smem + off);  // [cap] unordered pixel indices
+    off += (size_t)a.cap * 4;
+    s.sorted = reinterpret_cast<int *>(smem + off);  // [cap] row-major order
+    off += (size_t)a.cap * 4;
+    s.end = (off + 15) & ~(size_t)15;
+    return s;
+}
+
+// rank sort of the found pixel indices (distinct) into row-major order == np.nonzero order; all threads
+__device__ __forceinline__ void peaks_order(const int *found, int *sorted, int n, int tid, int nthr) {
+    for (int i = tid; i < n; i += nthr) {
+        const int mine = found[i];
+        int rank = 0;
+        for (int j = 0; j < n; j++) rank += (found[j] < mine);
+        sorted[rank] = mine;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// General kernel: one CTA per (band, part, image); any element type, any alignment, with or without the flip twin.
+// FLAVOUR is a template parameter so that the heatmap_nms instantiation does not carry the registers of the float64
+// centroid code (and the other way round).
+// ---------------------------------------------------------------------------------------------------------------
+template <typename T, int FLAVOUR>
+__global__ void __launch_bounds__(kPeakThreads, 5) peaks_kernel(PeakArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int bandi = blockIdx.x, part = blockIdx.y, img = blockIdx.z;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nwarps = kPeakThreads / 32;
+    const int w = a.w, h = a.h;
+
+    const int r0 = bandi * a.rows_per_band, r1 = min(r0 + a.rows_per_band, h);
+    const int l0 = max(r0 - a.halo, 0), l1 = min(r1 + a.halo, h);
+
+    auto stamp = [&](int col) {
+        if (a.timeline && tid == 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.timeline[((((size_t)img * kParts + part) * a.nbands) + bandi) * 6 + col] = t;
+        }
+    };
+    stamp(0);
+    float *band = reinterpret_cast<float *>(smem_raw);
+    const PeakScratch sc = peak_scratch(smem_raw, (size_t)a.band_bytes, a, nwarps);
+    float *ring = reinterpret_cast<float *>(smem_raw + sc.end);  // twin band while staging (ring_bytes)
+    __shared__ uint64_t bars[2];
+    __shared__ int s_found;
+    __shared__ float tab4[4][4];
+
+    {
+        const T *base = reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride;
+        const size_t hw = (size_t)h * w;
+        const T *up = base + (size_t)(a.chan0 + part) * hw;
+        // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
+        const T *twin = (a.twin_base >= 0) ? base + (size_t)(a.twin_base + c_flip_src[kLimbs + part]) * hw : nullptr;
+        const int nrows = l1 - l0;
+        // float32 + twin: both bands by the bulk-copy engine, the twin into its own buffer (one ring slot holds it all)
+        const int slot_rows = (a.ring_bytes >= nrows * w * 4) ? nrows : 0;
+        bool tma_flip = false;
+        if (sizeof(T) == 4) tma_flip = flip_tma_ok(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), ring, w, slot_rows);
+        if (tid == 0) {
+            mbar_init(&bars[0], 1);
+            mbar_init(&bars[1], 1);
+            fence_barrier_init();
+            s_found = 0;
+            if (tma_flip)
+                flip_tma_issue<1>(band, reinterpret_cast<const float *>(up), reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
+        }
+        cubic_tab4_init(tab4);
+        __syncthreads();
+        if (tma_flip) {
+            flip_tma_finish<1>(band, reinterpret_cast<const float *>(twin), l0, nrows, w, ring, slot_rows, bars);
+        } else {
+            uint32_t phase = 0;
+            stage_rows_fused<T>(band, up, twin, l0, nrows, w, &bars[0], phase);
+        }
+    }
+    stamp(1);
+    const PlainBand B{band, l0, w};
+    peaks_scan<FLAVOUR>(B, r0, r1, h, w, a.thr, a.cap, sc.found, &s_found, tid, kPeakThreads);
+    __syncthreads();
+    stamp(2);
+    const int n_raw = s_found;
+    const int n = min(n_raw, a.cap);
+    peaks_order(sc.found, sc.sorted, n, tid, kPeakThreads);
+    __syncthreads();
+
+    const size_t slot_base = (((size_t)img * kParts + part) * a.nbands + bandi) * a.cap;
+    peaks_refine<FLAVOUR>(B, a, n, sc.sorted, a.band_peaks + slot_base, slot_base, sc.hbuf_all + warp * sc.hbuf_per_warp, tab4, warp, nwarps);
+    if (tid == 0) {
+        a.band_count[((size_t)img * kParts + part) * a.nbands + bandi] = n;
+        if (n_raw > a.cap) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
+    }
+
+    stamp(3);
+    // ---- last CTA of this image packs (warp 0 only; the other warps leave as soon as their writes are out) ----
+    if (lane == 0 && (warp < n || tid == 0)) __threadfence();  // the lanes that wrote peaks / the count
+    if (warp != 0) {
+        asm volatile("bar.arrive 1, %0;" ::"n"(kPeakThreads) : "memory");
+        return;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(kPeakThreads) : "memory");
+    stamp(4);
+    peaks_tail(a, img, reinterpret_cast<int *>(smem_raw));  // band buffer: >= max(18*nbands+1, batch) ints by launch
+    stamp(5);
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// Streaming kernel (float32, 16-byte aligned rows): a persistent grid of warp-specialised CTAs over the
+// (image, part, band) items, TWO sets of band buffers per CTA.
+//   * warp 0, the control warp: claims items, keeps the bulk-copy engine one item ahead of the workers (the upright
+//     band — and the flipped image's band, TWIN — of item k+1 lands in the other buffer set while item k is worked
+//     on; item k+2 is requested the moment the workers release item k's set), publishes finished bands (one fence +
+//     one ticket per item) and packs an image when its last band is in.  All of its latencies (claim, fence, ticket,
+//     pack) overlap the workers' next item.
+//   * warps 1..7, the workers: wait for the data, scan, order, refine, write the band list, release the buffer set.
+//     They never fence and never wait for the control warp except for data.
+// With TWIN the average is taken on read (FlipBand): no fold pass.
+// Work distribution: item blockIdx.x first, then whatever the shared counter hands out — a CTA whose control warp is
+// packing an image simply claims fewer bands (with a fixed schedule the laggard becomes the last CTA, hence the
+// packer, of every image it touches).  Every CTA makes exactly one claim that fails, so a launch advances the
+// counter by exactly `items`; the host tracks the base instead of resetting it.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kPeakStreamCtasPerSm = 3;
+constexpr int kPeakWorkers = kPeakThreads - 32;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int FLAVOUR, bool TWIN>
+__global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stream_kernel(PeakArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nworkers = kPeakWorkers / 32;
+    constexpr int nplanes = TWIN ? 2 : 1;
+    const int w = a.w, h = a.h;
+    const size_t hw = (size_t)h * w;
+    const int per_image = a.nbands * kParts;
+    const int items = per_image * a.batch;
+
+    // buffer set b: upright band at b*nplanes*band_bytes, twin band right after it
+    auto buf_up = [&](int b) { return reinterpret_cast<float *>(smem_raw + (size_t)b * nplanes * a.band_bytes); };
+    auto buf_tw = [&](int b) { return reinterpret_cast<float *>(smem_raw + ((size_t)b * nplanes + 1) * a.band_bytes); };
+    const PeakScratch sc = peak_scratch(smem_raw, (size_t)2 * nplanes * a.band_bytes, a, nworkers);
+    int *tail_scratch = reinterpret_cast<int *>(smem_raw + sc.end);  // max(18*nbands+1, batch) ints
+    __shared__ uint64_t full[2];  // data of buffer set b has landed (or: no more items, see s_item)
+    __shared__ uint64_t done[2];  // the workers are finished with buffer set b
+    __shared__ int s_found[2];
+    __shared__ int s_item[2];     // item in buffer set b, -1: none (the workers leave)
+    __shared__ float tab4[4][4];
+
+    struct Item {
+        int img, part, bandi, r0, r1, l0, l1;
+    };
+    auto decode = [&](int item) {
+        Item it;
+        it.img = item / per_image;
+        const int rem = item - it.img * per_image;
+        it.part = rem / a.nbands;
+        it.bandi = rem - it.part * a.nbands;
+        it.r0 = it.bandi * a.rows_per_band;
+        it.r1 = min(it.r0 + a.rows_per_band, h);
+        it.l0 = max(it.r0 - a.halo, 0);
+        it.l1 = min(it.r1 + a.halo, h);
+        return it;
+    };
+    // one thread: publish `item` as the content of buffer set b and start its copies (or wake the workers up to leave)
+    auto request = [&](int item, int b) {
+        s_item[b] = item;
+        s_found[b] = 0;
+        if (item < 0) {
+            mbar_arrive(&full[b]);
+            return;
+        }
+        const Item it = decode(item);
+        const float *base = reinterpret_cast<const float *>(a.src) + (size_t)it.img * a.image_stride;
+        const uint32_t bytes = (uint32_t)(it.l1 - it.l0) * w * 4u;
+        mbar_expect_tx(&full[b], bytes * nplanes);
+        bulk_chunks(buf_up(b), base + (size_t)(a.chan0 + it.part) * hw + (size_t)it.l0 * w, bytes, &full[b]);
+        if (TWIN)  // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
+            bulk_chunks(buf_tw(b), base + (size_t)(a.twin_base + c_flip_src[kLimbs + it.part]) * hw + (size_t)it.l0 * w, bytes, &full[b]);
+    };
+    auto claim_to_item = [&](unsigned t) {
+        const unsigned rel = t - a.work_base + gridDim.x;
+        return rel < (unsigned)items ? (int)rel : -1;
+    };
+    auto stamp = [&](int item, int col) {
+        if (a.timeline) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            a.timeline[(size_t)item * 6 + col] = t;
+        }
+    };
+
+    int cur = (int)blockIdx.x, nxt = -1;  // control warp's view (the grid never exceeds the item count)
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        mbar_init(&done[0], nworkers);
+        mbar_init(&done[1], nworkers);
+        fence_barrier_init();
+        request(cur, 0);
+        nxt = claim_to_item(atomicAdd(a.work_counter, 1u));
+        request(nxt, 1);
+    }
+    cubic_tab4_init(tab4);
+    __syncthreads();
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------------------------------ control warp
+        nxt = __shfl_sync(0xffffffffu, nxt, 0);
+        for (int k = 0; cur >= 0; k++) {
+            const int b = k & 1;
+            // claim the item after next now, use the answer when this one is released (stop at the first failure)
+            unsigned claimed = 0;
+            const bool claiming = (lane == 0) && (nxt >= 0);
+            if (claiming) claimed = atomicAdd(a.work_counter, 1u);
+            mbar_wait(&done[b], (uint32_t)((k >> 1) & 1));
+            int next2 = -1;
+            if (lane == 0) {
+                stamp(cur, 4);
+                next2 = claiming ? claim_to_item(claimed) : -1;
+                fence_proxy_async();  // the workers' generic-proxy reads of this set come before the refill
+                request(next2, b);
+                if (!a.defer_pack) __threadfence();  // the band list the workers wrote (observed through done[b]) before the ticket
+            }
+            __syncwarp();
+            if (!a.defer_pack) peaks_tail(a, cur / per_image, tail_scratch);
+            if (lane == 0) stamp(cur, 5);
+            cur = nxt;
+            nxt = __shfl_sync(0xffffffffu, next2, 0);
+        }
+        return;
+    }
+
+    // ---------------------------------------------------------------------------------------------------- workers
+    const int wtid = tid - 32, wwarp = warp - 1;
+    auto workers_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(kPeakWorkers) : "memory"); };
+    for (int k = 0;; k++) {
+        const int b = k & 1;
+        unsigned long long t_wait = 0;
+        if (a.timeline && wtid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_wait));
+        mbar_wait(&full[b], (uint32_t)((k >> 1) & 1));
+        const int item = *reinterpret_cast<volatile int *>(&s_item[b]);
+        if (item < 0) break;
+        if (wtid == 0) {
+            if (a.timeline) a.timeline[(size_t)item * 6] = t_wait;
+            stamp(item, 1);
+        }
+        const Item it = decode(item);
+        typename std::conditional<TWIN, FlipBand, PlainBand>::type B;
+        if constexpr (TWIN) {
+            B.up = buf_up(b);
+            B.tw = buf_tw(b);
+        } else {
+            B.p = buf_up(b);
+        }
+        B.l0 = it.l0;
+        B.w = w;
+        peaks_scan<FLAVOUR>(B, it.r0, it.r1, h, w, a.thr, a.cap, sc.found, &s_found[b], wtid, kPeakWorkers);
+        workers_sync();
+        if (wtid == 0) stamp(item, 2);
+        const int n_raw = *reinterpret_cast<volatile int *>(&s_found[b]);
+        const int n = min(n_raw, a.cap);
+        peaks_order(sc.found, sc.sorted, n, wtid, kPeakWorkers);
+        workers_sync();
+        const size_t slot_base = (size_t)item * a.cap;  // == ((img*18 + part)*nbands + band) * cap
+        peaks_refine<FLAVOUR>(B, a, n, sc.sorted, a.band_peaks + slot_base, slot_base, sc.hbuf_all + wwarp * sc.hbuf_per_warp, tab4, wwarp, nworkers);
+        if (wtid == 0) {
+            a.band_count[item] = n;
+            if (n_raw > a.cap) atomicOr(a.status + it.img, IBP_ST_PEAK_OVERFLOW);
+            if (a.defer_pack && n > 0) atomicAdd(a.n_raw + it.img, n);
+            stamp(item, 3);
+        }
+        // release the buffer set (and, through the control warp's fence, the band list): one arrival per warp
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&done[b]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// After a streaming launch that left the band lists unpacked: one warp per image counts them — per-part totals
+// (clamped to the capacity), the first running id of every part (parse_skeletons.py:172-173), the image total — and
+// ranks its image among the batch by number of peaks (heaviest first, ties by index), which is the order the limb
+// kernel walks the images in.
+// ---------------------------------------------------------------------------------------------------------------
+struct IndexArgs {
+    const int *band_count;  // (batch, 18, nbands)
+    const int *n_raw;       // (batch)
+    int nbands, batch, cap, line_stride;
+    int *part_count;        // (batch, 18)
+    int *partbase;          // (batch, 19)
+    int *n_peaks;           // (batch)
+    int *order;             // (batch)
+    uint32_t *status;       // (batch)
+};
+
+__global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
+    const int img = blockIdx.x, lane = threadIdx.x;
+    const int items = kParts * a.nbands;
+    const int *bc = a.band_count + (size_t)img * items;
+    // every load first: the band counts of this image, the raw totals of the batch
+    constexpr int kRounds = (kParts * 16 + 31) / 32;  // nbands <= 16 (kMaxDeferBands)
+    int cv[kRounds];
+#pragma unroll
+    for (int r = 0; r < kRounds; r++) cv[r] = (r * 32 + lane < items) ? bc[r * 32 + lane] : 0;
+    const int mine = a.n_raw[img];
+    int rank = 0;
+    for (int u0 = 0; u0 < a.batch; u0 += 32) {
+        const int u = u0 + lane;
+        const int other = (u < a.batch) ? a.n_raw[u] : -1;
+        rank += __popc(__ballot_sync(0xffffffffu, (other > mine) || (other == mine && u < img && u < a.batch)));
+    }
+    if (lane == 0) a.order[rank] = img;
+
+    __shared__ int offs[kParts * 16 + 1];
+    int total = 0;
+#pragma unroll
+    for (int r = 0; r < kRounds; r++) {
+        const int i = r * 32 + lane;
+        int incl = cv[r];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (i < items) offs[i] = total + incl - cv[r];
+        total += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 0) offs[items] = total;
+    __syncwarp();
+    bool over = false;
+    if (lane < kParts) {
+        const int first = offs[lane * a.nbands];
+        const int c = offs[(lane + 1) * a.nbands] - first;
+        over = c > a.cap;
+        a.part_count[img * kParts + lane] = min(c, a.cap);
+        a.partbase[img * (kParts + 1) + lane] = first;
+    }
+    if (lane == 0) {
+        a.partbase[img * (kParts + 1) + kParts] = total;
+        a.n_peaks[img] = min(total, a.line_stride);
+    }
+    // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
+    if (__any_sync(0xffffffffu, over) && lane == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
 }
 
 }  // namespace ibp

@@ -5,7 +5,7 @@ import os
 import sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ["IBP_DEBUG"] = "24"
+os.environ["IBP_DEBUG"] = str(24 | int(os.environ.get("IBP_DEBUG", "0")))
 os.environ["IBP_TIMELINE_PK"] = "/tmp/ibp_timeline_pk.bin"
 os.environ["IBP_TIMELINE"] = "/tmp/ibp_timeline.bin"
 import torch
@@ -45,7 +45,40 @@ p = p.reshape(B, 18, -1, 6)
 p0 = p[..., 0].min()
 P = (p - p0) / 1000.0
 names = ["stage", "nms", "sort+refine", "wait warps", "ticket"]
+st = np.sort(P[..., 0].ravel())
+print("peak items started in the first microsecond: %d (= CTAs resident at launch)" % int((st < 1.0).sum()))
 print("peak CTAs: start max %.1f, end max %.1f us; duration mean %.2f max %.2f" % (P[..., 0].max(), P[..., 5].max(), (P[..., 5] - P[..., 0]).mean(), (P[..., 5] - P[..., 0]).max()))
 for i, nme in enumerate(names):
     d = P[..., i + 1] - P[..., i]
     print("  %-12s mean %.2f  p90 %.2f  max %.2f" % (nme, d.mean(), np.percentile(d, 90), d.max()))
+
+# ---- streaming peak kernel: per-CTA view (items c, c + G, c + 2G, ... belong to CTA c) ----
+G = int((st < 1.0).sum())
+flat = P.reshape(-1, 6)
+if G > 0 and flat.shape[0] > G:
+    gaps, busy = [], []
+    for c in range(G):
+        it = flat[c::G]
+        busy.append((it[:, 5] - it[:, 0]).sum())
+        gaps.extend((it[1:, 0] - it[:-1, 5]).tolist())
+    gaps = np.array(gaps)
+    print("per CTA: %d items, busy mean %.1f us, gap between items mean %.2f p90 %.2f max %.2f" % (
+        flat[0::G].shape[0], np.mean(busy), gaps.mean(), np.percentile(gaps, 90), gaps.max()))
+    it = flat[0::G]
+    for k in range(min(6, it.shape[0])):
+        print("  CTA 0 item %d: " % k + " ".join("%.2f" % v for v in it[k]))
+    first = flat[:G, 0]
+    last_end = np.array([flat[c::G][-1, 5] for c in range(G)])
+    print("first-item start: min %.1f p50 %.1f p90 %.1f max %.1f; last-item end: min %.1f p50 %.1f p90 %.1f max %.1f" % (
+        first.min(), np.median(first), np.percentile(first, 90), first.max(), last_end.min(), np.median(last_end),
+        np.percentile(last_end, 90), last_end.max()))
+    late = np.argsort(last_end)[-3:]
+    for c in late:
+        it = flat[c::G]
+        print("  CTA %d: " % c + " | ".join("%.1f-%.1f" % (v[0], v[5]) for v in it))
+    c = int(np.argmax(last_end))
+    it = flat[c::G]
+    for k in range(min(5, it.shape[0])):
+        print("  slow CTA %d item %d: " % (c, k) + " ".join("%.2f" % v for v in it[k]))
+    slow = np.where(last_end > 1.5 * np.median(last_end))[0]
+    print("slow CTAs (%d): %s" % (len(slow), slow.tolist()))
