@@ -110,6 +110,11 @@ struct ibp_handle {
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
     int defer_bands = 0;           // > 0: the last peak launch left its band lists unpacked (this many bands per plane)
     int defer_batch = 0;
+    int4 *d_item_meta = nullptr;   // [max_batch*30] limb items in heaviest-image-first order (index_bands_kernel)
+    unsigned *d_lb_work = nullptr; // work counter of the streaming limb kernel, never reset ...
+    unsigned lb_work_base = 0;     // ... its value before the next launch
+    size_t lb_occ_smem = 0;        // occupancy of the streaming limb kernel, cached per shared-memory size
+    int lb_occ = 0;
     int *d_partbase = nullptr;     // [max_batch][19] first id of each part + image total (index_bands_kernel)
     int *d_n_raw = nullptr;        // [max_batch] peaks per image, accumulated by the streaming peak kernel (lives after d_status)
     unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
@@ -203,6 +208,8 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_order);
     free_dev(h->d_pk_work);
     free_dev(h->d_partbase);
+    free_dev(h->d_item_meta);
+    free_dev(h->d_lb_work);
     free_dev(h->d_score64);
     free_dev(h->d_py_conn);
     free_dev(h->d_py_conn_count);
@@ -309,7 +316,7 @@ void ibp_default_limits(ibp_limits *l) {
     l->max_batch = 64;
     l->max_peaks_per_part = 128;
     l->max_candidates_per_limb = 1024;
-    l->max_bodies = 256;
+    l->max_bodies = 128;  // 128 * 160 B of grouping tables fit behind a 128x128 plane in the streaming limb kernel
     l->max_humans = 128;
     l->max_feat_h = 128;
     l->max_feat_w = 128;
@@ -380,6 +387,10 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMemset(h->d_ticket, 0, (2 * B + 1) * sizeof(unsigned)));
         CU(cudaMalloc(&h->d_order, B * sizeof(int)));
         CU(cudaMalloc(&h->d_partbase, B * (kParts + 1) * sizeof(int)));
+        CU(cudaMalloc(&h->d_item_meta, B * (kLimbs + 1) * sizeof(int4)));
+        CU(cudaMalloc(&h->d_lb_work, sizeof(unsigned)));
+        CU(cudaMemset(h->d_lb_work, 0, sizeof(unsigned)));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaMalloc(&h->d_pk_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_pk_work, 0, sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
@@ -686,6 +697,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
             ia.partbase = h->d_partbase;
             ia.n_peaks = h->d_n_peaks;
             ia.order = h->d_order;
+            ia.item_meta = h->d_item_meta;
             ia.status = h->d_status;
             index_bands_kernel<<<batch, 32, 0, st>>>(ia);
             h->launches++;
@@ -832,6 +844,10 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     a.band_count = nullptr;
     a.nbands = 0;
     a.partbase = nullptr;
+    a.item_meta = nullptr;
+    a.work_counter = nullptr;
+    a.work_base = 0;
+    a.plane_bytes = 0;
     a.batch = batch;
     a.peaks_out = h->d_peaks;
     a.line_out = h->d_line;
@@ -868,6 +884,34 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     g.humans = h->d_humans;
     g.n_humans = h->d_n_humans;
     g.status = h->d_status;
+    // Streaming kernel: the pipeline's common case (see k_limbs.cuh).  The grouping tables must fit behind the plane.
+    static const bool no_lstream = getenv("IBP_LIMBS_NO_STREAM") != nullptr;
+    const size_t nonplane = smem - ((plane_bytes + 15) & ~(size_t)15);
+    const size_t scratch_tail = (size_t)kPairChunk * sizeof(PairGeo) + (size_t)kPairChunk * a.max_steps * 4;
+    if (a.band_peaks && mode == IBP_LIMB_FEAT_PLANAR && a.stage_plane && dtype == IBP_F32 && twin_base >= 0 && dim1 % 4 == 0 &&
+        ((uintptr_t)limb_src & 15u) == 0 && (image_stride * 4) % 16 == 0 && h->L.max_peaks_per_part <= 128 &&
+        limb_phase_bytes(h, plane_bytes) >= group_phase_bytes(h) && nonplane >= group_phase_bytes(h) &&
+        scratch_tail >= (size_t)a.cand_cap * 8 && !no_lstream) {
+        a.item_meta = h->d_item_meta;
+        a.work_counter = h->d_lb_work;
+        a.work_base = h->lb_work_base;
+        a.plane_bytes = (int)((plane_bytes + 15) & ~(size_t)15);
+        const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
+        if (h->lb_occ_smem != smem) {  // every CTA of the grid must be resident (queue items wait for one another)
+            int per_sm = 0;
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, limbs_stream_kernel, kLimbStreamThreads, smem));
+            h->lb_occ = per_sm;
+            h->lb_occ_smem = smem;
+        }
+        if (h->lb_occ < 1) return fail(IBP_ERR_SHAPE, "assign: streaming limb kernel does not fit");
+        const int grid = std::min(items, h->lb_occ * h->sm_count);
+        h->lb_work_base += (unsigned)items;
+        StageTimer t(h, IBP_STAGE_LIMBS, st);
+        limbs_stream_kernel<<<grid, kLimbStreamThreads, smem, st>>>(a);
+        h->launches++;
+        CU(cudaGetLastError());
+        return IBP_OK;
+    }
     {
         StageTimer t(h, IBP_STAGE_LIMBS, st);
         const dim3 grid(kLimbs, batch);
@@ -974,6 +1018,7 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
     view->status = h->h_status;
     uint32_t any = 0;
     for (int b = 0; b < batch; b++) any |= h->h_status[b];
+    if (any & IBP_ST_STALLED) return fail(IBP_ERR_CUDA, "internal: the grouping of an image never saw all of its limbs finish");
     if (any & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
         return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", any);
     return IBP_OK;

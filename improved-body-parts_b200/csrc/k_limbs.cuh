@@ -65,6 +65,11 @@ struct LimbArgs {
     const DevPeak *band_peaks;  // (batch, 18, nbands, cap)
     const int *band_count;      // (batch, 18, nbands)
     int nbands;
+    // streaming kernel only: items (image rank, limb) in heaviest-first order with their image and list sizes
+    const int4 *item_meta;      // (batch*30) {image, nA, nB, -}
+    unsigned *work_counter;     // items beyond the first gridDim.x are claimed here; never reset ...
+    unsigned work_base;         // ... its value at launch (a launch adds exactly batch*30)
+    int plane_bytes;            // streaming kernel: bytes reserved for the plane at the start of shared memory
     const int *partbase;        // (batch, 19) first id of each part, [18] = peaks of the image (index_bands_kernel)
     int batch;
     DevPeak *peaks_out;         // (batch, 18, cap)
@@ -133,6 +138,252 @@ __device__ __forceinline__ void pair_sample_xy(const PairGeo &g, int i, int &px,
     const float fi = __int2float_rn(i);
     px = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ax, __fmul_rn(fi, g.sx)), 0.5));
     py = __double2int_rz(__dadd_rn((double)__fadd_rn(g.ay, __fmul_rn(fi, g.sy)), 0.5));
+}
+
+
+// Shared-memory views of one limb item (see the carve-up in the kernels).
+struct LimbSmem {
+    uint64_t *emu;      // introsort emulation array (cand_cap entries); may alias the plane in the one-shot kernel
+    DevPeak *sA, *sB;
+    unsigned char *used_a, *used_b;
+    float *line_a, *line_b;
+    uint64_t *keys;
+    float *cand_limb;
+    uint32_t *cand_pair;
+    PairGeo *geo;
+    float *vals;
+    int *wcnt;
+};
+
+__device__ __forceinline__ void limb_stamp(const LimbArgs &a, int img, int row, int col) {
+    if (a.timeline && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        a.timeline[((size_t)img * 31 + row) * 4 + col] = t;
+    }
+}
+
+// Scores every (a, b) pair of one limb from the staged plane, orders the accepted candidates and connects them
+// greedily (pafprocess.cpp:52-130).  All threads of the CTA; the number of connections written is returned on thread 0.
+// `plane_dead` is called by every thread once the last sample has been read (after a barrier): the streaming kernel starts
+// the next item's plane copy there, under the ordering / greedy tail.
+template <int kLimbThreads, class PlaneDead>
+__device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Sampler &smp, int img, int limb, int nA, int nB,
+                                              PlaneDead plane_dead) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint64_t *emu = m.emu;
+    DevPeak *sA = m.sA, *sB = m.sB;
+    unsigned char *used_a = m.used_a, *used_b = m.used_b;
+    float *line_a = m.line_a, *line_b = m.line_b;
+    uint64_t *keys = m.keys;
+    float *cand_limb = m.cand_limb;
+    uint32_t *cand_pair = m.cand_pair;
+    PairGeo *geo = m.geo;
+    float *vals = m.vals;
+    int *wcnt = m.wcnt;
+    int n_links = 0;
+    // ---- score all pairs; compact the accepted ones in pair order ----
+    const int npairs = (a.debug & 2) ? 0 : nA * nB;
+    int ncand = 0;
+    // Few pairs (the usual image): split every pair's samples over the threads (phases 0-2 below).  Many pairs (a
+    // crowd): one thread per pair does its own samples — enough parallelism already, no staging, fewer barriers.
+    const bool direct = npairs > kLimbThreads;
+    const int chunk_size = direct ? kLimbThreads : kPairChunk;
+    for (int base = 0; base < npairs; base += chunk_size) {
+        const int chunk = min(chunk_size, npairs - base);
+        if (!direct) {
+            // (0) geometry, one thread per pair
+            if (tid < chunk) {
+                const int p = base + tid;
+                const int ia = p / nB, ib = p - ia * nB;
+                geo[tid] = pair_geometry(sA[ia], sB[ib], a.max_steps);
+            }
+            __syncthreads();
+            // (1) samples, one thread per (pair, step)
+            for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
+                const int q = it / a.max_steps, i = it - q * a.max_steps;
+                const PairGeo g = geo[q];
+                if (i < g.steps) {
+                    int px, py;
+                    pair_sample_xy(g, i, px, py);
+                    vals[it] = smp.at(px, py);
+                }
+            }
+            __syncthreads();
+        }
+        // (2) criteria, one thread per pair
+        bool ok = false;
+        float ls = 0.f, rk = 0.f;
+        int ia = 0, ib = 0;
+        if (tid < chunk) {
+            const int p = base + tid;
+            ia = p / nB;
+            ib = p - ia * nB;
+            const DevPeak A = sA[ia], B = sB[ib];
+            const PairGeo g = direct ? pair_geometry(A, B, a.max_steps) : geo[tid];
+            if (g.steps > 0) {
+                const float len = limb_length(A, B);
+                const float *v = vals + tid * a.max_steps;
+                float sum = 0.0f;
+                int above = 0;
+                for (int i = 0; i < g.steps; i++) {
+                    float vi;
+                    if (direct) {
+                        int px, py;
+                        pair_sample_xy(g, i, px, py);
+                        vi = smp.at(px, py);
+                    } else {
+                        vi = v[i];
+                    }
+                    sum = __fadd_rn(sum, vi);   // :85
+                    above += (vi > a.thr);      // :87
+                }
+                // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
+                const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
+                const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
+                ls = __double2float_rn(__dadd_rn((double)__fdiv_rn(sum, __int2float_rn(g.steps)), pen));
+                const float need = __fmul_rn(__int2float_rn(g.steps), a.step_ratio);  // :91
+                if (__int2float_rn(above) > need && ls > 0.0f) {                      // :93
+                    ok = true;
+                    rk = __fadd_rn(__fadd_rn(__fmul_rn(a.w_limb, ls), __fmul_rn(a.w_a, A.score)), __fmul_rn(a.w_b, B.score));  // :94-96
+                }
+            }
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) wcnt[warp] = __popc(bal);
+        __syncthreads();
+        int woff = 0, tot = 0;
+#pragma unroll
+        for (int i = 0; i < kLimbThreads / 32; i++) {
+            const int t = wcnt[i];
+            if (i < warp) woff += t;
+            tot += t;
+        }
+        if (ok) {
+            const int idx = ncand + woff + __popc(bal & ((1u << lane) - 1u));
+            if (idx < a.cand_cap) {
+                keys[idx] = ((uint64_t)float_orderable(rk) << 32) | (uint32_t)idx;
+                cand_limb[idx] = ls;
+                cand_pair[idx] = ((uint32_t)ia << 16) | (uint32_t)ib;
+            }
+        }
+        ncand += tot;
+        __syncthreads();
+    }
+    plane_dead();
+    limb_stamp(a, img, limb, 2);
+    if (ncand > a.cand_cap) {
+        if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
+        ncand = a.cand_cap;
+    }
+
+    if (ncand > 0) {
+        // ---- order: descending on (score, index); keys are distinct because they carry the index ----
+        if (ncand <= kRankSortMax) {
+            // rank sort: one pass, two barriers — the common case (a handful of candidates per limb)
+            uint64_t mine[kRankSortMax / kLimbThreads];
+            int rank[kRankSortMax / kLimbThreads];
+#pragma unroll
+            for (int q = 0; q < kRankSortMax / kLimbThreads; q++) {
+                const int i = tid + q * kLimbThreads;
+                mine[q] = (i < ncand) ? keys[i] : 0;
+                rank[q] = 0;
+            }
+            for (int j = 0; j < ncand; j++) {
+                const uint64_t kj = keys[j];
+#pragma unroll
+                for (int q = 0; q < kRankSortMax / kLimbThreads; q++) rank[q] += (kj > mine[q]);
+            }
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < kRankSortMax / kLimbThreads; q++)
+                if (tid + q * kLimbThreads < ncand) keys[rank[q]] = mine[q];
+            __syncthreads();
+        } else {
+            int np2 = 1;
+            while (np2 < ncand) np2 <<= 1;
+            for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
+            __syncthreads();
+            for (int k = 2; k <= np2; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < np2; i += kLimbThreads) {
+                        const int l = i ^ j;
+                        if (l > i) {
+                            const uint64_t x = keys[i], y = keys[l];
+                            const bool desc = ((i & k) == 0);
+                            if (desc ? (x < y) : (x > y)) {
+                                keys[i] = y;
+                                keys[l] = x;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+        }
+        // duplicate keys?
+        bool dup = false;
+        for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
+        const bool emulate = __syncthreads_or(dup && ncand > 16);
+        if (emulate) {
+            // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
+            for (int i = tid; i < ncand; i += kLimbThreads) {
+                const uint64_t kv = keys[i];
+                const uint32_t idx = (uint32_t)kv;
+                emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
+                atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
+            }
+            __syncthreads();
+        }
+        const uint64_t *order = emulate ? emu : keys;
+
+        // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order ----
+        if (warp == 0) {
+            const int max_links = min(nA, nB);
+            DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
+            int nl = 0;
+            for (int base = 0; base < ncand && nl < max_links; base += 32) {
+                const int i = base + lane;
+                bool valid = i < ncand;
+                int ia = 0, ib = 0, cidx = 0;
+                if (valid) {
+                    cidx = (int)(uint32_t)order[i];
+                    const uint32_t pr = cand_pair[cidx];
+                    ia = (int)(pr >> 16);
+                    ib = (int)(pr & 0xffffu);
+                }
+                while (nl < max_links) {
+                    const bool free_now = valid && !used_a[ia] && !used_b[ib];
+                    const uint32_t bal = __ballot_sync(0xffffffffu, free_now);
+                    if (bal == 0) break;
+                    const int leader = __ffs(bal) - 1;
+                    if (lane == leader) {
+                        used_a[ia] = 1;
+                        used_b[ib] = 1;
+                        DevLink l;
+                        l.id_a = sA[ia].id;
+                        l.id_b = sB[ib].id;
+                        l.limb = cand_limb[cidx];
+                        l.len = limb_length(sA[ia], sB[ib]);
+                        l.gate = length_gate(l.len, a.group.len_rate);
+                        l.pad = 0.f;
+                        l.score_a = line_a[ia];
+                        l.score_b = line_b[ib];
+                        out[nl] = l;
+                        valid = false;
+                    }
+                    nl++;
+                    __syncwarp();
+                }
+            }
+            n_links = nl;
+        }
+    }
+    return n_links;
 }
 
 template <typename T, int kLimbThreads>
@@ -333,206 +584,21 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         }
 
         stamp(limb, 1);
-        // ---- score all pairs; compact the accepted ones in pair order ----
-        const int npairs = (a.debug & 2) ? 0 : nA * nB;
-        int ncand = 0;
-        // Few pairs (the usual image): split every pair's samples over the threads (phases 0-2 below).  Many pairs (a
-        // crowd): one thread per pair does its own samples — enough parallelism already, no staging, fewer barriers.
-        const bool direct = npairs > kLimbThreads;
-        const int chunk_size = direct ? kLimbThreads : kPairChunk;
-        for (int base = 0; base < npairs; base += chunk_size) {
-            const int chunk = min(chunk_size, npairs - base);
-            if (!direct) {
-                // (0) geometry, one thread per pair
-                if (tid < chunk) {
-                    const int p = base + tid;
-                    const int ia = p / nB, ib = p - ia * nB;
-                    geo[tid] = pair_geometry(sA[ia], sB[ib], a.max_steps);
-                }
-                __syncthreads();
-                // (1) samples, one thread per (pair, step)
-                for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
-                    const int q = it / a.max_steps, i = it - q * a.max_steps;
-                    const PairGeo g = geo[q];
-                    if (i < g.steps) {
-                        int px, py;
-                        pair_sample_xy(g, i, px, py);
-                        vals[it] = smp.at(px, py);
-                    }
-                }
-                __syncthreads();
-            }
-            // (2) criteria, one thread per pair
-            bool ok = false;
-            float ls = 0.f, rk = 0.f;
-            int ia = 0, ib = 0;
-            if (tid < chunk) {
-                const int p = base + tid;
-                ia = p / nB;
-                ib = p - ia * nB;
-                const DevPeak A = sA[ia], B = sB[ib];
-                const PairGeo g = direct ? pair_geometry(A, B, a.max_steps) : geo[tid];
-                if (g.steps > 0) {
-                    const float len = limb_length(A, B);
-                    const float *v = vals + tid * a.max_steps;
-                    float sum = 0.0f;
-                    int above = 0;
-                    for (int i = 0; i < g.steps; i++) {
-                        float vi;
-                        if (direct) {
-                            int px, py;
-                            pair_sample_xy(g, i, px, py);
-                            vi = smp.at(px, py);
-                        } else {
-                            vi = v[i];
-                        }
-                        sum = __fadd_rn(sum, vi);   // :85
-                        above += (vi > a.thr);      // :87
-                    }
-                    // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
-                    const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
-                    const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
-                    ls = __double2float_rn(__dadd_rn((double)__fdiv_rn(sum, __int2float_rn(g.steps)), pen));
-                    const float need = __fmul_rn(__int2float_rn(g.steps), a.step_ratio);  // :91
-                    if (__int2float_rn(above) > need && ls > 0.0f) {                      // :93
-                        ok = true;
-                        rk = __fadd_rn(__fadd_rn(__fmul_rn(a.w_limb, ls), __fmul_rn(a.w_a, A.score)), __fmul_rn(a.w_b, B.score));  // :94-96
-                    }
-                }
-            }
-            const uint32_t bal = __ballot_sync(0xffffffffu, ok);
-            if (lane == 0) wcnt[warp] = __popc(bal);
-            __syncthreads();
-            int woff = 0, tot = 0;
-#pragma unroll
-            for (int i = 0; i < kLimbThreads / 32; i++) {
-                const int t = wcnt[i];
-                if (i < warp) woff += t;
-                tot += t;
-            }
-            if (ok) {
-                const int idx = ncand + woff + __popc(bal & ((1u << lane) - 1u));
-                if (idx < a.cand_cap) {
-                    keys[idx] = ((uint64_t)float_orderable(rk) << 32) | (uint32_t)idx;
-                    cand_limb[idx] = ls;
-                    cand_pair[idx] = ((uint32_t)ia << 16) | (uint32_t)ib;
-                }
-            }
-            ncand += tot;
-            __syncthreads();
-        }
-        stamp(limb, 2);
-        if (ncand > a.cand_cap) {
-            if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
-            ncand = a.cand_cap;
-        }
-
-        if (ncand > 0) {
-            // ---- order: descending on (score, index); keys are distinct because they carry the index ----
-            if (ncand <= kRankSortMax) {
-                // rank sort: one pass, two barriers — the common case (a handful of candidates per limb)
-                uint64_t mine[kRankSortMax / kLimbThreads];
-                int rank[kRankSortMax / kLimbThreads];
-#pragma unroll
-                for (int q = 0; q < kRankSortMax / kLimbThreads; q++) {
-                    const int i = tid + q * kLimbThreads;
-                    mine[q] = (i < ncand) ? keys[i] : 0;
-                    rank[q] = 0;
-                }
-                for (int j = 0; j < ncand; j++) {
-                    const uint64_t kj = keys[j];
-#pragma unroll
-                    for (int q = 0; q < kRankSortMax / kLimbThreads; q++) rank[q] += (kj > mine[q]);
-                }
-                __syncthreads();
-#pragma unroll
-                for (int q = 0; q < kRankSortMax / kLimbThreads; q++)
-                    if (tid + q * kLimbThreads < ncand) keys[rank[q]] = mine[q];
-                __syncthreads();
-            } else {
-                int np2 = 1;
-                while (np2 < ncand) np2 <<= 1;
-                for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
-                __syncthreads();
-                for (int k = 2; k <= np2; k <<= 1) {
-                    for (int j = k >> 1; j > 0; j >>= 1) {
-                        for (int i = tid; i < np2; i += kLimbThreads) {
-                            const int l = i ^ j;
-                            if (l > i) {
-                                const uint64_t x = keys[i], y = keys[l];
-                                const bool desc = ((i & k) == 0);
-                                if (desc ? (x < y) : (x > y)) {
-                                    keys[i] = y;
-                                    keys[l] = x;
-                                }
-                            }
-                        }
-                        __syncthreads();
-                    }
-                }
-            }
-            // duplicate keys?
-            bool dup = false;
-            for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
-            const bool emulate = __syncthreads_or(dup && ncand > 16);
-            if (emulate) {
-                // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
-                for (int i = tid; i < ncand; i += kLimbThreads) {
-                    const uint64_t kv = keys[i];
-                    const uint32_t idx = (uint32_t)kv;
-                    emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
-                }
-                __syncthreads();
-                if (tid == 0) {
-                    const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
-                    atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
-                }
-                __syncthreads();
-            }
-            const uint64_t *order = emulate ? emu : keys;
-
-            // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order ----
-            if (warp == 0) {
-                const int max_links = min(nA, nB);
-                DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
-                int nl = 0;
-                for (int base = 0; base < ncand && nl < max_links; base += 32) {
-                    const int i = base + lane;
-                    bool valid = i < ncand;
-                    int ia = 0, ib = 0, cidx = 0;
-                    if (valid) {
-                        cidx = (int)(uint32_t)order[i];
-                        const uint32_t pr = cand_pair[cidx];
-                        ia = (int)(pr >> 16);
-                        ib = (int)(pr & 0xffffu);
-                    }
-                    while (nl < max_links) {
-                        const bool free_now = valid && !used_a[ia] && !used_b[ib];
-                        const uint32_t bal = __ballot_sync(0xffffffffu, free_now);
-                        if (bal == 0) break;
-                        const int leader = __ffs(bal) - 1;
-                        if (lane == leader) {
-                            used_a[ia] = 1;
-                            used_b[ib] = 1;
-                            DevLink l;
-                            l.id_a = sA[ia].id;
-                            l.id_b = sB[ib].id;
-                            l.limb = cand_limb[cidx];
-                            l.len = limb_length(sA[ia], sB[ib]);
-                            l.gate = length_gate(l.len, a.group.len_rate);
-                            l.pad = 0.f;
-                            l.score_a = line_a[ia];
-                            l.score_b = line_b[ib];
-                            out[nl] = l;
-                            valid = false;
-                        }
-                        nl++;
-                        __syncwarp();
-                    }
-                }
-                n_links = nl;
-            }
-        }
+        LimbSmem m;
+        m.emu = emu;
+        m.sA = sA;
+        m.sB = sB;
+        m.used_a = used_a;
+        m.used_b = used_b;
+        m.line_a = line_a;
+        m.line_b = line_b;
+        m.keys = keys;
+        m.cand_limb = cand_limb;
+        m.cand_pair = cand_pair;
+        m.geo = geo;
+        m.vals = vals;
+        m.wcnt = wcnt;
+        n_links = score_and_link<kLimbThreads>(a, m, smp, img, limb, nA, nB, [] {});
     }
     if (tid == 0) *link_count = n_links;
     stamp(limb, 3);
@@ -552,6 +618,283 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
     stamp(30, 0);
     group_image(a.group, img, smem_raw, (size_t)a.smem_bytes);
     stamp(30, 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Streaming variant: a persistent grid (two CTAs per SM) walks one work queue — per image, heaviest image first: its
+// 30 limbs, then "group this image" — item blockIdx.x first, then whatever the shared counter hands out.  Only for
+// the pipeline's common case: float32 network output with the flip twin, plane staged in shared memory, peak lists
+// left in bands by the streaming peak kernel (item_meta / partbase from index_bands_kernel).
+// The point of the loop: the plane buffer is dead once the last sample of an item has been read, long before the item
+// is finished (ordering, greedy selection, connection records, ticket, possibly the grouping of the whole image).
+// Thread 0 claims the next item at the top of each round, learns its image and list sizes while the CTA stages and
+// scores, and starts the bulk copy of the NEXT item's upright plane the moment scoring ends — so that plane is
+// (mostly) there when the next round begins and the round only streams the twin rows through the ring.
+// Grouping is a queue item of its own so that no CTA ever sits on a claimed limb while it runs a long chain: whoever
+// claims it waits (holding nothing else) until the image's 30 limbs have published their connections — they were
+// claimed just before by CTAs that never wait for anybody, so the wait is bounded by one limb's run time — groups, and
+// only then claims again.  The grouping tables live behind the plane buffer, so a copy in flight is never in their way.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kLimbStreamThreads = 256;
+
+__global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(LimbArgs a) {
+    constexpr int kLimbThreads = kLimbStreamThreads;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int tid = threadIdx.x;
+    const int items = a.batch * (kLimbs + 1);
+    const size_t hw = (size_t)a.h * a.w;
+    const uint32_t plane_copy_bytes = (uint32_t)(hw * 4);
+
+    // ---- carve shared memory: plane | peak lists | ring = candidate / geometry / sample scratch ----
+    float *plane_s = reinterpret_cast<float *>(smem_raw);
+    size_t off = (size_t)a.plane_bytes;
+    LimbSmem m;
+    m.sA = reinterpret_cast<DevPeak *>(smem_raw + off);
+    off += (size_t)a.cap * sizeof(DevPeak);
+    m.sB = reinterpret_cast<DevPeak *>(smem_raw + off);
+    off += (size_t)a.cap * sizeof(DevPeak);
+    m.used_a = smem_raw + off;
+    off += (size_t)a.cap;
+    m.used_b = smem_raw + off;
+    off += (size_t)a.cap;
+    off = (off + 15) & ~(size_t)15;
+    m.line_a = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)a.cap * 4;
+    m.line_b = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)a.cap * 4;
+    off = (off + 15) & ~(size_t)15;
+    const size_t ring_off = off;
+    m.keys = reinterpret_cast<uint64_t *>(smem_raw + off);
+    off += (size_t)a.cand_cap * 8;
+    m.cand_limb = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)a.cand_cap * 4;
+    m.cand_pair = reinterpret_cast<uint32_t *>(smem_raw + off);
+    off += (size_t)a.cand_cap * 4;
+    m.geo = reinterpret_cast<PairGeo *>(smem_raw + off);
+    m.emu = reinterpret_cast<uint64_t *>(smem_raw + off);  // geometry + sample scratch are idle by then (host checks the size)
+    off += (size_t)kPairChunk * sizeof(PairGeo);
+    m.vals = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)kPairChunk * a.max_steps * 4;
+    const int ring_bytes = (int)((off - ring_off) & ~(size_t)15);
+    float *ring = reinterpret_cast<float *>(smem_raw + ring_off);
+    const int slot_rows = min(a.h, (ring_bytes / kLimbRing) / (a.w * 4));
+    const int nchunks = (a.h + slot_rows - 1) / slot_rows;
+    __shared__ uint64_t bars[1 + kLimbRing];
+    __shared__ int wcnt[kLimbThreads / 32];
+    __shared__ int s_last;
+    __shared__ float tab4[4][4];
+    __shared__ int s_partbase[kParts + 1];
+    __shared__ int s_bc[kParts * kMaxDeferBands];
+    __shared__ int4 s_next;  // {image, nA, nB, limb (30: group the image)}; image < 0: no more work
+    m.wcnt = wcnt;
+
+    auto claim_to_item = [&](unsigned t) {
+        const unsigned rel = t - a.work_base + gridDim.x;
+        return rel < (unsigned)items ? (int)rel : -1;
+    };
+    auto upright_of = [&](int img, int limb) {
+        return reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride + (size_t)limb * hw;
+    };
+    auto twin_of = [&](int img, int limb) {  // flipped image: channel flip_paf_ord[limb] of its block (config/config.py:150-152)
+        return reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride + (size_t)(a.twin_base + c_flip_src[limb]) * hw;
+    };
+    auto twin_chunk = [&](const float *twin, int c) {  // one thread: chunk c of the twin plane into its ring slot
+        const int s = c % kLimbRing, first = c * slot_rows;
+        const int rows = min(slot_rows, a.h - first);
+        bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * a.w * 4u, &bars[1 + s]);
+    };
+
+    if (tid == 0) {
+        for (int i = 0; i <= kLimbRing; i++) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+        const int4 first = a.item_meta[blockIdx.x];  // the grid never exceeds the item count
+        if (first.y > 0 && first.z > 0) bulk_rows(plane_s, upright_of(first.x, first.w), plane_copy_bytes, &bars[0]);
+        s_next = first;
+    }
+    cubic_tab4_init(tab4);
+    __syncthreads();
+
+    uint32_t up_uses = 0;   // completed waits on bars[0] (one per item with pairs)
+    uint32_t ring_par = 0;  // bit s: parity of the next wait on ring slot s
+    for (;;) {
+        const int4 cur = s_next;
+        if (cur.x < 0) break;
+        const int img = cur.x, nA = cur.y, nB = cur.z, limb = cur.w;
+        unsigned claimed = 0;
+        int4 nmeta = make_int4(-1, 0, 0, 0);
+        // thread 0: who is next (one load, issued early), and — once the plane is dead — start its upright plane
+        auto resolve_next = [&]() {
+            if (tid == 0) {
+                const int nitem = claim_to_item(claimed);
+                if (nitem >= 0) nmeta = a.item_meta[nitem];
+            }
+        };
+        auto prefetch_next = [&]() {
+            if (tid == 0) {
+                if (nmeta.x >= 0 && nmeta.y > 0 && nmeta.z > 0) {
+                    fence_proxy_async();  // the samples read through the generic proxy come first
+                    bulk_rows(plane_s, upright_of(nmeta.x, nmeta.w), plane_copy_bytes, &bars[0]);
+                }
+                s_next = nmeta;
+            }
+        };
+        if (limb == kLimbs) {
+            // ---- group the image (pafprocess.cpp:133-285) once its 30 limbs are in ----
+            if (tid == 0) {
+                unsigned seen = 0;
+                for (int spins = 0; spins < (1 << 22); spins++) {
+                    asm volatile("ld.acquire.gpu.u32 %0, [%1];" : "=r"(seen) : "l"(a.ticket + img) : "memory");
+                    if (seen >= (unsigned)kLimbs) break;
+                    __nanosleep(100);
+                }
+                s_last = seen >= (unsigned)kLimbs;
+                if (s_last) a.ticket[img] = 0;  // ready for the next launch
+                else atomicOr(a.status + img, IBP_ST_STALLED);
+            }
+            __syncthreads();
+            if (s_last && !(a.debug & 1)) {
+                limb_stamp(a, img, 30, 0);
+                group_image(a.group, img, smem_raw + a.plane_bytes, (size_t)a.smem_bytes - (size_t)a.plane_bytes);
+                limb_stamp(a, img, 30, 1);
+            }
+            // claim only now: nothing must wait behind a grouping chain
+            if (tid == 0) claimed = atomicAdd(a.work_counter, 1u);
+            resolve_next();
+            prefetch_next();
+            __syncthreads();
+            continue;
+        }
+        const int pa = c_limb_a[limb], pb = c_limb_b[limb];
+        const bool pairs = nA > 0 && nB > 0;
+        const float *twin = twin_of(img, limb);
+        // thread 0: next claim out now, answer used later; the ring is free again: first twin chunks out
+        if (tid == 0) {
+            claimed = atomicAdd(a.work_counter, 1u);
+            if (pairs) {
+                fence_proxy_async();  // the previous round's generic-proxy use of the ring region comes first
+                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(twin, c);
+            }
+        }
+        limb_stamp(a, img, limb, 0);
+        {  // band counts / first ids of this image
+            const int nitems = kParts * a.nbands;
+            for (int i = tid; i < nitems; i += kLimbThreads) s_bc[i] = a.band_count[(size_t)img * nitems + i];
+            if (tid <= kParts) s_partbase[tid] = a.partbase[img * (kParts + 1) + tid];
+        }
+        __syncthreads();
+        // k-th peak of part p = entry (band, k - first of band) of the band lists, with its running id
+        auto gather_part = [&](int p, int k, DevPeak &out) {
+            const int *bc = s_bc + p * a.nbands;
+            int bnd = 0, first = 0;
+            for (; bnd + 1 < a.nbands; bnd++) {
+                const int c = bc[bnd];
+                if (k < first + c) break;
+                first += c;
+            }
+            out = a.band_peaks[(((size_t)img * kParts + p) * a.nbands + bnd) * a.cap + (k - first)];
+            out.id = s_partbase[p] + k;
+        };
+        // the CTA of limb l < 18 writes part l of the packed arrays the results are fetched from (evaluate.py:99-108)
+        auto pack_part = [&]() {
+            if (limb >= kParts) return;
+            const int n = min(s_partbase[limb + 1] - s_partbase[limb], a.cap);
+            for (int k = tid; k < n; k += kLimbThreads) {
+                DevPeak p;
+                gather_part(limb, k, p);
+                a.peaks_out[((size_t)img * kParts + limb) * a.cap + k] = p;
+                if (p.id < a.line_stride) {
+                    ibp_peak o;
+                    o.x = p.x;
+                    o.y = p.y;
+                    o.score = p.score;
+                    o.part = limb;
+                    a.line_out[(size_t)img * a.line_stride + p.id] = o;
+                }
+            }
+        };
+        int n_links = 0;
+        if (!pairs) {  // no pair => no candidate => no connection (covers the both-empty skip at :57)
+            pack_part();
+            resolve_next();
+            prefetch_next();
+        } else {
+            for (int i = tid; i < nA; i += kLimbThreads) {
+                DevPeak p;
+                gather_part(pa, i, p);
+                m.sA[i] = p;
+                m.used_a[i] = 0;
+                m.line_a[i] = p.score;  // ids are arrival order here, so peak_infos_line[id] is the peak itself
+            }
+            for (int i = tid; i < nB; i += kLimbThreads) {
+                DevPeak p;
+                gather_part(pb, i, p);
+                m.sB[i] = p;
+                m.used_b[i] = 0;
+                m.line_b[i] = p.score;
+            }
+            pack_part();
+            resolve_next();
+            // ---- fold the twin rows into the upright plane as they land (utils/parse_skeletons.py:91-92) ----
+            mbar_wait(&bars[0], up_uses & 1u);
+            up_uses++;
+            {
+                const int wv = a.w >> 2;
+                const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
+                float4 *d4 = reinterpret_cast<float4 *>(plane_s);
+                for (int c = 0; c < nchunks; c++) {
+                    const int s = c % kLimbRing;
+                    mbar_wait(&bars[1 + s], (ring_par >> s) & 1u);
+                    ring_par ^= 1u << s;
+                    const int first = c * slot_rows;
+                    const int rows = min(slot_rows, a.h - first);
+                    const float4 *r4 = reinterpret_cast<const float4 *>(ring + (size_t)s * slot_rows * a.w);
+                    float4 *o4 = d4 + (size_t)first * wv;
+                    for (int i = tid; i < rows * wv; i += kLimbThreads) {
+                        const int r = (shift >= 0) ? (i >> shift) : (i / wv);
+                        const int col = i - r * wv;
+                        float4 v = o4[i];
+                        const float4 t = r4[r * wv + (wv - 1 - col)];
+                        v.x = avg_like_numpy(v.x, t.w);
+                        v.y = avg_like_numpy(v.y, t.z);
+                        v.z = avg_like_numpy(v.z, t.y);
+                        v.w = avg_like_numpy(v.w, t.x);
+                        o4[i] = v;
+                    }
+                    if (c + kLimbRing < nchunks) {
+                        __syncthreads();  // everybody has read slot s
+                        if (tid == 0) {
+                            fence_proxy_async();
+                            twin_chunk(twin, c + kLimbRing);
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+            limb_stamp(a, img, limb, 1);
+            Sampler smp;
+            smp.mode = IBP_LIMB_FEAT_PLANAR;
+            smp.limb = limb;
+            smp.H = a.H;
+            smp.W = a.W;
+            smp.C = a.C;
+            smp.h = a.h;
+            smp.w = a.w;
+            smp.up = a.up;
+            smp.tab4 = tab4;
+            smp.base = plane_s;
+            n_links = score_and_link<kLimbThreads>(a, m, smp, img, limb, nA, nB, prefetch_next);
+        }
+        if (tid == 0) a.link_count[img * kLimbs + limb] = n_links;
+        limb_stamp(a, img, limb, 3);
+
+        // ---- publish: connections and count of this limb are out (warp 0 wrote them); the image's group item counts 30 ----
+        if (tid < 32) {
+            __threadfence();
+            __syncwarp();
+            if (tid == 0) atomicAdd(a.ticket + img, 1u);
+        }
+        __syncthreads();  // s_next, and every use of this round's shared data
+    }
 }
 
 }  // namespace ibp

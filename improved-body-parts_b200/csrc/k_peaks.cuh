@@ -827,6 +827,8 @@ struct IndexArgs {
     int *partbase;          // (batch, 19)
     int *n_peaks;           // (batch)
     int *order;             // (batch)
+    int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel.  Rank r (0 = most peaks) owns
+                            // [r*31, r*31+31): {image, nA, nB, limb} for its 30 limbs, then {image, 0, 0, 30} = "group it"
     uint32_t *status;       // (batch)
 };
 
@@ -876,6 +878,13 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
         a.partbase[img * (kParts + 1) + kParts] = total;
         a.n_peaks[img] = min(total, a.line_stride);
     }
+    if (a.item_meta && lane < kLimbs) {
+        const int pa = c_limb_a[lane], pb = c_limb_b[lane];
+        const int na = min(offs[(pa + 1) * a.nbands] - offs[pa * a.nbands], a.cap);
+        const int nb = min(offs[(pb + 1) * a.nbands] - offs[pb * a.nbands], a.cap);
+        a.item_meta[rank * (kLimbs + 1) + lane] = make_int4(img, na, nb, lane);
+    }
+    if (a.item_meta && lane == kLimbs) a.item_meta[rank * (kLimbs + 1) + kLimbs] = make_int4(img, 0, 0, kLimbs);
     // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
     if (__any_sync(0xffffffffu, over) && lane == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
 }

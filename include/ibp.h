@@ -58,6 +58,7 @@ extern "C" {
 #define IBP_ST_HUMAN_OVERFLOW 0x8u   /* more humans than limits.max_humans */
 #define IBP_ST_TIE_EMULATED 0x10u    /* a limb had > 16 candidates with duplicate sort keys; order taken from the
                                         libstdc++ introsort emulation (pafprocess.cpp:109) */
+#define IBP_ST_STALLED 0x40u         /* internal: the grouping of an image never saw all 30 limbs finish (ibp_fetch fails) */
 #define IBP_ST_TIE_UNDEFINED 0x20u   /* ...and the reference's std::sort would have read out of bounds there */
 
 /* Constants the reference compiles in (pafprocess.h:6-18) or reads from utils/config:16-27. */

@@ -103,3 +103,38 @@ def test_upsample_limbs_exact(pp):
     t = torch.from_numpy(np.ascontiguousarray(paf.transpose(2, 0, 1))[None]).cuda()
     got = pp.upsample_limbs(t, 4)[0].cpu().numpy()
     assert np.array_equal(got, O.limb_upsample(paf, 4))
+
+
+def test_streaming_kernels_default_limits(oracle):
+    """A batch through a handle with DEFAULT limits — the configuration bench.py runs, which takes the persistent
+    streaming kernels (peaks, band index, limbs) — against the oracle image by image: peaks, ids, skeletons, scores.
+    Twice, with a different batch in between, so that the work counters and tickets carried from launch to launch are
+    exercised too."""
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    B = 24
+    pp = PostProcessor(device=0, max_batch=B)
+    batch = np.stack([synth.make_network_output(400 + b, 1 + (b * 5) % 11)[0] for b in range(B)])
+    batch[3] = 0.0                                   # an image without any peak
+    batch[7, :, :30] = 0.0                           # peaks but no limb evidence: no connection at all
+    want = [_oracle_image(oracle, batch[b]) for b in range(B)]
+    other = np.stack([synth.make_network_output(900 + b, 3)[0] for b in range(5)])
+    for rnd in range(2):
+        res = pp(batch, 512)
+        for b in range(B):
+            _, _, peaks, jl, humans = want[b]
+            assert res.n_peaks[b] == jl.shape[0], (rnd, b)
+            assert np.array_equal(res.part_count[b], [len(p) for p in peaks])
+            got = res.peaks[b]
+            assert np.array_equal(got["x"], jl[:, 0].astype(np.int32))
+            assert np.array_equal(got["y"], jl[:, 1].astype(np.int32))
+            assert np.array_equal(got["score"], jl[:, 2])
+            assert np.array_equal(got["part"], jl[:, 4].astype(np.int32))
+            assert res.n_humans[b] == len(humans), (rnd, b)
+            for rec, (ids, score) in zip(res.humans[b], humans):
+                assert np.array_equal(rec["peak_id"], ids)
+                assert rec["score"] == score
+            assert res.status[b] & 0xF == 0
+        small = pp(other, 512)                       # a different batch size in between
+        assert small.n_humans.shape[0] == 5
+    assert pp.handle.launches == 2 * (3 + 3)         # peaks + band index + limbs per call: the streaming route ran
