@@ -40,7 +40,10 @@ struct GroupArgs {
     uint32_t *status;        // (batch)
 };
 
-constexpr size_t kBodyBytes = kParts * 8 + 16;  // shared bytes per row of the skeleton table
+// Slots of one row are 19 (not 18) int2 apart: with an odd stride in 8-byte units the 32 lanes of a warp, each reading
+// the same part of a different row, hit different banks.
+constexpr int kSlotStride = kParts + 1;
+constexpr size_t kBodyBytes = kSlotStride * 8 + 16;  // shared bytes per row of the skeleton table
 constexpr int kDeadId = -3;                      // id in every slot of an erased row: equals no peak id, not -1
 
 // pafprocess.cpp:154 / :186  min_len = (int)(length * LIMB_LENGTH_RATE), later compared with a float
@@ -72,7 +75,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
         loff[tid] = incl - n;  // loff[30] = total, loff[31] unused
     }
     // the first 32 rows can be scanned without a bounds test: give them ids that match nothing
-    for (int i = tid; i < 32 * kParts; i += (int)blockDim.x) slot[i] = make_int2(kDeadId, 0);
+    for (int i = tid; i < 32 * kSlotStride; i += (int)blockDim.x) slot[i] = make_int2(kDeadId, 0);
     __syncthreads();
     for (int l = warp; l < kLimbs; l += (int)(blockDim.x >> 5)) {
         const int n = loff[l + 1] - loff[l];
@@ -118,8 +121,8 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
             float4 my_row;
             if (nb <= 32) {
                 // one row per lane; rows >= nb still hold the never-matching initial ids, so no bounds test
-                const int ia = slot[lane * kParts + pa].x;
-                my_pb = slot[lane * kParts + pb];
+                const int ia = slot[lane * kSlotStride + pa].x;
+                my_pb = slot[lane * kSlotStride + pb];
                 my_row = row[lane];
                 const uint32_t bal = __ballot_sync(0xffffffffu, ia == l.id_a || my_pb.x == l.id_b);
                 hits = __popc(bal);
@@ -134,8 +137,8 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                     int2 pbv = make_int2(kDeadId, 0);
                     float4 rw = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (s < nb) {
-                        ia = slot[s * kParts + pa].x;
-                        pbv = slot[s * kParts + pb];
+                        ia = slot[s * kSlotStride + pa].x;
+                        pbv = slot[s * kSlotStride + pb];
                         rw = row[s];
                     }
                     const uint32_t bal = __ballot_sync(0xffffffffu, ia == l.id_a || pbv.x == l.id_b);
@@ -163,7 +166,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                 const bool grow = (cur_id == -1) & (gate > l.len);
                 const bool swap = !grow & (cur_sc <= l.limb) & ((cur_id == l.id_b) | ((cur_id != l.id_b) & (gate > l.len)));
                 if ((lane == (f & 31)) & (grow | swap)) {
-                    slot[f * kParts + pb] = make_int2(l.id_b, __float_as_int(l.limb));
+                    slot[f * kSlotStride + pb] = make_int2(l.id_b, __float_as_int(l.limb));
                     float4 nr;
                     // swap (:168-169 / :177-178) subtracts the values just written, then adds them back
                     nr.x = grow ? __fadd_rn(my_row.x, add) : __fadd_rn(__fsub_rn(my_row.x, add), add);
@@ -177,8 +180,8 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                 const int f = first, g = second;
                 int2 vm = make_int2(-1, 0), vo = make_int2(-1, 0);
                 if (lane < kParts) {
-                    vm = slot[f * kParts + lane];
-                    vo = slot[g * kParts + lane];
+                    vm = slot[f * kSlotStride + lane];
+                    vo = slot[g * kSlotStride + lane];
                 }
                 const float4 rf = row[f], rg = row[g];
                 const int idm = vm.x, ido = vo.x;
@@ -198,8 +201,8 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                     if (l.limb >= floor_score || l.len < rf.y) {  // :220, rf.y = (int)(length*16) of row f (:186)
                         if (lane < kParts) {
                             // :222-225 ids and scores are ADDED (+1 undoes the -1 of an empty slot)
-                            slot[f * kParts + lane] = make_int2(idm + (ido + 1), __float_as_int(__fadd_rn(scm, __fadd_rn(sco, 1.0f))));
-                            slot[g * kParts + lane] = make_int2(kDeadId, 0);  // :229 erase
+                            slot[f * kSlotStride + lane] = make_int2(idm + (ido + 1), __float_as_int(__fadd_rn(scm, __fadd_rn(sco, 1.0f))));
+                            slot[g * kSlotStride + lane] = make_int2(kDeadId, 0);  // :229 erase
                         }
                         if (lane == 0) {  // :226-228
                             float4 nr;
@@ -218,7 +221,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                 if (nb < S) {
                     if (lane < kParts) {
                         const bool end = (lane == pa || lane == pb);
-                        slot[nb * kParts + lane] = make_int2((lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1),
+                        slot[nb * kSlotStride + lane] = make_int2((lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1),
                                                              __float_as_int(end ? l.limb : -1.0f));
                     }
                     if (lane == 0)
@@ -251,7 +254,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
             const int o = n_out + __popc(bal & ((1u << lane) - 1u));
             if (o < a.max_humans) {
                 ibp_human hmn;
-                for (int k = 0; k < kParts; k++) hmn.peak_id[k] = slot[s * kParts + k].x;
+                for (int k = 0; k < kParts; k++) hmn.peak_id[k] = slot[s * kSlotStride + k].x;
                 hmn.score = __fdiv_rn(rw.x, __int2float_rn(cnt));
                 hmn.total = rw.x;
                 hmn.count = cnt;

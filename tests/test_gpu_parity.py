@@ -138,3 +138,25 @@ def test_streaming_kernels_default_limits(oracle):
         small = pp(other, 512)                       # a different batch size in between
         assert small.n_humans.shape[0] == 5
     assert pp.handle.launches == 2 * (3 + 3)         # peaks + band index + limbs per call: the streaming route ran
+
+
+def test_streaming_equals_one_shot_kernels_stress():
+    """Race hunt: the persistent streaming kernels (default limits) against the one-CTA-per-item kernels (a handle whose
+    limits rule the streaming route out) on random batches, everything compared bit for bit, several rounds back to back."""
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    B = 48
+    fast = PostProcessor(device=0, max_batch=B)
+    slow = PostProcessor(device=0, max_batch=B, max_bodies=1024, max_humans=256, max_candidates_per_limb=4096)
+    for rnd in range(5):
+        batch = synth.make_batch(7000 + 100 * rnd, B, people=(0, 12) if rnd % 2 else (1, 10))
+        for rep in range(2):
+            a = fast(batch, 512)
+            b = slow(batch, 512)
+            assert np.array_equal(a.n_peaks, b.n_peaks) and np.array_equal(a.part_count, b.part_count)
+            assert np.array_equal(a.n_humans, b.n_humans), (rnd, rep)
+            for i in range(B):
+                assert np.array_equal(a.peaks[i], b.peaks[i]), (rnd, rep, i)
+                assert np.array_equal(a.humans[i], b.humans[i]), (rnd, rep, i)
+            assert not (a.status & 0x4F).any()
+    assert fast.handle.launches == 3 * 10 and slow.handle.launches == 3 * 10
