@@ -110,6 +110,7 @@ struct ibp_handle {
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
     int defer_bands = 0;           // > 0: the last peak launch left its band lists unpacked (this many bands per plane)
     int defer_batch = 0;
+    int *d_yext = nullptr;         // [max_batch][18][2] y extent of each part's peaks, kept "empty" between launches
     int4 *d_item_meta = nullptr;   // [max_batch*30] limb items in heaviest-image-first order (index_bands_kernel)
     unsigned *d_lb_work = nullptr; // work counter of the streaming limb kernel, never reset ...
     unsigned lb_work_base = 0;     // ... its value before the next launch
@@ -209,6 +210,7 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_pk_work);
     free_dev(h->d_partbase);
     free_dev(h->d_item_meta);
+    free_dev(h->d_yext);
     free_dev(h->d_lb_work);
     free_dev(h->d_score64);
     free_dev(h->d_py_conn);
@@ -388,6 +390,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMalloc(&h->d_order, B * sizeof(int)));
         CU(cudaMalloc(&h->d_partbase, B * (kParts + 1) * sizeof(int)));
         CU(cudaMalloc(&h->d_item_meta, B * (kLimbs + 1) * sizeof(int4)));
+        CU(cudaMalloc(&h->d_yext, B * kParts * 2 * sizeof(int)));
+        CU(cudaMemset(h->d_yext, 0x80, B * kParts * 2 * sizeof(int)));  // 0x80808080: below every -y
         CU(cudaMalloc(&h->d_lb_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_lb_work, 0, sizeof(unsigned)));
         CU(cudaFuncSetAttribute(limbs_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -614,6 +618,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.order = h->d_order;
     a.batch = batch;
     a.defer_pack = 0;
+    a.yext = nullptr;
     a.n_raw = nullptr;
     a.work_counter = nullptr;
     a.work_base = 0;
@@ -674,6 +679,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
         static const bool no_defer = getenv("IBP_PEAKS_NO_DEFER") != nullptr;
         a.defer_pack = (may_defer && a.nbands <= kMaxDeferBands && !no_defer) ? 1 : 0;
         a.n_raw = h->d_n_raw;
+        a.yext = a.defer_pack ? h->d_yext : nullptr;
         if (a.defer_pack) {
             h->defer_bands = a.nbands;
             h->defer_batch = batch;
@@ -698,6 +704,9 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
             ia.n_peaks = h->d_n_peaks;
             ia.order = h->d_order;
             ia.item_meta = h->d_item_meta;
+            ia.yext = h->d_yext;
+            ia.h = fh;
+            ia.up = h->P.upsample;
             ia.status = h->d_status;
             index_bands_kernel<<<batch, 32, 0, st>>>(ia);
             h->launches++;

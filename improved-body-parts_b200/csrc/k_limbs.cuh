@@ -66,7 +66,7 @@ struct LimbArgs {
     const int *band_count;      // (batch, 18, nbands)
     int nbands;
     // streaming kernel only: items (image rank, limb) in heaviest-first order with their image and list sizes
-    const int4 *item_meta;      // (batch*30) {image, nA, nB, -}
+    const int4 *item_meta;      // (batch*31) work queue, see IndexArgs::item_meta
     unsigned *work_counter;     // items beyond the first gridDim.x are claimed here; never reset ...
     unsigned work_base;         // ... its value at launch (a launch adds exactly batch*30)
     int plane_bytes;            // streaming kernel: bytes reserved for the plane at the start of shared memory
@@ -643,7 +643,6 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     const int tid = threadIdx.x;
     const int items = a.batch * (kLimbs + 1);
     const size_t hw = (size_t)a.h * a.w;
-    const uint32_t plane_copy_bytes = (uint32_t)(hw * 4);
 
     // ---- carve shared memory: plane | peak lists | ring = candidate / geometry / sample scratch ----
     float *plane_s = reinterpret_cast<float *>(smem_raw);
@@ -678,14 +677,13 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     const int ring_bytes = (int)((off - ring_off) & ~(size_t)15);
     float *ring = reinterpret_cast<float *>(smem_raw + ring_off);
     const int slot_rows = min(a.h, (ring_bytes / kLimbRing) / (a.w * 4));
-    const int nchunks = (a.h + slot_rows - 1) / slot_rows;
     __shared__ uint64_t bars[1 + kLimbRing];
     __shared__ int wcnt[kLimbThreads / 32];
     __shared__ int s_last;
     __shared__ float tab4[4][4];
     __shared__ int s_partbase[kParts + 1];
     __shared__ int s_bc[kParts * kMaxDeferBands];
-    __shared__ int4 s_next;  // {image, nA, nB, limb (30: group the image)}; image < 0: no more work
+    __shared__ int4 s_next;  // {image, nA | nB << 16, limb (30: group the image), r0 | r1 << 16}; image < 0: no more work
     m.wcnt = wcnt;
 
     auto claim_to_item = [&](unsigned t) {
@@ -698,17 +696,24 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     auto twin_of = [&](int img, int limb) {  // flipped image: channel flip_paf_ord[limb] of its block (config/config.py:150-152)
         return reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride + (size_t)(a.twin_base + c_flip_src[limb]) * hw;
     };
-    auto twin_chunk = [&](const float *twin, int c) {  // one thread: chunk c of the twin plane into its ring slot
-        const int s = c % kLimbRing, first = c * slot_rows;
-        const int rows = min(slot_rows, a.h - first);
+    // Only the feature rows [r0, r1) that a sample of the item can touch are staged (at their own place in the buffer).
+    auto has_pairs = [](const int4 &it) { return (it.y & 0xffff) > 0 && (it.y >> 16) > 0 && it.z < kLimbs; };
+    auto twin_chunk = [&](const float *twin, int r0, int r1, int c) {  // one thread: chunk c of the twin rows into its ring slot
+        const int s = c % kLimbRing, first = r0 + c * slot_rows;
+        const int rows = min(slot_rows, r1 - first);
         bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * a.w * 4u, &bars[1 + s]);
+    };
+    auto upright_rows = [&](const int4 &it) {  // one thread: the upright rows of a limb item straight to their place
+        if (!has_pairs(it)) return;
+        const int r0 = it.w & 0xffff, r1 = it.w >> 16;
+        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, it.z) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * 4u, &bars[0]);
     };
 
     if (tid == 0) {
         for (int i = 0; i <= kLimbRing; i++) mbar_init(&bars[i], 1);
         fence_barrier_init();
         const int4 first = a.item_meta[blockIdx.x];  // the grid never exceeds the item count
-        if (first.y > 0 && first.z > 0) bulk_rows(plane_s, upright_of(first.x, first.w), plane_copy_bytes, &bars[0]);
+        upright_rows(first);
         s_next = first;
     }
     cubic_tab4_init(tab4);
@@ -719,7 +724,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     for (;;) {
         const int4 cur = s_next;
         if (cur.x < 0) break;
-        const int img = cur.x, nA = cur.y, nB = cur.z, limb = cur.w;
+        const int img = cur.x, nA = cur.y & 0xffff, nB = cur.y >> 16, limb = cur.z;
+        const int r0 = cur.w & 0xffff, r1 = cur.w >> 16;
         unsigned claimed = 0;
         int4 nmeta = make_int4(-1, 0, 0, 0);
         // thread 0: who is next (one load, issued early), and — once the plane is dead — start its upright plane
@@ -731,9 +737,9 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         };
         auto prefetch_next = [&]() {
             if (tid == 0) {
-                if (nmeta.x >= 0 && nmeta.y > 0 && nmeta.z > 0) {
+                if (nmeta.x >= 0 && has_pairs(nmeta)) {
                     fence_proxy_async();  // the samples read through the generic proxy come first
-                    bulk_rows(plane_s, upright_of(nmeta.x, nmeta.w), plane_copy_bytes, &bars[0]);
+                    upright_rows(nmeta);
                 }
                 s_next = nmeta;
             }
@@ -766,13 +772,14 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         }
         const int pa = c_limb_a[limb], pb = c_limb_b[limb];
         const bool pairs = nA > 0 && nB > 0;
+        const int nchunks = (r1 - r0 + slot_rows - 1) / slot_rows;
         const float *twin = twin_of(img, limb);
         // thread 0: next claim out now, answer used later; the ring is free again: first twin chunks out
         if (tid == 0) {
             claimed = atomicAdd(a.work_counter, 1u);
             if (pairs) {
                 fence_proxy_async();  // the previous round's generic-proxy use of the ring region comes first
-                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(twin, c);
+                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(twin, r0, r1, c);
             }
         }
         limb_stamp(a, img, limb, 0);
@@ -845,8 +852,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
                     const int s = c % kLimbRing;
                     mbar_wait(&bars[1 + s], (ring_par >> s) & 1u);
                     ring_par ^= 1u << s;
-                    const int first = c * slot_rows;
-                    const int rows = min(slot_rows, a.h - first);
+                    const int first = r0 + c * slot_rows;
+                    const int rows = min(slot_rows, r1 - first);
                     const float4 *r4 = reinterpret_cast<const float4 *>(ring + (size_t)s * slot_rows * a.w);
                     float4 *o4 = d4 + (size_t)first * wv;
                     for (int i = tid; i < rows * wv; i += kLimbThreads) {
@@ -864,7 +871,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
                         __syncthreads();  // everybody has read slot s
                         if (tid == 0) {
                             fence_proxy_async();
-                            twin_chunk(twin, c + kLimbRing);
+                            twin_chunk(twin, r0, r1, c + kLimbRing);
                         }
                     }
                 }

@@ -23,6 +23,8 @@
 // running ids across parts (parse_skeletons.py:172-173) and writes the part-major "line" array
 // (pafprocess.cpp:43-48) that grouping and the results index by peak id.
 #pragma once
+#include <climits>
+
 #include "ibp_device.cuh"
 
 namespace ibp {
@@ -57,6 +59,8 @@ struct PeakArgs {
     unsigned long long *timeline;  // experiments only: (batch, 18, nbands, 6) %globaltimer stamps, or null
     int *order;           // (batch) images sorted by descending number of peaks, written by the last CTA of the launch
     int batch;
+    int *yext;               // (batch, 18, 2) or null, defer_pack only: running {max(-y), max(y)} of each part's peaks;
+                             // "nothing yet" is any value below -2^30 (the index kernel resets the entries it read)
     int defer_pack;          // streaming kernel: 1 = leave the band lists as they are (no tickets, no pack, no order): the
                              // limb kernel gathers them itself; only n_raw[img] += peaks of the band
     int *n_raw;              // (batch) zero on entry when defer_pack
@@ -212,7 +216,7 @@ __device__ __forceinline__ void peaks_scan(const Acc &B, int r0, int r1, int h, 
 // ---- refine, one warp per peak: sorted[0..n) holds the pixel indices in row-major order ----
 template <int FLAVOUR, class Acc>
 __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, int n, const int *sorted, DevPeak *out, size_t slot_base,
-                                             float *hbuf, const float (*tab4)[4], int warp, int nwarps) {
+                                             float *hbuf, const float (*tab4)[4], int warp, int nwarps, int *yext = nullptr) {
     const int lane = threadIdx.x & 31;
     const int w = a.w, h = a.h;
     for (int k = warp; k < n; k += nwarps) {
@@ -263,6 +267,10 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = best;
                 p.id = k;
                 out[k] = p;
+                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                    atomicMax(yext, -p.y);
+                    atomicMax(yext + 1, p.y);
+                }
             }
             __syncwarp();
         } else if (FLAVOUR == IBP_PEAKS_CROSS_REFINE) {
@@ -344,6 +352,10 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = best;
                 p.id = k;
                 out[k] = p;
+                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                    atomicMax(yext, -p.y);
+                    atomicMax(yext + 1, p.y);
+                }
             }
             __syncwarp();
         } else {
@@ -397,6 +409,10 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = sc;
                 p.id = k;
                 out[k] = p;
+                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                    atomicMax(yext, -p.y);
+                    atomicMax(yext + 1, p.y);
+                }
                 if (a.band_subpix) {
                     double *sp = a.band_subpix + (slot_base + k) * 2;
                     sp[0] = fx;
@@ -800,7 +816,8 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
         peaks_order(sc.found, sc.sorted, n, wtid, kPeakWorkers);
         workers_sync();
         const size_t slot_base = (size_t)item * a.cap;  // == ((img*18 + part)*nbands + band) * cap
-        peaks_refine<FLAVOUR>(B, a, n, sc.sorted, a.band_peaks + slot_base, slot_base, sc.hbuf_all + wwarp * sc.hbuf_per_warp, tab4, wwarp, nworkers);
+        peaks_refine<FLAVOUR>(B, a, n, sc.sorted, a.band_peaks + slot_base, slot_base, sc.hbuf_all + wwarp * sc.hbuf_per_warp, tab4, wwarp, nworkers,
+                              (a.defer_pack && a.yext) ? a.yext + ((size_t)it.img * kParts + it.part) * 2 : nullptr);
         if (wtid == 0) {
             a.band_count[item] = n;
             if (n_raw > a.cap) atomicOr(a.status + it.img, IBP_ST_PEAK_OVERFLOW);
@@ -828,7 +845,10 @@ struct IndexArgs {
     int *n_peaks;           // (batch)
     int *order;             // (batch)
     int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel.  Rank r (0 = most peaks) owns
-                            // [r*31, r*31+31): {image, nA, nB, limb} for its 30 limbs, then {image, 0, 0, 30} = "group it"
+                            // [r*31, r*31+31): {image, nA | nB << 16, limb, r0 | r1 << 16} for its 30 limbs — [r0, r1) = the
+                            // feature rows any sample of the limb can touch — then {image, 0, 30, 0} = "group it"
+    int *yext;              // (batch, 18, 2) from the peak kernel, reset here
+    int h, up;              // feature rows, up-sampling factor
     uint32_t *status;       // (batch)
 };
 
@@ -878,13 +898,34 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
         a.partbase[img * (kParts + 1) + kParts] = total;
         a.n_peaks[img] = min(total, a.line_stride);
     }
-    if (a.item_meta && lane < kLimbs) {
-        const int pa = c_limb_a[lane], pb = c_limb_b[lane];
-        const int na = min(offs[(pa + 1) * a.nbands] - offs[pa * a.nbands], a.cap);
-        const int nb = min(offs[(pb + 1) * a.nbands] - offs[pb * a.nbands], a.cap);
-        a.item_meta[rank * (kLimbs + 1) + lane] = make_int4(img, na, nb, lane);
+    if (a.item_meta) {
+        // y extent of each part's peaks (up-sampled pixels)
+        __shared__ int ylo[kParts], yhi[kParts];
+        if (lane < kParts) {
+            int *e = a.yext + ((size_t)img * kParts + lane) * 2;
+            const int neg_lo = e[0], hi = e[1];
+            ylo[lane] = -neg_lo;
+            yhi[lane] = hi;
+            e[0] = e[1] = INT_MIN;  // ready for the next launch
+        }
+        __syncwarp();
+        if (lane < kLimbs) {
+            const int pa = c_limb_a[lane], pb = c_limb_b[lane];
+            const int na = min(offs[(pa + 1) * a.nbands] - offs[pa * a.nbands], a.cap);
+            const int nb = min(offs[(pb + 1) * a.nbands] - offs[pb * a.nbands], a.cap);
+            int r0 = 0, r1 = a.h;
+            if (a.up == 4 && na > 0 && nb > 0) {
+                // samples lie between the two end points (pafprocess.cpp:319-320); the x4 bicubic of an up-sampled row Y
+                // reads feature rows ((Y-2)>>2)-1 .. ((Y-2)>>2)+2 (ibp_device.cuh cubic_sample4); one more row either side
+                const int lo = min(ylo[pa], ylo[pb]), hi = max(yhi[pa], yhi[pb]);
+                r0 = max(0, ((lo - 2) >> 2) - 2);
+                r1 = min(a.h, ((hi - 2) >> 2) + 4);
+                if (r1 <= r0) { r0 = 0; r1 = a.h; }
+            }
+            a.item_meta[rank * (kLimbs + 1) + lane] = make_int4(img, na | (nb << 16), lane, r0 | (r1 << 16));
+        }
+        if (lane == kLimbs) a.item_meta[rank * (kLimbs + 1) + kLimbs] = make_int4(img, 0, kLimbs, 0);
     }
-    if (a.item_meta && lane == kLimbs) a.item_meta[rank * (kLimbs + 1) + kLimbs] = make_int4(img, 0, 0, kLimbs);
     // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
     if (__any_sync(0xffffffffu, over) && lane == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
 }
