@@ -44,7 +44,8 @@ struct GroupArgs {
 // the same part of a different row, hit different banks.
 constexpr int kSlotStride = kParts + 1;
 constexpr size_t kBodyBytes = kSlotStride * 8 + 16;  // shared bytes per row of the skeleton table
-constexpr int kDeadId = -3;                      // id in every slot of an erased row: equals no peak id, not -1
+constexpr int kDeadId = -3;
+constexpr int kGroupParallelMin = 4;  // connections of one limb type from which the one-per-lane path pays                      // id in every slot of an erased row: equals no peak id, not -1
 
 // pafprocess.cpp:154 / :186  min_len = (int)(length * LIMB_LENGTH_RATE), later compared with a float
 __device__ __forceinline__ float length_gate(float len, int len_rate) {
@@ -52,7 +53,8 @@ __device__ __forceinline__ float length_gate(float len, int len_rate) {
 }
 
 // All threads of the CTA call this; `smem` / `smem_bytes` is the CTA's dynamic shared memory (free for re-use).
-__device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigned char *smem, size_t smem_bytes) {
+__device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigned char *smem, size_t smem_bytes,
+                                            unsigned long long *tl = nullptr) {  // tl: experiments, two %globaltimer stamps
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int S = a.max_bodies;
     float4 *row = reinterpret_cast<float4 *>(smem);                       // [S] {total, gate, reach, count bits}
@@ -86,13 +88,58 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
     }
     __syncthreads();
     if (warp != 0) return;
+    if (tl && lane == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl[0]));
+
+    // :182-256 two rows matched: merge row g into row f when the rule says so.  The whole warp, lane k = part k.
+    auto merge_rows = [&](int f, int g, float link_score, float link_len, float link_gate) {
+        int2 vm = make_int2(-1, 0), vo = make_int2(-1, 0);
+        if (lane < kParts) {
+            vm = slot[f * kSlotStride + lane];
+            vo = slot[g * kSlotStride + lane];
+        }
+        const float4 rf = row[f], rg = row[g];
+        const int idm = vm.x, ido = vo.x;
+        const float scm = __int_as_float(vm.y), sco = __int_as_float(vo.y);
+        const bool hm = idm > 0, ho = ido > 0;  // :198-199 peak id 0 counts as unassigned
+        const bool overlap = __ballot_sync(0xffffffffu, hm && ho) != 0;
+        if (!overlap) {
+            // :201-205 running minimum with the 0.0f sentinel, evaluated in part order on every lane
+            float low_m = 0.0f, low_o = 0.0f;
+            for (int k = 0; k < kParts; k++) {
+                const int im = __shfl_sync(0xffffffffu, idm, k), io = __shfl_sync(0xffffffffu, ido, k);
+                const float sm = __shfl_sync(0xffffffffu, scm, k), so = __shfl_sync(0xffffffffu, sco, k);
+                if (im > 0) low_m = (low_m == 0.0f) ? sm : (sm < low_m ? sm : low_m);
+                if (io > 0) low_o = (low_o == 0.0f) ? so : (so < low_o ? so : low_o);
+            }
+            const float floor_score = __fmul_rn((low_o < low_m ? low_o : low_m), a.merge_tol);  // :219
+            if (link_score >= floor_score || link_len < rf.y) {  // :220, rf.y = (int)(length*16) of row f (:186)
+                if (lane < kParts) {
+                    // :222-225 ids and scores are ADDED (+1 undoes the -1 of an empty slot)
+                    slot[f * kSlotStride + lane] = make_int2(idm + (ido + 1), __float_as_int(__fadd_rn(scm, __fadd_rn(sco, 1.0f))));
+                    slot[g * kSlotStride + lane] = make_int2(kDeadId, 0);  // :229 erase
+                }
+                if (lane == 0) {  // :226-228
+                    float4 nr;
+                    nr.x = __fadd_rn(rf.x, __fadd_rn(rg.x, link_score));
+                    nr.y = fmaxf(rf.y, link_gate);
+                    nr.z = fmaxf(rf.z, link_len);
+                    nr.w = __int_as_float(__float_as_int(rf.w) + __float_as_int(rg.w));
+                    row[f] = nr;
+                    row[g] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+                }
+            }
+        }
+        // overlap: DELETE_SHARED_JOINTS is const false (pafprocess.h:16) => the branch at :231-256 does nothing
+        __syncwarp();
+    };
 
     int nb = 0;
     bool overflow = false;
+    const int my_loff = loff[lane];
     for (int limb = 0; limb < kLimbs; limb++) {
         const int pa = c_limb_a[limb], pb = c_limb_b[limb];
-        const int base_slot = loff[limb];
-        const int nl = loff[limb + 1] - base_slot;
+        const int base_slot = __shfl_sync(0xffffffffu, my_loff, limb);  // lane l holds loff[l]: no shared-memory round trip
+        const int nl = __shfl_sync(0xffffffffu, my_loff, limb + 1) - base_slot;
         const DevLink *G = a.links + ((size_t)img * kLimbs + limb) * a.cap;
         auto fetch = [&](int li) -> DevLink {
             union {
@@ -110,9 +157,79 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
             }
             return u.l;
         };
+        // ---- up to 32 rows: lane r keeps row r's two slots of this limb and its totals in registers ----
+        // The dependent chain of the common cases (extend a row, open a row) then never goes through shared memory,
+        // whose latency under the other CTA's staging traffic is what a connection otherwise costs.  Shared memory
+        // is brought up to date at the end of the limb (and around a merge, which touches all 18 slots of two rows).
+        bool limb_done = false;
+        if (nl > 0 && nb + nl <= 32 && base_slot + nl <= slots) {
+            limb_done = true;
+            int my_a = slot[lane * kSlotStride + pa].x;  // rows >= nb hold ids that match nothing
+            int2 my_b = slot[lane * kSlotStride + pb];
+            float4 my_row = row[lane];
+            const float4 *lp = reinterpret_cast<const float4 *>(slinks + base_slot);
+            union LinkBits {
+                float4 q[2];
+                DevLink l;
+            };
+            LinkBits nx;
+            nx.q[0] = lp[0];
+            nx.q[1] = lp[1];
+            for (int li = 0; li < nl; li++) {
+                const DevLink l = nx.l;
+                if (li + 1 < nl) {
+                    nx.q[0] = lp[2 * (li + 1)];
+                    nx.q[1] = lp[2 * (li + 1) + 1];
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, my_a == l.id_a || my_b.x == l.id_b);  // :143-150
+                if (bal == 0) {  // :257-273 a new row, owned by lane nb
+                    if (lane < kParts) {
+                        const bool end = (lane == pa || lane == pb);
+                        slot[nb * kSlotStride + lane] = make_int2((lane == pa) ? l.id_a : ((lane == pb) ? l.id_b : -1),
+                                                                  __float_as_int(end ? l.limb : -1.0f));
+                    }
+                    if (lane == nb) {
+                        my_a = l.id_a;
+                        my_b = make_int2(l.id_b, __float_as_int(l.limb));
+                        my_row = make_float4(__fadd_rn(__fadd_rn(l.score_a, l.score_b), l.limb), l.gate, l.len, __int_as_float(2));
+                    }
+                    nb++;
+                } else if ((bal & (bal - 1)) == 0) {  // :152-180 exactly one row, on the lane that owns it
+                    if (lane == __ffs(bal) - 1) {
+                        const float gate = my_row.y;  // :154
+                        const int cur_id = my_b.x;
+                        const float cur_sc = __int_as_float(my_b.y);
+                        const float add = __fadd_rn(l.score_b, l.limb);
+                        const bool grow = (cur_id == -1) & (gate > l.len);
+                        const bool swap = !grow & (cur_sc <= l.limb) & ((cur_id == l.id_b) | ((cur_id != l.id_b) & (gate > l.len)));
+                        if (grow | swap) {
+                            my_b = make_int2(l.id_b, __float_as_int(l.limb));
+                            // swap (:168-169 / :177-178) subtracts the values just written, then adds them back
+                            my_row.x = grow ? __fadd_rn(my_row.x, add) : __fadd_rn(__fsub_rn(my_row.x, add), add);
+                            my_row.y = fmaxf(gate, l.gate);
+                            my_row.z = fmaxf(my_row.z, l.len);
+                            my_row.w = __int_as_float(__float_as_int(my_row.w) + (grow ? 1 : 0));
+                        }
+                    }
+                } else if (__popc(bal) == 2) {  // :182-256 through shared memory, then back into the registers
+                    slot[lane * kSlotStride + pb] = my_b;
+                    row[lane] = my_row;
+                    __syncwarp();
+                    const int f = __ffs(bal) - 1;
+                    merge_rows(f, __ffs(bal & (bal - 1)) - 1, l.limb, l.len, l.gate);
+                    my_a = slot[lane * kSlotStride + pa].x;
+                    my_b = slot[lane * kSlotStride + pb];
+                    my_row = row[lane];
+                }
+                // three or more rows: the connection is silently dropped
+            }
+            slot[lane * kSlotStride + pb] = my_b;
+            row[lane] = my_row;
+            __syncwarp();
+        }
         DevLink nxt;
-        if (nl > 0) nxt = fetch(0);
-        for (int li = 0; li < nl; li++) {
+        if (nl > 0 && !limb_done) nxt = fetch(0);
+        for (int li = 0; li < nl && !limb_done; li++) {
             const DevLink l = nxt;
             if (li + 1 < nl) nxt = fetch(li + 1);  // off the dependent chain
             // :143-150 scan: first two matching rows, total number of matches
@@ -177,46 +294,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
                 }
                 __syncwarp();
             } else if (hits == 2) {  // :182-256
-                const int f = first, g = second;
-                int2 vm = make_int2(-1, 0), vo = make_int2(-1, 0);
-                if (lane < kParts) {
-                    vm = slot[f * kSlotStride + lane];
-                    vo = slot[g * kSlotStride + lane];
-                }
-                const float4 rf = row[f], rg = row[g];
-                const int idm = vm.x, ido = vo.x;
-                const float scm = __int_as_float(vm.y), sco = __int_as_float(vo.y);
-                const bool hm = idm > 0, ho = ido > 0;  // :198-199 peak id 0 counts as unassigned
-                const bool overlap = __ballot_sync(0xffffffffu, hm && ho) != 0;
-                if (!overlap) {
-                    // :201-205 running minimum with the 0.0f sentinel, evaluated in part order on every lane
-                    float low_m = 0.0f, low_o = 0.0f;
-                    for (int k = 0; k < kParts; k++) {
-                        const int im = __shfl_sync(0xffffffffu, idm, k), io = __shfl_sync(0xffffffffu, ido, k);
-                        const float sm = __shfl_sync(0xffffffffu, scm, k), so = __shfl_sync(0xffffffffu, sco, k);
-                        if (im > 0) low_m = (low_m == 0.0f) ? sm : (sm < low_m ? sm : low_m);
-                        if (io > 0) low_o = (low_o == 0.0f) ? so : (so < low_o ? so : low_o);
-                    }
-                    const float floor_score = __fmul_rn((low_o < low_m ? low_o : low_m), a.merge_tol);  // :219
-                    if (l.limb >= floor_score || l.len < rf.y) {  // :220, rf.y = (int)(length*16) of row f (:186)
-                        if (lane < kParts) {
-                            // :222-225 ids and scores are ADDED (+1 undoes the -1 of an empty slot)
-                            slot[f * kSlotStride + lane] = make_int2(idm + (ido + 1), __float_as_int(__fadd_rn(scm, __fadd_rn(sco, 1.0f))));
-                            slot[g * kSlotStride + lane] = make_int2(kDeadId, 0);  // :229 erase
-                        }
-                        if (lane == 0) {  // :226-228
-                            float4 nr;
-                            nr.x = __fadd_rn(rf.x, __fadd_rn(rg.x, l.limb));
-                            nr.y = fmaxf(rf.y, l.gate);
-                            nr.z = fmaxf(rf.z, l.len);
-                            nr.w = __int_as_float(__float_as_int(rf.w) + __float_as_int(rg.w));
-                            row[f] = nr;
-                            row[g] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-                        }
-                    }
-                }
-                // overlap: DELETE_SHARED_JOINTS is const false (pafprocess.h:16) => the branch at :231-256 does nothing
-                __syncwarp();
+                merge_rows(first, second, l.limb, l.len, l.gate);
             } else if (hits == 0) {  // :257-273
                 if (nb < S) {
                     if (lane < kParts) {
@@ -236,6 +314,7 @@ __device__ __forceinline__ void group_image(const GroupArgs &a, int img, unsigne
         }
     }
 
+    if (tl && lane == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl[1]));
     // :277-282 filter (order preserved; erased rows carry count -1) + results of the getters (:287-297)
     int n_out = 0;
     ibp_human *out = a.humans + (size_t)img * a.max_humans;

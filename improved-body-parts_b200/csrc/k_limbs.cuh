@@ -760,7 +760,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             __syncthreads();
             if (s_last && !(a.debug & 1)) {
                 limb_stamp(a, img, 30, 0);
-                group_image(a.group, img, smem_raw + a.plane_bytes, (size_t)a.smem_bytes - (size_t)a.plane_bytes);
+                group_image(a.group, img, smem_raw + a.plane_bytes, (size_t)a.smem_bytes - (size_t)a.plane_bytes,
+                            a.timeline ? a.timeline + ((size_t)img * 31 + 30) * 4 + 2 : nullptr);
                 limb_stamp(a, img, 30, 1);
             }
             // claim only now: nothing must wait behind a grouping chain

@@ -21,3 +21,9 @@ b = order[0]
 print("heaviest image per limb: start, staged, scored, end")
 for l in range(0, 30, 3):
     print("  limb %d: " % l + " ".join("%.1f" % v for v in T[b, l]))
+
+links = None
+print("grouping: staging / chain / filter (us), by image weight")
+for b in list(order[:5]) + list(order[30:33]) + list(order[-3:]):
+    g = T[b, 30]
+    print("  img %2d peaks %3d humans %2d: stage %.2f chain %.2f filter %.2f" % (b, res.n_peaks[b], res.n_humans[b], g[2] - g[0], g[3] - g[2], g[1] - g[3]))
