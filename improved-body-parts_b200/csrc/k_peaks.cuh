@@ -836,6 +836,8 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
 // ranks its image among the batch by number of peaks (heaviest first, ties by index), which is the order the limb
 // kernel walks the images in.
 // ---------------------------------------------------------------------------------------------------------------
+constexpr int kGroupLag = 8;  // images between the limbs of an image and its grouping in the streaming limb kernel's queue
+
 struct IndexArgs {
     const int *band_count;  // (batch, 18, nbands)
     const int *n_raw;       // (batch)
@@ -844,9 +846,10 @@ struct IndexArgs {
     int *partbase;          // (batch, 19)
     int *n_peaks;           // (batch)
     int *order;             // (batch)
-    int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel.  Rank r (0 = most peaks) owns
-                            // [r*31, r*31+31): {image, nA | nB << 16, limb, r0 | r1 << 16} for its 30 limbs — [r0, r1) = the
-                            // feature rows any sample of the limb can touch — then {image, 0, 30, 0} = "group it"
+    int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel, images by rank (0 = most peaks):
+                            // {image, nA | nB << 16, limb, r0 | r1 << 16} for the 30 limbs of an image — [r0, r1) = the
+                            // feature rows any sample of the limb can touch — and {image, 0, 30, 0} = "group it",
+                            // queued kGroupLag images after its limbs
     int *yext;              // (batch, 18, 2) from the peak kernel, reset here
     int h, up;              // feature rows, up-sampling factor
     uint32_t *status;       // (batch)
@@ -922,9 +925,15 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
                 r1 = min(a.h, ((hi - 2) >> 2) + 4);
                 if (r1 <= r0) { r0 = 0; r1 = a.h; }
             }
-            a.item_meta[rank * (kLimbs + 1) + lane] = make_int4(img, na | (nb << 16), lane, r0 | (r1 << 16));
+            // queue position: the 30 limbs of rank r follow those of rank r-1 and the "group it" items of ranks < r - lag
+            a.item_meta[rank * kLimbs + lane + max(0, rank - kGroupLag)] = make_int4(img, na | (nb << 16), lane, r0 | (r1 << 16));
         }
-        if (lane == kLimbs) a.item_meta[rank * (kLimbs + 1) + kLimbs] = make_int4(img, 0, kLimbs, 0);
+        // "group image of rank q" is queued kGroupLag images later (by then its limbs are finished and whoever claims it
+        // does not have to wait), the last ones at the very end
+        if (lane == kLimbs) {
+            const int pos = (rank + kGroupLag <= a.batch - 1) ? (rank + kGroupLag + 1) * kLimbs + rank : a.batch * kLimbs + rank;
+            a.item_meta[pos] = make_int4(img, 0, kLimbs, 0);
+        }
     }
     // ids would no longer be a running counter: flag it; ibp_fetch turns the flag into IBP_ERR_CAPACITY
     if (__any_sync(0xffffffffu, over) && lane == 0) atomicOr(a.status + img, IBP_ST_PEAK_OVERFLOW);
