@@ -254,6 +254,24 @@ int validate_limits(const ibp_limits &l) {
     return IBP_OK;
 }
 
+// Launch `kern` as a programmatic dependent of the previous kernel in the stream: its CTAs may be set up while that
+// kernel drains; the kernel itself waits (griddepcontrol.wait) before it touches anything the predecessor wrote.
+template <typename Args>
+cudaError_t launch_dependent(void (*kern)(Args), dim3 grid, dim3 block, size_t smem, cudaStream_t st, const Args &a) {
+    static const bool off = getenv("IBP_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = off ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kern, a);
+}
+
 struct StageTimer {
     ibp_handle *h;
     int stage;
@@ -708,7 +726,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
             ia.h = fh;
             ia.up = h->P.upsample;
             ia.status = h->d_status;
-            index_bands_kernel<<<batch, 32, 0, st>>>(ia);
+            CU(launch_dependent(index_bands_kernel, dim3(batch), dim3(32), 0, st, ia));
             h->launches++;
             h->order_batch = batch;
         }
@@ -916,7 +934,7 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         const int grid = std::min(items, h->lb_occ * h->sm_count);
         h->lb_work_base += (unsigned)items;
         StageTimer t(h, IBP_STAGE_LIMBS, st);
-        limbs_stream_kernel<<<grid, kLimbStreamThreads, smem, st>>>(a);
+        CU(launch_dependent(limbs_stream_kernel, dim3(grid), dim3(kLimbStreamThreads), smem, st, a));
         h->launches++;
         CU(cudaGetLastError());
         return IBP_OK;

@@ -709,6 +709,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, it.z) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * 4u, &bars[0]);
     };
 
+    pdl_wait();  // launched as a programmatic dependent: the work queue and the band lists come from the kernels before
     if (tid == 0) {
         for (int i = 0; i <= kLimbRing; i++) mbar_init(&bars[i], 1);
         fence_barrier_init();

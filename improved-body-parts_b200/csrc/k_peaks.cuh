@@ -743,6 +743,7 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
         }
     };
 
+    pdl_launch_dependents();  // the index kernel may be set up while this grid runs (it waits for our results itself)
     int cur = (int)blockIdx.x, nxt = -1;  // control warp's view (the grid never exceeds the item count)
     if (tid == 0) {
         mbar_init(&full[0], 1);
@@ -857,6 +858,8 @@ struct IndexArgs {
 
 __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
     const int img = blockIdx.x, lane = threadIdx.x;
+    pdl_launch_dependents();  // the limb kernel's CTAs may take their places
+    pdl_wait();               // the peak kernel's band lists
     const int items = kParts * a.nbands;
     const int *bc = a.band_count + (size_t)img * items;
     // every load first: the band counts of this image, the raw totals of the batch
