@@ -705,9 +705,10 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
         }
         a.work_counter = h->d_pk_work;
         a.work_base = h->pk_work_base;
-        h->pk_work_base += (unsigned)items;  // (items - grid) claims that succeed + one that fails per CTA
         StageTimer t(h, IBP_STAGE_PEAKS, st);
         kern<<<grid, kPeakThreads, smem_stream, st>>>(a);
+        CU(cudaGetLastError());
+        h->pk_work_base += (unsigned)items;  // once it runs: (items - grid) claims that succeed + one that fails per CTA
         h->launches++;
         if (a.defer_pack) {
             IndexArgs ia;
@@ -932,9 +933,9 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         }
         if (h->lb_occ < 1) return fail(IBP_ERR_SHAPE, "assign: streaming limb kernel does not fit");
         const int grid = std::min(items, h->lb_occ * h->sm_count);
-        h->lb_work_base += (unsigned)items;
         StageTimer t(h, IBP_STAGE_LIMBS, st);
         CU(launch_dependent(limbs_stream_kernel, dim3(grid), dim3(kLimbStreamThreads), smem, st, a));
+        h->lb_work_base += (unsigned)items;  // once it runs, the kernel advances its counter by exactly this much
         h->launches++;
         CU(cudaGetLastError());
         return IBP_OK;

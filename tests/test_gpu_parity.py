@@ -160,3 +160,28 @@ def test_streaming_equals_one_shot_kernels_stress():
                 assert np.array_equal(a.humans[i], b.humans[i]), (rnd, rep, i)
             assert not (a.status & 0x4F).any()
     assert fast.handle.launches == 3 * 10 and slow.handle.launches == 3 * 10
+
+
+@pytest.mark.parametrize("h,w", [(96, 160), (160, 96), (64, 72), (40, 132), (184, 64), (128, 130)])
+def test_streaming_kernels_other_map_sizes(oracle, h, w):
+    """Default limits (streaming route where the rows are 16-byte multiples, the one-shot kernels for w = 130) on maps
+    that are not 128x128: several bands per plane, a last band that is short, planes smaller than the ring."""
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    from oracle import np_oracle as O
+    B = 3
+    pp = PostProcessor(device=0, max_batch=B)
+    outs = [synth.make_network_output(600 + h + b, 2 + 2 * b, height=4 * h, width=4 * w)[0] for b in range(B)]
+    res = pp(np.stack(outs), 4 * h)
+    for b, out in enumerate(outs):
+        heat, paf = O.fuse_flip(out)
+        jl = O.joint_list(O.heatmap_nms(heat, 4))
+        oracle.process_paf_feat(jl[None], np.ascontiguousarray(paf.transpose(2, 0, 1)), 4, 4 * h)
+        want = oracle.humans()
+        assert res.n_peaks[b] == jl.shape[0]
+        assert np.array_equal(res.peaks[b]["x"], jl[:, 0].astype(np.int32))
+        assert np.array_equal(res.peaks[b]["y"], jl[:, 1].astype(np.int32))
+        assert np.array_equal(res.peaks[b]["score"], jl[:, 2])
+        assert res.n_humans[b] == len(want)
+        for rec, (ids, score) in zip(res.humans[b], want):
+            assert np.array_equal(rec["peak_id"], ids) and rec["score"] == score
