@@ -75,12 +75,14 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     float *T1 = F + a.cap_f;                         // first resize, horizontal   [n_fy][n_rx]
     float *I = T1 + a.cap_t1;                        // first resize, vertical     [n_ry][n_rx] = up_s on the tile's taps
     float *T2 = I + a.cap_i;                         // second resize, horizontal  [n_ry][nX]
-    int4 *row_q = reinterpret_cast<int4 *>(T2 + a.cap_t2);   // [cap_rows] stage C row table (cap_t2 = cap_rows * tile width)
-    int *row_ph = reinterpret_cast<int *>(row_q + a.cap_t2 / kMsTileX);
+    int4 *row_q = reinterpret_cast<int4 *>(T2 + a.cap_t2);   // [<= cap_rows] stage C row-group table (cap_t2 = cap_rows * tile width)
     __shared__ int x_idx[kMsTileX][4], y_idx[kMsTileY][4];
     __shared__ float x_w[kMsTileX][4], y_w[kMsTileY][4];
-    __shared__ float tab4[4][4];
-    cubic_tab4_init(tab4);
+
+    // the four weight sets of the x4 resize (phases 1/8, 3/8, 5/8, 7/8), same evaluation as the table
+    float tw[4][4];
+#pragma unroll
+    for (int ph = 0; ph < 4; ph++) cubic_weights(__fadd_rn(__int2float_rn(ph) * 0.25f, 0.125f), tw[ph]);
 
     double acc[kMsPerThread];
 #pragma unroll
@@ -130,57 +132,50 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
                 F[i] = a.flip ? avg_like_numpy(v, __ldg(twin + (size_t)y * S.w + (S.w - 1 - x))) : v;
             }
         }
-        // per intermediate row: offsets of its four source rows in T1 and its phase (stage C)
-        for (int r = tid; r < n_ry; r += kMsThreads) {
-            const int ry = ry_lo + r;
-            const int sy = (ry - 2) >> 2;
-            row_q[r] = make_int4((clampi(sy - 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy, 0, S.h - 1) - fy_lo) * n_rx,
+        // The x4 resize has four phases: outputs 4k+2 .. 4k+5 read the SAME four source pixels k-1 .. k+2 (clamped) and
+        // differ only in the weights.  Stages B and C therefore work on groups of four outputs: four shared-memory
+        // loads feed four results (the weights of the four phases sit in registers), instead of four loads each.
+        const int kx_lo = (rx_lo - 2) >> 2, n_kx = ((rx_hi - 2) >> 2) - kx_lo + 1;
+        const int ky_lo = (ry_lo - 2) >> 2, n_ky = ((ry_hi - 2) >> 2) - ky_lo + 1;
+        // per group of intermediate rows: offsets of its four source rows in T1 (stage C)
+        for (int k = tid; k < n_ky; k += kMsThreads) {
+            const int sy = ky_lo + k;
+            row_q[k] = make_int4((clampi(sy - 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy, 0, S.h - 1) - fy_lo) * n_rx,
                                  (clampi(sy + 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy + 2, 0, S.h - 1) - fy_lo) * n_rx);
-            row_ph[r] = (ry - 2) & 3;
         }
         __syncthreads();
-        // Stages B-D give every thread ONE column and let it walk rows: the four taps and weights of the column live in
-        // registers, there is no index division in the loops, and a warp reads consecutive columns of a row.
-        // ---- B: first resize, horizontal pass: feature rows x intermediate columns ----
-        if (n_rx <= kMsThreads) {
-            const int groups = kMsThreads / n_rx, g = tid / n_rx, c = tid - g * n_rx;
-            if (g < groups) {
-                const int rx = rx_lo + c;
-                const int sx = (rx - 2) >> 2;
-                const float w0 = tab4[(rx - 2) & 3][0], w1 = tab4[(rx - 2) & 3][1], w2 = tab4[(rx - 2) & 3][2], w3 = tab4[(rx - 2) & 3][3];
-                const float wv[4] = {w0, w1, w2, w3};
-                const int i0 = clampi(sx - 1, 0, S.w - 1) - fx_lo, i1 = clampi(sx, 0, S.w - 1) - fx_lo;
-                const int i2 = clampi(sx + 1, 0, S.w - 1) - fx_lo, i3 = clampi(sx + 2, 0, S.w - 1) - fx_lo;
-                for (int r = g; r < n_fy; r += groups) {
-                    const float *row = F + r * n_fx;
-                    T1[r * n_rx + c] = hsum4(row[i0], row[i1], row[i2], row[i3], wv);
-                }
-            }
-        } else {
-            for (int i = tid; i < n_fy * n_rx; i += kMsThreads) {
-                const int r = i / n_rx, c = i - r * n_rx;
-                const int rx = rx_lo + c;
-                const int sx = (rx - 2) >> 2;
-                const float *row = F + r * n_fx - fx_lo;
-                T1[i] = hsum4(row[clampi(sx - 1, 0, S.w - 1)], row[clampi(sx, 0, S.w - 1)], row[clampi(sx + 1, 0, S.w - 1)],
-                              row[clampi(sx + 2, 0, S.w - 1)], tab4[(rx - 2) & 3]);
-            }
+        // ---- B: first resize, horizontal pass: feature rows x intermediate columns, four columns per item ----
+        for (int i = tid; i < n_fy * n_kx; i += kMsThreads) {
+            const int r = i / n_kx, k = i - r * n_kx;
+            const int sx = kx_lo + k;
+            const float *row = F + r * n_fx - fx_lo;
+            const float f0 = row[clampi(sx - 1, 0, S.w - 1)], f1 = row[clampi(sx, 0, S.w - 1)];
+            const float f2 = row[clampi(sx + 1, 0, S.w - 1)], f3 = row[clampi(sx + 2, 0, S.w - 1)];
+            float *dst = T1 + r * n_rx - rx_lo;
+            const int rx = 4 * sx + 2;
+#pragma unroll
+            for (int ph = 0; ph < 4; ph++)
+                if (rx + ph >= rx_lo && rx + ph <= rx_hi) dst[rx + ph] = hsum4(f0, f1, f2, f3, tw[ph]);
         }
         __syncthreads();
         // ---- C: first resize, vertical pass (always the vector formula: padded widths are multiples of 64) ----
-        // the largest stage: a flat walk over (row, column) that keeps all threads busy, (r, c) advanced without a
-        // division, the four source rows and the phase of a row read from a small table filled before stage B's barrier
+        // the largest stage: a flat walk over (row group, column), (k, c) advanced without a division
         {
-            const int dr = kMsThreads / n_rx, dc = kMsThreads - dr * n_rx;
-            int r = tid / n_rx, c = tid - r * n_rx;
-            while (r < n_ry) {
-                const int4 q = row_q[r];
-                I[r * n_rx + c] = vsum4(T1[q.x + c], T1[q.y + c], T1[q.z + c], T1[q.w + c], tab4[row_ph[r]]);
+            const int dk = kMsThreads / n_rx, dc = kMsThreads - dk * n_rx;
+            int k = tid / n_rx, c = tid - k * n_rx;
+            while (k < n_ky) {
+                const int4 q = row_q[k];
+                const float t0 = T1[q.x + c], t1 = T1[q.y + c], t2 = T1[q.z + c], t3 = T1[q.w + c];
+                const int ry = 4 * (ky_lo + k) + 2;
+                float *dst = I + c - ry_lo * n_rx;
+#pragma unroll
+                for (int ph = 0; ph < 4; ph++)
+                    if (ry + ph >= ry_lo && ry + ph <= ry_hi) dst[(ry + ph) * n_rx] = vsum4(t0, t1, t2, t3, tw[ph]);
                 c += dc;
-                r += dr;
+                k += dk;
                 if (c >= n_rx) {
                     c -= n_rx;
-                    r++;
+                    k++;
                 }
             }
         }
