@@ -867,6 +867,12 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
     int cv[kRounds];
 #pragma unroll
     for (int r = 0; r < kRounds; r++) cv[r] = (r * 32 + lane < items) ? bc[r * 32 + lane] : 0;
+    int ext_lo = 0, ext_hi = 0;  // y extent of part `lane`
+    if (a.item_meta && lane < kParts) {
+        const int *e = a.yext + ((size_t)img * kParts + lane) * 2;
+        ext_lo = e[0];
+        ext_hi = e[1];
+    }
     const int mine = a.n_raw[img];
     int rank = 0;
     for (int u0 = 0; u0 < a.batch; u0 += 32) {
@@ -909,9 +915,8 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
         __shared__ int ylo[kParts], yhi[kParts];
         if (lane < kParts) {
             int *e = a.yext + ((size_t)img * kParts + lane) * 2;
-            const int neg_lo = e[0], hi = e[1];
-            ylo[lane] = -neg_lo;
-            yhi[lane] = hi;
+            ylo[lane] = -ext_lo;
+            yhi[lane] = ext_hi;
             e[0] = e[1] = INT_MIN;  // ready for the next launch
         }
         __syncwarp();
