@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     float *I = T1 + a.cap_t1;                        // first resize, vertical     [n_ry][n_rx] = up_s on the tile's taps
     float *T2 = I + a.cap_i;                         // second resize, horizontal  [n_ry][nX]
     int4 *row_q = reinterpret_cast<int4 *>(T2 + a.cap_t2);   // [<= cap_rows] stage C row-group table (cap_t2 = cap_rows * tile width)
-    __shared__ int x_idx[kMsTileX][4], y_idx[kMsTileY][4];
-    __shared__ float x_w[kMsTileX][4], y_w[kMsTileY][4];
+    __shared__ __align__(16) int x_idx[kMsTileX][4], y_idx[kMsTileY][4];  // read back as one 128-bit load per row
+    __shared__ __align__(16) float x_w[kMsTileX][4], y_w[kMsTileY][4];
 
     // the four weight sets of the x4 resize (phases 1/8, 3/8, 5/8, 7/8), same evaluation as the table
     float tw[4][4];
@@ -185,8 +185,10 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             constexpr int groups = kMsThreads / kMsTileX;
             const int g = tid / kMsTileX, c = tid % kMsTileX;
             if (c < nX) {
-                const int i0 = x_idx[c][0] - rx_lo, i1 = x_idx[c][1] - rx_lo, i2 = x_idx[c][2] - rx_lo, i3 = x_idx[c][3] - rx_lo;
-                const float wv[4] = {x_w[c][0], x_w[c][1], x_w[c][2], x_w[c][3]};
+                const int4 xi = *reinterpret_cast<const int4 *>(x_idx[c]);
+                const float4 xw4 = *reinterpret_cast<const float4 *>(x_w[c]);
+                const int i0 = xi.x - rx_lo, i1 = xi.y - rx_lo, i2 = xi.z - rx_lo, i3 = xi.w - rx_lo;
+                const float wv[4] = {xw4.x, xw4.y, xw4.z, xw4.w};
                 for (int r = g; r < n_ry; r += groups) {
                     const float *row = I + r * n_rx;
                     T2[r * kMsTileX + c] = hsum4(row[i0], row[i1], row[i2], row[i3], wv);
@@ -201,10 +203,13 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             const int r = i / kMsTileX, c = i - r * kMsTileX;
             if (r < nY && c < nX) {
                 const float *col = T2 + c - ry_lo * kMsTileX;
-                const float s0 = col[y_idx[r][0] * kMsTileX], s1 = col[y_idx[r][1] * kMsTileX];
-                const float s2 = col[y_idx[r][2] * kMsTileX], s3 = col[y_idx[r][3] * kMsTileX];
+                const int4 yi = *reinterpret_cast<const int4 *>(y_idx[r]);
+                const float4 yw4 = *reinterpret_cast<const float4 *>(y_w[r]);
+                const float yw[4] = {yw4.x, yw4.y, yw4.z, yw4.w};
+                const float s0 = col[yi.x * kMsTileX], s1 = col[yi.y * kMsTileX];
+                const float s2 = col[yi.z * kMsTileX], s3 = col[yi.w * kMsTileX];
                 const bool vec = ((X0 + c) * cn + c_local) < n_vec2;
-                const float v = vec ? vsum4(s0, s1, s2, s3, y_w[r]) : vsum4_tail(s0, s1, s2, s3, y_w[r]);
+                const float v = vec ? vsum4(s0, s1, s2, s3, yw) : vsum4_tail(s0, s1, s2, s3, yw);
                 acc[k] = __dadd_rn(acc[k], (double)__fdiv_rn(v, n_scales_f));
             }
         }
