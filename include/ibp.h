@@ -78,7 +78,10 @@ typedef struct ibp_params {
     int32_t refine_window;    /* 2: win_size at parse_skeletons.py:135 | offset_radius */
 } ibp_params;
 
-/* Fixed capacities of the device-side variable-length outputs. */
+/* Fixed capacities of the device-side variable-length outputs.  Defaults (ibp_default_limits): batch 64, 128 peaks per
+ * part, 1024 candidates per limb, 128 bodies, 128 humans, 128x128 maps.  With float32 network output, <= 128 peaks per
+ * part and grouping tables that fit behind a limb plane in shared memory (128 bodies at 128x128) ibp_postprocess_batch
+ * runs the persistent streaming kernels; larger limits (crowds) take the one-CTA-per-item kernels.  Same results. */
 typedef struct ibp_limits {
     int32_t max_batch;               /* images per call */
     int32_t max_peaks_per_part;      /* per image and joint type */
