@@ -440,7 +440,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(fuse_multiscale_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         if (limb_phase_bytes(h, 0) > kMaxDynSmem)
             return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_phase_bytes(h, 0), kMaxDynSmem);
         if (group_phase_bytes(h) > kMaxDynSmem)
@@ -510,7 +511,7 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
     a.W = img_w;
     a.out = out;
     a.heat32 = heat32;
-    size_t cap_f = 1, cap_t1 = 1, cap_i = 1, cap_t2 = 1;
+    size_t cap_r1 = 4, cap_i = 4, max_nkx = 1;
     for (int s = 0; s < n_scales; s++) {
         const ibp_scale_input &in = scales[s];
         if (!in.net_out || in.fh < 1 || in.fw < 1 || in.sh < 1 || in.sw < 1 || in.sh > in.fh * a.up || in.sw > in.fw * a.up)
@@ -524,35 +525,27 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
         // cv2.resize with an explicit dsize: inv_scale = (double)dsize / ssize; scale = 1. / inv_scale
         S.scale_x = 1.0 / ((double)img_w / (double)in.sw);
         S.scale_y = 1.0 / ((double)img_h / (double)in.sh);
-        // upper bounds of the tile footprints (see the kernel): taps of T destination pixels span <= (T-1)*scale + 6
-        const size_t n_rx = std::min<size_t>(in.sw, (size_t)((kMsTileX - 1) * S.scale_x) + 6);
-        const size_t n_ry = std::min<size_t>(in.sh, (size_t)((kMsTileY - 1) * S.scale_y) + 6);
-        const size_t n_fx = std::min<size_t>(in.fw, n_rx / 4 + 6), n_fy = std::min<size_t>(in.fh, n_ry / 4 + 6);
-        cap_f = std::max(cap_f, n_fy * n_fx);
-        cap_t1 = std::max(cap_t1, n_fy * n_rx);
-        cap_i = std::max(cap_i, n_ry * n_rx);
-        cap_t2 = std::max(cap_t2, n_ry * (size_t)kMsTileX);
+        max_nkx = std::max(max_nkx, ms_footprint(S.scale_x, S.scale_y, 0).n_kx);
     }
-    a.cap_f = (int)cap_f;
-    a.cap_t1 = (int)cap_t1;
+    // every scale narrow enough: the variant with compile-time row strides
+    const size_t stride = (4 * max_nkx <= (size_t)kMsStride) ? kMsStride : 0;
+    for (int s = 0; s < n_scales; s++) {
+        const MsFootprint f = ms_footprint(a.sc[s].scale_x, a.sc[s].scale_y, stride);
+        cap_r1 = std::max(cap_r1, f.r1);
+        cap_i = std::max(cap_i, f.i);
+    }
+    a.cap_r1 = (int)cap_r1;
     a.cap_i = (int)cap_i;
-    a.cap_t2 = (int)cap_t2;
-    // the four tiles (16-byte aligned as a whole) + the stage C row table: int4 + int per intermediate row
-    cap_t2 = (cap_t2 + 3) & ~(size_t)3;
-    cap_f = (cap_f + 3) & ~(size_t)3;
-    cap_t1 = (cap_t1 + 3) & ~(size_t)3;
-    cap_i = (cap_i + 3) & ~(size_t)3;
-    a.cap_f = (int)cap_f;
-    a.cap_t1 = (int)cap_t1;
-    a.cap_i = (int)cap_i;
-    a.cap_t2 = (int)cap_t2;
-    const size_t smem = (cap_f + cap_t1 + cap_i + cap_t2) * sizeof(float) + (cap_t2 / kMsTileX) * 20;
+    const size_t smem = (cap_r1 + cap_i) * sizeof(float);
     if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale: a scale factor this large needs %zu B of shared memory", smem);
     const dim3 grid((img_w + kMsTileX - 1) / kMsTileX, (img_h + kMsTileY - 1) / kMsTileY, (unsigned)batch * kLayers);
     if (grid.z > 65535u) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: batch %d too large for one launch (max %d)", batch, 65535 / kLayers);
     {
         StageTimer t(h, IBP_STAGE_FUSE, (cudaStream_t)stream);
-        fuse_multiscale_kernel<<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
+        if (stride)
+            fuse_multiscale_kernel<kMsStride><<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
+        else
+            fuse_multiscale_kernel<0><<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());

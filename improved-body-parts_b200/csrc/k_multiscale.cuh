@@ -25,7 +25,9 @@ namespace ibp {
 constexpr int kMsMaxScales = 8;
 constexpr int kMsTileX = 64, kMsTileY = 16;
 constexpr int kMsThreads = 256;
-constexpr int kMsPerThread = kMsTileX * kMsTileY / kMsThreads;
+constexpr int kMsWarps = kMsThreads / 32;
+constexpr int kMsRowsPerThread = kMsTileY / (kMsWarps / 2);  // stage E: a warp owns 32 columns x this many rows
+constexpr int kMsSegGroups = 4;                              // stage C: row groups (of 4 rows) per warp task
 
 struct MsScale {
     const float *src;   // (batch, 2, 50, h, w) network output of this scale
@@ -42,9 +44,30 @@ struct MsArgs {
     int H, W;           // image size
     double *out;        // (batch, 50, H, W) planar float64: [0,30) limb maps, [30,50) keypoint maps + background
     float *heat32;      // optional (batch, 18, H, W) float32 copy of the keypoint planes (find_peaks casts, l.291)
-    // shared-memory carve-up (floats), sized on the host for the largest scale
-    int cap_f, cap_t1, cap_i, cap_t2;
+    // shared-memory carve-up (floats), sized on the host for the largest scale (ms_footprint below)
+    int cap_r1, cap_i;
 };
+
+// Upper bounds of one tile's footprints for a scale: the taps of T destination pixels span <= (T-1)*scale + 6 source
+// pixels; they are produced in whole groups of four (the four phases of the x4 resize).
+constexpr int kMsStride = 152;  // the compiled constant-stride variant: scale factors up to ~2.2 at 64-wide tiles
+struct MsFootprint {
+    size_t n_ry, n_kx, n_ky, r1, i;
+};
+inline MsFootprint ms_footprint(double scale_x, double scale_y, size_t stride /* 0 = 4 * n_kx */) {
+    MsFootprint f;
+    const size_t n_rx = (size_t)((kMsTileX - 1) * scale_x) + 6;
+    f.n_ry = (size_t)((kMsTileY - 1) * scale_y) + 6;
+    f.n_kx = n_rx / 4 + 2;
+    f.n_ky = f.n_ry / 4 + 2;
+    const size_t n_fx = f.n_kx + 3, n_fy = f.n_ky + 3;
+    if (!stride) stride = 4 * f.n_kx;
+    const size_t f_t1 = ((n_fy * n_fx + 3) & ~(size_t)3) + n_fy * stride;  // F + T1
+    const size_t t2 = f.n_ry * kMsTileX;                                        // T2 reuses the same region
+    f.r1 = (std::max(f_t1, t2) + 3) & ~(size_t)3;
+    f.i = (4 * f.n_ky * stride + 3) & ~(size_t)3;
+    return f;
+}
 
 // left-associated four-tap sum: the scalar tail of OpenCV's vertical pass
 __device__ __forceinline__ float vsum4_tail(float s0, float s1, float s2, float s3, const float *b) {
@@ -60,9 +83,25 @@ __device__ __forceinline__ int ms_tap(int d, double scale, float *w) {
     return s;
 }
 
+// i / n for 0 <= i < 2^16 and small n, with inv = 1.0f / n: (i + 0.5) * inv is at least 0.5 / n away from an integer,
+// far more than the rounding error of the two float operations
+__device__ __forceinline__ int ms_div(int i, float inv) { return __float2int_rz(__fmul_rn(__fadd_rn(__int2float_rn(i), 0.5f), inv)); }
+
+// Stages per scale (all intermediates in shared memory; region R1 holds F and T1, later T2):
+//   A  F  [n_fy][n_fx]    fused feature pixels of source rows ky_lo-1 .. and columns kx_lo-1 .., border replicated on load
+//   B  T1 [n_fy][4 n_kx]  first resize, horizontal: item = (row, group of four columns), one 128-bit store
+//   C  I  [4 n_ky][4 n_kx] first resize, vertical: a warp owns 32 columns and walks down the row groups with a sliding
+//                          window of four T1 values (one load per four results)
+//   D  T2 [n_ry][64]      second resize, horizontal: a warp owns 32 output columns (taps and weights in registers) and
+//                          walks down the rows
+//   E  acc                second resize, vertical, /n_scales, float64 accumulate in registers
+// The instruction count per tile is what bounds this kernel (it is issue-bound), so every stage is written to need no
+// division, no clamp and no predicate per element.
+// STRIDE = row stride of T1 and I as a compile-time constant (row offsets become immediates), 0 = 4 * n_kx at run time.
+template <int STRIDE>
 __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int chan = blockIdx.z % kLayers, img = blockIdx.z / kLayers;
     const int X0 = blockIdx.x * kMsTileX, Y0 = blockIdx.y * kMsTileY;
     const int nX = min(kMsTileX, a.W - X0), nY = min(kMsTileY, a.H - Y0);
@@ -71,162 +110,182 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     const int c_local = (chan < kLimbs) ? chan : chan - kLimbs;
     const int n_vec2 = (a.W * cn) & ~3;  // elements of a destination row handled by the 4-lane vector loop
 
-    float *F = reinterpret_cast<float *>(smem_raw);  // fused feature pixels       [n_fy][n_fx]
-    float *T1 = F + a.cap_f;                         // first resize, horizontal   [n_fy][n_rx]
-    float *I = T1 + a.cap_t1;                        // first resize, vertical     [n_ry][n_rx] = up_s on the tile's taps
-    float *T2 = I + a.cap_i;                         // second resize, horizontal  [n_ry][nX]
-    int4 *row_q = reinterpret_cast<int4 *>(T2 + a.cap_t2);   // [<= cap_rows] stage C row-group table (cap_t2 = cap_rows * tile width)
-    __shared__ __align__(16) int x_idx[kMsTileX][4], y_idx[kMsTileY][4];  // read back as one 128-bit load per row
-    __shared__ __align__(16) float x_w[kMsTileX][4], y_w[kMsTileY][4];
+    float *R1 = reinterpret_cast<float *>(smem_raw);
+    float *I = R1 + a.cap_r1;
+    // taps of the second resize for the scale at hand: clamped source index (x: absolute; y: times the T2 row stride)
+    // and weights, one 128-bit entry each
+    __shared__ int4 x_idx[kMsTileX], y_idx[kMsTileY];
+    __shared__ float4 x_w[kMsTileX], y_w[kMsTileY];
+    __shared__ int s_bounds[kMsMaxScales][4];  // per scale: first / last source column and row the tile taps
+
+    if (tid < 4 * a.n_scales) {
+        const int s = tid >> 2, which = tid & 3;
+        float w4[4];
+        int v;
+        if (which == 0) v = clampi(ms_tap(X0, a.sc[s].scale_x, w4) - 1, 0, a.sc[s].sw - 1);
+        else if (which == 1) v = clampi(ms_tap(X0 + nX - 1, a.sc[s].scale_x, w4) + 2, 0, a.sc[s].sw - 1);
+        else if (which == 2) v = clampi(ms_tap(Y0, a.sc[s].scale_y, w4) - 1, 0, a.sc[s].sh - 1);
+        else v = clampi(ms_tap(Y0 + nY - 1, a.sc[s].scale_y, w4) + 2, 0, a.sc[s].sh - 1);
+        s_bounds[s][which] = v;
+    }
 
     // the four weight sets of the x4 resize (phases 1/8, 3/8, 5/8, 7/8), same evaluation as the table
     float tw[4][4];
 #pragma unroll
     for (int ph = 0; ph < 4; ph++) cubic_weights(__fadd_rn(__int2float_rn(ph) * 0.25f, 0.125f), tw[ph]);
 
-    double acc[kMsPerThread];
+    double acc[kMsRowsPerThread];
 #pragma unroll
-    for (int k = 0; k < kMsPerThread; k++) acc[k] = 0.0;
+    for (int k = 0; k < kMsRowsPerThread; k++) acc[k] = 0.0;
     const float n_scales_f = __int2float_rn(a.n_scales);
+    const bool n_pow2 = (a.n_scales & (a.n_scales - 1)) == 0;  // then v / n == v * (1 / n) bit for bit
+    const float inv_scales = __fdiv_rn(1.0f, n_scales_f);
+
+    // stage E geometry: warp = (column half, row segment)
+    const int e_col = (warp & 1) * 32 + lane, e_row0 = (warp >> 1) * kMsRowsPerThread;
+    const bool e_vec = ((X0 + e_col) * cn + c_local) < n_vec2;
+    const bool e_all_vec = __all_sync(0xffffffffu, e_vec);
 
     for (int s = 0; s < a.n_scales; s++) {
         const MsScale S = a.sc[s];
-        __syncthreads();  // previous scale's tables and tiles are no longer read
-        // ---- taps of the second resize for this tile's columns and rows (clamped to the CROPPED map) ----
-        if (tid < nX) {
+        __syncthreads();  // bounds written (first pass); previous scale's T2 and tap tables no longer read
+        const int rx_lo = s_bounds[s][0], rx_hi = s_bounds[s][1], ry_lo = s_bounds[s][2], ry_hi = s_bounds[s][3];
+        const int n_ry = ry_hi - ry_lo + 1;
+        // x4 resize: destination r reads source (r-2)>>2 - 1 .. +2 with the weights of phase (r-2)&3, so destinations
+        // 4k+2 .. 4k+5 ("group k") share their four sources.  Whole groups are produced.
+        const int kx_lo = (rx_lo - 2) >> 2, n_kx = ((rx_hi - 2) >> 2) - kx_lo + 1;
+        const int ky_lo = (ry_lo - 2) >> 2, n_ky = ((ry_hi - 2) >> 2) - ky_lo + 1;
+        const int cx0 = 4 * kx_lo + 2, cy0 = 4 * ky_lo + 2;  // first column / row of I
+        const int nrx = STRIDE ? STRIDE : 4 * n_kx;          // row stride of T1 and I
+        const int n_fx = n_kx + 3, n_fy = n_ky + 3;
+        float *F = R1;
+        float *T1 = R1 + ((n_fy * n_fx + 3) & ~3);
+        float *T2 = R1;
+
+        // tap tables of this scale (read by D and E, two barriers from here)
+        if (tid < kMsTileX + kMsTileY) {
             float w4[4];
-            const int sx = ms_tap(X0 + tid, S.scale_x, w4);
-            for (int k = 0; k < 4; k++) {
-                x_idx[tid][k] = clampi(sx - 1 + k, 0, S.sw - 1);
-                x_w[tid][k] = w4[k];
-            }
-        } else if (tid >= 128 && tid - 128 < nY) {
-            const int j = tid - 128;
-            float w4[4];
-            const int sy = ms_tap(Y0 + j, S.scale_y, w4);
-            for (int k = 0; k < 4; k++) {
-                y_idx[j][k] = clampi(sy - 1 + k, 0, S.sh - 1);
-                y_w[j][k] = w4[k];
+            if (tid < kMsTileX) {
+                const int sx = ms_tap(min(X0 + tid, a.W - 1), S.scale_x, w4);
+                x_idx[tid] = make_int4(clampi(sx - 1, 0, S.sw - 1), clampi(sx, 0, S.sw - 1), clampi(sx + 1, 0, S.sw - 1), clampi(sx + 2, 0, S.sw - 1));
+                x_w[tid] = make_float4(w4[0], w4[1], w4[2], w4[3]);
+            } else {
+                const int r = tid - kMsTileX;
+                const int sy = ms_tap(min(Y0 + r, a.H - 1), S.scale_y, w4);
+                y_idx[r] = make_int4(clampi(sy - 1, 0, S.sh - 1) * kMsTileX, clampi(sy, 0, S.sh - 1) * kMsTileX,
+                                     clampi(sy + 1, 0, S.sh - 1) * kMsTileX, clampi(sy + 2, 0, S.sh - 1) * kMsTileX);
+                y_w[r] = make_float4(w4[0], w4[1], w4[2], w4[3]);
             }
         }
-        __syncthreads();
-        // taps are monotonic in the destination index: the first and last entries bound the range
-        const int rx_lo = x_idx[0][0], rx_hi = x_idx[nX - 1][3];
-        const int ry_lo = y_idx[0][0], ry_hi = y_idx[nY - 1][3];
-        const int n_rx = rx_hi - rx_lo + 1, n_ry = ry_hi - ry_lo + 1;
-        // feature pixels tapped by the first resize (x`up`, up == 4: tap (r-2)>>2, phase (r-2)&3), clamped to the map
-        const int fx_lo = clampi(((rx_lo - 2) >> 2) - 1, 0, S.w - 1), fx_hi = clampi(((rx_hi - 2) >> 2) + 2, 0, S.w - 1);
-        const int fy_lo = clampi(((ry_lo - 2) >> 2) - 1, 0, S.h - 1), fy_hi = clampi(((ry_hi - 2) >> 2) + 2, 0, S.h - 1);
-        const int n_fx = fx_hi - fx_lo + 1, n_fy = fy_hi - fy_lo + 1;
-
-        // ---- A: feature tile, flip average on the way in (l.232-248) ----
+        // ---- A: feature tile, flip average on the way in (l.232-248); the replicate border of the first resize is
+        //         materialised here so that B and C index without clamps ----
         {
             const size_t hw = (size_t)S.h * S.w;
             const float *base = S.src + (size_t)img * 2 * kLayers * hw;
             const float *upr = base + (size_t)chan * hw;
             const float *twin = base + (size_t)(kLayers + c_flip_src[chan]) * hw;
+            const float inv = __frcp_rn(__int2float_rn(n_fx));
             for (int i = tid; i < n_fy * n_fx; i += kMsThreads) {
-                const int r = i / n_fx, c = i - r * n_fx;
-                const int y = fy_lo + r, x = fx_lo + c;
-                const float v = __ldg(upr + (size_t)y * S.w + x);
-                F[i] = a.flip ? avg_like_numpy(v, __ldg(twin + (size_t)y * S.w + (S.w - 1 - x))) : v;
+                const int r = ms_div(i, inv), c = i - r * n_fx;
+                const int y = clampi(ky_lo - 1 + r, 0, S.h - 1), x = clampi(kx_lo - 1 + c, 0, S.w - 1);
+                const float v = __ldg(upr + y * S.w + x);
+                F[i] = a.flip ? avg_like_numpy(v, __ldg(twin + y * S.w + (S.w - 1 - x))) : v;
             }
         }
-        // The x4 resize has four phases: outputs 4k+2 .. 4k+5 read the SAME four source pixels k-1 .. k+2 (clamped) and
-        // differ only in the weights.  Stages B and C therefore work on groups of four outputs: four shared-memory
-        // loads feed four results (the weights of the four phases sit in registers), instead of four loads each.
-        const int kx_lo = (rx_lo - 2) >> 2, n_kx = ((rx_hi - 2) >> 2) - kx_lo + 1;
-        const int ky_lo = (ry_lo - 2) >> 2, n_ky = ((ry_hi - 2) >> 2) - ky_lo + 1;
-        // per group of intermediate rows: offsets of its four source rows in T1 (stage C)
-        for (int k = tid; k < n_ky; k += kMsThreads) {
-            const int sy = ky_lo + k;
-            row_q[k] = make_int4((clampi(sy - 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy, 0, S.h - 1) - fy_lo) * n_rx,
-                                 (clampi(sy + 1, 0, S.h - 1) - fy_lo) * n_rx, (clampi(sy + 2, 0, S.h - 1) - fy_lo) * n_rx);
-        }
         __syncthreads();
-        // ---- B: first resize, horizontal pass: feature rows x intermediate columns, four columns per item ----
-        for (int i = tid; i < n_fy * n_kx; i += kMsThreads) {
-            const int r = i / n_kx, k = i - r * n_kx;
-            const int sx = kx_lo + k;
-            const float *row = F + r * n_fx - fx_lo;
-            const float f0 = row[clampi(sx - 1, 0, S.w - 1)], f1 = row[clampi(sx, 0, S.w - 1)];
-            const float f2 = row[clampi(sx + 1, 0, S.w - 1)], f3 = row[clampi(sx + 2, 0, S.w - 1)];
-            float *dst = T1 + r * n_rx - rx_lo;
-            const int rx = 4 * sx + 2;
-#pragma unroll
-            for (int ph = 0; ph < 4; ph++)
-                if (rx + ph >= rx_lo && rx + ph <= rx_hi) dst[rx + ph] = hsum4(f0, f1, f2, f3, tw[ph]);
-        }
-        __syncthreads();
-        // ---- C: first resize, vertical pass (always the vector formula: padded widths are multiples of 64) ----
-        // the largest stage: a flat walk over (row group, column), (k, c) advanced without a division
+        // ---- B: first resize, horizontal pass ----
         {
-            const int dk = kMsThreads / n_rx, dc = kMsThreads - dk * n_rx;
-            int k = tid / n_rx, c = tid - k * n_rx;
-            while (k < n_ky) {
-                const int4 q = row_q[k];
-                const float t0 = T1[q.x + c], t1 = T1[q.y + c], t2 = T1[q.z + c], t3 = T1[q.w + c];
-                const int ry = 4 * (ky_lo + k) + 2;
-                float *dst = I + c - ry_lo * n_rx;
-#pragma unroll
-                for (int ph = 0; ph < 4; ph++)
-                    if (ry + ph >= ry_lo && ry + ph <= ry_hi) dst[(ry + ph) * n_rx] = vsum4(t0, t1, t2, t3, tw[ph]);
-                c += dc;
-                k += dk;
-                if (c >= n_rx) {
-                    c -= n_rx;
-                    k++;
+            const float inv = __frcp_rn(__int2float_rn(n_kx));
+            for (int i = tid; i < n_fy * n_kx; i += kMsThreads) {
+                const int r = ms_div(i, inv), k = i - r * n_kx;
+                const float *row = F + r * n_fx + k;
+                const float f0 = row[0], f1 = row[1], f2 = row[2], f3 = row[3];
+                *reinterpret_cast<float4 *>(T1 + r * nrx + 4 * k) =
+                    make_float4(hsum4(f0, f1, f2, f3, tw[0]), hsum4(f0, f1, f2, f3, tw[1]), hsum4(f0, f1, f2, f3, tw[2]), hsum4(f0, f1, f2, f3, tw[3]));
+            }
+        }
+        __syncthreads();
+        // ---- C: first resize, vertical pass (always the vector formula: a row of the x4 image has 4*w*cn elements) ----
+        {
+            const int n_cols = 4 * n_kx;
+            const int n_chunks = (n_cols + 31) >> 5, n_seg = (n_ky + kMsSegGroups - 1) / kMsSegGroups;
+            const float inv = __frcp_rn(__int2float_rn(n_chunks));
+            for (int t = warp; t < n_chunks * n_seg; t += kMsWarps) {
+                const int seg = ms_div(t, inv), c = (t - seg * n_chunks) * 32 + lane;
+                if (c < n_cols) {
+                    const int k0 = seg * kMsSegGroups, k1 = min(k0 + kMsSegGroups, n_ky);
+                    const float *p = T1 + k0 * nrx + c;
+                    float *q = I + 4 * k0 * nrx + c;
+                    float t0 = p[0], t1 = p[nrx], t2 = p[2 * nrx];
+                    p += 3 * nrx;
+                    for (int k = k0; k < k1; k++) {
+                        const float t3 = *p;
+                        q[0] = vsum4(t0, t1, t2, t3, tw[0]);
+                        q[nrx] = vsum4(t0, t1, t2, t3, tw[1]);
+                        q[2 * nrx] = vsum4(t0, t1, t2, t3, tw[2]);
+                        q[3 * nrx] = vsum4(t0, t1, t2, t3, tw[3]);
+                        t0 = t1, t1 = t2, t2 = t3;
+                        p += nrx;
+                        q += 4 * nrx;
+                    }
                 }
             }
         }
         __syncthreads();
-        // ---- D: second resize, horizontal pass: intermediate rows x output columns ----
+        // ---- D: second resize, horizontal pass: rows ry_lo .. ry_hi of I -> T2[n_ry][64] ----
         {
-            constexpr int groups = kMsThreads / kMsTileX;
-            const int g = tid / kMsTileX, c = tid % kMsTileX;
+            const int c = (warp & 1) * 32 + lane, blk = warp >> 1;
+            const int rb = (n_ry + kMsWarps / 2 - 1) / (kMsWarps / 2);
+            const int r0 = blk * rb, r1 = min(r0 + rb, n_ry);
             if (c < nX) {
-                const int4 xi = *reinterpret_cast<const int4 *>(x_idx[c]);
-                const float4 xw4 = *reinterpret_cast<const float4 *>(x_w[c]);
-                const int i0 = xi.x - rx_lo, i1 = xi.y - rx_lo, i2 = xi.z - rx_lo, i3 = xi.w - rx_lo;
+                const int4 xi = x_idx[c];
+                const float4 xw4 = x_w[c];
                 const float wv[4] = {xw4.x, xw4.y, xw4.z, xw4.w};
-                for (int r = g; r < n_ry; r += groups) {
-                    const float *row = I + r * n_rx;
-                    T2[r * kMsTileX + c] = hsum4(row[i0], row[i1], row[i2], row[i3], wv);
+                const float *row = I + (ry_lo - cy0 + r0) * nrx - cx0;
+                const float *p0 = row + xi.x, *p1 = row + xi.y, *p2 = row + xi.z, *p3 = row + xi.w;
+                float *dst = T2 + r0 * kMsTileX + c;
+#pragma unroll 4
+                for (int r = r0; r < r1; r++) {
+                    *dst = hsum4(*p0, *p1, *p2, *p3, wv);
+                    p0 += nrx, p1 += nrx, p2 += nrx, p3 += nrx;
+                    dst += kMsTileX;
                 }
             }
         }
         __syncthreads();
         // ---- E: second resize, vertical pass, /n_scales in float32, accumulate in float64 (l.280-281) ----
+        if (e_col < nX) {
+            const float *col = T2 + e_col - ry_lo * kMsTileX;
 #pragma unroll
-        for (int k = 0; k < kMsPerThread; k++) {
-            const int i = tid + k * kMsThreads;
-            const int r = i / kMsTileX, c = i - r * kMsTileX;
-            if (r < nY && c < nX) {
-                const float *col = T2 + c - ry_lo * kMsTileX;
-                const int4 yi = *reinterpret_cast<const int4 *>(y_idx[r]);
-                const float4 yw4 = *reinterpret_cast<const float4 *>(y_w[r]);
-                const float yw[4] = {yw4.x, yw4.y, yw4.z, yw4.w};
-                const float s0 = col[yi.x * kMsTileX], s1 = col[yi.y * kMsTileX];
-                const float s2 = col[yi.z * kMsTileX], s3 = col[yi.w * kMsTileX];
-                const bool vec = ((X0 + c) * cn + c_local) < n_vec2;
-                const float v = vec ? vsum4(s0, s1, s2, s3, yw) : vsum4_tail(s0, s1, s2, s3, yw);
-                acc[k] = __dadd_rn(acc[k], (double)__fdiv_rn(v, n_scales_f));
+            for (int k = 0; k < kMsRowsPerThread; k++) {
+                const int r = e_row0 + k;
+                if (r < nY) {
+                    const int4 yi = y_idx[r];
+                    const float4 yw4 = y_w[r];
+                    const float yw[4] = {yw4.x, yw4.y, yw4.z, yw4.w};
+                    const float s0 = col[yi.x], s1 = col[yi.y], s2 = col[yi.z], s3 = col[yi.w];
+                    float v;
+                    if (e_all_vec) v = vsum4(s0, s1, s2, s3, yw);
+                    else v = e_vec ? vsum4(s0, s1, s2, s3, yw) : vsum4_tail(s0, s1, s2, s3, yw);
+                    acc[k] = __dadd_rn(acc[k], (double)(n_pow2 ? __fmul_rn(v, inv_scales) : __fdiv_rn(v, n_scales_f)));
+                }
             }
         }
     }
 
-    double *out = a.out + ((size_t)img * kLayers + chan) * (size_t)a.H * a.W;
-    float *h32 = (a.heat32 && chan >= kLimbs && chan < kLimbs + kParts)
-                     ? a.heat32 + ((size_t)img * kParts + (chan - kLimbs)) * (size_t)a.H * a.W
-                     : nullptr;
+    if (e_col < nX) {
+        double *out = a.out + ((size_t)img * kLayers + chan) * (size_t)a.H * a.W;
+        float *h32 = (a.heat32 && chan >= kLimbs && chan < kLimbs + kParts)
+                         ? a.heat32 + ((size_t)img * kParts + (chan - kLimbs)) * (size_t)a.H * a.W
+                         : nullptr;
 #pragma unroll
-    for (int k = 0; k < kMsPerThread; k++) {
-        const int i = tid + k * kMsThreads;
-        const int r = i / kMsTileX, c = i - r * kMsTileX;
-        if (r < nY && c < nX) {
-            const size_t o = (size_t)(Y0 + r) * a.W + (X0 + c);
-            out[o] = acc[k];
-            if (h32) h32[o] = __double2float_rn(acc[k]);
+        for (int k = 0; k < kMsRowsPerThread; k++) {
+            const int r = e_row0 + k;
+            if (r < nY) {
+                const size_t o = (size_t)(Y0 + r) * a.W + (X0 + e_col);
+                out[o] = acc[k];
+                if (h32) h32[o] = __double2float_rn(acc[k]);
+            }
         }
     }
 }
