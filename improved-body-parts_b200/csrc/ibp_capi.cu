@@ -440,8 +440,10 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         if (limb_phase_bytes(h, 0) > kMaxDynSmem)
             return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_phase_bytes(h, 0), kMaxDynSmem);
         if (group_phase_bytes(h) > kMaxDynSmem)
@@ -507,6 +509,7 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
     a.n_scales = n_scales;
     a.up = h->P.upsample;
     a.flip = flip_avg ? 1 : 0;
+    a.one = 1.0f;
     a.H = img_h;
     a.W = img_w;
     a.out = out;
@@ -542,10 +545,10 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
     if (grid.z > 65535u) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale: batch %d too large for one launch (max %d)", batch, 65535 / kLayers);
     {
         StageTimer t(h, IBP_STAGE_FUSE, (cudaStream_t)stream);
-        if (stride)
-            fuse_multiscale_kernel<kMsStride><<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
-        else
-            fuse_multiscale_kernel<0><<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
+        const bool pow2 = (n_scales & (n_scales - 1)) == 0;
+        auto kern = stride ? (pow2 ? fuse_multiscale_kernel<kMsStride, true> : fuse_multiscale_kernel<kMsStride, false>)
+                           : (pow2 ? fuse_multiscale_kernel<0, true> : fuse_multiscale_kernel<0, false>);
+        kern<<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());

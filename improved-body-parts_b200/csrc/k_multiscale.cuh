@@ -26,7 +26,7 @@ constexpr int kMsMaxScales = 8;
 constexpr int kMsTileX = 64, kMsTileY = 16;
 constexpr int kMsThreads = 256;
 constexpr int kMsWarps = kMsThreads / 32;
-constexpr int kMsRowsPerThread = kMsTileY / (kMsWarps / 2);  // stage E: a warp owns 32 columns x this many rows
+constexpr int kMsRowsPerWarp = kMsTileY / kMsWarps;          // stage E: a warp owns this many rows of the tile
 constexpr int kMsSegGroups = 4;                              // stage C: row groups (of 4 rows) per warp task
 
 struct MsScale {
@@ -41,6 +41,7 @@ struct MsArgs {
     int n_scales;
     int up;             // model stride (first resize factor); the kernel supports 4
     int flip;           // average with the flipped twin
+    float one;          // 1.0f, opaque to the compiler (see add2)
     int H, W;           // image size
     double *out;        // (batch, 50, H, W) planar float64: [0,30) limb maps, [30,50) keypoint maps + background
     float *heat32;      // optional (batch, 18, H, W) float32 copy of the keypoint planes (find_peaks casts, l.291)
@@ -83,6 +84,24 @@ __device__ __forceinline__ int ms_tap(int d, double scale, float *w) {
     return s;
 }
 
+// Packed float32x2 arithmetic of sm_100: FMUL2 / FFMA2 work on two floats per lane at the issue rate of the scalar
+// instructions (measured, tools/ubench/f32x2.cu), so they halve the arithmetic instructions of an issue-bound kernel.
+// Each half rounds like the scalar operation.  The ADD must not be written as add.rn.f32x2 or __fadd2_rn: ptxas 12.9
+// contracts a packed multiply feeding a packed add into ONE FFMA2 (a single rounding) even with -fmad=false and
+// explicit .rn, which breaks parity with OpenCV's separate multiply and add.  It is therefore issued as
+// fma(x, one, y) with `one` = 1.0f passed in at run time: x*1 is exact, the sum is rounded once, and the compiler can
+// neither simplify nor fuse it.
+__device__ __forceinline__ float2 dup2(float v) { return make_float2(v, v); }
+__device__ __forceinline__ float2 add2(float2 x, float2 y, float2 one) { return __ffma2_rn(x, one, y); }
+// ((s0*a0 + s1*a1) + s2*a2) + s3*a3 on both halves
+__device__ __forceinline__ float2 hsum4x2(float2 s0, float2 s1, float2 s2, float2 s3, float2 a0, float2 a1, float2 a2, float2 a3, float2 one) {
+    return add2(add2(add2(__fmul2_rn(s0, a0), __fmul2_rn(s1, a1), one), __fmul2_rn(s2, a2), one), __fmul2_rn(s3, a3), one);
+}
+// s0*b0 + (s1*b1 + (s2*b2 + s3*b3)) on both halves
+__device__ __forceinline__ float2 vsum4x2(float2 s0, float2 s1, float2 s2, float2 s3, float2 b0, float2 b1, float2 b2, float2 b3, float2 one) {
+    return add2(__fmul2_rn(s0, b0), add2(__fmul2_rn(s1, b1), add2(__fmul2_rn(s2, b2), __fmul2_rn(s3, b3), one), one), one);
+}
+
 // i / n for 0 <= i < 2^16 and small n, with inv = 1.0f / n: (i + 0.5) * inv is at least 0.5 / n away from an integer,
 // far more than the rounding error of the two float operations
 __device__ __forceinline__ int ms_div(int i, float inv) { return __float2int_rz(__fmul_rn(__fadd_rn(__int2float_rn(i), 0.5f), inv)); }
@@ -98,7 +117,8 @@ __device__ __forceinline__ int ms_div(int i, float inv) { return __float2int_rz(
 // The instruction count per tile is what bounds this kernel (it is issue-bound), so every stage is written to need no
 // division, no clamp and no predicate per element.
 // STRIDE = row stride of T1 and I as a compile-time constant (row offsets become immediates), 0 = 4 * n_kx at run time.
-template <int STRIDE>
+// POW2: the number of scales is a power of two, v / n is then v * (1 / n) bit for bit.
+template <int STRIDE, bool POW2>
 __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -114,8 +134,8 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     float *I = R1 + a.cap_r1;
     // taps of the second resize for the scale at hand: clamped source index (x: absolute; y: times the T2 row stride)
     // and weights, one 128-bit entry each
-    __shared__ int4 x_idx[kMsTileX], y_idx[kMsTileY];
-    __shared__ float4 x_w[kMsTileX], y_w[kMsTileY];
+    __shared__ int4 x_idx[kMsTileX], y_idx[kMsTileY];  // y: byte offset of the T2 row
+    __shared__ float4 x_w[kMsTileX], y_w[kMsTileY][2];  // y: each weight twice (packed pairs of columns)
     __shared__ int s_bounds[kMsMaxScales][4];  // per scale: first / last source column and row the tile taps
 
     if (tid < 4 * a.n_scales) {
@@ -134,17 +154,16 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
 #pragma unroll
     for (int ph = 0; ph < 4; ph++) cubic_weights(__fadd_rn(__int2float_rn(ph) * 0.25f, 0.125f), tw[ph]);
 
-    double acc[kMsRowsPerThread];
+    // stage E geometry: a warp owns kMsRowsPerWarp full rows of the tile, a lane two adjacent columns
+    double acc[kMsRowsPerWarp][2];
 #pragma unroll
-    for (int k = 0; k < kMsRowsPerThread; k++) acc[k] = 0.0;
+    for (int k = 0; k < kMsRowsPerWarp; k++) acc[k][0] = acc[k][1] = 0.0;
     const float n_scales_f = __int2float_rn(a.n_scales);
-    const bool n_pow2 = (a.n_scales & (a.n_scales - 1)) == 0;  // then v / n == v * (1 / n) bit for bit
-    const float inv_scales = __fdiv_rn(1.0f, n_scales_f);
-
-    // stage E geometry: warp = (column half, row segment)
-    const int e_col = (warp & 1) * 32 + lane, e_row0 = (warp >> 1) * kMsRowsPerThread;
-    const bool e_vec = ((X0 + e_col) * cn + c_local) < n_vec2;
-    const bool e_all_vec = __all_sync(0xffffffffu, e_vec);
+    const float2 inv_scales2 = dup2(__fdiv_rn(1.0f, n_scales_f));
+    const float2 one2 = dup2(a.one);
+    const int e_col = 2 * lane, e_row0 = warp * kMsRowsPerWarp;
+    const bool e_vec0 = ((X0 + e_col) * cn + c_local) < n_vec2, e_vec1 = ((X0 + e_col + 1) * cn + c_local) < n_vec2;
+    const bool e_all_vec = __all_sync(0xffffffffu, e_vec0 && e_vec1);
 
     for (int s = 0; s < a.n_scales; s++) {
         const MsScale S = a.sc[s];
@@ -172,9 +191,11 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             } else {
                 const int r = tid - kMsTileX;
                 const int sy = ms_tap(min(Y0 + r, a.H - 1), S.scale_y, w4);
-                y_idx[r] = make_int4(clampi(sy - 1, 0, S.sh - 1) * kMsTileX, clampi(sy, 0, S.sh - 1) * kMsTileX,
-                                     clampi(sy + 1, 0, S.sh - 1) * kMsTileX, clampi(sy + 2, 0, S.sh - 1) * kMsTileX);
-                y_w[r] = make_float4(w4[0], w4[1], w4[2], w4[3]);
+                constexpr int rb = kMsTileX * (int)sizeof(float);
+                y_idx[r] = make_int4(clampi(sy - 1, 0, S.sh - 1) * rb, clampi(sy, 0, S.sh - 1) * rb, clampi(sy + 1, 0, S.sh - 1) * rb,
+                                     clampi(sy + 2, 0, S.sh - 1) * rb);
+                y_w[r][0] = make_float4(w4[0], w4[0], w4[1], w4[1]);
+                y_w[r][1] = make_float4(w4[2], w4[2], w4[3], w4[3]);
             }
         }
         // ---- A: feature tile, flip average on the way in (l.232-248); the replicate border of the first resize is
@@ -193,37 +214,42 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             }
         }
         __syncthreads();
-        // ---- B: first resize, horizontal pass ----
+        // ---- B: first resize, horizontal pass; the pairs are phases (0,1) and (2,3) of one group ----
         {
             const float inv = __frcp_rn(__int2float_rn(n_kx));
             for (int i = tid; i < n_fy * n_kx; i += kMsThreads) {
                 const int r = ms_div(i, inv), k = i - r * n_kx;
                 const float *row = F + r * n_fx + k;
-                const float f0 = row[0], f1 = row[1], f2 = row[2], f3 = row[3];
-                *reinterpret_cast<float4 *>(T1 + r * nrx + 4 * k) =
-                    make_float4(hsum4(f0, f1, f2, f3, tw[0]), hsum4(f0, f1, f2, f3, tw[1]), hsum4(f0, f1, f2, f3, tw[2]), hsum4(f0, f1, f2, f3, tw[3]));
+                const float2 f0 = dup2(row[0]), f1 = dup2(row[1]), f2 = dup2(row[2]), f3 = dup2(row[3]);
+                const float2 lo = hsum4x2(f0, f1, f2, f3, make_float2(tw[0][0], tw[1][0]), make_float2(tw[0][1], tw[1][1]),
+                                          make_float2(tw[0][2], tw[1][2]), make_float2(tw[0][3], tw[1][3]), one2);
+                const float2 hi = hsum4x2(f0, f1, f2, f3, make_float2(tw[2][0], tw[3][0]), make_float2(tw[2][1], tw[3][1]),
+                                          make_float2(tw[2][2], tw[3][2]), make_float2(tw[2][3], tw[3][3]), one2);
+                *reinterpret_cast<float4 *>(T1 + r * nrx + 4 * k) = make_float4(lo.x, lo.y, hi.x, hi.y);
             }
         }
         __syncthreads();
-        // ---- C: first resize, vertical pass (always the vector formula: a row of the x4 image has 4*w*cn elements) ----
+        // ---- C: first resize, vertical pass (always the vector formula: a row of the x4 image has 4*w*cn elements);
+        //         the pairs are two adjacent columns ----
         {
             const int n_cols = 4 * n_kx;
-            const int n_chunks = (n_cols + 31) >> 5, n_seg = (n_ky + kMsSegGroups - 1) / kMsSegGroups;
+            const int n_chunks = (n_cols + 63) >> 6, n_seg = (n_ky + kMsSegGroups - 1) / kMsSegGroups;
             const float inv = __frcp_rn(__int2float_rn(n_chunks));
             for (int t = warp; t < n_chunks * n_seg; t += kMsWarps) {
-                const int seg = ms_div(t, inv), c = (t - seg * n_chunks) * 32 + lane;
+                const int seg = ms_div(t, inv), c = (t - seg * n_chunks) * 64 + 2 * lane;
                 if (c < n_cols) {
                     const int k0 = seg * kMsSegGroups, k1 = min(k0 + kMsSegGroups, n_ky);
                     const float *p = T1 + k0 * nrx + c;
                     float *q = I + 4 * k0 * nrx + c;
-                    float t0 = p[0], t1 = p[nrx], t2 = p[2 * nrx];
+                    float2 t0 = *reinterpret_cast<const float2 *>(p), t1 = *reinterpret_cast<const float2 *>(p + nrx);
+                    float2 t2 = *reinterpret_cast<const float2 *>(p + 2 * nrx);
                     p += 3 * nrx;
                     for (int k = k0; k < k1; k++) {
-                        const float t3 = *p;
-                        q[0] = vsum4(t0, t1, t2, t3, tw[0]);
-                        q[nrx] = vsum4(t0, t1, t2, t3, tw[1]);
-                        q[2 * nrx] = vsum4(t0, t1, t2, t3, tw[2]);
-                        q[3 * nrx] = vsum4(t0, t1, t2, t3, tw[3]);
+                        const float2 t3 = *reinterpret_cast<const float2 *>(p);
+#pragma unroll
+                        for (int ph = 0; ph < 4; ph++)
+                            *reinterpret_cast<float2 *>(q + ph * nrx) =
+                                vsum4x2(t0, t1, t2, t3, dup2(tw[ph][0]), dup2(tw[ph][1]), dup2(tw[ph][2]), dup2(tw[ph][3]), one2);
                         t0 = t1, t1 = t2, t2 = t3;
                         p += nrx;
                         q += 4 * nrx;
@@ -232,7 +258,7 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             }
         }
         __syncthreads();
-        // ---- D: second resize, horizontal pass: rows ry_lo .. ry_hi of I -> T2[n_ry][64] ----
+        // ---- D: second resize, horizontal pass: rows ry_lo .. ry_hi of I -> T2[n_ry][64]; the pairs are two rows ----
         {
             const int c = (warp & 1) * 32 + lane, blk = warp >> 1;
             const int rb = (n_ry + kMsWarps / 2 - 1) / (kMsWarps / 2);
@@ -240,34 +266,50 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             if (c < nX) {
                 const int4 xi = x_idx[c];
                 const float4 xw4 = x_w[c];
-                const float wv[4] = {xw4.x, xw4.y, xw4.z, xw4.w};
+                const float2 w0 = dup2(xw4.x), w1 = dup2(xw4.y), w2 = dup2(xw4.z), w3 = dup2(xw4.w);
                 const float *row = I + (ry_lo - cy0 + r0) * nrx - cx0;
                 const float *p0 = row + xi.x, *p1 = row + xi.y, *p2 = row + xi.z, *p3 = row + xi.w;
                 float *dst = T2 + r0 * kMsTileX + c;
-#pragma unroll 4
-                for (int r = r0; r < r1; r++) {
+                int r = r0;
+#pragma unroll 2
+                for (; r + 1 < r1; r += 2) {
+                    const float2 v = hsum4x2(make_float2(p0[0], p0[nrx]), make_float2(p1[0], p1[nrx]), make_float2(p2[0], p2[nrx]),
+                                             make_float2(p3[0], p3[nrx]), w0, w1, w2, w3, one2);
+                    dst[0] = v.x;
+                    dst[kMsTileX] = v.y;
+                    p0 += 2 * nrx, p1 += 2 * nrx, p2 += 2 * nrx, p3 += 2 * nrx;
+                    dst += 2 * kMsTileX;
+                }
+                if (r < r1) {
+                    const float wv[4] = {xw4.x, xw4.y, xw4.z, xw4.w};
                     *dst = hsum4(*p0, *p1, *p2, *p3, wv);
-                    p0 += nrx, p1 += nrx, p2 += nrx, p3 += nrx;
-                    dst += kMsTileX;
                 }
             }
         }
         __syncthreads();
-        // ---- E: second resize, vertical pass, /n_scales in float32, accumulate in float64 (l.280-281) ----
+        // ---- E: second resize, vertical pass, /n_scales in float32, accumulate in float64 (l.280-281);
+        //         the pairs are two adjacent columns ----
         if (e_col < nX) {
-            const float *col = T2 + e_col - ry_lo * kMsTileX;
+            const char *col = reinterpret_cast<const char *>(T2 + e_col) - ry_lo * (kMsTileX * (int)sizeof(float));
 #pragma unroll
-            for (int k = 0; k < kMsRowsPerThread; k++) {
+            for (int k = 0; k < kMsRowsPerWarp; k++) {
                 const int r = e_row0 + k;
                 if (r < nY) {
                     const int4 yi = y_idx[r];
-                    const float4 yw4 = y_w[r];
-                    const float yw[4] = {yw4.x, yw4.y, yw4.z, yw4.w};
-                    const float s0 = col[yi.x], s1 = col[yi.y], s2 = col[yi.z], s3 = col[yi.w];
-                    float v;
-                    if (e_all_vec) v = vsum4(s0, s1, s2, s3, yw);
-                    else v = e_vec ? vsum4(s0, s1, s2, s3, yw) : vsum4_tail(s0, s1, s2, s3, yw);
-                    acc[k] = __dadd_rn(acc[k], (double)(n_pow2 ? __fmul_rn(v, inv_scales) : __fdiv_rn(v, n_scales_f)));
+                    const float4 wa = y_w[r][0], wb = y_w[r][1];
+                    const float2 s0 = *reinterpret_cast<const float2 *>(col + yi.x), s1 = *reinterpret_cast<const float2 *>(col + yi.y);
+                    const float2 s2 = *reinterpret_cast<const float2 *>(col + yi.z), s3 = *reinterpret_cast<const float2 *>(col + yi.w);
+                    float2 v = vsum4x2(s0, s1, s2, s3, make_float2(wa.x, wa.y), make_float2(wa.z, wa.w), make_float2(wb.x, wb.y),
+                                       make_float2(wb.z, wb.w), one2);
+                    if (!e_all_vec) {  // the scalar tail of a destination row sums left to right
+                        const float yw[4] = {wa.x, wa.z, wb.x, wb.z};
+                        if (!e_vec0) v.x = vsum4_tail(s0.x, s1.x, s2.x, s3.x, yw);
+                        if (!e_vec1) v.y = vsum4_tail(s0.y, s1.y, s2.y, s3.y, yw);
+                    }
+                    if (POW2) v = __fmul2_rn(v, inv_scales2);
+                    else v = make_float2(__fdiv_rn(v.x, n_scales_f), __fdiv_rn(v.y, n_scales_f));
+                    acc[k][0] = __dadd_rn(acc[k][0], (double)v.x);
+                    acc[k][1] = __dadd_rn(acc[k][1], (double)v.y);
                 }
             }
         }
@@ -278,13 +320,23 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
         float *h32 = (a.heat32 && chan >= kLimbs && chan < kLimbs + kParts)
                          ? a.heat32 + ((size_t)img * kParts + (chan - kLimbs)) * (size_t)a.H * a.W
                          : nullptr;
+        const bool two = e_col + 1 < nX, wide = two && ((a.W & 1) == 0);  // X0 and e_col are even: 16-byte aligned pairs
 #pragma unroll
-        for (int k = 0; k < kMsRowsPerThread; k++) {
+        for (int k = 0; k < kMsRowsPerWarp; k++) {
             const int r = e_row0 + k;
             if (r < nY) {
                 const size_t o = (size_t)(Y0 + r) * a.W + (X0 + e_col);
-                out[o] = acc[k];
-                if (h32) h32[o] = __double2float_rn(acc[k]);
+                if (wide) {
+                    *reinterpret_cast<double2 *>(out + o) = make_double2(acc[k][0], acc[k][1]);
+                    if (h32) *reinterpret_cast<float2 *>(h32 + o) = make_float2(__double2float_rn(acc[k][0]), __double2float_rn(acc[k][1]));
+                } else {
+                    out[o] = acc[k][0];
+                    if (two) out[o + 1] = acc[k][1];
+                    if (h32) {
+                        h32[o] = __double2float_rn(acc[k][0]);
+                        if (two) h32[o + 1] = __double2float_rn(acc[k][1]);
+                    }
+                }
             }
         }
     }
