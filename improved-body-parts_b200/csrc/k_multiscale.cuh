@@ -23,7 +23,7 @@
 namespace ibp {
 
 constexpr int kMsMaxScales = 8;
-constexpr int kMsTileX = 64, kMsTileY = 16;
+constexpr int kMsTileX = 64, kMsTileY = 24;
 constexpr int kMsThreads = 256;
 constexpr int kMsWarps = kMsThreads / 32;
 constexpr int kMsRowsPerWarp = kMsTileY / kMsWarps;          // stage E: a warp owns this many rows of the tile
