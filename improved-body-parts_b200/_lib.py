@@ -58,6 +58,12 @@ class BatchView(C.Structure):
                 ("n_humans", C.POINTER(C.c_int32)), ("humans", C.c_void_p), ("status", C.POINTER(C.c_uint32))]
 
 
+class CocoView(C.Structure):
+    _fields_ = [("batch", C.c_int32), ("offsets", C.POINTER(C.c_int32)), ("rows", C.POINTER(C.c_float)),
+                ("status", C.POINTER(C.c_uint32))]
+
+
+COCO_ROW = 52  # 17 x (x, y, v) + score, include/ibp.h IBP_COCO_ROW
 PEAK_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("score", "<f4"), ("part", "<i4")])
 HUMAN_DTYPE = np.dtype([("peak_id", "<i4", (NUM_PARTS,)), ("score", "<f4"), ("total", "<f4"), ("count", "<i4"),
                         ("reach", "<f4")])
@@ -128,6 +134,10 @@ def lib():
     L.ibp_find_humans.argtypes = [vp, C.POINTER(PyParams), ip, vp]
     L.ibp_fetch_people.restype = ip
     L.ibp_fetch_people.argtypes = [vp, ip, vp, ip, vp]
+    L.ibp_fetch_coco.restype = ip
+    L.ibp_fetch_coco.argtypes = [vp, ip, C.POINTER(CocoView), vp]
+    L.ibp_prepare_image.restype = ip
+    L.ibp_prepare_image.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp, vp]
     L.ibp_launch_count.restype = C.c_int64
     L.ibp_launch_count.argtypes = [vp]
     L.ibp_set_profiling.restype = ip
@@ -143,7 +153,7 @@ EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_fuse_multiscale", "ibp_upsample_limbs",
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
            "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
-           "ibp_get_stage_ms"]
+           "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image"]
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
 
@@ -307,6 +317,19 @@ class Handle:
         if n < 0:
             check(n)
         return out[:n].copy()
+
+    def fetch_coco(self, batch, stream=0):
+        """-> list over images of (n, 52) float32 arrays: 17 x (x, y, v) in COCO order + score (evaluate.py:182-209)."""
+        view = CocoView()
+        check(lib().ibp_fetch_coco(self._h, batch, C.byref(view), stream))
+        off = np.ctypeslib.as_array(view.offsets, (batch + 1,)).copy()
+        total = int(off[batch])
+        rows = np.ctypeslib.as_array(view.rows, (total, COCO_ROW)).copy() if total else np.zeros((0, COCO_ROW), np.float32)
+        return [rows[off[b]:off[b + 1]] for b in range(batch)]
+
+    def prepare_image(self, img_ptr, batch, img_h, img_w, max_downsample, pad_value, flip, out_ptr, stream=0):
+        check(lib().ibp_prepare_image(self._h, img_ptr, batch, img_h, img_w, max_downsample, pad_value, 1 if flip else 0,
+                                      out_ptr, stream))
 
     def fetch(self, batch, stream=0, raise_on_overflow=True):
         view = BatchView()

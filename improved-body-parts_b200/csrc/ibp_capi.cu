@@ -11,6 +11,7 @@
 
 #include "ibp_device.cuh"
 #include "k_fuse.cuh"
+#include "k_glue.cuh"
 #include "k_limbs.cuh"
 #include "k_multiscale.cuh"
 #include "k_peaks.cuh"
@@ -133,6 +134,9 @@ struct ibp_handle {
     ibp_human *h_humans = nullptr;
     uint32_t *h_status = nullptr;
     DevPeak *h_peaks_stage = nullptr;  // one image worth of per-part lists for ibp_set_peaks
+    // compacted COCO rows (ibp_fetch_coco), allocated on first use
+    int *d_coco_off = nullptr, *h_coco_off = nullptr;
+    float *d_coco_rows = nullptr, *h_coco_rows = nullptr;
     int64_t launches = 0;
     // optional per-kernel timing with events recorded on the launching stream (ibp_set_profiling)
     int profiling = 0;
@@ -220,6 +224,10 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_py_n_people);
     free_host(h->h_n_peaks);
     free_host(h->h_part_count);
+    free_dev(h->d_coco_off);
+    free_dev(h->d_coco_rows);
+    free_host(h->h_coco_off);
+    free_host(h->h_coco_rows);
     free_host(h->h_line);
     free_host(h->h_n_humans);
     free_host(h->h_humans);
@@ -1045,6 +1053,76 @@ int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream) {
     if (any & IBP_ST_STALLED) return fail(IBP_ERR_CUDA, "internal: the grouping of an image never saw all of its limbs finish");
     if (any & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
         return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", any);
+    return IBP_OK;
+}
+
+int ibp_fetch_coco(ibp_handle *h, int batch, ibp_coco_view *view, void *stream) {
+    if (!h || !view) return fail(IBP_ERR_ARG, "ibp_fetch_coco: null argument");
+    if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_fetch_coco: batch %d exceeds limit %d", batch, h->L.max_batch);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t B = h->L.max_batch, cap_rows = B * h->L.max_humans;
+    if (!h->d_coco_off) {
+        CU(cudaMalloc(&h->d_coco_off, (B + 1) * sizeof(int)));
+        CU(cudaMalloc(&h->d_coco_rows, cap_rows * kCocoRow * sizeof(float)));
+        CU(cudaMallocHost(&h->h_coco_off, (B + 1) * sizeof(int)));
+        CU(cudaMallocHost(&h->h_coco_rows, cap_rows * kCocoRow * sizeof(float)));
+    }
+    CocoArgs a;
+    a.n_humans = h->d_n_humans;
+    a.humans = h->d_humans;
+    a.line = h->d_line;
+    a.batch = batch;
+    a.human_stride = h->L.max_humans;
+    a.line_stride = h->line_stride;
+    a.offsets = h->d_coco_off;
+    a.rows = h->d_coco_rows;
+    coco_rows_kernel<<<batch, 128, 0, st>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h->h_coco_off, h->d_coco_off, ((size_t)batch + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_status, h->d_status, (size_t)batch * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const size_t total = (size_t)h->h_coco_off[batch];
+    if (total) {
+        CU(cudaMemcpyAsync(h->h_coco_rows, h->d_coco_rows, total * kCocoRow * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    view->batch = batch;
+    view->offsets = h->h_coco_off;
+    view->rows = h->h_coco_rows;
+    view->status = h->h_status;
+    uint32_t any = 0;
+    for (int b = 0; b < batch; b++) any |= h->h_status[b];
+    if (any & IBP_ST_STALLED) return fail(IBP_ERR_CUDA, "internal: the grouping of an image never saw all of its limbs finish");
+    if (any & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW | IBP_ST_BODY_OVERFLOW | IBP_ST_HUMAN_OVERFLOW))
+        return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", any);
+    return IBP_OK;
+}
+
+int ibp_prepare_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, int max_downsample, int pad_value, int flip,
+                      float *out, void *stream) {
+    if (!h || !img || !out) return fail(IBP_ERR_ARG, "ibp_prepare_image: null argument");
+    if (batch < 1 || img_h < 1 || img_w < 1 || max_downsample < 1) return fail(IBP_ERR_SHAPE, "ibp_prepare_image: bad shape");
+    if (pad_value < 0 || pad_value > 255) return fail(IBP_ERR_ARG, "ibp_prepare_image: pad value %d is not a uint8", pad_value);
+    if (batch > 65535) return fail(IBP_ERR_ARG, "ibp_prepare_image: batch %d too large for one launch", batch);
+    CU(cudaSetDevice(h->device));
+    PrepArgs a;
+    a.img = img;
+    a.out = out;
+    a.batch = batch;
+    a.h = img_h;
+    a.w = img_w;
+    // utils/util.py:59-62 tiles row -2 / column -2 of the image: empty for a one-row / one-column image, which stays unpadded
+    a.hp = img_h == 1 ? 1 : (img_h + max_downsample - 1) / max_downsample * max_downsample;
+    a.wp = img_w == 1 ? 1 : (img_w + max_downsample - 1) / max_downsample * max_downsample;
+    if (a.hp > 65535) return fail(IBP_ERR_SHAPE, "ibp_prepare_image: image too tall (%d rows)", a.hp);
+    a.flip = flip ? 1 : 0;
+    a.pad_value = pad_value;
+    const dim3 grid((a.wp + 255) / 256, a.hp, batch);
+    prepare_image_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
     return IBP_OK;
 }
 

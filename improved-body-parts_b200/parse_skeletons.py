@@ -48,8 +48,9 @@ def pad_right_down_corner(img, stride, pad_value):
 
 
 def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, config=None):
-    """-> (heatmaps (h,w,20), pafs (h,w,30)) float32 HWC, like parse_skeletons.py:28-103.  Image preparation stays
-    on the host exactly as in the reference (scale pinned to 1.0, l.36); the flip average runs on the device."""
+    """-> (heatmaps (h,w,20), pafs (h,w,30)) float32 HWC, like parse_skeletons.py:28-103.  The scale is pinned to 1.0
+    (l.36), so the cv2.resize is a copy unless the image is too big; padding, /255 and the flipped twin (l.54-72) and
+    the flip average (l.80-96) run on the device."""
     import cv2
     scale = 1.0  # parse_skeletons.py:36
     img_h, img_w, _ = image.shape
@@ -57,12 +58,10 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
         scale = min(2600 / img_h, 3800 / img_w)
         print("Input image: '{}' is too big, shrink it!".format(input_image_path))
     img = cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC)
-    padded, _ = pad_right_down_corner(img, model_cfg['max_downsample'], model_cfg['padValue'])
-    x = np.float32(padded / 255)
-    batch = np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0)  # l.69-72
     pp = _processor()
+    batch = pp.prepare_images(img, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)  # l.54-72
     with torch.no_grad():
-        out = model(torch.from_numpy(batch).to(pp.device))
+        out = model(batch)
     if isinstance(out, (list, tuple)):
         out = out[-1][0]  # last stack, scale 0 (l.80)
     fused = pp.fuse_flip(out[None, ...], flip_avg)[0]  # (50,h,w)

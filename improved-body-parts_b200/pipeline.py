@@ -56,6 +56,34 @@ class PostProcessor:
     def __call__(self, net_out, min_img_size):
         return self.fetch(self.enqueue(net_out, min_img_size))
 
+    def fetch_coco(self, batch):
+        """Instead of fetch(): the humans of the batch as COCO rows built on the device (evaluate.py:182-209), one
+        compacted copy.  -> list over images of (n, 52) float32: 17 x (x, y, v) in ORDER_COCO + score."""
+        with torch.cuda.device(self.device):
+            rows = self.handle.fetch_coco(batch, _stream_ptr(self.device))
+        self._keep = None
+        return rows
+
+    def prepare_images(self, images, max_downsample=64, pad_value=128, flip=True):
+        """utils/parse_skeletons.py:52-72 after the resize, on the device: uint8 (B,h,w,3) or (h,w,3) HWC -> float32
+        (B*(2 if flip else 1), hp, wp, 3) CUDA tensor [img0, flip(img0), img1, ...], padded right/down with `pad_value`
+        to multiples of `max_downsample` (utils/util.py:44-65) and divided by 255 like np.float32(img / 255)."""
+        if isinstance(images, np.ndarray):
+            images = torch.from_numpy(np.ascontiguousarray(images))
+        if images.dim() == 3:
+            images = images[None, ...]
+        if images.dtype != torch.uint8 or images.dim() != 4 or images.shape[3] != 3:
+            raise ValueError("images must be uint8 (B, h, w, 3), got %s %s" % (images.dtype, tuple(images.shape)))
+        images = images.to(self.device).contiguous()
+        B, h, w, _ = images.shape
+        hp = h if h == 1 else -(-h // max_downsample) * max_downsample  # util.py:59-62: a dimension of 1 stays unpadded
+        wp = w if w == 1 else -(-w // max_downsample) * max_downsample
+        out = torch.empty((B * (2 if flip else 1), hp, wp, 3), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self.handle.prepare_image(images.data_ptr(), B, h, w, max_downsample, pad_value, flip, out.data_ptr(),
+                                      _stream_ptr(self.device))
+        return out
+
     # ---- stages on tensors (used by the parse_skeletons mirror and by tests) ---------------------------------
     def fuse_flip(self, net_out, flip_avg=True):
         """(B,2,50,h,w) CUDA tensor -> (B,50,h,w) float32 CUDA tensor (K1)."""

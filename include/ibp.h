@@ -202,6 +202,28 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
 int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw,
                           int min_img_size, void *stream);
 int ibp_fetch(ibp_handle *h, int batch, ibp_batch_view *view, void *stream);
+/* Batched result materialisation — evaluate.py:182-209 append_result on the device: every
+ * human of the batch as one row of IBP_COCO_ROW floats, 17 x (x, y, v) in COCO order (ORDER_COCO, evaluate.py:40; v = 1
+ * and the peak's integer position for a found part, zeros otherwise) followed by the human's score (get_score).  Rows
+ * of all images are compacted on the device; the call copies offsets[batch+1] and exactly offsets[batch] rows.
+ * Valid after ibp_postprocess_batch / ibp_assign; host pointers into pinned memory owned by the handle. */
+#define IBP_COCO_ROW 52
+typedef struct ibp_coco_view {
+    int32_t batch;
+    const int32_t *offsets; /* [batch + 1]: rows of image b are rows[offsets[b] .. offsets[b+1]) */
+    const float *rows;      /* [offsets[batch]][IBP_COCO_ROW] */
+    const uint32_t *status; /* [batch] IBP_ST_* bits */
+} ibp_coco_view;
+int ibp_fetch_coco(ibp_handle *h, int batch, ibp_coco_view *view, void *stream);
+
+/* Image preparation — utils/parse_skeletons.py:52-72 after the cv2.resize: pad right/down to a
+ * multiple of `max_downsample` with `pad_value` (utils/util.py:44-65 padRightDownCorner), np.float32(img / 255), and the
+ * horizontally flipped twin.  DEVICE pointers: img (batch,h,w,3) uint8 HWC; out (batch, flip ? 2 : 1, hp, wp, 3) float32
+ * HWC with hp, wp = h, w rounded up to the multiple (a dimension of 1 stays 1: util.py:59-62 tiles an empty slice there)
+ * — the (2*batch, hp, wp, 3) tensor the model is called on (l.72). */
+int ibp_prepare_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, int max_downsample,
+                      int pad_value, int flip, float *out, void *stream);
+
 /* Sub-pixel coordinates of the IBP_PEAKS_BOX_CENTROID flavour (utils/util.py:188-213 returns float64 x, y): after
  * ibp_fetch, copies image `image`'s (x, y) pairs in peak-id order into host_xy[capacity][2].  Returns the number of
  * peaks written (>= 0) or a negative error code. */

@@ -397,3 +397,43 @@ def find_humans(connected_limbs, special_limb, joint_list, len_rate=16, connecti
     keep = [p for p in people if not (p[19, 0] < 2 or p[18, 0] / p[19, 0] < 0.45)]         # l.591-596
     assoc = np.array(keep, dtype=np.float64).reshape(-1, 20, 2)
     return assoc, cand
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Image preparation — utils/parse_skeletons.py:52-72 (after the resize), utils/util.py:44-65
+# ----------------------------------------------------------------------------------------------------------
+def prepare_input(image, max_downsample=64, pad_value=128, flip=True):
+    """uint8 (h,w,3) -> float32 (2 or 1, hp, wp, 3): the tensor the model is called on (l.72).
+
+    padRightDownCorner pads below and to the right with `img*0 + padValue` (uint8), l.59 divides by 255 in float64
+    and rounds once to float32, l.69-70 mirrors the PADDED image (the pad ends up on the left of the twin)."""
+    h, w = image.shape[:2]
+    ph = 0 if h % max_downsample == 0 else max_downsample - h % max_downsample
+    pw = 0 if w % max_downsample == 0 else max_downsample - w % max_downsample
+    if h == 1:
+        ph = 0  # util.py:59 tiles img[-2:-1], which is empty for a one-row image: nothing is appended
+    if w == 1:
+        pw = 0  # util.py:61 likewise for a one-column image
+    padded = np.full((h + ph, w + pw, image.shape[2]), pad_value, dtype=image.dtype)
+    padded[:h, :w] = image
+    x = f32(padded / 255)
+    if not flip:
+        return x[None, ...]
+    return np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Result rows — evaluate.py:182-209 (append_result, --run_refactor branch)
+# ----------------------------------------------------------------------------------------------------------
+def coco_rows(peak_xy, humans):
+    """peak_xy (N,2) integer peak positions by id; humans = [(ids[18], score)] -> (n, 52) float32: the `keypoints`
+    list (17 x (x, y, v), CMU-18 reordered by ORDER_COCO, v = 1 for a found part, zeros otherwise) then `score`."""
+    rows = np.zeros((len(humans), 17 * 3 + 1), dtype=np.float32)
+    for k, (ids, score) in enumerate(humans):
+        cmu = np.zeros((NUM_KEYPOINTS, 3), dtype=np.float64)
+        for i in range(NUM_KEYPOINTS):
+            if ids[i] >= 0:
+                cmu[i] = (peak_xy[ids[i]][0], peak_xy[ids[i]][1], 1)
+        rows[k, :51] = cmu[ORDER_COCO, :].reshape(51)
+        rows[k, 51] = score
+    return rows
