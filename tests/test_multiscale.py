@@ -88,7 +88,9 @@ def test_gpu_predict_mirror_with_canned_model():
     from improved_body_parts_b200 import parse_skeletons as PS, synth
     from improved_body_parts_b200.config import config_reader
     test_cfg, model_cfg = config_reader()
-    for img_h, img_w, ss in [(333, 427, (0.5, 1.0)), (250, 333, None)]:
+    # (170, 200): three scales = the division by a non-power of two; multiplier 512/170 = 3.01 = the kernel variant with
+    # run-time row strides (wider tiles than the compiled constant)
+    for img_h, img_w, ss in [(333, 427, (0.5, 1.0)), (250, 333, None), (170, 200, (0.4, 0.7, 1.0)), (170, 200, (1.0,))]:
         if ss is None:
             shapes = [(1.0, (img_h, img_w), O.padded_size(img_h, img_w), None)]
         else:

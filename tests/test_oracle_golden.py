@@ -36,7 +36,7 @@ def load_case(path):
     return out, heat, paf, g
 
 
-CASES = sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(p).startswith(("orig_", "ms_", "py_")))
+CASES = sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(p).startswith(("orig_", "ms_", "py_", "prep_", "coco_")))
 
 
 def test_golden_files_present():
