@@ -187,7 +187,8 @@ class Refactored:
         self.last = self.pp.fetch(self.batch)
 
     def h2d(self):
-        return self.host_sets[0].numel() * self.host_sets[0].element_size()
+        # ibp_postprocess_batch uploads the 48 limb + keypoint planes of each half; the 2 background planes stay behind
+        return self.host_sets[0].numel() * self.host_sets[0].element_size() // 50 * 48
 
     def d2h(self):
         L = self.pp.handle.limits

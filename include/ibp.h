@@ -196,7 +196,8 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
 
 /* ---------------------------------------------------------------------------------------------------------------
  * 3. Batched pipeline: everything evaluate.py:75-129 does after the model call, for `batch` images.
- *    net_out (batch,2,50,h,w); on_host != 0 means a HOST pointer (pinned or pageable) that is copied in-stream.
+ *    net_out (batch,2,50,h,w); on_host != 0 means a HOST pointer (pinned or pageable) that is copied in-stream: the 48
+ *    limb + keypoint planes of each half only, the two background planes are never read on this path.
  *    ibp_fetch waits for the stream, copies the packed results to the handle's pinned buffers and fills `view`.
  * ------------------------------------------------------------------------------------------------------------- */
 int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw,
