@@ -116,10 +116,69 @@ __device__ __forceinline__ int ms_div(int i, float inv) { return __float2int_rz(
 //   E  acc                second resize, vertical, /n_scales, float64 accumulate in registers
 // The instruction count per tile is what bounds this kernel (it is issue-bound), so every stage is written to need no
 // division, no clamp and no predicate per element.
+// Stage A in two halves: `ms_feature_loads` issues the global loads of up to kMsPrefetch feature pixels per thread
+// (the upright value and the mirrored twin) into registers, `ms_feature_store` averages and stores them.  Called back
+// to back for the first scale; for the others the loads are issued one scale ahead, before stage C, so that their
+// latency is covered by C, D and E.  (Tiles wider than kMsPrefetch * 256 pixels fetch the rest at store time.)
+constexpr int kMsPrefetch = 3;
+struct MsFeat {
+    int kx_lo, ky_lo, n_fx, n_fy;
+};
+__device__ __forceinline__ MsFeat ms_feat(const int *b) {
+    MsFeat f;
+    f.kx_lo = (b[0] - 2) >> 2;
+    f.ky_lo = (b[2] - 2) >> 2;
+    f.n_fx = ((b[1] - 2) >> 2) - f.kx_lo + 4;
+    f.n_fy = ((b[3] - 2) >> 2) - f.ky_lo + 4;
+    return f;
+}
+__device__ __forceinline__ void ms_planes(const MsScale &S, int img, int chan, const float *&upr, const float *&twin) {
+    const size_t hw = (size_t)S.h * S.w;
+    const float *base = S.src + (size_t)img * 2 * kLayers * hw;
+    upr = base + (size_t)chan * hw;
+    twin = base + (size_t)(kLayers + c_flip_src[chan]) * hw;
+}
+__device__ __forceinline__ void ms_feature_loads(const MsScale &S, const MsFeat &f, int img, int chan, bool flip, float *pu, float *pt) {
+    const float *upr, *twin;
+    ms_planes(S, img, chan, upr, twin);
+    const float inv = __frcp_rn(__int2float_rn(f.n_fx));
+    const int n = f.n_fy * f.n_fx;
+#pragma unroll
+    for (int j = 0; j < kMsPrefetch; j++) {
+        const int i = threadIdx.x + j * kMsThreads;
+        if (i < n) {
+            const int r = ms_div(i, inv), c = i - r * f.n_fx;
+            const int y = clampi(f.ky_lo - 1 + r, 0, S.h - 1), x = clampi(f.kx_lo - 1 + c, 0, S.w - 1);
+            pu[j] = __ldg(upr + y * S.w + x);
+            if (flip) pt[j] = __ldg(twin + y * S.w + (S.w - 1 - x));
+        }
+    }
+}
+__device__ __forceinline__ void ms_feature_store(const MsScale &S, const MsFeat &f, int img, int chan, bool flip, const float *pu, const float *pt,
+                                                 float *F) {
+    const int n = f.n_fy * f.n_fx;
+#pragma unroll
+    for (int j = 0; j < kMsPrefetch; j++) {
+        const int i = threadIdx.x + j * kMsThreads;
+        if (i < n) F[i] = flip ? avg_like_numpy(pu[j], pt[j]) : pu[j];
+    }
+    if (n > kMsPrefetch * kMsThreads) {
+        const float *upr, *twin;
+        ms_planes(S, img, chan, upr, twin);
+        const float inv = __frcp_rn(__int2float_rn(f.n_fx));
+        for (int i = threadIdx.x + kMsPrefetch * kMsThreads; i < n; i += kMsThreads) {
+            const int r = ms_div(i, inv), c = i - r * f.n_fx;
+            const int y = clampi(f.ky_lo - 1 + r, 0, S.h - 1), x = clampi(f.kx_lo - 1 + c, 0, S.w - 1);
+            const float v = __ldg(upr + y * S.w + x);
+            F[i] = flip ? avg_like_numpy(v, __ldg(twin + y * S.w + (S.w - 1 - x))) : v;
+        }
+    }
+}
+
 // STRIDE = row stride of T1 and I as a compile-time constant (row offsets become immediates), 0 = 4 * n_kx at run time.
 // POW2: the number of scales is a power of two, v / n is then v * (1 / n) bit for bit.
 template <int STRIDE, bool POW2>
-__global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
+__global__ void __launch_bounds__(kMsThreads, 4) fuse_multiscale_kernel(MsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int chan = blockIdx.z % kLayers, img = blockIdx.z / kLayers;
@@ -165,6 +224,7 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
     const bool e_vec0 = ((X0 + e_col) * cn + c_local) < n_vec2, e_vec1 = ((X0 + e_col + 1) * cn + c_local) < n_vec2;
     const bool e_all_vec = __all_sync(0xffffffffu, e_vec0 && e_vec1);
 
+    float pu[kMsPrefetch], pt[kMsPrefetch];  // feature pixels in flight (stage A)
     for (int s = 0; s < a.n_scales; s++) {
         const MsScale S = a.sc[s];
         __syncthreads();  // bounds written (first pass); previous scale's T2 and tap tables no longer read
@@ -199,19 +259,11 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             }
         }
         // ---- A: feature tile, flip average on the way in (l.232-248); the replicate border of the first resize is
-        //         materialised here so that B and C index without clamps ----
+        //         materialised here so that B and C index without clamps.  The loads were issued a scale ago. ----
         {
-            const size_t hw = (size_t)S.h * S.w;
-            const float *base = S.src + (size_t)img * 2 * kLayers * hw;
-            const float *upr = base + (size_t)chan * hw;
-            const float *twin = base + (size_t)(kLayers + c_flip_src[chan]) * hw;
-            const float inv = __frcp_rn(__int2float_rn(n_fx));
-            for (int i = tid; i < n_fy * n_fx; i += kMsThreads) {
-                const int r = ms_div(i, inv), c = i - r * n_fx;
-                const int y = clampi(ky_lo - 1 + r, 0, S.h - 1), x = clampi(kx_lo - 1 + c, 0, S.w - 1);
-                const float v = __ldg(upr + y * S.w + x);
-                F[i] = a.flip ? avg_like_numpy(v, __ldg(twin + y * S.w + (S.w - 1 - x))) : v;
-            }
+            const MsFeat f = ms_feat(s_bounds[s]);
+            if (s == 0) ms_feature_loads(S, f, img, chan, a.flip != 0, pu, pt);
+            ms_feature_store(S, f, img, chan, a.flip != 0, pu, pt, F);
         }
         __syncthreads();
         // ---- B: first resize, horizontal pass; the pairs are phases (0,1) and (2,3) of one group ----
@@ -229,6 +281,7 @@ __global__ void __launch_bounds__(kMsThreads) fuse_multiscale_kernel(MsArgs a) {
             }
         }
         __syncthreads();
+        if (s + 1 < a.n_scales) ms_feature_loads(a.sc[s + 1], ms_feat(s_bounds[s + 1]), img, chan, a.flip != 0, pu, pt);
         // ---- C: first resize, vertical pass (always the vector formula: a row of the x4 image has 4*w*cn elements);
         //         the pairs are two adjacent columns ----
         {
