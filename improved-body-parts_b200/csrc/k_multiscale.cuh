@@ -27,7 +27,6 @@ constexpr int kMsTileX = 64, kMsTileY = 24;
 constexpr int kMsThreads = 256;
 constexpr int kMsWarps = kMsThreads / 32;
 constexpr int kMsRowsPerWarp = kMsTileY / kMsWarps;          // stage E: a warp owns this many rows of the tile
-constexpr int kMsSegGroups = 4;                              // stage C: row groups (of 4 rows) per warp task
 
 struct MsScale {
     const float *src;   // (batch, 2, 50, h, w) network output of this scale
@@ -286,12 +285,16 @@ __global__ void __launch_bounds__(kMsThreads, 4) fuse_multiscale_kernel(MsArgs a
         //         the pairs are two adjacent columns ----
         {
             const int n_cols = 4 * n_kx;
-            const int n_chunks = (n_cols + 63) >> 6, n_seg = (n_ky + kMsSegGroups - 1) / kMsSegGroups;
+            // tasks = (64-column chunk, run of row groups): as many runs per chunk as gives every warp about one task
+            // (8, 4, 2 or 1: a shift, the run length needs no division)
+            const int n_chunks = (n_cols + 63) >> 6;
+            const int run_shift = n_chunks == 1 ? 3 : (n_chunks == 2 ? 2 : (n_chunks <= 4 ? 1 : 0));
+            const int run_len = (n_ky + (1 << run_shift) - 1) >> run_shift;
             const float inv = __frcp_rn(__int2float_rn(n_chunks));
-            for (int t = warp; t < n_chunks * n_seg; t += kMsWarps) {
+            for (int t = warp; t < (n_chunks << run_shift); t += kMsWarps) {
                 const int seg = ms_div(t, inv), c = (t - seg * n_chunks) * 64 + 2 * lane;
-                if (c < n_cols) {
-                    const int k0 = seg * kMsSegGroups, k1 = min(k0 + kMsSegGroups, n_ky);
+                const int k0 = seg * run_len, k1 = min(k0 + run_len, n_ky);
+                if (c < n_cols && k0 < n_ky) {
                     const float *p = T1 + k0 * nrx + c;
                     float *q = I + 4 * k0 * nrx + c;
                     float2 t0 = *reinterpret_cast<const float2 *>(p), t1 = *reinterpret_cast<const float2 *>(p + nrx);
