@@ -353,7 +353,9 @@ def run_ours(args, rank, world, local_rank):
     tfile = os.path.join(ROOT, "profiles", "r1_traffic.json")
     if os.path.exists(tfile):
         t = json.load(open(tfile))
-        if t.get("workload") == args.workload and batch == (64 if args.workload != "configs2" else 32):
+        # keyed by kernel (peaks / index / limbs: configs1 at batch 64; fuse: configs2 at batch 32); per launch, so only
+        # meaningful at the batch size it was captured on
+        if (args.workload, batch) in (("configs1", 64), ("configs2", 32)):
             traffic = t["kernels"]
     dominant = max((k for k in stage_ms if k in algo), key=lambda k: stage_ms[k])
     achieved = algo[dominant] * batch / (stage_ms[dominant] * 1e-3) / 1e9
