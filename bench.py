@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--workload", default="configs1", choices=["configs1", "configs2", "configs3"],
                     help="configs1 (default, the headline): batch 64 of 128x128x50 maps, refactored + C++ route; "
                          "configs2: flip + 4-scale fusion to 640x480, original route; configs3: crowd 40-60 people")
+    ap.add_argument("--depth", type=int, default=3, help="configs1/3: batches in flight (PipelinedPostProcessor lanes); 1 = one "
+                                                         "batch at a time on one stream")
     ap.add_argument("--batch", type=int, default=0, help="images per step and GPU (0 = the workload's default)")
     return ap.parse_args()
 
@@ -149,7 +151,7 @@ class Refactored:
     def __init__(self, args, rank, dev, crowd):
         import torch
         from improved_body_parts_b200 import synth
-        from improved_body_parts_b200.pipeline import PostProcessor
+        from improved_body_parts_b200.pipeline import PipelinedPostProcessor
         self.batch = args.batch or BATCH
         self.crowd = crowd
         people, scale = ((40, 60), (0.2, 0.45)) if crowd else ((1, 10), (0.35, 0.9))
@@ -160,7 +162,13 @@ class Refactored:
         self.host_sets = [torch.from_numpy(b).pin_memory() for b in sets]
         self.dev_sets = [h.to(dev) for h in self.host_sets]
         lim = dict(max_peaks_per_part=256, max_candidates_per_limb=1024, max_bodies=512, max_humans=256) if crowd else {}
-        self.pp = PostProcessor(device=dev.index, max_batch=self.batch, **lim)
+        # `depth` batches in flight, each lane with its own handle and stream (pipeline.PipelinedPostProcessor)
+        self.depth = max(1, getattr(args, "depth", 3))
+        self.pipe = PipelinedPostProcessor(device=dev.index, depth=self.depth, max_batch=self.batch, **lim)
+        self.pp = self.pipe.lanes[0]
+        self.pps = self.pipe.lanes
+        self.dev_obj = dev
+        self.e2e_mode = False
         self.workload = ("configs[3]: crowd stress, synthetic batch %d, 128x128x50 maps, flip twin, %d-%d people/image"
                          if crowd else "configs[1]: synthetic batch %d, 512x512 input, stride-4 128x128x50 maps, flip twin, "
                                        "%d-%d people/image") % (self.batch, people[0], people[1])
@@ -169,22 +177,35 @@ class Refactored:
         self.route = "refactored + C++ (predict_refactor, heatmap_nms, process_paf)"
 
     def step_dev(self, s):
-        self.pp.enqueue(self.dev_sets[s % 2], IMG)
+        self.pipe.submit(self.dev_sets[s % 2], IMG, replace=True)  # kernels only: results of earlier batches are dropped
+
+    def join(self):
+        """End of a timed region: everything in flight has finished (and, end to end, has been read back)."""
+        if self.e2e_mode:
+            self.last = (self.pipe.drain() or [self.last])[-1]
+        self.pipe.synchronize()
+
+    def _step_host(self, sets, s):
+        self.e2e_mode = True
+        if self.pipe.full():
+            self.last = self.pipe.collect()               # packed skeletons of the oldest batch, device -> host
+        self.pipe.submit(sets[s % 2], IMG)                # pinned host -> device inside the timed region
 
     def step_e2e(self, s):
-        self.pp.enqueue(self.host_sets[s % 2], IMG)   # pinned host -> device inside the timed region
-        self.last = self.pp.fetch(self.batch)          # packed skeletons device -> host
+        self._step_host(self.host_sets, s)
 
     def step_e2e_f16(self, s):
         """The same call on float16 network output — what the reference's default amp O1 model hands over
         (parse_skeletons.py:75-80); the flip average is then taken in half precision like numpy does."""
         if not hasattr(self, "host16"):
             self.host16 = [h.half().pin_memory() for h in self.host_sets]
-        self.pp.enqueue(self.host16[s % 2], IMG)
-        self.last = self.pp.fetch(self.batch)
+        self._step_host(self.host16, s)
 
     def finish(self):
-        self.last = self.pp.fetch(self.batch)
+        res = self.pipe.drain()
+        if res:
+            self.last = res[-1]
+        self.e2e_mode = False
 
     def h2d(self):
         # ibp_postprocess_batch uploads the 48 limb + keypoint planes of each half; the 2 background planes stay behind
@@ -299,6 +320,8 @@ def run_ours(args, rank, world, local_rank):
         e0.record()
         for s in range(steps):
             fn(s)
+        if hasattr(wl, "join"):
+            wl.join()
         e1.record()
         torch.cuda.synchronize(dev)
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -311,29 +334,36 @@ def run_ours(args, rank, world, local_rank):
     for s in range(args.warmup):
         wl.step_dev(s)
     wl.finish()
-    launches0 = pp.handle.launches
+    handles = [p.handle for p in getattr(wl, "pps", [pp])]
+    launches0 = sum(h.launches for h in handles)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
     ms = timed(wl.step_dev, args.steps)
-    launches = pp.handle.launches - launches0
+    launches = sum(h.launches for h in handles) - launches0
     wl.finish()
 
     # ---- end to end through the public API with HOST buffers (`e2e`) ----
     for s in range(min(args.warmup, 3)):
         wl.step_e2e(s)
+    wl.finish()  # nothing in flight when the timed region starts; K uploads, K read-backs inside it
     ms_e2e = timed(wl.step_e2e, args.steps)
+    wl.finish()
     ms_e2e16 = None
     if hasattr(wl, "step_e2e_f16"):  # informational: float16 hand-over (the reference's amp default), same public call
         for s in range(3):
             wl.step_e2e_f16(s)
+        wl.finish()
         ms_e2e16 = timed(wl.step_e2e_f16, args.steps)
+        wl.finish()
 
     # ---- per-kernel device times for the roofline (events on the launching stream inside the library) ----
+    # per-kernel times: one batch at a time on the first lane
+    step_one = (lambda s: pp.enqueue(wl.dev_sets[s % 2], IMG)) if hasattr(wl, "pipe") else wl.step_dev
     pp.handle.set_profiling(True)
     acc = {}
     for s in range(args.steps):
-        wl.step_dev(s)
+        step_one(s)
         for k, v in pp.handle.stage_ms().items():
             acc.setdefault(k, []).append(v)
     pp.handle.set_profiling(False)
@@ -364,7 +394,8 @@ def run_ours(args, rank, world, local_rank):
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f64" if args.workload == "configs2" else "f32", "data": "synthetic",
            "config": {"workload": wl.workload, "route": wl.route, "batch_per_gpu": batch, "global_batch": world * batch,
-                      "parallelism": "images sharded, %d rank(s), no collective" % world, "l2_policy": wl.l2},
+                      "parallelism": "images sharded, %d rank(s), no collective" % world, "l2_policy": wl.l2,
+                      **({"batches_in_flight": wl.depth} if hasattr(wl, "depth") else {})},
            "e2e": {"value": world * batch * args.steps / (ms_e2e * 1e-3), "unit": UNIT,
                    "h2d_bytes_per_step": world * wl.h2d(), "d2h_bytes_per_step": world * wl.d2h(),
                    **({"note": wl.e2e_note} if hasattr(wl, "e2e_note") else {})},

@@ -185,6 +185,74 @@ class PostProcessor:
 
 
 # ---- result conversions ------------------------------------------------------------------------------------------
+class PipelinedPostProcessor:
+    """Several batches in flight on one GPU.  The limb kernel is a latency chain with a long, thin tail (the grouping
+    of the last images) and the peak kernel a bandwidth kernel: with `depth` independent PostProcessors — each with its
+    own handle (scratch, result buffers) and its own CUDA stream — the tail of one batch runs under the head of the
+    next, and with host inputs the upload of a batch runs under the kernels and the read-back of the previous ones.
+    Batches are independent, results come back in submission order.
+
+        pipe = PipelinedPostProcessor(device=0, depth=3, max_batch=64)
+        for net_out in stream_of_batches:
+            pipe.submit(net_out, img_h)
+            if pipe.full():
+                handle_result(pipe.collect())
+        for res in pipe.drain():
+            handle_result(res)
+    """
+
+    def __init__(self, device=0, depth=3, max_batch=64, max_feat=(128, 128), **limit_overrides):
+        if depth < 1:
+            raise ValueError("depth must be >= 1")
+        self.lanes = [PostProcessor(device, max_batch, max_feat, **limit_overrides) for _ in range(depth)]
+        self.device = self.lanes[0].device
+        self.streams = [torch.cuda.Stream(self.device) for _ in range(depth)]
+        self.depth = depth
+        self._pending = []  # [(lane, batch size)] oldest first
+        self._next = 0
+
+    def full(self):
+        return len(self._pending) == self.depth
+
+    def submit(self, net_out, min_img_size, replace=False):
+        """Launch a batch on the next lane (its stream first waits for the caller's current stream, where `net_out` was
+        produced).  A lane whose previous result was not collected refuses, unless `replace` drops that result."""
+        k = self._next
+        busy = [i for i, (lane, _) in enumerate(self._pending) if lane == k]
+        if busy:
+            if not replace:
+                raise RuntimeError("every lane holds an uncollected batch: collect() before submitting more")
+            del self._pending[busy[0]]
+        st = self.streams[k]
+        st.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(st):
+            B = self.lanes[k].enqueue(net_out, min_img_size)
+        self._pending.append((k, B))
+        self._next = (k + 1) % self.depth
+        return B
+
+    def collect(self, coco=False):
+        """Result of the oldest batch in flight (waits for that lane's stream only): a BatchResult, or with coco=True the
+        COCO rows built on the device (PostProcessor.fetch_coco)."""
+        if not self._pending:
+            raise RuntimeError("nothing in flight")
+        k, B = self._pending.pop(0)
+        with torch.cuda.stream(self.streams[k]):
+            return self.lanes[k].fetch_coco(B) if coco else self.lanes[k].fetch(B)
+
+    def drain(self, coco=False):
+        return [self.collect(coco) for _ in range(len(self._pending))]
+
+    def synchronize(self):
+        """The caller's current stream waits for everything in flight (results stay collectable)."""
+        for st in self.streams:
+            torch.cuda.current_stream(self.device).wait_stream(st)
+
+    @property
+    def launches(self):
+        return sum(lane.handle.launches for lane in self.lanes)
+
+
 def to_humans(result):
     """BatchResult -> list (per image) of [Human] exactly as evaluate.py:111-129 builds them."""
     return [humans_from_result(result.peaks[b], result.humans[b]) for b in range(result.batch)]
