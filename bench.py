@@ -425,7 +425,7 @@ def run_ours(args, rank, world, local_rank):
            "gpu_launches": int(launches),
            "clocks": clocks,
            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic_bytes,
+                        "frac": achieved / peak, "frac_of_nominal_8000": achieved / 8000.0, "traffic": traffic_bytes,
                         # the limb kernel stages only the rows its samples can touch: what it really moves per second
                         "achieved_on_traffic": (traffic_bytes / (stage_ms[dominant] * 1e-3) / 1e9) if traffic_bytes else None, "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": algo[dominant] * batch},
