@@ -223,10 +223,14 @@ class PipelinedPostProcessor:
             if not replace:
                 raise RuntimeError("every lane holds an uncollected batch: collect() before submitting more")
             del self._pending[busy[0]]
+        if isinstance(net_out, np.ndarray):
+            net_out = torch.from_numpy(net_out)
         st = self.streams[k]
         st.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(st):
             B = self.lanes[k].enqueue(net_out, min_img_size)
+        if net_out.is_cuda:
+            net_out.record_stream(st)  # the caller may drop its reference before the lane has read the tensor
         self._pending.append((k, B))
         self._next = (k + 1) % self.depth
         return B
