@@ -168,3 +168,22 @@ def test_gather_world_size_2_gloo(tmp_path):
                          capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout + res.stderr
     assert res.stdout.count("ok") == 2
+
+
+def test_no_contracted_packed_multiply_add():
+    """ptxas contracts a packed float32x2 multiply feeding a packed add into ONE FFMA2 (a single
+    rounding), which would break parity with OpenCV's separate multiply and add.  The kernels therefore issue every
+    packed add as fma(x, one, y) with `one` a run-time 1.0f, which shows in the SASS as a scalar uniform-register
+    multiplier (URn.F32) — any other FFMA2 would be a fused multiply-add that slipped in."""
+    import re
+    import shutil
+    import subprocess
+    from improved_body_parts_b200 import _lib
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(tool) or not os.path.exists(_lib.LIB_PATH):
+        pytest.skip("cuobjdump or the library is not available")
+    sass = subprocess.run([tool, "-sass", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    packed = re.findall(r"\bFFMA2\s+([^;]*);", sass)
+    assert len(packed) > 50, "the multi-scale kernel is expected to use packed float32x2 arithmetic"
+    bad = [p for p in packed if not re.match(r"R\d+, R\d+(\.reuse)?\.F32x2\.HI_LO, UR\d+\.F32, R\d+(\.reuse)?\.F32x2\.HI_LO\s*$", p.strip())]
+    assert not bad, "fused packed multiply-add in the library: %s" % bad[:3]
