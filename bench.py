@@ -433,7 +433,7 @@ def run_ours(args, rank, world, local_rank):
            "stage_gbs": {k: algo[k] * batch / (stage_ms[k] * 1e-3) / 1e9 for k in stage_ms if k in algo},
            "whole_step_gbs": sum(algo.values()) * batch / (ms / args.steps * 1e-3) / 1e9,
            "humans_last_batch": wl.humans()}
-    if not args.no_cpu_baseline and hasattr(wl, "cpu_sample"):
+    if not args.no_cpu_baseline and hasattr(wl, "cpu_sample") and world == 1:  # rank 0 at N = 1 only
         out["cpu_baseline"] = cpu_baseline(args.cpu_sample or max(8, 8 * (os.cpu_count() or 1)), wl)
     return out
 
