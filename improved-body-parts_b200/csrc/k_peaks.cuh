@@ -837,7 +837,7 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
 // ranks its image among the batch by number of peaks (heaviest first, ties by index), which is the order the limb
 // kernel walks the images in.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int kGroupLag = 8;  // images between the limbs of an image and its grouping in the streaming limb kernel's queue
+constexpr int kGroupLag = 16;  // images between the limbs of an image and its grouping in the streaming limb kernel's queue
 
 struct IndexArgs {
     const int *band_count;  // (batch, 18, nbands)
