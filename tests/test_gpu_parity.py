@@ -185,3 +185,38 @@ def test_streaming_kernels_other_map_sizes(oracle, h, w):
         assert res.n_humans[b] == len(want)
         for rec, (ids, score) in zip(res.humans[b], want):
             assert np.array_equal(rec["peak_id"], ids) and rec["score"] == score
+
+
+def test_bench_workload_exact(oracle):
+    """The batch bench.py times (BASELINE.json configs[1], seeds 2000.., default limits, three batches in flight): every
+    image's peaks and skeletons equal the oracle's; with the unmodified reference library present, its getters as well."""
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PipelinedPostProcessor
+    from oracle import np_oracle as O
+    from oracle.cpu_lib import Reference, reference_available
+    n = 24
+    batch = synth.make_batch(2000, n, people=(1, 10), height=512, width=512)
+    pipe = PipelinedPostProcessor(device=0, depth=3, max_batch=n)
+    for _ in range(3):
+        pipe.submit(batch, 512)
+    results = pipe.drain()
+    ref = Reference() if reference_available() else None
+    total = 0
+    for b in range(n):
+        _, paf, _, jl, humans = _oracle_image(oracle, batch[b])
+        for res in results:
+            assert res.n_peaks[b] == jl.shape[0]
+            assert np.array_equal(res.peaks[b]["x"], jl[:, 0].astype(np.int32))
+            assert np.array_equal(res.peaks[b]["y"], jl[:, 1].astype(np.int32))
+            assert np.array_equal(res.peaks[b]["score"], jl[:, 2])
+            assert res.n_humans[b] == len(humans)
+            for rec, (ids, score) in zip(res.humans[b], humans):
+                assert np.array_equal(rec["peak_id"], ids) and rec["score"] == score
+        if ref is not None and b < 8 and jl.shape[0]:
+            ref.process_paf(jl[None], O.limb_upsample(paf, 4), 512)
+            assert ref.get_num_humans() == len(humans)
+            for k, (ids, score) in enumerate(humans):
+                assert [ref.get_part_peak_id(k, p) for p in range(18)] == list(ids)
+                assert np.float32(ref.get_score(k)) == np.float32(score)
+        total += len(humans)
+    assert total > n  # the workload has people in it
