@@ -130,3 +130,26 @@ def test_gpu_original_route_device_resident():
         assert np.array_equal(got[b][0][:, :2], table[:, :2]) and np.array_equal(got[b][0][:, 2], table[:, 2])
         assert np.array_equal(got[b][2], assoc)
         assert assoc.shape[0] >= 1
+
+
+@pytest.mark.gpu
+def test_gpu_bench_workload_configs2_exact():
+    """One image of the workload bench.py --workload configs2 times (640x480, flip + 4 scales, seed 2001): the
+    four-kernel original route against the oracle, end to end."""
+    import torch
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    img_h, img_w, ss = 480, 640, (0.5, 1.0, 1.5, 2.0)
+    shapes = synth.multiscale_shapes(img_h, img_w, ss)
+    outs = synth.make_multiscale_output(2001, 4, img_h, img_w, ss)[0]
+    pp = PostProcessor(device=0, max_batch=1)
+    ts = [torch.from_numpy(o[None]).cuda() for o in outs]
+    table_g, counts_g, assoc_g = pp.original_route(ts, [s[1] for s in shapes], img_h, img_w)[0]
+    heat, paf = O.predict_fuse(outs, img_h, img_w, [s[0] for s in shapes])
+    peaks = O.find_peaks(heat, 0.1, 2)
+    table, counts = O.peaks_table(peaks)
+    cl, sp = O.find_connections(peaks, paf, img_h)
+    assoc, _ = O.find_humans(cl, sp, peaks)
+    assert table.shape[0] > 10 and assoc.shape[0] >= 1
+    assert np.array_equal(counts_g, counts) and np.array_equal(table_g[:, :3], table[:, :3])
+    assert np.array_equal(assoc_g, assoc)
