@@ -17,7 +17,7 @@ ERR_NAMES = {-1: "IBP_ERR_SHAPE", -2: "IBP_ERR_PART", -3: "IBP_ERR_CAPACITY", -4
              -6: "IBP_ERR_NO_DEVICE"}
 IBP_F32, IBP_F16 = 0, 1
 LIMB_FULLRES_HWC, LIMB_FEAT_PLANAR = 0, 1
-PEAKS_CROSS_REFINE, PEAKS_BOX_CENTROID = 0, 1
+PEAKS_CROSS_REFINE, PEAKS_BOX_CENTROID, PEAKS_CROSS_RAW = 0, 1, 2
 ST_PEAK_OVERFLOW, ST_CAND_OVERFLOW, ST_BODY_OVERFLOW, ST_HUMAN_OVERFLOW = 0x1, 0x2, 0x4, 0x8
 ST_TIE_EMULATED, ST_TIE_UNDEFINED = 0x10, 0x20
 

@@ -2,11 +2,15 @@
 // seven-call protocol of the reference's pafprocess module, and the batched pipeline.
 // Host-side only: buffers, launch geometry, error reporting.  No compute happens on the CPU.
 #include <algorithm>
+#include <atomic>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "ibp_device.cuh"
@@ -146,12 +150,15 @@ struct ibp_handle {
 
 namespace {
 
-int ensure_stage(ibp_handle *h, size_t bytes) {
+// `st` is the stream the caller is about to copy into the buffer on: the zero fill is ordered on that same stream (a
+// plain cudaMemset runs on the legacy default stream, which a cudaStreamNonBlocking stream never waits for)
+int ensure_stage(ibp_handle *h, size_t bytes, cudaStream_t st) {
     if (h->stage_bytes >= bytes) return IBP_OK;
+    if (h->d_stage) CU(cudaDeviceSynchronize());  // a regrow: nothing in flight may still read the old buffer
     free_dev(h->d_stage);
     h->stage_bytes = 0;
     CU(cudaMalloc(&h->d_stage, bytes));
-    CU(cudaMemset(h->d_stage, 0, bytes));  // planes that are never uploaded (the background channels) stay zero
+    CU(cudaMemsetAsync(h->d_stage, 0, bytes, st));  // planes that are never uploaded (the background channels) stay zero
     h->stage_bytes = bytes;
     return IBP_OK;
 }
@@ -181,6 +188,7 @@ int ensure_py(ibp_handle *h) {
     CU(cudaMemset(h->d_py_n_people, 0, B * sizeof(int)));
     CU(cudaFuncSetAttribute(py_connections_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
     CU(cudaFuncSetAttribute(py_humans_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+    CU(cudaDeviceSynchronize());  // the fills above ran on the legacy stream: done before any user stream touches the buffers
     return IBP_OK;
 }
 int ensure_fused(ibp_handle *h, size_t floats) {
@@ -405,13 +413,16 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMalloc(&h->d_n_peaks, B * sizeof(int)));
         CU(cudaMalloc(&h->d_humans, B * h->L.max_humans * sizeof(ibp_human)));
         CU(cudaMalloc(&h->d_n_humans, B * sizeof(int)));
-        CU(cudaMalloc(&h->d_status, 2 * B * sizeof(uint32_t)));  // status words, then the per-image raw peak counts
+        // status words, then the per-image raw peak counts, then the streaming limb kernel's image tickets: one region,
+        // zeroed by ONE memset at the start of every pipeline launch (a ticket left behind by a stalled launch cannot
+        // reach the next one)
+        CU(cudaMalloc(&h->d_status, 3 * B * sizeof(uint32_t)));
         h->d_n_raw = reinterpret_cast<int *>(h->d_status + B);
         CU(cudaMemset(h->d_part_count, 0, B * kParts * sizeof(int)));
         CU(cudaMemset(h->d_link_count, 0, B * kLimbs * sizeof(int)));
         CU(cudaMemset(h->d_n_peaks, 0, B * sizeof(int)));
         CU(cudaMemset(h->d_n_humans, 0, B * sizeof(int)));
-        CU(cudaMemset(h->d_status, 0, 2 * B * sizeof(uint32_t)));
+        CU(cudaMemset(h->d_status, 0, 3 * B * sizeof(uint32_t)));
         CU(cudaMalloc(&h->d_ticket, (2 * B + 1) * sizeof(unsigned)));
         CU(cudaMemset(h->d_ticket, 0, (2 * B + 1) * sizeof(unsigned)));
         CU(cudaMalloc(&h->d_order, B * sizeof(int)));
@@ -457,6 +468,9 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
             return fail(IBP_ERR_ARG, "limits need %zu B of shared memory for the limb kernel (max %zu)", limb_phase_bytes(h, 0), kMaxDynSmem);
         if (group_phase_bytes(h) > kMaxDynSmem)
             return fail(IBP_ERR_ARG, "max_bodies=%d needs %zu B of shared memory (max %zu)", h->L.max_bodies, group_phase_bytes(h), kMaxDynSmem);
+        // the fills above ran on the legacy default stream, which a cudaStreamNonBlocking stream (torch's) never waits
+        // for: they are complete before the first launch on any user stream
+        CU(cudaDeviceSynchronize());
         return IBP_OK;
     };
     rc = alloc();
@@ -596,7 +610,10 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     h->defer_bands = 0;
     if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "find_peaks: batch %d exceeds limit %d", batch, h->L.max_batch);
     if (fh < 1 || fw < 1 || fw > 32767 || fh > 32767) return fail(IBP_ERR_SHAPE, "find_peaks: bad shape");
-    if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID) return fail(IBP_ERR_ARG, "find_peaks: flavour %d", flavour);
+    if (flavour != IBP_PEAKS_CROSS_REFINE && flavour != IBP_PEAKS_BOX_CENTROID && flavour != IBP_PEAKS_CROSS_RAW)
+        return fail(IBP_ERR_ARG, "find_peaks: flavour %d", flavour);
+    const int raw = flavour == IBP_PEAKS_CROSS_RAW;
+    if (raw) flavour = IBP_PEAKS_CROSS_REFINE;  // same kernel, the refine step reports the pixel itself
     if (flavour == IBP_PEAKS_BOX_CENTROID && h->P.refine_window != 2)
         return fail(IBP_ERR_ARG, "find_peaks: the centroid flavour supports offset_radius == 2 only");
     PeakArgs a;
@@ -624,6 +641,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.thr = h->P.peak_thresh;
     a.cap = h->L.max_peaks_per_part;
     a.flavour = flavour;
+    a.raw = raw;
     int rc = ensure_bands(h, a.nbands);
     if (rc != IBP_OK) return rc;
     a.band_peaks = h->d_band_peaks;
@@ -666,7 +684,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     size_t scratch = (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
     scratch += (size_t)a.cap * 8;
     scratch = (scratch + 15) & ~(size_t)15;
-    CU(cudaMemsetAsync(h->d_status, 0, (size_t)2 * h->L.max_batch * sizeof(uint32_t), st));  // status + raw counts
+    CU(cudaMemsetAsync(h->d_status, 0, (size_t)3 * h->L.max_batch * sizeof(uint32_t), st));  // status + raw counts + limb tickets
 
     // Streaming kernel: float32 planes whose rows the bulk-copy engine can move (16-byte aligned everywhere).
     const bool twin = twin_base >= 0;
@@ -775,7 +793,16 @@ int ibp_find_peaks(ibp_handle *h, const float *maps, int chan_stride, int first_
     return launch_peaks(h, maps, IBP_F32, (size_t)chan_stride * fh * fw, first_chan, -1, batch, fh, fw, flavour, (cudaStream_t)stream);
 }
 
+namespace {
+int set_peaks_impl(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride, cudaStream_t st, bool wait);
+}
 int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride) {
+    return set_peaks_impl(h, image, host_peaks, n, row_stride, nullptr, true);
+}
+namespace {
+// Copies go out asynchronously on `st` from the handle's pinned mirrors; wait = false leaves them in flight (the caller
+// launches on the same stream and does not touch the mirrors before it has synchronised).
+int set_peaks_impl(ibp_handle *h, int image, const float *host_peaks, int n, int row_stride, cudaStream_t st, bool wait) {
     if (!h || (n > 0 && !host_peaks)) return fail(IBP_ERR_ARG, "ibp_set_peaks: null argument");
     if (image < 0 || image >= h->L.max_batch) return fail(IBP_ERR_ARG, "ibp_set_peaks: image %d out of range", image);
     if (n < 0 || row_stride < 5) return fail(IBP_ERR_SHAPE, "ibp_set_peaks: need rows of >= 5 floats [x,y,score,id,part]");
@@ -812,13 +839,20 @@ int ibp_set_peaks(ibp_handle *h, int image, const float *host_peaks, int n, int 
     h->order_batch = 0;  // the peak kernel's image order no longer describes the lists
     h->defer_bands = 0;
     memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
-    CU(cudaMemcpy(h->d_peaks + (size_t)image * kParts * cap, h->h_peaks_stage, (size_t)kParts * cap * sizeof(DevPeak), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(h->d_part_count + (size_t)image * kParts, counts, sizeof(counts), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(h->d_line + (size_t)image * h->line_stride, line, (size_t)std::max(n, 1) * sizeof(ibp_peak), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(h->d_n_peaks + image, &n, sizeof(int), cudaMemcpyHostToDevice));
-    CU(cudaMemset(h->d_status + image, 0, sizeof(uint32_t)));
+    // per part only the filled entries (a handle grown for one crowd image keeps large per-part strides)
+    for (int p = 0; p < kParts; p++)
+        if (counts[p])
+            CU(cudaMemcpyAsync(h->d_peaks + ((size_t)image * kParts + p) * cap, h->h_peaks_stage + (size_t)p * cap,
+                               (size_t)counts[p] * sizeof(DevPeak), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->d_part_count + (size_t)image * kParts, h->h_part_count + (size_t)image * kParts, sizeof(counts),
+                       cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->d_line + (size_t)image * h->line_stride, line, (size_t)std::max(n, 1) * sizeof(ibp_peak), cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->d_n_peaks + image, h->h_n_peaks + image, sizeof(int), cudaMemcpyHostToDevice, st));
+    CU(cudaMemsetAsync(h->d_status + image, 0, sizeof(uint32_t), st));
+    if (wait) CU(cudaStreamSynchronize(st));
     return IBP_OK;
 }
+}  // namespace
 
 // ------------------------------------------------------------------------------------------------ K3 + K4
 namespace {
@@ -921,11 +955,15 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     static const bool no_lstream = getenv("IBP_LIMBS_NO_STREAM") != nullptr;
     const size_t nonplane = smem - ((plane_bytes + 15) & ~(size_t)15);
     const size_t scratch_tail = (size_t)kPairChunk * sizeof(PairGeo) + (size_t)kPairChunk * a.max_steps * 4;
+    // the twin rows stream through kLimbRing slots carved from the candidate / geometry / sample scratch: a slot must hold
+    // at least one feature row (wider maps take the one-CTA-per-item kernel, whose staging falls back to plain loads)
+    const size_t ring_slot_bytes = ((((size_t)a.cand_cap * 16 + scratch_tail) & ~(size_t)15) / kLimbRing);
     if (a.band_peaks && mode == IBP_LIMB_FEAT_PLANAR && a.stage_plane && dtype == IBP_F32 && twin_base >= 0 && dim1 % 4 == 0 &&
         ((uintptr_t)limb_src & 15u) == 0 && (image_stride * 4) % 16 == 0 && h->L.max_peaks_per_part <= 128 &&
         limb_phase_bytes(h, plane_bytes) >= group_phase_bytes(h) && nonplane >= group_phase_bytes(h) &&
-        scratch_tail >= (size_t)a.cand_cap * 8 && !no_lstream) {
+        scratch_tail >= (size_t)a.cand_cap * 8 && ring_slot_bytes >= (size_t)dim1 * 4 && !no_lstream) {
         a.item_meta = h->d_item_meta;
+        a.ticket = h->d_status + 2 * (size_t)h->L.max_batch;  // zeroed by launch_peaks' memset on this stream
         a.work_counter = h->d_lb_work;
         a.work_base = h->lb_work_base;
         a.plane_bytes = (int)((plane_bytes + 15) & ~(size_t)15);
@@ -985,7 +1023,7 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
     const void *dev_in = net_out;
     if (on_host) {
         const size_t bytes = elems * (dtype == IBP_F16 ? 2 : 4);
-        int rc = ensure_stage(h, bytes);
+        int rc = ensure_stage(h, bytes, st);
         if (rc != IBP_OK) return rc;
         // the path reads the 30 limb and 18 keypoint planes of each half (parse_skeletons.py:137 skips the two background
         // channels): only those cross the bus, 4 % fewer bytes on a copy that is 98 % of the end-to-end step
@@ -1266,9 +1304,13 @@ int ibp_fetch_connections(ibp_handle *h, int image, double *rows, int32_t *count
     CU(cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
     const size_t cap = h->L.max_peaks_per_part;
+    uint32_t status = 0;
     CU(cudaMemcpyAsync(counts, h->d_py_conn_count + (size_t)image * kLimbs, kLimbs * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(rows, h->d_py_conn + (size_t)image * kLimbs * cap * 6, kLimbs * cap * 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&status, h->d_status + image, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
+    if (status & (IBP_ST_PEAK_OVERFLOW | IBP_ST_CAND_OVERFLOW))
+        return fail(IBP_ERR_CAPACITY, "a device buffer overflowed (status bits 0x%x); raise ibp_limits", status);
     return IBP_OK;
 }
 
@@ -1345,6 +1387,120 @@ ibp_handle *g_legacy = nullptr;
 ibp_batch_view g_view;
 bool g_view_valid = false;
 uint32_t g_legacy_status = 0;
+
+// Pageable host memory -> device through pinned slots that several host threads fill in parallel: one thread's memcpy
+// into a pinned buffer (what a pageable cudaMemcpy does inside the driver) runs at 10-12 GB/s, a fraction of the bus.
+// Each worker owns kSlots pinned slots and a stream of its own; chunk c goes to worker c % T.  The consumer stream waits
+// for every worker's last DMA through an event.  Workers are detached and live for the process (the legacy protocol is
+// process-global state anyway, pafprocess.cpp:16-17).
+class HostStager {
+public:
+    static constexpr size_t kChunk = 512 * 1024;
+    static constexpr int kSlots = 3;
+    static HostStager *get(int device) {
+        static std::mutex mu;
+        static HostStager *inst = nullptr;
+        std::lock_guard<std::mutex> lk(mu);
+        if (!inst || inst->device_ != device) {
+            HostStager *s = new HostStager();
+            if (!s->init(device)) return nullptr;  // (leaks a few words on failure; the caller falls back to cudaMemcpy)
+            inst = s;
+        }
+        return inst;
+    }
+    // enqueue the upload of [src, src + bytes) to dst and make `consumer` wait for it
+    bool upload(const char *src, char *dst, size_t bytes, cudaStream_t consumer) {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            src_ = src;
+            dst_ = dst;
+            bytes_ = bytes;
+            pending_ = nthreads_;
+            failed_ = false;
+            gen_++;
+        }
+        cv_.notify_all();
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            done_cv_.wait(lk, [&] { return pending_ == 0; });
+        }
+        if (failed_) return false;
+        for (int t = 0; t < nthreads_; t++)
+            if (cudaStreamWaitEvent(consumer, w_[t].done, 0) != cudaSuccess) return false;
+        return true;
+    }
+
+private:
+    struct Worker {
+        char *slot[kSlots] = {nullptr};
+        cudaEvent_t free_ev[kSlots] = {nullptr};
+        cudaStream_t st = nullptr;
+        cudaEvent_t done = nullptr;
+    };
+    bool init(int device) {
+        device_ = device;
+        unsigned hc = std::thread::hardware_concurrency();
+        nthreads_ = (int)std::max(1u, std::min(4u, hc ? hc : 1u));
+        const char *e = getenv("IBP_STAGER_THREADS");
+        if (e && atoi(e) >= 1) nthreads_ = std::min(atoi(e), 16);
+        w_.resize(nthreads_);
+        if (cudaSetDevice(device) != cudaSuccess) return false;
+        for (auto &w : w_) {
+            if (cudaStreamCreateWithFlags(&w.st, cudaStreamNonBlocking) != cudaSuccess) return false;
+            if (cudaEventCreateWithFlags(&w.done, cudaEventDisableTiming) != cudaSuccess) return false;
+            for (int k = 0; k < kSlots; k++) {
+                if (cudaMallocHost(&w.slot[k], kChunk) != cudaSuccess) return false;
+                if (cudaEventCreateWithFlags(&w.free_ev[k], cudaEventDisableTiming) != cudaSuccess) return false;
+            }
+        }
+        for (int t = 0; t < nthreads_; t++) std::thread([this, t] { run(t); }).detach();
+        return true;
+    }
+    void run(int t) {
+        cudaSetDevice(device_);
+        Worker &w = w_[t];
+        unsigned long long seen = 0;
+        for (;;) {
+            const char *src;
+            char *dst;
+            size_t bytes;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return gen_ != seen; });
+                seen = gen_;
+                src = src_, dst = dst_, bytes = bytes_;
+            }
+            bool ok = true;
+            const size_t nchunks = (bytes + kChunk - 1) / kChunk;
+            int k = 0;
+            for (size_t c = t; c < nchunks && ok; c += nthreads_, k = (k + 1) % kSlots) {
+                const size_t off = c * kChunk, len = std::min(kChunk, bytes - off);
+                ok = cudaEventSynchronize(w.free_ev[k]) == cudaSuccess;  // the slot's previous DMA has left it
+                if (!ok) break;
+                memcpy(w.slot[k], src + off, len);
+                ok = cudaMemcpyAsync(dst + off, w.slot[k], len, cudaMemcpyHostToDevice, w.st) == cudaSuccess &&
+                     cudaEventRecord(w.free_ev[k], w.st) == cudaSuccess;
+            }
+            ok = ok && cudaEventRecord(w.done, w.st) == cudaSuccess;
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (!ok) failed_ = true;
+                pending_--;
+            }
+            done_cv_.notify_all();
+        }
+    }
+    int device_ = -1, nthreads_ = 1;
+    std::vector<Worker> w_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_cv_;
+    unsigned long long gen_ = 0;
+    int pending_ = 0;
+    bool failed_ = false;
+    const char *src_ = nullptr;
+    char *dst_ = nullptr;
+    size_t bytes_ = 0;
+};
 }  // namespace
 
 int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, int f3, const float *pafmap, int min_img_size) {
@@ -1353,12 +1509,17 @@ int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, 
     if (p1 < 0 || p2 < 0 || p3 < 5 || f1 < 1 || f2 < 1 || f3 < kLimbs)
         return fail(IBP_ERR_SHAPE, "process_paf: peaks must be (p1,p2,>=5) and pafmap (H,W,>=30); got (%d,%d,%d) (%d,%d,%d)", p1, p2, p3, f1, f2, f3);
     const int n = p1 * p2;
-    // capacity: grow the process-global handle when a part has more peaks than it can hold
+    // capacity: grow the process-global handle when a part has more peaks than it can hold; y extent of the joint list
     int counts[kParts] = {0};
+    int y_lo = INT_MAX, y_hi = INT_MIN;
     for (int i = 0; i < n; i++) {
-        const int part = (int)peaks[(size_t)i * p3 + 4];
+        const float *r = peaks + (size_t)i * p3;
+        const int part = (int)r[4];
         if (part < 0 || part >= kParts) return fail(IBP_ERR_PART, "joint %d has part id %d outside [0,18)", i, part);
         counts[part]++;
+        const int y = (int)r[1];  // pafprocess.cpp:36
+        y_lo = std::min(y_lo, y);
+        y_hi = std::max(y_hi, y);
     }
     int need = 128;
     for (int p = 0; p < kParts; p++)
@@ -1378,19 +1539,59 @@ int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, 
         if (rc != IBP_OK) return rc;
     }
     ibp_handle *h = g_legacy;
-    int rc = ibp_set_peaks(h, 0, peaks, n, p3);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = nullptr;  // the legacy default stream: ordered after whatever the caller did on it (a CUDA tensor argument)
+    int rc = set_peaks_impl(h, 0, peaks, n, p3, st, false);
     if (rc != IBP_OK) return rc;
-    const size_t bytes = (size_t)f1 * f2 * f3 * sizeof(float);
-    rc = ensure_stage(h, bytes);
-    if (rc != IBP_OK) return rc;
-    CU(cudaMemcpy(h->d_stage, pafmap, bytes, cudaMemcpyHostToDevice));
-    rc = ibp_assign(h, (const float *)h->d_stage, IBP_LIMB_FULLRES_HWC, 1, f1, f2, f3, min_img_size, nullptr);
+
+    // The limb map.  Where does the caller's array live?  Device memory (a CUDA tensor handed through
+    // __cuda_array_interface__): sampled in place.  Host memory: only the image rows between the extreme peaks can be
+    // sampled (every sample lies on the segment between two peaks, pafprocess.cpp:319-320; one spare row either side),
+    // so only those rows cross the bus — pinned memory straight by DMA, pageable memory through the threaded stager.
+    const float *dev_map = nullptr;
+    cudaPointerAttributes attr;
+    memset(&attr, 0, sizeof(attr));
+    if (cudaPointerGetAttributes(&attr, pafmap) != cudaSuccess) {
+        cudaGetLastError();
+        attr.type = cudaMemoryTypeUnregistered;
+    }
+    if (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) {
+        if (attr.type == cudaMemoryTypeDevice && attr.device != h->device)
+            return fail(IBP_ERR_ARG, "process_paf: the limb map lives on device %d, the handle on device %d (IBP_DEVICE)", attr.device, h->device);
+        dev_map = pafmap;
+    } else if (n > 0) {
+        const size_t row_bytes = (size_t)f2 * f3 * sizeof(float);
+        rc = ensure_stage(h, (size_t)f1 * row_bytes, st);
+        if (rc != IBP_OK) return rc;
+        const int r0 = std::max(0, std::min(y_lo, f1 - 1) - 1), r1 = std::min(f1 - 1, std::max(y_hi, 0) + 1);
+        const size_t off = (size_t)r0 * row_bytes, bytes = (size_t)(r1 - r0 + 1) * row_bytes;
+        char *dst = (char *)h->d_stage + off;
+        const char *src = (const char *)pafmap + off;
+        static const bool no_stager = getenv("IBP_NO_STAGER") != nullptr;
+        bool sent = false;
+        if (attr.type == cudaMemoryTypeHost) {  // pinned / registered: the copy engine reads it directly
+            CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+            sent = true;
+        } else if (bytes >= 4 * HostStager::kChunk && !no_stager) {
+            HostStager *stager = HostStager::get(h->device);
+            // the stager's streams do not order after `st`: the zero fill of a fresh staging buffer must be over first
+            if (stager && cudaStreamSynchronize(st) == cudaSuccess) sent = stager->upload(src, dst, bytes, st);
+            if (!sent) cudaGetLastError();
+        }
+        if (!sent) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+        dev_map = (const float *)h->d_stage;
+    } else {
+        rc = ensure_stage(h, 256, st);
+        if (rc != IBP_OK) return rc;
+        dev_map = (const float *)h->d_stage;  // no peaks: nothing is sampled
+    }
+    rc = ibp_assign(h, dev_map, IBP_LIMB_FULLRES_HWC, 1, f1, f2, f3, min_img_size, st);
     if (rc != IBP_OK) return rc;
     // results: humans + status only; the peak list is already on the host (ibp_set_peaks filled h_line)
-    CU(cudaMemcpyAsync(h->h_n_humans, h->d_n_humans, sizeof(int), cudaMemcpyDeviceToHost, 0));
-    CU(cudaMemcpyAsync(h->h_humans, h->d_humans, (size_t)h->L.max_humans * sizeof(ibp_human), cudaMemcpyDeviceToHost, 0));
-    CU(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, 0));
-    CU(cudaStreamSynchronize(0));
+    CU(cudaMemcpyAsync(h->h_n_humans, h->d_n_humans, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_humans, h->d_humans, (size_t)h->L.max_humans * sizeof(ibp_human), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(h->h_status, h->d_status, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
     g_view.batch = 1;
     g_view.peak_stride = h->line_stride;
     g_view.human_stride = h->L.max_humans;

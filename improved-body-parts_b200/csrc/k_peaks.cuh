@@ -44,6 +44,8 @@ struct PeakArgs {
     float thr;
     int cap;              // max peaks per (image, part); also per band
     int flavour;
+    int raw;              // cross flavour only: heatmap_nms(bool_refine_center=False), utils/parse_skeletons.py:163-166 — no patch
+                          // refine: x, y stay the FEATURE-map pixel, score = the raw map value
     DevPeak *band_peaks;  // (batch, 18, nbands, cap) scratch
     double *band_subpix;  // (batch, 18, nbands, cap, 2) scratch, centroid flavour: float64 x, y like the reference
     int *band_count;      // (batch, 18, nbands) scratch
@@ -222,7 +224,17 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
     for (int k = warp; k < n; k += nwarps) {
         const int pix = sorted[k];
         const int py = pix / w, px = pix - py * w;
-        if (FLAVOUR == IBP_PEAKS_CROSS_REFINE && a.up == 4 && a.win == 2 && px >= 2 && px + 2 < w && py >= 2 && py + 2 < h) {
+        if (FLAVOUR == IBP_PEAKS_CROSS_REFINE && a.raw) {
+            if (lane == 0) {
+                DevPeak p;
+                p.x = px;
+                p.y = py;
+                p.score = B.at(py, px);
+                p.id = k;
+                out[k] = p;
+            }
+            __syncwarp();
+        } else if (FLAVOUR == IBP_PEAKS_CROSS_REFINE && a.up == 4 && a.win == 2 && px >= 2 && px + 2 < w && py >= 2 && py + 2 < h) {
             // The common case — a full 5x5 patch up-sampled x4 to 20x20 — entirely in registers: lane X < 20 owns
             // output column X; its five horizontal sums (one per patch row) stay in registers, and the twenty vertical
             // combinations use compile-time row indices and the 4x4 phase table.  Same operations in the same order

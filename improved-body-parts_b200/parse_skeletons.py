@@ -20,11 +20,18 @@ NUM_HEATMAPS = NUM_KEYPOINTS + 2
 NUM_PAFS = 30
 
 _pp = {}
+# capacities of the single-image handles behind the mirrors; doubled on IBP_ERR_CAPACITY (the reference's lists are
+# unbounded, a crowd image must not fail here because the defaults were sized for ten people)
+_GROWTH = [dict(max_peaks_per_part=128, max_candidates_per_limb=1024, max_bodies=128, max_humans=128),
+           dict(max_peaks_per_part=256, max_candidates_per_limb=2048, max_bodies=256, max_humans=256),
+           dict(max_peaks_per_part=512, max_candidates_per_limb=4096, max_bodies=512, max_humans=512),
+           dict(max_peaks_per_part=1024, max_candidates_per_limb=4096, max_bodies=1024, max_humans=1024)]
+_level = [0]
 
 
 def _processor(device=0, upsample=4, peak_thresh=0.1, refine_window=2):
     """One single-image PostProcessor per (device, peak parameters): the constants live in the handle."""
-    key = (device, int(upsample), float(peak_thresh), int(refine_window))
+    key = (device, int(upsample), float(peak_thresh), int(refine_window), _level[0])
     if key not in _pp:
         p = _lib.default_params()
         p.upsample, p.peak_thresh, p.refine_window = key[1], key[2], key[3]
@@ -32,10 +39,28 @@ def _processor(device=0, upsample=4, peak_thresh=0.1, refine_window=2):
         if not torch.cuda.is_available():
             raise _lib.IbpError(-6, "no CUDA device: improved-body-parts_b200 has no CPU fallback")
         pp.device = torch.device("cuda", device)
-        pp.handle = _lib.Handle(device, params=p, max_batch=1, max_feat_h=4096, max_feat_w=4096)
+        pp.handle = _lib.Handle(device, params=p, max_batch=1, **_GROWTH[_level[0]])
         pp.max_batch = 1
         _pp[key] = pp
     return _pp[key]
+
+
+def _growing(fn):
+    """Run fn(); on IBP_ERR_CAPACITY move every mirror to the next capacity level (new handles) and run it again."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        while True:
+            try:
+                return fn(*args, **kwargs)
+            except _lib.IbpError as e:
+                if e.code != -3 or _level[0] + 1 >= len(_GROWTH):
+                    raise
+                for k in [k for k in _pp if k[4] == _level[0]]:
+                    _pp.pop(k).handle.close()
+                _level[0] += 1
+    return wrapper
 
 
 def pad_right_down_corner(img, stride, pad_value):
@@ -69,14 +94,15 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
 
 
+@_growing
 def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
-    """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176)."""
-    if not bool_refine_center:
-        raise NotImplementedError("bool_refine_center=False is not on the reference's path (evaluate.py:76)")
-    pp = _processor(upsample=int(upsample_factor))
+    """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176).
+    bool_refine_center=False (l.163-166): no patch refine — x, y = compute_resized_coords(pixel) = (p + 0.5) * f - 0.5 in
+    float32 (l.122-123), score = the map value at the pixel."""
+    pp = _processor(upsample=max(int(upsample_factor), 1))
     maps = torch.from_numpy(np.ascontiguousarray(heatmaps[:, :, :NUM_KEYPOINTS], dtype=np.float32))
     maps = maps.to(pp.device).permute(2, 0, 1).contiguous()[None, ...]
-    pp.find_peaks(maps, 0)
+    pp.find_peaks(maps, 0, flavour=_lib.PEAKS_CROSS_REFINE if bool_refine_center else _lib.PEAKS_CROSS_RAW)
     res = pp.fetch(1)
     peaks = res.peaks[0]
     out, pos = [], 0
@@ -84,7 +110,12 @@ def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
         n = int(res.part_count[0, part])
         rows = np.zeros((n, 4), dtype=np.float32)
         sel = peaks[pos:pos + n]
-        rows[:, 0], rows[:, 1], rows[:, 2] = sel["x"], sel["y"], sel["score"]
+        if bool_refine_center:
+            rows[:, 0], rows[:, 1] = sel["x"], sel["y"]
+        else:  # l.122-123 on the integer pixel the device reports
+            xy = (np.stack([sel["x"], sel["y"]], axis=1).astype(np.float32) + 0.5) * upsample_factor - 0.5
+            rows[:, 0], rows[:, 1] = xy[:, 0], xy[:, 1]
+        rows[:, 2] = sel["score"]
         rows[:, 3] = np.arange(pos, pos + n)
         out.append(rows)
         pos += n
@@ -98,6 +129,7 @@ def limb_upsample(pafs, upsample_factor=4):
     return pp.upsample_limbs(t[None, ...], int(upsample_factor))[0].cpu().numpy()
 
 
+@_growing
 def find_peaks(heatmap_avg, test_cfg):
     """heatmap_avg (H,W,>=18) -> list of 18 lists of (x, y, score, id) like parse_skeletons.py:286-321: 3x3 NMS with
     `value >= thre1` (utils/util.py:177-185), 5x5 centroid refinement in float64 (utils/util.py:188-213; border peaks
@@ -169,6 +201,7 @@ def _check_pairs(joint2limb_pairs):
         raise ValueError("joint2limb_pairs must be the 30 canonical limbs (config/config.py:114-121)")
 
 
+@_growing
 def find_connections(all_peaks, paf_avg, img_height, test_cfg, joint2limb_pairs=None):
     """-> (connected_limbs, special_limb) like parse_skeletons.py:324-410: connected_limbs[k] is [] when both joint
     lists of limb k are empty (k is listed in special_limb), else an (n,6) float64 array of rows
@@ -196,6 +229,7 @@ def find_connections(all_peaks, paf_avg, img_height, test_cfg, joint2limb_pairs=
     return connected, special
 
 
+@_growing
 def find_humans(connected_limbs, special_limb, joint_list, test_cfg, joint2limb_pairs=None):
     """-> (person_to_joint_assoc (P,20,2) float64, joint_candidates (N,4)) like parse_skeletons.py:413-599."""
     _check_pairs(joint2limb_pairs)

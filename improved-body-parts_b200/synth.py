@@ -134,15 +134,58 @@ def make_network_output(seed, n_people, height=512, width=512, stride=4, noise=0
     return out, joints
 
 
+_shared_out = {}  # arrays in anonymous shared memory, inherited by forked workers (results are written in place, not pickled)
+
+
+def _shared_array(shape):
+    import mmap
+    n = int(np.prod(shape)) * 4
+    return np.frombuffer(mmap.mmap(-1, max(n, 1)), dtype=f32, count=int(np.prod(shape))).reshape(shape)
+
+
+def _pool_run(fn, jobs, workers):
+    """Run fn(job) for every job over forked worker processes (numpy only; call it before CUDA is initialised)."""
+    import multiprocessing as mp
+    import os
+    workers = min(workers or (os.cpu_count() or 1), len(jobs))
+    if workers <= 1:
+        for j in jobs:
+            fn(j)
+        return
+    with mp.get_context("fork").Pool(workers) as pool:
+        pool.map(fn, jobs, chunksize=1)
+
+
+def _batch_image(args):
+    base_seed, i, people, height, width, stride, noise, scale = args
+    rng = np.random.default_rng(base_seed + i)
+    n = int(rng.integers(people[0], people[1] + 1))
+    _shared_out["batch"][i] = make_network_output(base_seed + i, n, height, width, stride, noise, scale)[0]
+
+
 def make_batch(base_seed, batch, people=(1, 10), height=512, width=512, stride=4, noise=0.01,
-               scale=(0.35, 0.9)):
-    """(B, 2, 50, h, w) float32 — seeds follow SURVEY.md §8(d): base_seed + image index."""
-    outs = []
-    for i in range(batch):
-        rng = np.random.default_rng(base_seed + i)
-        n = int(rng.integers(people[0], people[1] + 1))
-        outs.append(make_network_output(base_seed + i, n, height, width, stride, noise, scale)[0])
-    return np.stack(outs)
+               scale=(0.35, 0.9), workers=1):
+    """(B, 2, 50, h, w) float32 — seeds follow SURVEY.md §8(d): base_seed + image index.  workers != 1 renders the
+    images in that many forked processes (0 = all cores); the result does not depend on it."""
+    shape = (batch, 2, NUM_LIMBS + NUM_PARTS + 2, height // stride, width // stride)
+    _shared_out["batch"] = _shared_array(shape) if workers != 1 else np.empty(shape, dtype=f32)
+    _pool_run(_batch_image, [(base_seed, i, people, height, width, stride, noise, scale) for i in range(batch)], workers)
+    return _shared_out.pop("batch")
+
+
+def _multiscale_image(args):
+    i, seed, n_people, img_h, img_w, scale_search = args
+    for k, o in enumerate(make_multiscale_output(seed, n_people, img_h, img_w, scale_search)[0]):
+        _shared_out["ms"][k][i] = o
+
+
+def make_multiscale_batch(seeds_people, img_h=480, img_w=640, scale_search=(0.5, 1.0, 1.5, 2.0), workers=1):
+    """[(seed, n_people)] -> list over scales of (B, 2, 50, h_s, w_s) float32 (make_multiscale_output per image)."""
+    B = len(seeds_people)
+    shapes = [(B, 2, NUM_LIMBS + NUM_PARTS + 2) + tuple(s[3]) for s in multiscale_shapes(img_h, img_w, scale_search)]
+    _shared_out["ms"] = [_shared_array(s) if workers != 1 else np.empty(s, dtype=f32) for s in shapes]
+    _pool_run(_multiscale_image, [(i, s, n, img_h, img_w, tuple(scale_search)) for i, (s, n) in enumerate(seeds_people)], workers)
+    return _shared_out.pop("ms")
 
 
 def multiscale_shapes(img_h, img_w, scale_search=(0.5, 1.0, 1.5, 2.0), boxsize=512, max_downsample=64, stride=4):

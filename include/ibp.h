@@ -51,6 +51,10 @@ extern "C" {
 #define IBP_PEAKS_BOX_CENTROID 1 /* find_peaks: 3x3 NMS, >= thr, 5x5 centroid refine
                                     (utils/parse_skeletons.py:286-321, utils/util.py:177-213) */
 
+#define IBP_PEAKS_CROSS_RAW 2    /* heatmap_nms(bool_refine_center=False): the cross NMS of flavour 0 without the patch
+                                    refine — x, y = the feature-map pixel, score = the map value there
+                                    (utils/parse_skeletons.py:163-166); the caller maps to (x + 0.5) * up - 0.5 (l.122-123) */
+
 /* per-image status bits (ibp_batch_view.status) */
 #define IBP_ST_PEAK_OVERFLOW 0x1u    /* more peaks of one part than limits.max_peaks_per_part */
 #define IBP_ST_CAND_OVERFLOW 0x2u    /* more accepted pairs on one limb than limits.max_candidates_per_limb */

@@ -153,3 +153,17 @@ def test_gpu_bench_workload_configs2_exact():
     assert table.shape[0] > 10 and assoc.shape[0] >= 1
     assert np.array_equal(counts_g, counts) and np.array_equal(table_g[:, :3], table[:, :3])
     assert np.array_equal(assoc_g, assoc)
+
+
+def test_cv2_fusion_route_equals_restatement():
+    """oracle/cpu_path.predict_fuse_cv2 (the reference's own cv2.resize calls on 20/30-channel maps, what bench.py's CPU
+    baseline of configs[2] times and what the batch parity test uses as its checker) == the numpy restatement that the
+    goldens of the reference's predict pin (test_oracle_predict_fuse_matches_reference)."""
+    from improved_body_parts_b200 import synth
+    from oracle import cpu_path
+    for seed, (img_h, img_w, ss) in ((4243, (240, 320, (1.0, 2.0))), (4244, (200, 150, (0.5, 1.5)))):
+        shapes = synth.multiscale_shapes(img_h, img_w, ss)
+        outs = synth.make_multiscale_output(seed, 3, img_h, img_w, ss)[0]
+        a = O.predict_fuse(outs, img_h, img_w, [s[0] for s in shapes])
+        b = cpu_path.predict_fuse_cv2(outs, img_h, img_w, [s[0] for s in shapes])
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])

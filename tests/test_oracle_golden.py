@@ -36,7 +36,7 @@ def load_case(path):
     return out, heat, paf, g
 
 
-CASES = sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(p).startswith(("orig_", "ms_", "py_", "prep_", "coco_")))
+CASES = sorted(p for p in glob.glob(os.path.join(GOLD, "*.npz")) if os.path.basename(p).startswith(("fixture", "crowd", "synth_")))
 
 
 def test_golden_files_present():
@@ -135,3 +135,42 @@ def test_cpu_path_equals_oracle(oracle):
         for p, (x, y, s) in parts.items():
             assert (x, y) == (int(jl[ids[p], 0]), int(jl[ids[p], 1]))
         assert abs(score - wscore) <= 1e-4 * abs(wscore)
+
+
+RAW = sorted(glob.glob(os.path.join(GOLD, "raw_*.npz")))
+
+
+def load_raw(path):
+    from improved_body_parts_b200 import synth
+    g = np.load(path)
+    out, _ = synth.make_network_output(int(g["seed"]), int(g["people"]))
+    assert hashlib.sha256(out.tobytes()).hexdigest() == str(g["net_out_sha256"]), "input generator drifted"
+    return O.fuse_flip(out)[0], int(g["factor"]), g["rows"]
+
+
+@pytest.mark.parametrize("path", RAW, ids=[os.path.basename(p) for p in RAW])
+def test_oracle_heatmap_nms_without_refine(path):
+    """heatmap_nms(bool_refine_center=False) (parse_skeletons.py:163-166): goldens from the reference's own function."""
+    heat, factor, rows = load_raw(path)
+    assert len(RAW) >= 4
+    got = O.joint_list(O.heatmap_nms(heat, factor, bool_refine_center=False))
+    assert np.array_equal(got, rows)
+
+
+@pytest.mark.parametrize("path", CASES, ids=[os.path.basename(p) for p in CASES])
+def test_stock_cv2_with_ipp_gives_the_same_coordinates(path):
+    """The goldens are generated with cv2.ipp.setUseIPP(False).  Stock cv2 — what the reference really
+    runs, IPP's closed-source cubic kernel for 1-channel float patches — must give the SAME peak coordinates and ids;
+    only score bits may differ, by far less than the 1e-4 tolerance of north_star.  oracle/cpu_path.heatmap_nms_cv2 is
+    the reference's loop issuing the reference's cv2 / scipy calls with cv2's default (IPP on where the build has it)."""
+    import cv2
+    from oracle import cpu_path
+    _, heat, _, g = load_case(path)
+    cv2.ipp.setUseIPP(True)
+    stock = O.joint_list(cpu_path.heatmap_nms_cv2(heat, 4))
+    jl = g["joint_list"].reshape(-1, 5)
+    assert stock.shape == jl.shape
+    assert np.array_equal(stock[:, [0, 1, 3, 4]], jl[:, [0, 1, 3, 4]])          # x, y, id, part: identical
+    assert np.allclose(stock[:, 2], jl[:, 2], rtol=1e-5, atol=0)                  # score: within 1e-5 relative
+    differing = int(np.count_nonzero(stock[:, 2] != jl[:, 2]))
+    assert differing <= max(int(g["ipp_peak_mismatch"]), 0) + jl.shape[0] // 2   # bookkeeping of make_golden.py stays plausible
