@@ -119,7 +119,8 @@ struct ibp_handle {
     int4 *d_item_meta = nullptr;   // [max_batch*30] limb items in heaviest-image-first order (index_bands_kernel)
     unsigned *d_lb_work = nullptr; // work counter of the streaming limb kernel, never reset ...
     unsigned lb_work_base = 0;     // ... its value before the next launch
-    size_t lb_occ_smem = 0;        // occupancy of the streaming limb kernel, cached per shared-memory size
+    const void *lb_occ_kern = nullptr;
+    size_t lb_occ_smem = 0;        // occupancy of the streaming limb kernel, cached per (instantiation, shared-memory size)
     int lb_occ = 0;
     int *d_partbase = nullptr;     // [max_batch][19] first id of each part + image total (index_bands_kernel)
     int *d_n_raw = nullptr;        // [max_batch] peaks per image, accumulated by the streaming peak kernel (lives after d_status)
@@ -432,7 +433,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMemset(h->d_yext, 0x80, B * kParts * 2 * sizeof(int)));  // 0x80808080: below every -y
         CU(cudaMalloc(&h->d_lb_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_lb_work, 0, sizeof(unsigned)));
-        CU(cudaFuncSetAttribute(limbs_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaMalloc(&h->d_pk_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_pk_work, 0, sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
@@ -452,6 +454,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(peaks_kernel<__half, IBP_PEAKS_BOX_CENTROID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true, __half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false, __half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device));
@@ -626,7 +630,11 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
     a.w = fw;
     a.halo = std::max(h->P.refine_window, 1);
     static const bool no_stream = getenv("IBP_PEAKS_NO_STREAM") != nullptr;
-    const bool stream_ok = dtype == IBP_F32 && fw % 4 == 0 && ((uintptr_t)src & 15u) == 0 && (image_stride * 4) % 16 == 0 && !no_stream;
+    // streaming kernel: rows that the bulk-copy engine can move (16-byte multiples at 16-byte aligned addresses); float16
+    // network output (the reference's amp O1 default, parse_skeletons.py:75) streams for the heatmap_nms flavour
+    const size_t esz = dtype == IBP_F16 ? 2 : 4;
+    const bool stream_ok = ((size_t)fw * esz) % 16 == 0 && ((uintptr_t)src & 15u) == 0 && (image_stride * esz) % 16 == 0 && !no_stream &&
+                           (dtype == IBP_F32 || flavour == IBP_PEAKS_CROSS_REFINE);
     int rows_target = std::max<int>(4 * a.halo, (int)(peak_band_target(stream_ok) / ((size_t)fw * 4)));
     int nbands = (fh + rows_target - 1) / rows_target;
     a.rows_per_band = (fh + nbands - 1) / nbands;
@@ -688,7 +696,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
 
     // Streaming kernel: float32 planes whose rows the bulk-copy engine can move (16-byte aligned everywhere).
     const bool twin = twin_base >= 0;
-    const size_t row_bytes = (size_t)rows_buf * fw * 4;
+    const size_t row_bytes = (size_t)rows_buf * fw * esz;
     const size_t row_buf = (row_bytes + 15) & ~(size_t)15;
     const size_t tail_ints = std::max<size_t>((size_t)kParts * a.nbands + 1, (size_t)batch);
     const size_t smem_stream = 2 * (twin ? 2 : 1) * row_buf + scratch + ((tail_ints * 4 + 15) & ~(size_t)15);
@@ -697,7 +705,9 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
         a.ring_bytes = 0;
         const int items = a.nbands * kParts * batch;
         void (*kern)(PeakArgs) = nullptr;
-        if (flavour == IBP_PEAKS_CROSS_REFINE)
+        if (dtype == IBP_F16)
+            kern = twin ? peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true, __half> : peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false, __half>;
+        else if (flavour == IBP_PEAKS_CROSS_REFINE)
             kern = twin ? peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, true> : peaks_stream_kernel<IBP_PEAKS_CROSS_REFINE, false>;
         else
             kern = twin ? peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, true> : peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, false>;
@@ -953,31 +963,38 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     g.status = h->d_status;
     // Streaming kernel: the pipeline's common case (see k_limbs.cuh).  The grouping tables must fit behind the plane.
     static const bool no_lstream = getenv("IBP_LIMBS_NO_STREAM") != nullptr;
-    const size_t nonplane = smem - ((plane_bytes + 15) & ~(size_t)15);
     const size_t scratch_tail = (size_t)kPairChunk * sizeof(PairGeo) + (size_t)kPairChunk * a.max_steps * 4;
     // the twin rows stream through kLimbRing slots carved from the candidate / geometry / sample scratch: a slot must hold
     // at least one feature row (wider maps take the one-CTA-per-item kernel, whose staging falls back to plain loads)
     const size_t ring_slot_bytes = ((((size_t)a.cand_cap * 16 + scratch_tail) & ~(size_t)15) / kLimbRing);
-    if (a.band_peaks && mode == IBP_LIMB_FEAT_PLANAR && a.stage_plane && dtype == IBP_F32 && twin_base >= 0 && dim1 % 4 == 0 &&
-        ((uintptr_t)limb_src & 15u) == 0 && (image_stride * 4) % 16 == 0 && h->L.max_peaks_per_part <= 128 &&
-        limb_phase_bytes(h, plane_bytes) >= group_phase_bytes(h) && nonplane >= group_phase_bytes(h) &&
-        scratch_tail >= (size_t)a.cand_cap * 8 && ring_slot_bytes >= (size_t)dim1 * 4 && !no_lstream) {
+    // the streaming kernel keeps the plane in the element type of the network output (a float16 flip average is exact in
+    // float16): half the shared memory per item for the reference's amp O1 default
+    const size_t esz = dtype == IBP_F16 ? 2 : 4;
+    const size_t plane_s_bytes = (((size_t)dim0 * dim1 * esz) + 15) & ~(size_t)15;
+    const size_t smem_s = limb_smem_bytes(h, plane_s_bytes);
+    if (a.band_peaks && mode == IBP_LIMB_FEAT_PLANAR && a.stage_plane && twin_base >= 0 && ((size_t)dim1 * esz) % 16 == 0 &&
+        ((uintptr_t)limb_src & 15u) == 0 && (image_stride * esz) % 16 == 0 && h->L.max_peaks_per_part <= 128 &&
+        limb_phase_bytes(h, plane_s_bytes) >= group_phase_bytes(h) && smem_s - plane_s_bytes >= group_phase_bytes(h) &&
+        scratch_tail >= (size_t)a.cand_cap * 8 && ring_slot_bytes >= (size_t)dim1 * esz && smem_s <= kMaxDynSmem && !no_lstream) {
         a.item_meta = h->d_item_meta;
         a.ticket = h->d_status + 2 * (size_t)h->L.max_batch;  // zeroed by launch_peaks' memset on this stream
         a.work_counter = h->d_lb_work;
         a.work_base = h->lb_work_base;
-        a.plane_bytes = (int)((plane_bytes + 15) & ~(size_t)15);
+        a.plane_bytes = (int)plane_s_bytes;
+        a.smem_bytes = (int)smem_s;
+        void (*kern)(LimbArgs) = dtype == IBP_F16 ? limbs_stream_kernel<__half> : limbs_stream_kernel<float>;
         const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
-        if (h->lb_occ_smem != smem) {  // every CTA of the grid must be resident (queue items wait for one another)
+        if (h->lb_occ_smem != smem_s || h->lb_occ_kern != (const void *)kern) {  // every CTA of the grid must be resident (queue items wait for one another)
             int per_sm = 0;
-            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, limbs_stream_kernel, kLimbStreamThreads, smem));
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kLimbStreamThreads, smem_s));
             h->lb_occ = per_sm;
-            h->lb_occ_smem = smem;
+            h->lb_occ_smem = smem_s;
+            h->lb_occ_kern = (const void *)kern;
         }
         if (h->lb_occ < 1) return fail(IBP_ERR_SHAPE, "assign: streaming limb kernel does not fit");
         const int grid = std::min(items, h->lb_occ * h->sm_count);
         StageTimer t(h, IBP_STAGE_LIMBS, st);
-        CU(launch_dependent(limbs_stream_kernel, dim3(grid), dim3(kLimbStreamThreads), smem, st, a));
+        CU(launch_dependent(kern, dim3(grid), dim3(kLimbStreamThreads), smem_s, st, a));
         h->lb_work_base += (unsigned)items;  // once it runs, the kernel advances its counter by exactly this much
         h->launches++;
         CU(cudaGetLastError());

@@ -91,8 +91,13 @@ __device__ __forceinline__ float vsum4(float s0, float s1, float s2, float s3, c
     return __fadd_rn(__fmul_rn(s0, b[0]), __fadd_rn(__fmul_rn(s1, b[1]), __fadd_rn(__fmul_rn(s2, b[2]), __fmul_rn(s3, b[3]))));
 }
 
-// value of pixel (X,Y) of cv2.resize(plane(h,w), fx=up, fy=up, INTER_CUBIC); `plane` may be shared or global
-__device__ __forceinline__ float cubic_sample(const float *plane, int h, int w, int up, int X, int Y) {
+__device__ __forceinline__ float to_f32(float a) { return a; }
+__device__ __forceinline__ float to_f32(__half a) { return __half2float(a); }
+
+// value of pixel (X,Y) of cv2.resize(plane(h,w), fx=up, fy=up, INTER_CUBIC); `plane` may be shared or global.  A plane of
+// __half holds values that are exact in half precision (a float16 flip average): widening them is lossless.
+template <typename T>
+__device__ __forceinline__ float cubic_sample(const T *plane, int h, int w, int up, int X, int Y) {
     float xw[4], yw[4];
     const int sx = cubic_tap(X, up, xw);
     const int sy = cubic_tap(Y, up, yw);
@@ -100,22 +105,23 @@ __device__ __forceinline__ float cubic_sample(const float *plane, int h, int w, 
     float r[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        const float *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
-        r[k] = hsum4(row[x0], row[x1], row[x2], row[x3], xw);
+        const T *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
+        r[k] = hsum4(to_f32(row[x0]), to_f32(row[x1]), to_f32(row[x2]), to_f32(row[x3]), xw);
     }
     return vsum4(r[0], r[1], r[2], r[3], yw);
 }
 
 // same value through the phase table (up == 4 only)
-__device__ __forceinline__ float cubic_sample4(const float *plane, int h, int w, const float (*tab)[4], int X, int Y) {
+template <typename T>
+__device__ __forceinline__ float cubic_sample4(const T *plane, int h, int w, const float (*tab)[4], int X, int Y) {
     const int sx = (X - 2) >> 2, sy = (Y - 2) >> 2;
     const float *xw = tab[(X - 2) & 3], *yw = tab[(Y - 2) & 3];
     const int x0 = clampi(sx - 1, 0, w - 1), x1 = clampi(sx, 0, w - 1), x2 = clampi(sx + 1, 0, w - 1), x3 = clampi(sx + 2, 0, w - 1);
     float r[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        const float *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
-        r[k] = hsum4(row[x0], row[x1], row[x2], row[x3], xw);
+        const T *row = plane + (size_t)clampi(sy - 1 + k, 0, h - 1) * w;
+        r[k] = hsum4(to_f32(row[x0]), to_f32(row[x1]), to_f32(row[x2]), to_f32(row[x3]), xw);
     }
     return vsum4(r[0], r[1], r[2], r[3], yw);
 }
@@ -196,8 +202,28 @@ __device__ __forceinline__ float avg_like_numpy(__half a, __half b) {
     const __half s = __float2half_rn(__fadd_rn(__half2float(a), __half2float(b)));
     return __half2float(__float2half_rn(__fmul_rn(__half2float(s), 0.5f)));
 }
-__device__ __forceinline__ float to_f32(float a) { return a; }
-__device__ __forceinline__ float to_f32(__half a) { return __half2float(a); }
+// one 16-byte vector of a staged row folded with the vector that mirrors it in the twin row: o[q] = avg(o[q], t[V-1-q]),
+// kept in the element type (the float16 average is exact in float16)
+__device__ __forceinline__ void fold_mirrored(float4 &o, const float4 &t) {
+    o.x = avg_like_numpy(o.x, t.w);
+    o.y = avg_like_numpy(o.y, t.z);
+    o.z = avg_like_numpy(o.z, t.y);
+    o.w = avg_like_numpy(o.w, t.x);
+}
+__device__ __forceinline__ void fold_mirrored(uint4 &o, const uint4 &t) {  // eight __half
+    __half *a = reinterpret_cast<__half *>(&o);
+    const __half *m = reinterpret_cast<const __half *>(&t);
+#pragma unroll
+    for (int q = 0; q < 8; q++) a[q] = __float2half_rn(avg_like_numpy(a[q], m[7 - q]));
+}
+template <typename T>
+struct Vec16 {
+    using type = float4;
+};
+template <>
+struct Vec16<__half> {
+    using type = uint4;
+};
 
 template <typename T>
 __device__ __forceinline__ void stage_rows_fused(float *dst, const T *up, const T *twin, int row0, int nrows, int w, uint64_t *bar,
@@ -280,7 +306,7 @@ __device__ __forceinline__ void bulk_chunks(void *dst, const void *src, uint32_t
         done += chunk;
     }
 }
-__device__ __forceinline__ void bulk_rows(float *dst, const float *src, uint32_t bytes, uint64_t *bar) {
+__device__ __forceinline__ void bulk_rows(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     mbar_expect_tx(bar, bytes);
     uint32_t done = 0;
     while (done < bytes) {

@@ -90,8 +90,10 @@ __device__ __forceinline__ uint32_t float_orderable(float f) {
 }
 __device__ __forceinline__ uint32_t float_orderable_inv(uint32_t k) { return (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; }
 
-struct Sampler {
-    const float *base;  // mode 0: image base; mode 1: plane base (shared or global)
+template <typename P = float>
+struct SamplerT {
+    const float *base;  // mode 0: image base; mode 1 with P = float: plane base (shared or global)
+    const P *plane;     // mode 1: plane base when P is not float (the streaming kernel's float16 plane)
     const float (*tab4)[4];
     int mode, limb;
     int H, W, C, h, w, up;
@@ -103,10 +105,16 @@ struct Sampler {
         }
         px = clampi(px, 0, w * up - 1);
         py = clampi(py, 0, h * up - 1);
-        if (up == 4) return cubic_sample4(base, h, w, tab4, px, py);
-        return cubic_sample(base, h, w, up, px, py);
+        if constexpr (std::is_same<P, float>::value) {
+            if (up == 4) return cubic_sample4(base, h, w, tab4, px, py);
+            return cubic_sample(base, h, w, up, px, py);
+        } else {
+            if (up == 4) return cubic_sample4(plane, h, w, tab4, px, py);
+            return cubic_sample(plane, h, w, up, px, py);
+        }
     }
 };
+using Sampler = SamplerT<float>;
 
 __device__ __forceinline__ float limb_length(const DevPeak &A, const DevPeak &B) {
     const float dx = __int2float_rn(B.x - A.x), dy = __int2float_rn(B.y - A.y);  // :68-69
@@ -167,8 +175,8 @@ __device__ __forceinline__ void limb_stamp(const LimbArgs &a, int img, int row, 
 // greedily (pafprocess.cpp:52-130).  All threads of the CTA; the number of connections written is returned on thread 0.
 // `plane_dead` is called by every thread once the last sample has been read (after a barrier): the streaming kernel starts
 // the next item's plane copy there, under the ordering / greedy tail.
-template <int kLimbThreads, class PlaneDead>
-__device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Sampler &smp, int img, int limb, int nA, int nB,
+template <int kLimbThreads, class Smp, class PlaneDead>
+__device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Smp &smp, int img, int limb, int nA, int nB,
                                               PlaneDead plane_dead) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *emu = m.emu;
@@ -558,6 +566,7 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
         __syncthreads();
 
         Sampler smp;
+        smp.plane = nullptr;
         smp.mode = a.mode;
         smp.limb = limb;
         smp.H = a.H;
@@ -637,15 +646,18 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kLimbStreamThreads = 256;
 
+template <typename T>
 __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(LimbArgs a) {
     constexpr int kLimbThreads = kLimbStreamThreads;
+    constexpr int V = 16 / (int)sizeof(T);  // elements per 16-byte vector
+    using Vec = typename Vec16<T>::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x;
     const int items = a.batch * (kLimbs + 1);
     const size_t hw = (size_t)a.h * a.w;
 
     // ---- carve shared memory: plane | peak lists | ring = candidate / geometry / sample scratch ----
-    float *plane_s = reinterpret_cast<float *>(smem_raw);
+    T *plane_s = reinterpret_cast<T *>(smem_raw);
     size_t off = (size_t)a.plane_bytes;
     LimbSmem m;
     m.sA = reinterpret_cast<DevPeak *>(smem_raw + off);
@@ -675,8 +687,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     m.vals = reinterpret_cast<float *>(smem_raw + off);
     off += (size_t)kPairChunk * a.max_steps * 4;
     const int ring_bytes = (int)((off - ring_off) & ~(size_t)15);
-    float *ring = reinterpret_cast<float *>(smem_raw + ring_off);
-    const int slot_rows = min(a.h, (ring_bytes / kLimbRing) / (a.w * 4));
+    T *ring = reinterpret_cast<T *>(smem_raw + ring_off);
+    const int slot_rows = min(a.h, (ring_bytes / kLimbRing) / (a.w * (int)sizeof(T)));
     __shared__ uint64_t bars[1 + kLimbRing];
     __shared__ int wcnt[kLimbThreads / 32];
     __shared__ int s_last;
@@ -691,22 +703,22 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         return rel < (unsigned)items ? (int)rel : -1;
     };
     auto upright_of = [&](int img, int limb) {
-        return reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride + (size_t)limb * hw;
+        return reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride + (size_t)limb * hw;
     };
     auto twin_of = [&](int img, int limb) {  // flipped image: channel flip_paf_ord[limb] of its block (config/config.py:150-152)
-        return reinterpret_cast<const float *>(a.src) + (size_t)img * a.image_stride + (size_t)(a.twin_base + c_flip_src[limb]) * hw;
+        return reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride + (size_t)(a.twin_base + c_flip_src[limb]) * hw;
     };
     // Only the feature rows [r0, r1) that a sample of the item can touch are staged (at their own place in the buffer).
     auto has_pairs = [](const int4 &it) { return (it.y & 0xffff) > 0 && (it.y >> 16) > 0 && it.z < kLimbs; };
-    auto twin_chunk = [&](const float *twin, int r0, int r1, int c) {  // one thread: chunk c of the twin rows into its ring slot
+    auto twin_chunk = [&](const T *twin, int r0, int r1, int c) {  // one thread: chunk c of the twin rows into its ring slot
         const int s = c % kLimbRing, first = r0 + c * slot_rows;
         const int rows = min(slot_rows, r1 - first);
-        bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * a.w * 4u, &bars[1 + s]);
+        bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * a.w * (uint32_t)sizeof(T), &bars[1 + s]);
     };
     auto upright_rows = [&](const int4 &it) {  // one thread: the upright rows of a limb item straight to their place
         if (!has_pairs(it)) return;
         const int r0 = it.w & 0xffff, r1 = it.w >> 16;
-        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, it.z) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * 4u, &bars[0]);
+        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, it.z) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * (uint32_t)sizeof(T), &bars[0]);
     };
 
     pdl_wait();  // launched as a programmatic dependent: the work queue and the band lists come from the kernels before
@@ -775,7 +787,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         const int pa = c_limb_a[limb], pb = c_limb_b[limb];
         const bool pairs = nA > 0 && nB > 0;
         const int nchunks = (r1 - r0 + slot_rows - 1) / slot_rows;
-        const float *twin = twin_of(img, limb);
+        const T *twin = twin_of(img, limb);
         // thread 0: next claim out now, answer used later; the ring is free again: first twin chunks out
         if (tid == 0) {
             claimed = atomicAdd(a.work_counter, 1u);
@@ -847,26 +859,22 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             mbar_wait(&bars[0], up_uses & 1u);
             up_uses++;
             {
-                const int wv = a.w >> 2;
+                const int wv = a.w / V;
                 const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
-                float4 *d4 = reinterpret_cast<float4 *>(plane_s);
+                Vec *d4 = reinterpret_cast<Vec *>(plane_s);
                 for (int c = 0; c < nchunks; c++) {
                     const int s = c % kLimbRing;
                     mbar_wait(&bars[1 + s], (ring_par >> s) & 1u);
                     ring_par ^= 1u << s;
                     const int first = r0 + c * slot_rows;
                     const int rows = min(slot_rows, r1 - first);
-                    const float4 *r4 = reinterpret_cast<const float4 *>(ring + (size_t)s * slot_rows * a.w);
-                    float4 *o4 = d4 + (size_t)first * wv;
+                    const Vec *r4 = reinterpret_cast<const Vec *>(ring + (size_t)s * slot_rows * a.w);
+                    Vec *o4 = d4 + (size_t)first * wv;
                     for (int i = tid; i < rows * wv; i += kLimbThreads) {
                         const int r = (shift >= 0) ? (i >> shift) : (i / wv);
                         const int col = i - r * wv;
-                        float4 v = o4[i];
-                        const float4 t = r4[r * wv + (wv - 1 - col)];
-                        v.x = avg_like_numpy(v.x, t.w);
-                        v.y = avg_like_numpy(v.y, t.z);
-                        v.z = avg_like_numpy(v.z, t.y);
-                        v.w = avg_like_numpy(v.w, t.x);
+                        Vec v = o4[i];
+                        fold_mirrored(v, r4[r * wv + (wv - 1 - col)]);
                         o4[i] = v;
                     }
                     if (c + kLimbRing < nchunks) {
@@ -880,7 +888,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
                 __syncthreads();
             }
             limb_stamp(a, img, limb, 1);
-            Sampler smp;
+            SamplerT<T> smp;
             smp.mode = IBP_LIMB_FEAT_PLANAR;
             smp.limb = limb;
             smp.H = a.H;
@@ -890,7 +898,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             smp.w = a.w;
             smp.up = a.up;
             smp.tab4 = tab4;
-            smp.base = plane_s;
+            smp.base = reinterpret_cast<const float *>(plane_s);
+            smp.plane = plane_s;
             n_links = score_and_link<kLimbThreads>(a, m, smp, img, limb, nA, nB, prefetch_next);
         }
         if (tid == 0) a.link_count[img * kLimbs + limb] = n_links;

@@ -118,14 +118,33 @@ __device__ __forceinline__ double np_pairwise_sum_f64(const double *a, int n) {
 // (utils/parse_skeletons.py:91-93) is taken when a value is read — the scan reads every value once, everything
 // else touches a few pixels around a peak, so the extra pass that would fold one into the other is not needed.
 // ---------------------------------------------------------------------------------------------------------------
-struct PlainBand {
-    const float *p;
-    int l0, w;
-    __device__ __forceinline__ float at(int y, int x) const { return p[(y - l0) * w + x]; }
-    __device__ __forceinline__ float4 at4(int y, int x) const { return *reinterpret_cast<const float4 *>(p + (y - l0) * w + x); }
+// four consecutive elements of a staged band as they lie in memory (x % 4 == 0, rows 16-byte multiples)
+__device__ __forceinline__ float4 load4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+struct Half4 {
+    __half x, y, z, w;
 };
-struct FlipBand {
-    const float *up, *tw;
+__device__ __forceinline__ Half4 load4(const __half *p) {
+    const uint2 raw = *reinterpret_cast<const uint2 *>(p);
+    Half4 h;
+    h.x = __ushort_as_half((unsigned short)(raw.x & 0xffffu));
+    h.y = __ushort_as_half((unsigned short)(raw.x >> 16));
+    h.z = __ushort_as_half((unsigned short)(raw.y & 0xffffu));
+    h.w = __ushort_as_half((unsigned short)(raw.y >> 16));
+    return h;
+}
+template <typename T>
+struct PlainBandT {
+    const T *p;
+    int l0, w;
+    __device__ __forceinline__ float at(int y, int x) const { return to_f32(p[(y - l0) * w + x]); }
+    __device__ __forceinline__ float4 at4(int y, int x) const {
+        const auto v = load4(p + (y - l0) * w + x);
+        return make_float4(to_f32(v.x), to_f32(v.y), to_f32(v.z), to_f32(v.w));
+    }
+};
+template <typename T>
+struct FlipBandT {
+    const T *up, *tw;
     int l0, w;
     __device__ __forceinline__ float at(int y, int x) const {
         const int r = (y - l0) * w;
@@ -133,15 +152,13 @@ struct FlipBand {
     }
     __device__ __forceinline__ float4 at4(int y, int x) const {  // x % 4 == 0, w % 4 == 0
         const int r = (y - l0) * w;
-        float4 a = *reinterpret_cast<const float4 *>(up + r + x);
-        const float4 m = *reinterpret_cast<const float4 *>(tw + r + (w - 4 - x));
-        a.x = avg_like_numpy(a.x, m.w);
-        a.y = avg_like_numpy(a.y, m.z);
-        a.z = avg_like_numpy(a.z, m.y);
-        a.w = avg_like_numpy(a.w, m.x);
-        return a;
+        const auto a = load4(up + r + x);
+        const auto m = load4(tw + r + (w - 4 - x));
+        return make_float4(avg_like_numpy(a.x, m.w), avg_like_numpy(a.y, m.z), avg_like_numpy(a.z, m.y), avg_like_numpy(a.w, m.x));
     }
 };
+using PlainBand = PlainBandT<float>;
+using FlipBand = FlipBandT<float>;
 
 // ---- non-maximum suppression over the owned rows [r0, r1) ----
 // Neighbour rows / columns are clamped to the map, which is what both border rules amount to: scipy's 'reflect'
@@ -690,7 +707,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <int FLAVOUR, bool TWIN>
+template <int FLAVOUR, bool TWIN, typename T = float>
 __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stream_kernel(PeakArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -702,8 +719,8 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
     const int items = per_image * a.batch;
 
     // buffer set b: upright band at b*nplanes*band_bytes, twin band right after it
-    auto buf_up = [&](int b) { return reinterpret_cast<float *>(smem_raw + (size_t)b * nplanes * a.band_bytes); };
-    auto buf_tw = [&](int b) { return reinterpret_cast<float *>(smem_raw + ((size_t)b * nplanes + 1) * a.band_bytes); };
+    auto buf_up = [&](int b) { return reinterpret_cast<T *>(smem_raw + (size_t)b * nplanes * a.band_bytes); };
+    auto buf_tw = [&](int b) { return reinterpret_cast<T *>(smem_raw + ((size_t)b * nplanes + 1) * a.band_bytes); };
     const PeakScratch sc = peak_scratch(smem_raw, (size_t)2 * nplanes * a.band_bytes, a, nworkers);
     int *tail_scratch = reinterpret_cast<int *>(smem_raw + sc.end);  // max(18*nbands+1, batch) ints
     __shared__ uint64_t full[2];  // data of buffer set b has landed (or: no more items, see s_item)
@@ -736,8 +753,8 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
             return;
         }
         const Item it = decode(item);
-        const float *base = reinterpret_cast<const float *>(a.src) + (size_t)it.img * a.image_stride;
-        const uint32_t bytes = (uint32_t)(it.l1 - it.l0) * w * 4u;
+        const T *base = reinterpret_cast<const T *>(a.src) + (size_t)it.img * a.image_stride;
+        const uint32_t bytes = (uint32_t)(it.l1 - it.l0) * w * (uint32_t)sizeof(T);
         mbar_expect_tx(&full[b], bytes * nplanes);
         bulk_chunks(buf_up(b), base + (size_t)(a.chan0 + it.part) * hw + (size_t)it.l0 * w, bytes, &full[b]);
         if (TWIN)  // flipped image: channel 30 + flip_heat_ord[part] of its block (config/config.py:150-152)
@@ -812,7 +829,7 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
             stamp(item, 1);
         }
         const Item it = decode(item);
-        typename std::conditional<TWIN, FlipBand, PlainBand>::type B;
+        typename std::conditional<TWIN, FlipBandT<T>, PlainBandT<T>>::type B;
         if constexpr (TWIN) {
             B.up = buf_up(b);
             B.tw = buf_tw(b);
