@@ -369,6 +369,12 @@ class Refactored:
     def step_one(self, s):
         self.pp.enqueue(self.dev_sets[s % 2], IMG)
 
+    def step_dev_f16(self, s):
+        """Device-resident float16 network output (the reference's amp O1 default): same kernels, half the plane bytes."""
+        if not hasattr(self, "dev16"):
+            self.dev16 = [d.half() for d in self.dev_sets]
+        self.pipe.submit(self.dev16[s % 2], IMG, replace=True)
+
     def join(self):
         """End of a timed region: everything in flight has finished (and, end to end, has been read back)."""
         if self.e2e_mode:
@@ -419,6 +425,9 @@ class Refactored:
 
     def release(self):
         del self.pipe, self.pp, self.pps, self.dev_sets, self.host_sets
+        for k in ("dev16", "host16"):
+            if hasattr(self, k):
+                delattr(self, k)
 
 
 class MultiScale:
@@ -569,6 +578,12 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
     launches0 = sum(h.launches for h in handles)
     ms, regions = timed_median(wl.step_dev, args.steps, after=wl.finish)
     launches = (sum(h.launches for h in handles) - launches0) // len(regions)
+    ms_dev16 = None
+    if hasattr(wl, "step_dev_f16"):
+        for s in range(3):
+            wl.step_dev_f16(s)
+        wl.finish()
+        ms_dev16, _ = timed_median(wl.step_dev_f16, args.steps, after=wl.finish)
 
     # ---- end to end through the public API with HOST buffers (`e2e`) ----
     for s in range(min(args.warmup, 3)):
@@ -634,6 +649,9 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
            "stage_gbs": {k: algo[k] * batch / (stage_ms[k] * 1e-3) / 1e9 for k in stage_ms if k in algo},
            "whole_step_gbs": sum(algo.values()) * batch / (ms / args.steps * 1e-3) / 1e9,
            "humans_last_batch": wl.humans()}
+    if ms_dev16:
+        out["value_f16"] = {"value": world * batch * args.steps / (ms_dev16 * 1e-3), "unit": UNIT, "ms_per_step": ms_dev16 / args.steps,
+                            "note": "device-resident float16 network output (the reference's amp O1 default), same streaming kernels"}
     if ms_e2e16:
         out["e2e_f16"] = {"value": world * batch * args.steps / (ms_e2e16 * 1e-3), "unit": UNIT,
                           "h2d_bytes_per_step": world * wl.h2d() // 2,
@@ -709,8 +727,13 @@ def run_ours(args, rank, world, local_rank, inputs):
         if nm == "configs2":
             return MultiScale(nm, args, dev, inputs[nm], rank)
         if nm == "configs4":
-            from improved_body_parts_b200 import sweep
-            return sweep.SweepWorkload(nm, args, dev, rank, world)
+            import copy
+            import sweep
+            a4 = copy.copy(args)
+            a4.batch = args.batch if name == "configs4" else 0
+            # as an extra of the default run: a bounded sweep (the 10 000-image sweep is `--workload configs4`)
+            a4.sweep_images = args.sweep_images or (10000 if name == "configs4" else 768)
+            return sweep.SweepWorkload(nm, a4, dev, rank, world)
         return Refactored(nm, args, dev, inputs[nm], rank)
 
     wl = build(name)
@@ -736,7 +759,8 @@ def run_ours(args, rank, world, local_rank, inputs):
 
     if world == 1 and not args.no_extras and name == "configs1":
         extras = {}
-        have_model = os.path.exists(os.path.join(ROOT, "baseline", "_ref", "models", "posenet.py"))
+        import sweep
+        have_model = sweep.model_available()
         for nm in ("configs2", "configs3", "configs4"):
             if (nm not in inputs and nm != "configs4") or (nm == "configs4" and not have_model):
                 continue
