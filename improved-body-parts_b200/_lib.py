@@ -138,6 +138,8 @@ def lib():
     L.ibp_fetch_coco.argtypes = [vp, ip, C.POINTER(CocoView), vp]
     L.ibp_prepare_image.restype = ip
     L.ibp_prepare_image.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp, vp]
+    L.ibp_find_peaks_noalloc.restype = ip
+    L.ibp_find_peaks_noalloc.argtypes = [vp, ip, ip, ip, ip, ip, vp, vp, vp, vp, vp]
     L.ibp_launch_count.restype = C.c_int64
     L.ibp_launch_count.argtypes = [vp]
     L.ibp_set_profiling.restype = ip
@@ -153,7 +155,8 @@ EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_fuse_multiscale", "ibp_upsample_limbs",
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
            "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
-           "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image"]
+           "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image", "ibp_find_peaks_noalloc"]
+NOALLOC_MAX_BATCH, NOALLOC_MAX_BANDS, NOALLOC_CAP = 8, 8, 64  # include/ibp.h §5
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
 

@@ -24,6 +24,24 @@
 
 using namespace ibp;
 
+// ---------------------------------------------------------------------------------------------------------------
+// Scratch of ibp_find_peaks_noalloc (include/ibp.h §5): ONE file-scope device array, held by every GPU that loads the
+// library until the process exits.  In host code `g_noalloc_scratch` is a host-side stand-in, NOT a device address: the
+// entry point asks the runtime for the device address once per device (cudaGetSymbolAddress, with that device current)
+// and hands that pointer to the kernel.
+// ---------------------------------------------------------------------------------------------------------------
+struct NoAllocScratch {
+    DevPeak band_peaks[IBP_NOALLOC_MAX_BATCH * kParts * IBP_NOALLOC_MAX_BANDS * IBP_NOALLOC_CAP];  // per-band lists
+    DevPeak peaks[IBP_NOALLOC_MAX_BATCH * kParts * IBP_NOALLOC_CAP];                               // per-part lists
+    // ---- everything from here on is cleared at the start of every call ----
+    int band_count[IBP_NOALLOC_MAX_BATCH * kParts * IBP_NOALLOC_MAX_BANDS];
+    unsigned ticket[IBP_NOALLOC_MAX_BATCH];
+    unsigned batch_ticket;
+    int order[IBP_NOALLOC_MAX_BATCH];
+};
+static_assert(sizeof(NoAllocScratch) <= IBP_NOALLOC_SCRATCH_BYTES, "IBP_NOALLOC_SCRATCH_BYTES too small");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[IBP_NOALLOC_SCRATCH_BYTES];
+
 namespace {
 
 thread_local std::string g_err;
@@ -1638,5 +1656,104 @@ int ibp_get_part_x(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n
 int ibp_get_part_y(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n_peaks[0]) ? g_view.peaks[cid].y : 0; }
 float ibp_get_part_score(int cid) { return (g_view_valid && cid >= 0 && cid < g_view.n_peaks[0]) ? g_view.peaks[cid].score : 0.0f; }
 uint32_t ibp_get_status(void) { return g_legacy_status; }
+
+// ------------------------------------------------------------------------------------------------ allocation-free peaks
+// No counterpart in the reference (include/ibp.h §5).  Nothing in here
+// allocates: no cudaMalloc / cudaFree / cudaMallocHost / cudaStreamCreate / cudaEventCreate, no std::vector.
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+NoAllocScratch *g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};  // DEVICE address of g_noalloc_scratch, per device
+std::mutex g_noalloc_mu;
+}  // namespace
+
+int ibp_find_peaks_noalloc(const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw, ibp_peak *out_peaks,
+                           int32_t *out_part_count, int32_t *out_n_peaks, uint32_t *out_status, void *stream) {
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(IBP_ERR_ARG, "ibp_find_peaks_noalloc: device %d not supported (max %d)", dev, kNoAllocMaxDevices);
+    auto kern = peaks_kernel<float, IBP_PEAKS_CROSS_REFINE>;
+    {
+        // set-up, once per device, with that device current: the DEVICE address of the scratch array (its name is only a
+        // host-side stand-in here) and the kernel's shared-memory opt-in
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[dev]) {
+            void *p = nullptr;
+            CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+            if (!p) return fail(IBP_ERR_CUDA, "ibp_find_peaks_noalloc: cudaGetSymbolAddress returned a null address");
+            CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+            g_noalloc_ptr[dev] = static_cast<NoAllocScratch *>(p);
+        }
+    }
+    if (batch == 0) return IBP_OK;  // set-up only (callers about to capture a graph)
+    if (!maps || !out_peaks || !out_part_count || !out_n_peaks || !out_status) return fail(IBP_ERR_ARG, "ibp_find_peaks_noalloc: null argument");
+    if (batch < 0 || batch > IBP_NOALLOC_MAX_BATCH)
+        return fail(IBP_ERR_ARG, "ibp_find_peaks_noalloc: batch %d outside [0,%d] (IBP_NOALLOC_MAX_BATCH: the static scratch array is sized for it)",
+                    batch, IBP_NOALLOC_MAX_BATCH);
+    if (fh < 1 || fw < 1 || fw > 2048 || fh > 32767 || first_chan < 0 || first_chan + kParts > chan_stride)
+        return fail(IBP_ERR_SHAPE, "ibp_find_peaks_noalloc: bad shape (chan_stride %d, first_chan %d, %dx%d; fw <= 2048)", chan_stride, first_chan, fh, fw);
+    NoAllocScratch *S = g_noalloc_ptr[dev];
+    cudaStream_t st = (cudaStream_t)stream;
+
+    // the geometry of launch_peaks' one-CTA-per-band route, default parameters (ibp_default_params)
+    PeakArgs a;
+    memset(&a, 0, sizeof(a));
+    a.src = maps;
+    a.dtype = IBP_F32;
+    a.image_stride = (size_t)chan_stride * fh * fw;
+    a.chan0 = first_chan;
+    a.twin_base = -1;
+    a.h = fh;
+    a.w = fw;
+    a.halo = 2;
+    const int rows_target = std::max<int>(4 * a.halo, (int)(kPeakBandTarget / ((size_t)fw * 4)));
+    int nbands = (fh + rows_target - 1) / rows_target;
+    a.rows_per_band = (fh + nbands - 1) / nbands;
+    a.nbands = (fh + a.rows_per_band - 1) / a.rows_per_band;
+    if (a.nbands > IBP_NOALLOC_MAX_BANDS)
+        return fail(IBP_ERR_SHAPE, "ibp_find_peaks_noalloc: a %dx%d map needs %d bands of %d rows, the static scratch array holds %d "
+                                   "(IBP_NOALLOC_MAX_BANDS); use ibp_find_peaks", fh, fw, a.nbands, a.rows_per_band, IBP_NOALLOC_MAX_BANDS);
+    const int rows_buf = std::min(a.rows_per_band + 2 * a.halo, fh);
+    size_t band_bytes = std::max((size_t)rows_buf * fw * 4, (size_t)(kParts * a.nbands + 1) * 4);
+    band_bytes = std::max(band_bytes, (size_t)batch * 4);
+    band_bytes = (band_bytes + 15) & ~(size_t)15;
+    a.band_bytes = (int)band_bytes;
+    a.ring_bytes = 0;
+    a.up = 4;
+    a.win = 2;
+    a.thr = 0.1f;
+    a.cap = IBP_NOALLOC_CAP;
+    a.flavour = IBP_PEAKS_CROSS_REFINE;
+    a.raw = 0;
+    a.band_peaks = S->band_peaks;
+    a.band_subpix = nullptr;
+    a.band_count = S->band_count;
+    a.ticket = S->ticket;
+    a.peaks = S->peaks;
+    a.subpix = nullptr;
+    a.part_count = out_part_count;
+    a.line = out_peaks;
+    a.line_stride = kParts * IBP_NOALLOC_CAP;
+    a.n_peaks = out_n_peaks;
+    a.status = out_status;
+    a.batch_ticket = &S->batch_ticket;
+    a.timeline = nullptr;
+    a.order = S->order;
+    a.batch = batch;
+    const int side = 2 * a.win + 1;
+    size_t scratch = (((size_t)(kPeakThreads / 32) * side * side * a.up * 4) + 7) & ~(size_t)7;
+    scratch += (size_t)a.cap * 8;
+    scratch = (scratch + 15) & ~(size_t)15;
+    const size_t smem = band_bytes + scratch;
+    if (smem > kMaxDynSmem) return fail(IBP_ERR_SHAPE, "ibp_find_peaks_noalloc: rows of %d floats do not fit shared memory", fw);
+
+    // the array keeps the last call's contents (a call that died mid-way leaves tickets behind): clear what must start at
+    // zero, on the caller's stream; the status words are the caller's
+    const size_t tail = sizeof(NoAllocScratch) - offsetof(NoAllocScratch, band_count);
+    CU(cudaMemsetAsync(S->band_count, 0, tail, st));
+    CU(cudaMemsetAsync(out_status, 0, (size_t)batch * sizeof(uint32_t), st));
+    kern<<<dim3(a.nbands, kParts, batch), kPeakThreads, smem, st>>>(a);
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
 
 }  // extern "C"

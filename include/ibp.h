@@ -264,6 +264,34 @@ int ibp_find_humans(ibp_handle *h, const ibp_py_params *params, int batch, void 
 /* person_to_joint_assoc of one image: people (n,20,2) float64; returns n (>= 0) or a negative error code. */
 int ibp_fetch_people(ibp_handle *h, int image, double *people, int capacity, void *stream);
 
+/* ---------------------------------------------------------------------------------------------------------------
+ * 5. Allocation-free peak extraction.  NO COUNTERPART IN THE REFERENCE: added for
+ *    callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *    Same computation as ibp_find_peaks with IBP_PEAKS_CROSS_REFINE (heatmap_nms, 4-connected NMS > thresh, 5x5 bicubic x4
+ *    refine, running ids) with the default parameters (thresh 0.1, up-sampling 4, window 2), but without a handle: the
+ *    call allocates nothing — no cudaMalloc / cudaFree / cudaMallocHost, no allocating library routine.  Its scratch (the
+ *    per-band peak lists, the per-part lists, band counts and tickets) lives in ONE file-scope `static __device__` array
+ *    of IBP_NOALLOC_SCRATCH_BYTES (about 1.3 MB) that every GPU loading the library holds until the process exits.
+ *    Limits (rejected with IBP_ERR_ARG / IBP_ERR_SHAPE and a message in ibp_last_error() beyond them):
+ *      batch <= IBP_NOALLOC_MAX_BATCH (8); at most IBP_NOALLOC_MAX_BANDS (8) bands per plane, i.e.
+ *      fh <= 8 * max(8, 4096 / fw) rows (256 rows at fw = 128); fw <= 2048; IBP_NOALLOC_CAP (64) peaks per joint type.
+ *    All pointers are DEVICE pointers on the calling thread's CURRENT device:
+ *      maps (batch, chan_stride, fh, fw) planar float32, keypoint j in channel first_chan + j           [in]
+ *      out_peaks (batch, 18 * IBP_NOALLOC_CAP) rows, part-major, index == peak id                      [out]
+ *      out_part_count (batch, 18), out_n_peaks (batch), out_status (batch) IBP_ST_* bits               [out]
+ *    Asynchronous on `stream`.  The first call on a device does the one-time set-up (address of the scratch array,
+ *    kernel attributes; nothing is allocated) — under graph capture make one call with batch == 0 beforehand, which
+ *    does only that.  EVERY call shares the one scratch array: calls that overlap on the GPU (different streams,
+ *    different threads, concurrent graph launches) RACE; serialise them.  The array keeps the last call's contents;
+ *    the call clears what must start at zero itself (memset nodes on `stream`). */
+#define IBP_NOALLOC_MAX_BATCH 8
+#define IBP_NOALLOC_MAX_BANDS 8
+#define IBP_NOALLOC_CAP 64
+#define IBP_NOALLOC_SCRATCH_BYTES (1360 * 1024)
+int ibp_find_peaks_noalloc(const float *maps, int chan_stride, int first_chan, int batch, int fh, int fw,
+                           ibp_peak *out_peaks, int32_t *out_part_count, int32_t *out_n_peaks, uint32_t *out_status,
+                           void *stream);
+
 /* number of kernels this library has launched through `h` since creation (bench.py's gpu_launches) */
 int64_t ibp_launch_count(const ibp_handle *h);
 
