@@ -553,7 +553,7 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    def timed_median(fn, steps, after=None, max_reps=15):
+    def timed_median(fn, steps, after=None, max_reps=40):
         first = timed(fn, steps)
         if after:
             after()
@@ -589,13 +589,13 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
     for s in range(min(args.warmup, 3)):
         wl.step_e2e(s)
     wl.finish()  # nothing in flight when the timed region starts; K uploads, K read-backs inside it
-    ms_e2e, regions_e2e = timed_median(wl.step_e2e, args.steps, after=wl.finish, max_reps=5)
+    ms_e2e, regions_e2e = timed_median(wl.step_e2e, args.steps, after=wl.finish, max_reps=3)
     ms_e2e16 = None
     if hasattr(wl, "step_e2e_f16"):  # float16 hand-over (the reference's amp O1 default), same public call
         for s in range(3):
             wl.step_e2e_f16(s)
         wl.finish()
-        ms_e2e16, _ = timed_median(wl.step_e2e_f16, args.steps, after=wl.finish, max_reps=5)
+        ms_e2e16, _ = timed_median(wl.step_e2e_f16, args.steps, after=wl.finish, max_reps=3)
 
     # ---- per-kernel device times for the roofline: one batch at a time on the first lane, events on the launching
     #      stream inside the library ----

@@ -867,11 +867,16 @@ int set_peaks_impl(ibp_handle *h, int image, const float *host_peaks, int n, int
     h->order_batch = 0;  // the peak kernel's image order no longer describes the lists
     h->defer_bands = 0;
     memcpy(h->h_part_count + (size_t)image * kParts, counts, sizeof(counts));
-    // per part only the filled entries (a handle grown for one crowd image keeps large per-part strides)
-    for (int p = 0; p < kParts; p++)
-        if (counts[p])
-            CU(cudaMemcpyAsync(h->d_peaks + ((size_t)image * kParts + p) * cap, h->h_peaks_stage + (size_t)p * cap,
-                               (size_t)counts[p] * sizeof(DevPeak), cudaMemcpyHostToDevice, st));
+    // one copy while the per-part stride is small; per part only the filled entries once a handle has grown for a crowd
+    if ((size_t)kParts * cap * sizeof(DevPeak) <= 128 * 1024) {
+        CU(cudaMemcpyAsync(h->d_peaks + (size_t)image * kParts * cap, h->h_peaks_stage, (size_t)kParts * cap * sizeof(DevPeak),
+                           cudaMemcpyHostToDevice, st));
+    } else {
+        for (int p = 0; p < kParts; p++)
+            if (counts[p])
+                CU(cudaMemcpyAsync(h->d_peaks + ((size_t)image * kParts + p) * cap, h->h_peaks_stage + (size_t)p * cap,
+                                   (size_t)counts[p] * sizeof(DevPeak), cudaMemcpyHostToDevice, st));
+    }
     CU(cudaMemcpyAsync(h->d_part_count + (size_t)image * kParts, h->h_part_count + (size_t)image * kParts, sizeof(counts),
                        cudaMemcpyHostToDevice, st));
     CU(cudaMemcpyAsync(h->d_line + (size_t)image * h->line_stride, line, (size_t)std::max(n, 1) * sizeof(ibp_peak), cudaMemcpyHostToDevice, st));
