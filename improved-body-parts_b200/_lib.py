@@ -138,6 +138,10 @@ def lib():
     L.ibp_fetch_coco.argtypes = [vp, ip, C.POINTER(CocoView), vp]
     L.ibp_prepare_image.restype = ip
     L.ibp_prepare_image.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, vp, vp]
+    L.ibp_resized_size.restype = None
+    L.ibp_resized_size.argtypes = [ip, ip, C.c_double, C.c_double, C.POINTER(ip), C.POINTER(ip)]
+    L.ibp_resize_image.restype = ip
+    L.ibp_resize_image.argtypes = [vp, vp, ip, ip, ip, C.c_double, C.c_double, vp, ip, ip, vp]
     L.ibp_find_peaks_noalloc.restype = ip
     L.ibp_find_peaks_noalloc.argtypes = [vp, ip, ip, ip, ip, ip, vp, vp, vp, vp, vp]
     L.ibp_launch_count.restype = C.c_int64
@@ -155,7 +159,8 @@ EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp
            "ibp_create", "ibp_destroy", "ibp_last_error", "ibp_device_count", "ibp_fuse_flip", "ibp_fuse_multiscale", "ibp_upsample_limbs",
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
            "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
-           "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image", "ibp_find_peaks_noalloc"]
+           "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image", "ibp_find_peaks_noalloc",
+           "ibp_resized_size", "ibp_resize_image"]
 NOALLOC_MAX_BATCH, NOALLOC_MAX_BANDS, NOALLOC_CAP = 8, 8, 64  # include/ibp.h §5
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
@@ -182,6 +187,13 @@ def py_params(test_cfg=None):
         p.len_rate = int(test_cfg.get('len_rate', p.len_rate))
         p.connection_tole = float(test_cfg.get('connection_tole', p.connection_tole))
     return p
+
+
+def resized_size(img_h, img_w, fx, fy):
+    """(out_h, out_w) of cv2.resize(img, (0, 0), fx=fx, fy=fy): rint(h * fy), rint(w * fx)."""
+    oh, ow = C.c_int(), C.c_int()
+    lib().ibp_resized_size(int(img_h), int(img_w), float(fx), float(fy), C.byref(oh), C.byref(ow))
+    return oh.value, ow.value
 
 
 def default_limits():
@@ -333,6 +345,9 @@ class Handle:
     def prepare_image(self, img_ptr, batch, img_h, img_w, max_downsample, pad_value, flip, out_ptr, stream=0):
         check(lib().ibp_prepare_image(self._h, img_ptr, batch, img_h, img_w, max_downsample, pad_value, 1 if flip else 0,
                                       out_ptr, stream))
+
+    def resize_image(self, img_ptr, batch, img_h, img_w, fx, fy, out_ptr, out_h, out_w, stream=0):
+        check(lib().ibp_resize_image(self._h, img_ptr, batch, img_h, img_w, float(fx), float(fy), out_ptr, out_h, out_w, stream))
 
     def fetch(self, batch, stream=0, raise_on_overflow=True):
         view = BatchView()

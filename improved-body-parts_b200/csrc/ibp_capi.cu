@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <atomic>
 #include <condition_variable>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -20,6 +21,7 @@
 #include "k_multiscale.cuh"
 #include "k_peaks.cuh"
 #include "k_pyroute.cuh"
+#include "k_resize.cuh"
 #include "k_upsample.cuh"
 
 using namespace ibp;
@@ -1204,6 +1206,39 @@ int ibp_prepare_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, i
     a.pad_value = pad_value;
     const dim3 grid((a.wp + 255) / 256, a.hp, batch);
     prepare_image_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+void ibp_resized_size(int img_h, int img_w, double fx, double fy, int *out_h, int *out_w) {
+    // cv2.resize with dsize = (0, 0): Size(saturate_cast<int>(cols * fx), saturate_cast<int>(rows * fy)), which rounds half to even
+    if (out_h) *out_h = (int)nearbyint((double)img_h * fy);
+    if (out_w) *out_w = (int)nearbyint((double)img_w * fx);
+}
+
+int ibp_resize_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, double fx, double fy, uint8_t *out, int out_h,
+                     int out_w, void *stream) {
+    if (!h || !img || !out) return fail(IBP_ERR_ARG, "ibp_resize_image: null argument");
+    if (batch < 1 || batch > 65535 || img_h < 1 || img_w < 1 || !(fx > 0.0) || !(fy > 0.0)) return fail(IBP_ERR_SHAPE, "ibp_resize_image: bad shape / factor");
+    int oh = 0, ow = 0;
+    ibp_resized_size(img_h, img_w, fx, fy, &oh, &ow);
+    if (oh < 1 || ow < 1 || oh > 65535) return fail(IBP_ERR_SHAPE, "ibp_resize_image: a %dx%d image times (%g, %g) gives %dx%d", img_h, img_w, fy, fx, oh, ow);
+    if (oh != out_h || ow != out_w)
+        return fail(IBP_ERR_SHAPE, "ibp_resize_image: cv2 would produce %dx%d for these factors, the output buffer is %dx%d", oh, ow, out_h, out_w);
+    CU(cudaSetDevice(h->device));
+    ResizeArgs a;
+    a.img = img;
+    a.out = out;
+    a.batch = batch;
+    a.h = img_h;
+    a.w = img_w;
+    a.dh = oh;
+    a.dw = ow;
+    a.scale_x = 1.0 / fx;  // dsize empty: scale = 1 / inv_scale, not src / dst
+    a.scale_y = 1.0 / fy;
+    a.lanes = 8;
+    resize_u8_cubic_kernel<<<dim3((ow + 127) / 128, oh, batch), 128, 0, (cudaStream_t)stream>>>(a);
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;

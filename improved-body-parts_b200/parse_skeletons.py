@@ -76,14 +76,13 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
     """-> (heatmaps (h,w,20), pafs (h,w,30)) float32 HWC, like parse_skeletons.py:28-103.  The scale is pinned to 1.0
     (l.36), so the cv2.resize is a copy unless the image is too big; padding, /255 and the flipped twin (l.54-72) and
     the flip average (l.80-96) run on the device."""
-    import cv2
     scale = 1.0  # parse_skeletons.py:36
     img_h, img_w, _ = image.shape
     if scale * img_h > 2600 or scale * img_w > 3800:  # l.46-49
         scale = min(2600 / img_h, 3800 / img_w)
         print("Input image: '{}' is too big, shrink it!".format(input_image_path))
-    img = cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC)
     pp = _processor()
+    img = _scaled_image(pp, image, scale)  # l.52, on the device (a scale of exactly 1.0 is an identity)
     batch = pp.prepare_images(img, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)  # l.54-72
     with torch.no_grad():
         out = model(batch)
@@ -95,6 +94,18 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
 
 
 @_growing
+def _scaled_image(pp, image, scale):
+    """cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC) (l.52 / l.204) on the device:
+    uint8 (h,w,3) numpy / tensor -> uint8 (1, rint(h*scale), rint(w*scale), 3) CUDA tensor."""
+    t = image if isinstance(image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(image))
+    if t.dtype != torch.uint8 or t.dim() != 3 or t.shape[2] != 3:
+        raise ValueError("image must be uint8 (h, w, 3) BGR, got %s %s" % (t.dtype, tuple(t.shape)))
+    t = t.to(pp.device)
+    if scale == 1.0:
+        return t[None, ...]
+    return pp.resize_images(t, scale)
+
+
 def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
     """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176).
     bool_refine_center=False (l.163-166): no patch refine — x, y = compute_resized_coords(pixel) = (p + 0.5) * f - 0.5 in
@@ -164,9 +175,9 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
     The reference computes the scale-search multipliers (l.186) and then pins them to [1.] (l.188); `scale_search=None`
     does the same.  Pass a list such as test_cfg['scale_search'] to run the multi-scale averaging the reference ships
     but never reaches.  rotation_search is [0.0] (utils/config:15): the rotation branch (l.215-218, 265-267) is not
-    implemented.  Image preparation per scale stays on the host exactly as in the reference; everything after the
-    model calls (flip average, cubic x stride, crop, cubic resize to the image, average) is one kernel launch."""
-    import cv2
+    implemented.  The image goes to the device once (uint8); per scale the cubic resize (l.204), the pad to a multiple of
+    max_downsample with padValue, the /255 and the flipped twin (l.206-224) run there; everything after the model calls
+    (flip average, cubic x stride, crop, cubic resize to the image, average) is one kernel launch."""
     img_h, img_w, _ = image.shape
     if scale_search is None:
         multiplier = [1.]  # l.188
@@ -175,21 +186,20 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
     if any(a != 0 for a in test_cfg.get('rotation_search', [0.0])):
         raise NotImplementedError("rotation_search != 0 is not on the reference's path (utils/config:15)")
     pp = _processor()
+    img_dev = torch.from_numpy(np.ascontiguousarray(image)).to(pp.device)  # one upload, uint8
     outs, sizes = [], []
     for scale in multiplier:
         if scale * img_h > 2600 or scale * img_w > 3800:  # l.196-199
             scale = min(2600 / img_h, 3800 / img_w)
             print("Input image: '{}' is too big, shrink it!".format(input_image_path))
-        scaled = cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC)
-        padded, _ = pad_right_down_corner(scaled, model_cfg['max_downsample'], model_cfg['padValue'])
-        x = np.float32(padded / 255)
-        batch = np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0)  # l.221-224
+        scaled = _scaled_image(pp, img_dev, scale)                                                       # l.204
+        batch = pp.prepare_images(scaled, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)  # l.206-224
         with torch.no_grad():
-            out = model(torch.from_numpy(batch).to(pp.device))
+            out = model(batch)
         if isinstance(out, (list, tuple)):
             out = out[-1][0]  # last stack, scale 0 (l.232)
         outs.append(out.to(pp.device, torch.float32)[None, ...])
-        sizes.append(scaled.shape[:2])
+        sizes.append(tuple(int(v) for v in scaled.shape[1:3]))
     fused, _ = pp.fuse_multiscale(outs, sizes, img_h, img_w, flip_avg, want_heat32=False)
     hwc = fused[0].permute(1, 2, 0).contiguous().cpu().numpy()
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()

@@ -84,6 +84,24 @@ class PostProcessor:
                                       _stream_ptr(self.device))
         return out
 
+    def resize_images(self, images, fx, fy=None):
+        """cv2.resize(img, (0, 0), fx=fx, fy=fy, interpolation=cv2.INTER_CUBIC) for uint8 (B,h,w,3) / (h,w,3) HWC images on
+        the device (utils/parse_skeletons.py:204, :52) -> uint8 (B, rint(h*fy), rint(w*fx), 3) CUDA tensor."""
+        fy = fx if fy is None else fy
+        if isinstance(images, np.ndarray):
+            images = torch.from_numpy(np.ascontiguousarray(images))
+        if images.dim() == 3:
+            images = images[None, ...]
+        if images.dtype != torch.uint8 or images.dim() != 4 or images.shape[3] != 3:
+            raise ValueError("images must be uint8 (B, h, w, 3), got %s %s" % (images.dtype, tuple(images.shape)))
+        images = images.to(self.device).contiguous()
+        B, h, w, _ = images.shape
+        oh, ow = _lib.resized_size(h, w, fx, fy)
+        out = torch.empty((B, oh, ow, 3), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            self.handle.resize_image(images.data_ptr(), B, h, w, fx, fy, out.data_ptr(), oh, ow, _stream_ptr(self.device))
+        return out
+
     # ---- stages on tensors (used by the parse_skeletons mirror and by tests) ---------------------------------
     def fuse_flip(self, net_out, flip_avg=True):
         """(B,2,50,h,w) CUDA tensor -> (B,50,h,w) float32 CUDA tensor (K1)."""

@@ -229,6 +229,15 @@ int ibp_fetch_coco(ibp_handle *h, int batch, ibp_coco_view *view, void *stream);
 int ibp_prepare_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, int max_downsample,
                       int pad_value, int flip, float *out, void *stream);
 
+/* Image resize of the scale search — utils/parse_skeletons.py:204 (predict) / :52 (predict_refactor):
+ * cv2.resize(image, (0, 0), fx=fx, fy=fy, interpolation=cv2.INTER_CUBIC) on uint8 HWC images, OpenCV's own 8-bit path
+ * (11-bit fixed-point taps, integer horizontal pass, float vertical pass, integer tail; csrc/k_resize.cuh), bit-exact
+ * against cv2 with IPP off.  DEVICE pointers: img (batch,h,w,3), out (batch,out_h,out_w,3) with (out_h, out_w) =
+ * ibp_resized_size (rint(h*fy), rint(w*fx), cv2's saturate_cast<int>); any other size is IBP_ERR_SHAPE. */
+void ibp_resized_size(int img_h, int img_w, double fx, double fy, int *out_h, int *out_w);
+int ibp_resize_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, double fx, double fy, uint8_t *out,
+                     int out_h, int out_w, void *stream);
+
 /* Sub-pixel coordinates of the IBP_PEAKS_BOX_CENTROID flavour (utils/util.py:188-213 returns float64 x, y): after
  * ibp_fetch, copies image `image`'s (x, y) pairs in peak-id order into host_xy[capacity][2].  Returns the number of
  * peaks written (>= 0) or a negative error code. */

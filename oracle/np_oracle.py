@@ -423,6 +423,49 @@ def prepare_input(image, max_downsample=64, pad_value=128, flip=True):
 
 
 # ----------------------------------------------------------------------------------------------------------
+# Image resize of the scale search — utils/parse_skeletons.py:204 / :52: cv2.resize(image, (0,0), fx, fy, INTER_CUBIC) on
+# uint8.  Third-party arithmetic (OpenCV 4.13 resize.cpp, 8-bit cubic path), restated; pinned by tests/golden/resize_9x.npz
+# (outputs of cv2.resize itself, IPP off) and against the live cv2 in tests/test_resize.py.
+# ----------------------------------------------------------------------------------------------------------
+def _u8_axis(n_src, n_dst, scale):
+    """Per destination index: four clamped source indices and the 11-bit fixed-point taps."""
+    d = np.arange(n_dst, dtype=np.float64)
+    fx = ((d + 0.5) * scale - 0.5).astype(f32)
+    s = np.floor(fx).astype(np.int64)
+    t = (fx - s.astype(f32)).astype(f32)
+    w = np.stack(_cubic_weights(t), axis=1).astype(f32)                       # (n_dst, 4) float32, A = -0.75
+    taps = np.clip(np.rint(w * f32(2048)), -32768, 32767).astype(np.int64)     # saturate_cast<short>(w * 2048)
+    idx = np.clip(s[:, None] + np.arange(-1, 3)[None, :], 0, n_src - 1)
+    return idx, taps
+
+
+def cv_resize_cubic_u8(img, fx, fy=None, lanes=8):
+    """cv2.resize(img, (0, 0), fx=fx, fy=fy, interpolation=cv2.INTER_CUBIC) for a uint8 (h,w,c) image."""
+    fy = fx if fy is None else fy
+    h, w, cn = img.shape
+    dh, dw = int(np.rint(h * fy)), int(np.rint(w * fx))       # saturate_cast<int>(double): half to even
+    xi, xa = _u8_axis(w, dw, 1.0 / fx)                          # dsize empty: scale = 1 / inv_scale
+    yi, yb = _u8_axis(h, dh, 1.0 / fy)
+    src = img.astype(np.int64)
+    H = np.zeros((h, dw, cn), dtype=np.int64)                   # horizontal pass, int
+    for k in range(4):
+        H += src[:, xi[:, k], :] * xa[:, k][None, :, None]
+    H = H.reshape(h, dw * cn)
+    rows = [H[yi[:, k]] for k in range(4)]                      # (dh, dw*cn) each
+    scale = f32(1.0) / f32(2048 * 2048)
+    b = [(yb[:, k].astype(f32) * scale)[:, None] for k in range(4)]
+    S = [r.astype(f32) for r in rows]
+    acc = (S[0] * b[0]) + ((S[1] * b[1]) + ((S[2] * b[2]) + (S[3] * b[3])))   # float32, separate multiplies and adds
+    body = np.clip(np.rint(acc), 0, 255).astype(np.uint8)
+    t = sum(rows[k] * yb[:, k][:, None] for k in range(4))
+    tail = np.clip((t + (1 << 21)) >> 22, 0, 255).astype(np.uint8)             # FixedPtCast<int, uchar, 22>
+    n_vec = (dw * cn // lanes) * lanes
+    out = body
+    out[:, n_vec:] = tail[:, n_vec:]
+    return out.reshape(dh, dw, cn)
+
+
+# ----------------------------------------------------------------------------------------------------------
 # Result rows — evaluate.py:182-209 (append_result, --run_refactor branch)
 # ----------------------------------------------------------------------------------------------------------
 def coco_rows(peak_xy, humans):
