@@ -142,6 +142,12 @@ def lib():
     L.ibp_resized_size.argtypes = [ip, ip, C.c_double, C.c_double, C.POINTER(ip), C.POINTER(ip)]
     L.ibp_resize_image.restype = ip
     L.ibp_resize_image.argtypes = [vp, vp, ip, ip, ip, C.c_double, C.c_double, vp, ip, ip, vp]
+    L.ibp_rotation_matrix.restype = None
+    L.ibp_rotation_matrix.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
+    L.ibp_warp_affine.restype = ip
+    L.ibp_warp_affine.argtypes = [vp, vp, vp, ip, ip, ip, ip, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_double), vp]
+    L.ibp_crop_resize_accumulate.restype = ip
+    L.ibp_crop_resize_accumulate.argtypes = [vp, vp, ip, ip, ip, ip, ip, ip, ip, ip, vp, vp]
     L.ibp_find_peaks_noalloc.restype = ip
     L.ibp_find_peaks_noalloc.argtypes = [vp, ip, ip, ip, ip, ip, vp, vp, vp, vp, vp]
     L.ibp_launch_count.restype = C.c_int64
@@ -160,7 +166,7 @@ EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
            "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
            "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image", "ibp_find_peaks_noalloc",
-           "ibp_resized_size", "ibp_resize_image"]
+           "ibp_resized_size", "ibp_resize_image", "ibp_rotation_matrix", "ibp_warp_affine", "ibp_crop_resize_accumulate"]
 NOALLOC_MAX_BATCH, NOALLOC_MAX_BANDS, NOALLOC_CAP = 8, 8, 64  # include/ibp.h §5
 STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
 
@@ -194,6 +200,13 @@ def resized_size(img_h, img_w, fx, fy):
     oh, ow = C.c_int(), C.c_int()
     lib().ibp_resized_size(int(img_h), int(img_w), float(fx), float(fy), C.byref(oh), C.byref(ow))
     return oh.value, ow.value
+
+
+def rotation_matrix(cx, cy, angle_deg, scale=1.0):
+    """cv2.getRotationMatrix2D((cx, cy), angle_deg, scale) -> (2,3) float64."""
+    m = (C.c_double * 6)()
+    lib().ibp_rotation_matrix(float(cx), float(cy), float(angle_deg), float(scale), m)
+    return np.array(list(m), dtype=np.float64).reshape(2, 3)
 
 
 def default_limits():
@@ -348,6 +361,15 @@ class Handle:
 
     def resize_image(self, img_ptr, batch, img_h, img_w, fx, fy, out_ptr, out_h, out_w, stream=0):
         check(lib().ibp_resize_image(self._h, img_ptr, batch, img_h, img_w, float(fx), float(fy), out_ptr, out_h, out_w, stream))
+
+    def warp_affine(self, src_ptr, dst_ptr, batch, channels, hh, ww, strides, matrix, stream=0):
+        """strides = element strides (batch, channel, row, pixel); matrix = the forward 2x3 matrix as given to cv2.warpAffine."""
+        m = (C.c_double * 6)(*[float(v) for v in np.asarray(matrix, dtype=np.float64).reshape(6)])
+        check(lib().ibp_warp_affine(self._h, src_ptr, dst_ptr, batch, channels, hh, ww, int(strides[0]), int(strides[1]),
+                                    int(strides[2]), int(strides[3]), m, stream))
+
+    def crop_resize_accumulate(self, maps_ptr, batch, ph, pw, sh, sw, img_h, img_w, n_items, out_ptr, stream=0):
+        check(lib().ibp_crop_resize_accumulate(self._h, maps_ptr, batch, ph, pw, sh, sw, img_h, img_w, int(n_items), out_ptr, stream))
 
     def fetch(self, batch, stream=0, raise_on_overflow=True):
         view = BatchView()

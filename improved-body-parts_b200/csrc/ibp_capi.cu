@@ -22,6 +22,7 @@
 #include "k_peaks.cuh"
 #include "k_pyroute.cuh"
 #include "k_resize.cuh"
+#include "k_warp.cuh"
 #include "k_upsample.cuh"
 
 using namespace ibp;
@@ -1239,6 +1240,84 @@ int ibp_resize_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, in
     a.scale_y = 1.0 / fy;
     a.lanes = 8;
     resize_u8_cubic_kernel<<<dim3((ow + 127) / 128, oh, batch), 128, 0, (cudaStream_t)stream>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+void ibp_rotation_matrix(double cx, double cy, double angle_deg, double scale, double *m) {
+    // cv::getRotationMatrix2D (imgwarp.cpp): angle *= CV_PI / 180; alpha = cos * scale; beta = sin * scale
+    if (!m) return;
+    const double angle = angle_deg * (3.1415926535897932384626433832795 / 180);
+    const double alpha = std::cos(angle) * scale, beta = std::sin(angle) * scale;
+    cx = (double)(float)cx;  // the centre is a Point2f
+    cy = (double)(float)cy;
+    m[0] = alpha;
+    m[1] = beta;
+    m[2] = (1 - alpha) * cx - beta * cy;
+    m[3] = -beta;
+    m[4] = alpha;
+    m[5] = beta * cx + (1 - alpha) * cy;
+}
+
+int ibp_warp_affine(ibp_handle *h, const float *src, float *dst, int batch, int channels, int hh, int ww, int64_t batch_stride,
+                    int64_t chan_stride, int64_t row_stride, int64_t pix_stride, const double *m6, void *stream) {
+    if (!h || !src || !dst || !m6) return fail(IBP_ERR_ARG, "ibp_warp_affine: null argument");
+    if (src == dst) return fail(IBP_ERR_ARG, "ibp_warp_affine: in-place warp is not supported");
+    if (batch < 1 || batch > 65535 || channels < 1 || hh < 1 || ww < 1 || hh > 65535) return fail(IBP_ERR_SHAPE, "ibp_warp_affine: bad shape");
+    CU(cudaSetDevice(h->device));
+    WarpArgs a;
+    a.src = src;
+    a.dst = dst;
+    a.batch = batch;
+    a.channels = channels;
+    a.h = hh;
+    a.w = ww;
+    a.bs = batch_stride;
+    a.cs = chan_stride;
+    a.ys = row_stride;
+    a.xs = pix_stride;
+    // cv::warpAffine without WARP_INVERSE_MAP: invert the 2x3 matrix in double, operation by operation
+    double M[6];
+    for (int i = 0; i < 6; i++) M[i] = m6[i];
+    double D = M[0] * M[4] - M[1] * M[3];
+    D = D != 0 ? 1. / D : 0;
+    const double A11 = M[4] * D, A22 = M[0] * D;
+    M[0] = A11;
+    M[1] *= -D;
+    M[3] *= -D;
+    M[4] = A22;
+    const double b1 = -M[0] * M[2] - M[1] * M[5];
+    const double b2 = -M[3] * M[2] - M[4] * M[5];
+    M[2] = b1;
+    M[5] = b2;
+    for (int i = 0; i < 6; i++) a.m[i] = M[i];
+    warp_affine_kernel<<<dim3((ww + 127) / 128, hh, batch), 128, 0, (cudaStream_t)stream>>>(a);
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+int ibp_crop_resize_accumulate(ibp_handle *h, const float *maps, int batch, int ph, int pw, int sh, int sw, int img_h, int img_w, int n_items,
+                               double *out, void *stream) {
+    if (!h || !maps || !out) return fail(IBP_ERR_ARG, "ibp_crop_resize_accumulate: null argument");
+    if (batch < 1 || batch > 65535 || ph < 1 || pw < 1 || sh < 1 || sw < 1 || sh > ph || sw > pw || img_h < 1 || img_w < 1 || img_h > 65535 || n_items < 1)
+        return fail(IBP_ERR_SHAPE, "ibp_crop_resize_accumulate: bad shape (maps %dx%d, crop %dx%d, image %dx%d, %d items)", ph, pw, sh, sw, img_h, img_w, n_items);
+    CU(cudaSetDevice(h->device));
+    CropResizeArgs a;
+    a.src = maps;
+    a.batch = batch;
+    a.ph = ph;
+    a.pw = pw;
+    a.sh = sh;
+    a.sw = sw;
+    a.H = img_h;
+    a.W = img_w;
+    a.scale_x = 1.0 / ((double)img_w / (double)sw);
+    a.scale_y = 1.0 / ((double)img_h / (double)sh);
+    a.divisor = (float)n_items;
+    a.out = out;
+    crop_resize_accumulate_kernel<<<dim3((img_w + 127) / 128, img_h, batch), 128, 0, (cudaStream_t)stream>>>(a);
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;

@@ -83,17 +83,37 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
         print("Input image: '{}' is too big, shrink it!".format(input_image_path))
     pp = _processor()
     img = _scaled_image(pp, image, scale)  # l.52, on the device (a scale of exactly 1.0 is an identity)
-    batch = pp.prepare_images(img, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)  # l.54-72
-    with torch.no_grad():
-        out = model(batch)
-    if isinstance(out, (list, tuple)):
-        out = out[-1][0]  # last stack, scale 0 (l.80)
-    fused = pp.fuse_flip(out[None, ...], flip_avg)[0]  # (50,h,w)
-    hwc = fused.permute(1, 2, 0).contiguous().cpu().numpy()
+    fused = None
+    for angle in test_cfg.get('rotation_search', [0.0]):  # l.45: product([1.], rotate_angle); the LAST item is returned (l.101-102)
+        if angle == 0:
+            batch = pp.prepare_images(img, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)  # l.54-72
+        else:
+            batch, m_rev = _rotated_input(pp, img, model_cfg, angle)                                        # l.63-66
+        with torch.no_grad():
+            out = model(batch)
+        if isinstance(out, (list, tuple)):
+            out = out[-1][0]  # last stack, scale 0 (l.80)
+        fused = pp.fuse_flip(out[None, ...], flip_avg)  # (1,50,h,w)
+        if angle != 0:
+            # l.98-100: the matrix built for the PADDED INPUT size is applied to the feature-resolution maps as it is
+            fused = pp.warp_affine(fused, m_rev, "planar")
+    hwc = fused[0].permute(1, 2, 0).contiguous().cpu().numpy()
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
 
 
 @_growing
+def _rotated_input(pp, scaled, model_cfg, angle):
+    """l.54-72 / l.206-224 with angle != 0: pad, /255, cv2.warpAffine by `angle` about (rows/2, cols/2) — the reference passes
+    (shape[0]/2, shape[1]/2) as the (x, y) centre, kept — then the flipped twin of the ROTATED image.  -> (batch (2,hp,wp,3),
+    reverse matrix)."""
+    x = pp.prepare_images(scaled, model_cfg['max_downsample'], model_cfg['padValue'], flip=False)  # (1,hp,wp,3)
+    hp, wp = int(x.shape[1]), int(x.shape[2])
+    m_fwd = _lib.rotation_matrix(hp / 2, wp / 2, angle, 1)
+    m_rev = _lib.rotation_matrix(hp / 2, wp / 2, -angle, 1)
+    x = pp.warp_affine(x, m_fwd, "hwc")
+    return torch.cat((x, x.flip(2)), dim=0), m_rev
+
+
 def _scaled_image(pp, image, scale):
     """cv2.resize(image, (0, 0), fx=scale, fy=scale, interpolation=cv2.INTER_CUBIC) (l.52 / l.204) on the device:
     uint8 (h,w,3) numpy / tensor -> uint8 (1, rint(h*scale), rint(w*scale), 3) CUDA tensor."""
@@ -174,8 +194,8 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
 
     The reference computes the scale-search multipliers (l.186) and then pins them to [1.] (l.188); `scale_search=None`
     does the same.  Pass a list such as test_cfg['scale_search'] to run the multi-scale averaging the reference ships
-    but never reaches.  rotation_search is [0.0] (utils/config:15): the rotation branch (l.215-218, 265-267) is not
-    implemented.  The image goes to the device once (uint8); per scale the cubic resize (l.204), the pad to a multiple of
+    but never reaches.  rotation_search is [0.0] in utils/config:15; a non-zero angle takes the rotation branch
+    (l.215-218, 265-267; _predict_with_rotation below).  The image goes to the device once (uint8); per scale the cubic resize (l.204), the pad to a multiple of
     max_downsample with padValue, the /255 and the flipped twin (l.206-224) run there; everything after the model calls
     (flip average, cubic x stride, crop, cubic resize to the image, average) is one kernel launch."""
     img_h, img_w, _ = image.shape
@@ -183,8 +203,9 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
         multiplier = [1.]  # l.188
     else:
         multiplier = [x * model_cfg['boxsize'] / img_h for x in scale_search]  # l.186
-    if any(a != 0 for a in test_cfg.get('rotation_search', [0.0])):
-        raise NotImplementedError("rotation_search != 0 is not on the reference's path (utils/config:15)")
+    angles = list(test_cfg.get('rotation_search', [0.0]))
+    if any(a != 0 for a in angles):
+        return _predict_with_rotation(image, model, multiplier, angles, model_cfg, input_image_path, flip_avg)
     pp = _processor()
     img_dev = torch.from_numpy(np.ascontiguousarray(image)).to(pp.device)  # one upload, uint8
     outs, sizes = [], []
@@ -202,6 +223,41 @@ def predict(image, model, test_cfg, model_cfg, input_image_path, flip_avg=True, 
         sizes.append(tuple(int(v) for v in scaled.shape[1:3]))
     fused, _ = pp.fuse_multiscale(outs, sizes, img_h, img_w, flip_avg, want_heat32=False)
     hwc = fused[0].permute(1, 2, 0).contiguous().cpu().numpy()
+    return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
+
+
+def _predict_with_rotation(image, model, multiplier, angles, model_cfg, input_image_path, flip_avg):
+    """predict() when rotation_search has a non-zero angle (l.196-281, the reference's loop order product(multiplier,
+    rotate_angle)).  A warp sits between the two resizes of such an item, so the fused multi-scale kernel cannot take it;
+    per item: x4 maps at the padded size (the fused kernel with ONE scale and an identity second resize — exact), backward
+    warp (l.265-267), then crop + cubic resize to the image + /n + float64 accumulate (l.272-281) in one kernel."""
+    img_h, img_w, _ = image.shape
+    pp = _processor()
+    img_dev = torch.from_numpy(np.ascontiguousarray(image)).to(pp.device)
+    n_items = len(multiplier) * len(angles)
+    avg = torch.zeros((1, NUM_PAFS + NUM_HEATMAPS, img_h, img_w), dtype=torch.float64, device=pp.device)
+    for scale in multiplier:
+        for angle in angles:
+            if scale * img_h > 2600 or scale * img_w > 3800:  # l.196-199
+                scale = min(2600 / img_h, 3800 / img_w)
+                print("Input image: '{}' is too big, shrink it!".format(input_image_path))
+            scaled = _scaled_image(pp, img_dev, scale)
+            if angle == 0:
+                batch = pp.prepare_images(scaled, model_cfg['max_downsample'], model_cfg['padValue'], flip=True)
+            else:
+                batch, m_rev = _rotated_input(pp, scaled, model_cfg, angle)
+            with torch.no_grad():
+                out = model(batch)
+            if isinstance(out, (list, tuple)):
+                out = out[-1][0]
+            out = out.to(pp.device, torch.float32)[None, ...]
+            ph, pw = int(out.shape[3]) * model_cfg['stride'], int(out.shape[4]) * model_cfg['stride']
+            up64, _ = pp.fuse_multiscale([out], [(ph, pw)], ph, pw, flip_avg, want_heat32=False)  # l.232-263
+            up = up64.float()  # values are float32 results widened: narrowing is exact
+            if angle != 0:
+                up = pp.warp_affine(up, m_rev, "planar")
+            pp.crop_resize_accumulate(up, scaled.shape[1:3], avg, n_items)
+    hwc = avg[0].permute(1, 2, 0).contiguous().cpu().numpy()
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
 
 

@@ -102,6 +102,31 @@ class PostProcessor:
             self.handle.resize_image(images.data_ptr(), B, h, w, fx, fy, out.data_ptr(), oh, ow, _stream_ptr(self.device))
         return out
 
+    def warp_affine(self, t, matrix, layout="planar"):
+        """cv2.warpAffine(x, matrix, (0, 0)) (INTER_LINEAR, constant 0 border, same size) on a float32 CUDA tensor:
+        layout "planar" = (B,C,h,w) maps, "hwc" = (B,h,w,C) images (utils/parse_skeletons.py:215-218, :265-267, :98-100)."""
+        t = t.to(self.device, torch.float32).contiguous()
+        out = torch.empty_like(t)
+        if layout == "planar":
+            B, Cn, h, w = t.shape
+            strides = (Cn * h * w, h * w, w, 1)
+        else:
+            B, h, w, Cn = t.shape
+            strides = (h * w * Cn, 1, w * Cn, Cn)
+        with torch.cuda.device(self.device):
+            self.handle.warp_affine(t.data_ptr(), out.data_ptr(), B, Cn, h, w, strides, matrix, _stream_ptr(self.device))
+        return out
+
+    def crop_resize_accumulate(self, maps, scaled_size, out, n_items):
+        """maps (B,50,ph,pw) float32 x4 maps at the padded size -> cropped to scaled_size, cubic-resized to out's (H,W),
+        / n_items in float32, added to out (B,50,H,W) float64 (utils/parse_skeletons.py:272-281)."""
+        maps = maps.to(self.device, torch.float32).contiguous()
+        B, _, ph, pw = maps.shape
+        with torch.cuda.device(self.device):
+            self.handle.crop_resize_accumulate(maps.data_ptr(), B, ph, pw, int(scaled_size[0]), int(scaled_size[1]), out.shape[2],
+                                               out.shape[3], n_items, out.data_ptr(), _stream_ptr(self.device))
+        return out
+
     # ---- stages on tensors (used by the parse_skeletons mirror and by tests) ---------------------------------
     def fuse_flip(self, net_out, flip_avg=True):
         """(B,2,50,h,w) CUDA tensor -> (B,50,h,w) float32 CUDA tensor (K1)."""

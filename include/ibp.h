@@ -238,6 +238,22 @@ void ibp_resized_size(int img_h, int img_w, double fx, double fy, int *out_h, in
 int ibp_resize_image(ibp_handle *h, const uint8_t *img, int batch, int img_h, int img_w, double fx, double fy, uint8_t *out,
                      int out_h, int out_w, void *stream);
 
+/* The rotation_search branch (knob utils/config:15) — utils/parse_skeletons.py:215-218, :265-267
+ * (predict) and :63-66, :98-100 (predict_refactor).
+ * ibp_rotation_matrix: cv2.getRotationMatrix2D(center=(cx, cy), angle [degrees], scale) -> m[6] (2x3, row-major, double).
+ * ibp_warp_affine: cv2.warpAffine(src, M, (0, 0)) with the defaults (INTER_LINEAR, BORDER_CONSTANT 0, output size = source
+ *   size) for float32 DEVICE data of `channels` channels addressed by element strides (batch, channel, row, pixel), the
+ *   same for src and dst: planar maps (B,C,h,w) = strides (C*h*w, h*w, w, 1); an HWC image (B,h,w,3) = (h*w*3, 1, w*3, 3).
+ *   m = the FORWARD matrix as the caller would pass it to cv2 (the library inverts it like cv::warpAffine does).
+ * ibp_crop_resize_accumulate: one (scale, rotation) item of predict's tail when a warp sits between the two resizes
+ *   (l.272-281): maps (batch,50,ph,pw) planar float32 at the padded input size are cropped to (sh,sw), resized to
+ *   (img_h,img_w) with cv2's INTER_CUBIC, divided by `n_items` in float32 and ADDED to out (batch,50,img_h,img_w) float64. */
+void ibp_rotation_matrix(double cx, double cy, double angle_deg, double scale, double *m6);
+int ibp_warp_affine(ibp_handle *h, const float *src, float *dst, int batch, int channels, int hh, int ww, int64_t batch_stride,
+                    int64_t chan_stride, int64_t row_stride, int64_t pix_stride, const double *m6, void *stream);
+int ibp_crop_resize_accumulate(ibp_handle *h, const float *maps, int batch, int ph, int pw, int sh, int sw, int img_h, int img_w,
+                               int n_items, double *out, void *stream);
+
 /* Sub-pixel coordinates of the IBP_PEAKS_BOX_CENTROID flavour (utils/util.py:188-213 returns float64 x, y): after
  * ibp_fetch, copies image `image`'s (x, y) pairs in peak-id order into host_xy[capacity][2].  Returns the number of
  * peaks written (>= 0) or a negative error code. */

@@ -466,6 +466,94 @@ def cv_resize_cubic_u8(img, fx, fy=None, lanes=8):
 
 
 # ----------------------------------------------------------------------------------------------------------
+# rotation_search branch — utils/parse_skeletons.py:215-218, :265-267 (predict), :63-66, :98-100 (predict_refactor).
+# Third-party arithmetic: cv2.getRotationMatrix2D and cv2.warpAffine (INTER_LINEAR, BORDER_CONSTANT 0, same size) of OpenCV
+# 4.13 for float32 data — the fixed-point remap path (imgwarp.cpp), restated; checked against the live cv2 for 1/3/4/20/30
+# channels (tests/test_rotation.py) and pinned through goldens of the reference's own predict (tests/golden/rot_11x.npz).
+# ----------------------------------------------------------------------------------------------------------
+def rotation_matrix(cx, cy, angle_deg, scale=1.0):
+    import math
+    angle = angle_deg * (math.pi / 180)
+    alpha, beta = math.cos(angle) * scale, math.sin(angle) * scale
+    cx, cy = float(f32(cx)), float(f32(cy))  # Point2f
+    return np.array([[alpha, beta, (1 - alpha) * cx - beta * cy], [-beta, alpha, beta * cx + (1 - alpha) * cy]], dtype=np.float64)
+
+
+def warp_affine(src, matrix):
+    """cv2.warpAffine(src (h,w,c) float32, matrix, (0, 0)) with the default flags."""
+    src = np.asarray(src, dtype=f32)
+    squeeze = src.ndim == 2
+    if squeeze:
+        src = src[:, :, None]
+    h, w = src.shape[:2]
+    M = np.asarray(matrix, dtype=np.float64).reshape(-1).copy()
+    D = M[0] * M[4] - M[1] * M[3]                       # cv::warpAffine: invert (no WARP_INVERSE_MAP)
+    D = 1. / D if D != 0 else 0.
+    A11, A22 = M[4] * D, M[0] * D
+    M[0] = A11
+    M[1] *= -D
+    M[3] *= -D
+    M[4] = A22
+    b1 = -M[0] * M[2] - M[1] * M[5]
+    b2 = -M[3] * M[2] - M[4] * M[5]
+    M[2], M[5] = b1, b2
+    x, y = np.arange(w, dtype=np.float64), np.arange(h, dtype=np.float64)
+    rint = lambda v: np.rint(v).astype(np.int64)        # saturate_cast<int>(double)
+    adelta, bdelta = rint(M[0] * x * 1024), rint(M[3] * x * 1024)
+    X0, Y0 = rint((M[1] * y + M[2]) * 1024) + 16, rint((M[4] * y + M[5]) * 1024) + 16
+    X, Y = (X0[:, None] + adelta[None, :]) >> 5, (Y0[:, None] + bdelta[None, :]) >> 5
+    sx, sy = np.clip(X >> 5, -32768, 32767), np.clip(Y >> 5, -32768, 32767)
+    t = (np.arange(32, dtype=f32) * f32(1.0 / 32)).astype(f32)
+    c0, c1 = (f32(1) - t).astype(f32), t
+    fx, fy = X & 31, Y & 31
+    w00, w01 = c0[fy] * c0[fx], c0[fy] * c1[fx]
+    w10, w11 = c1[fy] * c0[fx], c1[fy] * c1[fx]
+
+    def px(yy, xx):
+        ok = (yy >= 0) & (yy < h) & (xx >= 0) & (xx < w)
+        return np.where(ok[..., None], src[np.clip(yy, 0, h - 1), np.clip(xx, 0, w - 1)], f32(0))
+
+    out = px(sy, sx) * w00[..., None]
+    out = out + px(sy, sx + 1) * w01[..., None]
+    out = out + px(sy + 1, sx) * w10[..., None]
+    out = out + px(sy + 1, sx + 1) * w11[..., None]
+    return out[:, :, 0] if squeeze else out
+
+
+def rotated_input(scaled_u8, angle, max_downsample=64, pad_value=128):
+    """l.206-224 with a rotation: pad, /255, warpAffine about (rows/2, cols/2) given as (x, y), flipped twin of the rotated
+    image.  -> ((2,hp,wp,3) float32, reverse matrix)."""
+    x = prepare_input(scaled_u8, max_downsample, pad_value, flip=False)[0]
+    if angle != 0:
+        m_fwd = rotation_matrix(x.shape[0] / 2, x.shape[1] / 2, angle, 1)
+        x = warp_affine(x, m_fwd)
+    m_rev = rotation_matrix(x.shape[0] / 2, x.shape[1] / 2, -angle, 1)
+    return np.concatenate((x[None, ...], x[:, ::-1, :][None, ...]), axis=0), m_rev
+
+
+def predict_fuse_rot(items, img_h, img_w, stride=4, flip_avg=True):
+    """predict() after the model calls with a rotation search.  items, in the reference's loop order: (net_out (2,50,h,w),
+    scaled (sh,sw), angle).  -> heatmap_avg (H,W,20), paf_avg (H,W,30) float64."""
+    heatmap_avg = np.zeros((img_h, img_w, NUM_HEATMAPS))
+    paf_avg = np.zeros((img_h, img_w, NUM_PAFS))
+    n = len(items)
+    for out, (sh, sw), angle in items:
+        pad_h, pad_w = out.shape[2] * stride, out.shape[3] * stride
+        heat, paf = fuse_flip(out, flip_avg)
+        heat = cv_resize_cubic(heat, pad_h, pad_w, 1.0 / stride, 1.0 / stride)
+        paf = cv_resize_cubic(paf, pad_h, pad_w, 1.0 / stride, 1.0 / stride)
+        if angle != 0:                                                                  # l.265-267
+            m_rev = rotation_matrix(pad_h / 2, pad_w / 2, -angle, 1)
+            heat, paf = warp_affine(heat, m_rev), warp_affine(paf, m_rev)
+        heat, paf = heat[:sh, :sw, :], paf[:sh, :sw, :]
+        heat = cv_resize_cubic(heat, img_h, img_w)
+        paf = cv_resize_cubic(paf, img_h, img_w)
+        heatmap_avg = heatmap_avg + heat / n
+        paf_avg = paf_avg + paf / n
+    return heatmap_avg, paf_avg
+
+
+# ----------------------------------------------------------------------------------------------------------
 # Result rows — evaluate.py:182-209 (append_result, --run_refactor branch)
 # ----------------------------------------------------------------------------------------------------------
 def coco_rows(peak_xy, humans):
