@@ -101,7 +101,6 @@ def predict_refactor(image, model, test_cfg, model_cfg, input_image_path, flip_a
     return hwc[:, :, NUM_PAFS:NUM_PAFS + NUM_HEATMAPS].copy(), hwc[:, :, :NUM_PAFS].copy()
 
 
-@_growing
 def _rotated_input(pp, scaled, model_cfg, angle):
     """l.54-72 / l.206-224 with angle != 0: pad, /255, cv2.warpAffine by `angle` about (rows/2, cols/2) — the reference passes
     (shape[0]/2, shape[1]/2) as the (x, y) centre, kept — then the flipped twin of the ROTATED image.  -> (batch (2,hp,wp,3),
@@ -126,6 +125,7 @@ def _scaled_image(pp, image, scale):
     return pp.resize_images(t, scale)
 
 
+@_growing
 def heatmap_nms(heatmaps, upsample_factor=1., bool_refine_center=True):
     """heatmaps (h,w,>=18) float32 HWC -> list of 18 arrays (n,4) float32 [x, y, score, id] (l.126-176).
     bool_refine_center=False (l.163-166): no patch refine — x, y = compute_resized_coords(pixel) = (p + 0.5) * f - 0.5 in
