@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -19,6 +20,7 @@
 #include "k_glue.cuh"
 #include "k_limbs.cuh"
 #include "k_multiscale.cuh"
+#include "k_msstrip.cuh"
 #include "k_peaks.cuh"
 #include "k_pyroute.cuh"
 #include "k_resize.cuh"
@@ -150,6 +152,10 @@ struct ibp_handle {
     size_t timeline_pk_n = 0;
     float *d_fused = nullptr;
     size_t fused_floats = 0;
+    // strip form of the multi-scale kernel: per-column tap tables of every scale (device + pinned staging), cached by shape
+    SsXEntry *d_ms_xtab = nullptr, *h_ms_xtab = nullptr;
+    size_t ms_xtab_cap = 0;
+    std::vector<int> ms_xtab_key;
     void *d_stage = nullptr;  // host input staging / legacy limb map
     size_t stage_bytes = 0;
     // pinned host mirrors
@@ -234,6 +240,8 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_n_humans);
     free_dev(h->d_status);
     free_dev(h->d_fused);
+    free_dev(h->d_ms_xtab);
+    free_host(h->h_ms_xtab);
     free_dev(h->d_stage);
     free_dev(h->d_band_peaks);
     free_dev(h->d_band_subpix);
@@ -485,6 +493,8 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_strip_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(fuse_strip_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -544,6 +554,189 @@ int ibp_fuse_flip(ibp_handle *h, const void *net_out, int dtype, int batch, int 
     return IBP_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------ K1 multi-scale, strip form
+namespace {
+
+// Host mirror of cubic_weights / ms_tap (ibp_device.cuh, k_multiscale.cuh): plain IEEE float and double operations in the
+// same order, no contraction (the library is built with -ffp-contract=off for the host too), so the tables hold the
+// very bits the device would compute.
+void host_cubic_weights(float t, float *w) {
+    const float A = -0.75f;
+    const float t1 = t + 1.0f, u = 1.0f - t;
+    float x = A * t1;
+    x = x - 5.0f * A;
+    x = x * t1;
+    x = x + 8.0f * A;
+    x = x * t1;
+    w[0] = x - 4.0f * A;
+    x = (A + 2.0f) * t;
+    x = x - (A + 3.0f);
+    x = x * t;
+    x = x * t;
+    w[1] = x + 1.0f;
+    x = (A + 2.0f) * u;
+    x = x - (A + 3.0f);
+    x = x * u;
+    x = x * u;
+    w[2] = x + 1.0f;
+    x = 1.0f - w[0];
+    x = x - w[1];
+    w[3] = x - w[2];
+}
+int host_ms_tap(int d, double scale, float *w) {
+    double t = (double)d + 0.5;
+    t = t * scale;
+    t = t - 0.5;
+    float f = (float)t;
+    const int s = (int)floorf(f);
+    f = f - (float)s;
+    host_cubic_weights(f, w);
+    return s;
+}
+inline int floor_div4(int v) { return v >= 0 ? v / 4 : -((-v + 3) / 4); }
+
+// Returns IBP_OK with *used = true when the strip kernel took the call; *used = false when the shape is outside what it
+// handles (the tile kernel then runs).
+int launch_fuse_strip(ibp_handle *h, const MsArgs &m, int batch, cudaStream_t st, bool *used) {
+    *used = false;
+    static const char *force = getenv("IBP_MS_KERNEL");  // "tile" / "strip": experiments and the tests that hold both to the goldens
+    if (!force || strcmp(force, "strip")) return IBP_OK;  // opt-in until it beats the tile kernel
+    const int H = m.H, W = m.W, ns = m.n_scales;
+    if (H < kSsRows || (size_t)batch * kLayers > 65535u) return IBP_OK;
+    const int n_strips = (W + kSsCols - 1) / kSsCols;
+
+    // per-row tables of the whole image, and from them the exact sizes of the rolling buffers
+    std::vector<SsYEntry> ytab((size_t)ns * H);
+    std::vector<SsXEntry> xtab((size_t)ns * W);
+    auto sa = std::make_unique<SsArgs>();
+    SsArgs &a = *sa;
+    memset(&a, 0, sizeof(SsArgs) - sizeof(a.ytab));
+    int nc_max = 1, cap_max = 2, s1_max = 4, nfx_max = 4, hist_floats = 0;
+    for (int s = 0; s < ns; s++) {
+        const MsScale &S = m.sc[s];
+        for (int Y = 0; Y < H; Y++) {
+            SsYEntry &e = ytab[(size_t)s * H + Y];
+            const int y0 = host_ms_tap(Y, S.scale_y, e.w) - 1;
+            e.g = floor_div4(y0 + 1);
+            e.o = y0 - (4 * e.g - 2);
+        }
+        for (int X = 0; X < W; X++) {
+            SsXEntry &e = xtab[(size_t)s * W + X];
+            e.xv0 = host_ms_tap(X, S.scale_x, e.w) - 1;
+            e.pad[0] = e.pad[1] = e.pad[2] = 0;
+        }
+        int n_kx_s = 1;
+        for (int X0 = 0; X0 < W; X0 += kSsCols) {
+            const int x_lo = xtab[(size_t)s * W + X0].xv0, x_hi = xtab[(size_t)s * W + std::min(X0 + kSsCols - 1, W - 1)].xv0 + 3;
+            nc_max = std::max(nc_max, x_hi - x_lo + 1);
+            const int kx_lo = floor_div4(std::min(std::max(x_lo, 0), S.sw - 1) - 2), kx_hi = floor_div4(std::min(std::max(x_hi, 0), S.sw - 1) - 2);
+            n_kx_s = std::max(n_kx_s, kx_hi - kx_lo + 1);
+        }
+        SsScale &D = a.sc[s];
+        D.src = S.src;
+        D.h = S.h, D.w = S.w, D.sh = S.sh, D.sw = S.sw;
+        D.s1 = 4 * n_kx_s;
+        D.hist_off = hist_floats;
+        D.kprime = floor_div4(S.sh - 3);
+        hist_floats += 4 * D.s1;
+        s1_max = std::max(s1_max, D.s1);
+        nfx_max = std::max(nfx_max, n_kx_s + 3);
+    }
+    // rows per launch (the per-row table travels in the parameter space) and per warp
+    int rows_cap = (kSsYCap / ns) & ~(kSsRows - 1);
+    if (rows_cap < kSsRows) return IBP_OK;
+    const long long items_wanted = 16LL * h->sm_count * 16;  // ~16 waves of resident warps
+    const long long per_chain = (long long)n_strips * kLayers * batch;
+    long long chains = std::max(1LL, (items_wanted + per_chain - 1) / per_chain);
+    int chain_rows = (int)((H + chains - 1) / chains);
+    chain_rows = std::max(40, chain_rows);
+    chain_rows = std::min((chain_rows + kSsRows - 1) & ~(kSsRows - 1), rows_cap);
+    const int chunk_rows = (rows_cap / chain_rows) * chain_rows;
+    // row groups a phase produces: exact, from the table, for the segment boundaries this launch plan creates
+    for (int s = 0; s < ns; s++) {
+        const SsYEntry *yt = &ytab[(size_t)s * H];
+        int cap = 2;
+        for (int c0 = 0; c0 < H; c0 += chunk_rows)
+            for (int Yc = c0; Yc < std::min(c0 + chunk_rows, H); Yc += chain_rows) {
+                const int Yc1 = std::min(std::min(Yc + chain_rows, c0 + chunk_rows), H);
+                int g_cur = yt[Yc].g;
+                for (int Ys = Yc; Ys < Yc1; Ys += kSsRows) {
+                    const int g_need = yt[std::min(Ys + kSsRows, Yc1) - 1].g;
+                    cap = std::max(cap, g_need - g_cur);
+                    g_cur = g_need;
+                }
+            }
+        a.sc[s].cap = cap;
+        cap_max = std::max(cap_max, cap);
+    }
+    if (cap_max > kSsMaxNew) return IBP_OK;  // a down-scale this steep: the tile kernel
+    const int t1_rows = std::max(cap_max, 5);
+    a.it_stride = 16 * (cap_max | 1);  // an odd number of 16-byte slots per column: conflict-free 128-bit stores
+    a.f_stride = (nfx_max + 1) & ~1;
+    size_t off = ((size_t)nc_max * a.it_stride + 15) & ~(size_t)15;
+    a.off_t1 = (int)off;
+    off += (size_t)t1_rows * s1_max * sizeof(float);
+    a.off_f = (int)off;
+    off += (((size_t)t1_rows * a.f_stride * sizeof(float)) + 15) & ~(size_t)15;
+    a.off_hist = (int)off;
+    off += (size_t)hist_floats * sizeof(float);
+    a.off_tw = (int)off;
+    off += 32 * sizeof(float) + 2 * kMsMaxScales * sizeof(int);
+    const size_t smem = off;
+    if (smem > 48 * 1024) return IBP_OK;
+
+    // per-column tables on the device (cached by shape)
+    std::vector<int> key = {W, ns};
+    for (int s = 0; s < ns; s++) key.push_back(m.sc[s].sw);
+    const size_t n_x = (size_t)ns * W;
+    if (key != h->ms_xtab_key) {
+        if (h->ms_xtab_cap < n_x) {
+            CU(cudaDeviceSynchronize());
+            free_dev(h->d_ms_xtab);
+            free_host(h->h_ms_xtab);
+            h->ms_xtab_cap = 0;
+            CU(cudaMalloc(&h->d_ms_xtab, n_x * sizeof(SsXEntry)));
+            CU(cudaMallocHost(&h->h_ms_xtab, n_x * sizeof(SsXEntry)));
+            h->ms_xtab_cap = n_x;
+        } else {
+            CU(cudaStreamSynchronize(st));  // the staging buffer may still feed an earlier copy
+        }
+        memcpy(h->h_ms_xtab, xtab.data(), n_x * sizeof(SsXEntry));
+        CU(cudaMemcpyAsync(h->d_ms_xtab, h->h_ms_xtab, n_x * sizeof(SsXEntry), cudaMemcpyHostToDevice, st));
+        h->ms_xtab_key = key;
+    }
+    for (int s = 0; s < ns; s++) a.sc[s].xtab = h->d_ms_xtab + (size_t)s * W;
+
+    a.n_scales = ns;
+    a.flip = m.flip;
+    a.H = H;
+    a.W = W;
+    a.one = 1.0f;
+    a.out = m.out;
+    a.heat32 = m.heat32;
+    a.chain_rows = chain_rows;
+    const bool pow2 = (ns & (ns - 1)) == 0;
+    {
+        StageTimer t(h, IBP_STAGE_FUSE, st);
+        for (int y0 = 0; y0 < H; y0 += chunk_rows) {
+            const int y1 = std::min(y0 + chunk_rows, H), n = y1 - y0;
+            a.y0 = y0;
+            a.y1 = y1;
+            for (int s = 0; s < ns; s++) memcpy(&a.ytab[(size_t)s * n], &ytab[(size_t)s * H + y0], (size_t)n * sizeof(SsYEntry));
+            const dim3 grid(n_strips, (n + chain_rows - 1) / chain_rows, (unsigned)batch * kLayers);
+            if (pow2) fuse_strip_kernel<true><<<grid, kSsCols, smem, st>>>(a);
+            else fuse_strip_kernel<false><<<grid, kSsCols, smem, st>>>(a);
+            h->launches++;
+        }
+    }
+    CU(cudaGetLastError());
+    *used = true;
+    return IBP_OK;
+}
+
+}  // namespace
+
 // ------------------------------------------------------------------------------------------------ K1 multi-scale
 int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w, int flip_avg,
                         double *out, float *heat32, void *stream) {
@@ -577,6 +770,11 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
         S.scale_x = 1.0 / ((double)img_w / (double)in.sw);
         S.scale_y = 1.0 / ((double)img_h / (double)in.sh);
         max_nkx = std::max(max_nkx, ms_footprint(S.scale_x, S.scale_y, 0).n_kx);
+    }
+    {
+        bool used = false;
+        const int rc = launch_fuse_strip(h, a, batch, (cudaStream_t)stream, &used);
+        if (rc != IBP_OK || used) return rc;
     }
     // every scale narrow enough: the variant with compile-time row strides
     const size_t stride = (4 * max_nkx <= (size_t)kMsStride) ? kMsStride : 0;
