@@ -493,8 +493,6 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(upsample_limbs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(fuse_strip_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(fuse_strip_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<kMsStride, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(fuse_multiscale_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -639,7 +637,7 @@ int launch_fuse_strip(ibp_handle *h, const MsArgs &m, int batch, cudaStream_t st
         D.s1 = 4 * n_kx_s;
         D.hist_off = hist_floats;
         D.kprime = floor_div4(S.sh - 3);
-        hist_floats += 4 * D.s1;
+        hist_floats += kSsHist * D.s1;
         s1_max = std::max(s1_max, D.s1);
         nfx_max = std::max(nfx_max, n_kx_s + 3);
     }
@@ -671,18 +669,21 @@ int launch_fuse_strip(ibp_handle *h, const MsArgs &m, int batch, cudaStream_t st
         cap_max = std::max(cap_max, cap);
     }
     if (cap_max > kSsMaxNew) return IBP_OK;  // a down-scale this steep: the tile kernel
-    const int t1_rows = std::max(cap_max, 5);
-    a.it_stride = 16 * (cap_max | 1);  // an odd number of 16-byte slots per column: conflict-free 128-bit stores
+    const int t1_rows = kSsHist + std::max(cap_max, 5);
+    const int slots = cap_max | 1;  // an odd number of 16-byte slots per column: conflict-free 128-bit stores
+    const int it_stride = 16 * slots;
     a.f_stride = (nfx_max + 1) & ~1;
-    size_t off = ((size_t)nc_max * a.it_stride + 15) & ~(size_t)15;
+    // I_T first; stage A's feature rows share its space (B has consumed them before C writes I_T)
+    size_t off = std::max((size_t)nc_max * it_stride, (size_t)kSsMaxNew * a.f_stride * sizeof(float));
+    off = (off + 15) & ~(size_t)15;
     a.off_t1 = (int)off;
     off += (size_t)t1_rows * s1_max * sizeof(float);
-    a.off_f = (int)off;
-    off += (((size_t)t1_rows * a.f_stride * sizeof(float)) + 15) & ~(size_t)15;
     a.off_hist = (int)off;
     off += (size_t)hist_floats * sizeof(float);
     a.off_tw = (int)off;
-    off += 32 * sizeof(float) + 2 * kMsMaxScales * sizeof(int);
+    off += 32 * sizeof(float) + 2 * kMsMaxScales * sizeof(int) + kMsMaxScales * sizeof(int4);
+    a.off_pf = (int)off;
+    off += 2 * (size_t)kSsMaxNew * a.f_stride * sizeof(float);
     const size_t smem = off;
     if (smem > 48 * 1024) return IBP_OK;
 
@@ -717,6 +718,8 @@ int launch_fuse_strip(ibp_handle *h, const MsArgs &m, int batch, cudaStream_t st
     a.heat32 = m.heat32;
     a.chain_rows = chain_rows;
     const bool pow2 = (ns & (ns - 1)) == 0;
+    // rows of the interleaved 30- / 20-channel images that do not end on a multiple of four elements have a scalar tail
+    const bool tail = ((W * kLimbs) & 3) != 0 || ((W * (kLayers - kLimbs)) & 3) != 0;
     {
         StageTimer t(h, IBP_STAGE_FUSE, st);
         for (int y0 = 0; y0 < H; y0 += chunk_rows) {
@@ -725,8 +728,17 @@ int launch_fuse_strip(ibp_handle *h, const MsArgs &m, int batch, cudaStream_t st
             a.y1 = y1;
             for (int s = 0; s < ns; s++) memcpy(&a.ytab[(size_t)s * n], &ytab[(size_t)s * H + y0], (size_t)n * sizeof(SsYEntry));
             const dim3 grid(n_strips, (n + chain_rows - 1) / chain_rows, (unsigned)batch * kLayers);
-            if (pow2) fuse_strip_kernel<true><<<grid, kSsCols, smem, st>>>(a);
-            else fuse_strip_kernel<false><<<grid, kSsCols, smem, st>>>(a);
+            void (*kern)(const SsArgs) = nullptr;
+#define IBP_SS_PICK(N) (tail ? (pow2 ? fuse_strip_kernel<N, true, true> : fuse_strip_kernel<N, false, true>) \
+                             : (pow2 ? fuse_strip_kernel<N, true, false> : fuse_strip_kernel<N, false, false>))
+            switch (slots) {
+                case 3: kern = IBP_SS_PICK(3); break;
+                case 5: kern = IBP_SS_PICK(5); break;
+                case 7: kern = IBP_SS_PICK(7); break;
+                default: kern = IBP_SS_PICK(9); break;
+            }
+#undef IBP_SS_PICK
+            kern<<<grid, kSsCols, smem, st>>>(a);
             h->launches++;
         }
     }

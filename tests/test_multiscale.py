@@ -167,3 +167,19 @@ def test_cv2_fusion_route_equals_restatement():
         a = O.predict_fuse(outs, img_h, img_w, [s[0] for s in shapes])
         b = cpu_path.predict_fuse_cv2(outs, img_h, img_w, [s[0] for s in shapes])
         assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+@pytest.mark.gpu
+def test_gpu_strip_kernel_exact_in_subprocess():
+    """The opt-in strip form of the fusion kernel (csrc/k_msstrip.cuh, IBP_MS_KERNEL=strip, read once per process) against
+    the same goldens of the reference's predict and the configs2 bench image, in a process of its own."""
+    import subprocess
+    import sys
+    if os.environ.get("IBP_MS_KERNEL") == "strip":
+        pytest.skip("already inside the strip-kernel run")
+    env = dict(os.environ, IBP_MS_KERNEL="strip")
+    res = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-k",
+                          "fuse_multiscale_exact or predict_mirror or configs2_exact or device_resident"],
+                         env=env, capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert " passed" in res.stdout
