@@ -107,6 +107,10 @@ def lib():
     L.ibp_fuse_flip.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
     L.ibp_fuse_multiscale.restype = ip
     L.ibp_fuse_multiscale.argtypes = [vp, C.POINTER(ScaleInput), ip, ip, ip, ip, ip, vp, vp, vp]
+    L.ibp_fuse_multiscale_linear.restype = ip
+    L.ibp_fuse_multiscale_linear.argtypes = [vp, C.POINTER(ScaleInput), ip, ip, ip, ip, ip, vp, vp, vp]
+    L.ibp_smooth_gaussian.restype = ip
+    L.ibp_smooth_gaussian.argtypes = [vp, vp, vp, ip, ip, ip, ip, C.c_float, vp]
     L.ibp_upsample_limbs.restype = ip
     L.ibp_upsample_limbs.argtypes = [vp, vp, ip, ip, ip, ip, ip, vp, vp]
     L.ibp_find_peaks.restype = ip
@@ -166,9 +170,10 @@ EXPORTS = ["ibp_process_paf", "ibp_get_num_humans", "ibp_get_part_peak_id", "ibp
            "ibp_find_peaks", "ibp_set_peaks", "ibp_assign", "ibp_postprocess_batch", "ibp_fetch", "ibp_fetch_subpix", "ibp_default_py_params", "ibp_set_peaks64", "ibp_find_connections",
            "ibp_fetch_connections", "ibp_set_connections", "ibp_find_humans", "ibp_fetch_people", "ibp_launch_count", "ibp_set_profiling",
            "ibp_get_stage_ms", "ibp_fetch_coco", "ibp_prepare_image", "ibp_find_peaks_noalloc",
-           "ibp_resized_size", "ibp_resize_image", "ibp_rotation_matrix", "ibp_warp_affine", "ibp_crop_resize_accumulate"]
+           "ibp_resized_size", "ibp_resize_image", "ibp_rotation_matrix", "ibp_warp_affine", "ibp_crop_resize_accumulate",
+           "ibp_fuse_multiscale_linear", "ibp_smooth_gaussian"]
 NOALLOC_MAX_BATCH, NOALLOC_MAX_BANDS, NOALLOC_CAP = 8, 8, 64  # include/ibp.h §5
-STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample"]
+STAGES = ["fuse", "peaks", "pack", "limbs", "group", "upsample", "smooth"]
 
 
 def check(rc):
@@ -278,11 +283,17 @@ class Handle:
     def fuse_flip(self, net_out_ptr, dtype, batch, fh, fw, fused_ptr, flip_avg=True, stream=0):
         check(lib().ibp_fuse_flip(self._h, net_out_ptr, dtype, batch, fh, fw, int(bool(flip_avg)), fused_ptr, stream))
 
-    def fuse_multiscale(self, scales, batch, img_h, img_w, out_ptr, heat32_ptr=None, flip_avg=True, stream=0):
-        """scales: [(net_out_ptr, fh, fw, sh, sw)] per scale of the search."""
+    def fuse_multiscale(self, scales, batch, img_h, img_w, out_ptr, heat32_ptr=None, flip_avg=True, stream=0, interp="cubic"):
+        """scales: [(net_out_ptr, fh, fw, sh, sw)] per scale of the search.  interp: "cubic" = the reference's operator,
+        "linear" = the second operator mode (ibp_fuse_multiscale_linear)."""
         arr = (ScaleInput * len(scales))(*[ScaleInput(int(p), int(fh), int(fw), int(sh), int(sw)) for p, fh, fw, sh, sw in scales])
-        check(lib().ibp_fuse_multiscale(self._h, arr, len(scales), batch, img_h, img_w, int(bool(flip_avg)), out_ptr,
-                                        heat32_ptr, stream))
+        if interp not in ("cubic", "linear"):
+            raise ValueError("interp must be 'cubic' or 'linear', got %r" % (interp,))
+        fn = lib().ibp_fuse_multiscale if interp == "cubic" else lib().ibp_fuse_multiscale_linear
+        check(fn(self._h, arr, len(scales), batch, img_h, img_w, int(bool(flip_avg)), out_ptr, heat32_ptr, stream))
+
+    def smooth_gaussian(self, maps_ptr, out_ptr, planes, img_h, img_w, ksize, sigma, stream=0):
+        check(lib().ibp_smooth_gaussian(self._h, maps_ptr, out_ptr, planes, img_h, img_w, int(ksize), float(sigma), stream))
 
     def upsample_limbs(self, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream=0):
         check(lib().ibp_upsample_limbs(self._h, fused_ptr, chan_stride, batch, fh, fw, up, out_ptr, stream))

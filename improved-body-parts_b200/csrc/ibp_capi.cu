@@ -21,6 +21,7 @@
 #include "k_limbs.cuh"
 #include "k_multiscale.cuh"
 #include "k_msstrip.cuh"
+#include "k_linear.cuh"
 #include "k_peaks.cuh"
 #include "k_pyroute.cuh"
 #include "k_resize.cuh"
@@ -156,6 +157,10 @@ struct ibp_handle {
     SsXEntry *d_ms_xtab = nullptr, *h_ms_xtab = nullptr;
     size_t ms_xtab_cap = 0;
     std::vector<int> ms_xtab_key;
+    // bilinear operator mode: composed tap tables of every scale (x then y), cached by shape
+    LinTap *d_lin_tab = nullptr, *h_lin_tab = nullptr;
+    size_t lin_tab_cap = 0;
+    std::vector<int> lin_tab_key;
     void *d_stage = nullptr;  // host input staging / legacy limb map
     size_t stage_bytes = 0;
     // pinned host mirrors
@@ -242,6 +247,8 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_fused);
     free_dev(h->d_ms_xtab);
     free_host(h->h_ms_xtab);
+    free_dev(h->d_lin_tab);
+    free_host(h->h_lin_tab);
     free_dev(h->d_stage);
     free_dev(h->d_band_peaks);
     free_dev(h->d_band_subpix);
@@ -807,6 +814,177 @@ int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scal
         auto kern = stride ? (pow2 ? fuse_multiscale_kernel<kMsStride, true> : fuse_multiscale_kernel<kMsStride, false>)
                            : (pow2 ? fuse_multiscale_kernel<0, true> : fuse_multiscale_kernel<0, false>);
         kern<<<grid, kMsThreads, smem, (cudaStream_t)stream>>>(a);
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------ second operator mode
+namespace {
+
+struct Lin1 {
+    int i0, i1;
+    float a0, a1;
+};
+// cv2.resize INTER_LINEAR, one axis: source coordinate (d + 0.5) * scale - 0.5 in float, taps floor and floor + 1, the
+// fraction forced to 0 where the pair would leave the source (resize.cpp, the xofs / alpha set-up of the generic path)
+Lin1 cv_linear_tap(int d, double scale, int n_src) {
+    double t = (double)d + 0.5;
+    t = t * scale;
+    t = t - 0.5;
+    float f = (float)t;
+    int s = (int)floorf(f);
+    f = f - (float)s;
+    if (s < 0) f = 0.f, s = 0;
+    if (s >= n_src - 1) f = 0.f, s = n_src - 1;
+    return {s, std::min(s + 1, n_src - 1), 1.0f - f, f};
+}
+// destination index d of the second resize (crop of n_crop -> n_dst) composed with the x4 resize (n_feat -> 4 n_feat)
+bool lin_compose(int d, double scale2, int n_crop, int n_feat, float fold, LinTap *out) {
+    const Lin1 t2 = cv_linear_tap(d, scale2, n_crop);
+    int idx[4];
+    float wgt[4];
+    const int u[2] = {t2.i0, t2.i1};
+    const float b[2] = {t2.a0, t2.a1};
+    for (int k = 0; k < 2; k++) {
+        const Lin1 t1 = cv_linear_tap(u[k], 0.25, n_feat);
+        idx[2 * k] = t1.i0, wgt[2 * k] = b[k] * t1.a0;
+        idx[2 * k + 1] = t1.i1, wgt[2 * k + 1] = b[k] * t1.a1;
+    }
+    int first = idx[0];
+    for (int k = 1; k < 4; k++) first = std::min(first, idx[k]);
+    const int base = std::max(0, std::min(first, n_feat - 3));
+    out->base = base;
+    out->c[0] = out->c[1] = out->c[2] = 0.f;
+    for (int k = 0; k < 4; k++) {
+        const int j = idx[k] - base;
+        if (j < 0 || j > 2) return false;
+        out->c[j] += wgt[k] * fold;
+    }
+    return true;
+}
+
+}  // namespace
+
+int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w, int flip_avg,
+                               double *out, float *heat32, void *stream) {
+    if (!h || !scales || !out) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale_linear: null argument");
+    if (n_scales < 1 || n_scales > kLinMaxScales) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale_linear: 1..%d scales, got %d", kLinMaxScales, n_scales);
+    if (batch < 1 || img_h < 1 || img_w < 1 || (size_t)batch * kLayers > 65535u) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: bad shape");
+    if (h->P.upsample != 4) return fail(IBP_ERR_ARG, "ibp_fuse_multiscale_linear: supports stride 4 only (params.upsample = %d)", h->P.upsample);
+    CU(cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int H = img_h, W = img_w, ns = n_scales;
+    std::vector<int> key = {H, W, ns};
+    for (int s = 0; s < ns; s++) {
+        const ibp_scale_input &in = scales[s];
+        if (!in.net_out || in.fh < 3 || in.fw < 3 || in.sh < 1 || in.sw < 1 || in.sh > in.fh * 4 || in.sw > in.fw * 4)
+            return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d: feature (%d,%d), scaled image (%d,%d)", s, in.fh, in.fw, in.sh, in.sw);
+        key.insert(key.end(), {in.fh, in.fw, in.sh, in.sw});
+    }
+    const size_t n_tab = (size_t)ns * (W + H);
+    if (key != h->lin_tab_key) {
+        std::vector<LinTap> tab(n_tab);
+        const float fold = 1.0f / (float)ns;  // "/ n_scales" of parse_skeletons.py:280-281, folded into the row weights
+        for (int s = 0; s < ns; s++) {
+            const ibp_scale_input &in = scales[s];
+            const double sx = 1.0 / ((double)W / (double)in.sw), sy = 1.0 / ((double)H / (double)in.sh);
+            LinTap *xt = &tab[(size_t)s * (W + H)], *yt = xt + W;
+            for (int X = 0; X < W; X++)
+                if (!lin_compose(X, sx, in.sw, in.fw, 1.0f, &xt[X])) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: taps of column %d span more than three", X);
+            for (int Y = 0; Y < H; Y++)
+                if (!lin_compose(Y, sy, in.sh, in.fh, fold, &yt[Y])) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: taps of row %d span more than three", Y);
+        }
+        if (h->lin_tab_cap < n_tab) {
+            CU(cudaDeviceSynchronize());
+            free_dev(h->d_lin_tab);
+            free_host(h->h_lin_tab);
+            h->lin_tab_cap = 0;
+            CU(cudaMalloc(&h->d_lin_tab, n_tab * sizeof(LinTap)));
+            CU(cudaMallocHost(&h->h_lin_tab, n_tab * sizeof(LinTap)));
+            h->lin_tab_cap = n_tab;
+        } else {
+            CU(cudaStreamSynchronize(st));  // the staging buffer may still feed an earlier copy
+        }
+        memcpy(h->h_lin_tab, tab.data(), n_tab * sizeof(LinTap));
+        CU(cudaMemcpyAsync(h->d_lin_tab, h->h_lin_tab, n_tab * sizeof(LinTap), cudaMemcpyHostToDevice, st));
+        h->lin_tab_key = key;
+    }
+    LinArgs a;
+    memset(&a, 0, sizeof(a));
+    for (int s = 0; s < ns; s++) {
+        a.sc[s].src = scales[s].net_out;
+        a.sc[s].h = scales[s].fh;
+        a.sc[s].w = scales[s].fw;
+        a.sc[s].xtab = h->d_lin_tab + (size_t)s * (W + H);
+        a.sc[s].ytab = a.sc[s].xtab + W;
+    }
+    a.n_scales = ns;
+    a.flip = flip_avg ? 1 : 0;
+    a.H = H;
+    a.W = W;
+    a.out = out;
+    a.heat32 = heat32;
+    // rows per warp: enough chains for ~8 waves of 16 resident CTAs per SM, at least 32 rows each (a chain start costs three feature rows)
+    const long long cols = (W + kLinThreads - 1) / kLinThreads;
+    const long long per_chain = cols * kLayers * batch;
+    const long long want = 8LL * 16 * h->sm_count;
+    const long long chains = std::max(1LL, std::min((long long)(H + 31) / 32, (want + per_chain - 1) / per_chain));
+    a.chain_rows = (int)((H + chains - 1) / chains);
+    const dim3 grid((unsigned)cols, (unsigned)((H + a.chain_rows - 1) / a.chain_rows), (unsigned)batch * kLayers);
+    {
+        StageTimer t(h, IBP_STAGE_FUSE, st);
+        switch (ns) {
+            case 1: fuse_linear_kernel<1><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 2: fuse_linear_kernel<2><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 3: fuse_linear_kernel<3><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 4: fuse_linear_kernel<4><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 5: fuse_linear_kernel<5><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 6: fuse_linear_kernel<6><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 7: fuse_linear_kernel<7><<<grid, kLinThreads, 0, st>>>(a); break;
+            default: fuse_linear_kernel<8><<<grid, kLinThreads, 0, st>>>(a); break;
+        }
+    }
+    h->launches++;
+    CU(cudaGetLastError());
+    return IBP_OK;
+}
+
+int ibp_smooth_gaussian(ibp_handle *h, const float *maps, float *out, int planes, int img_h, int img_w, int ksize, float sigma, void *stream) {
+    if (!h || !maps || !out) return fail(IBP_ERR_ARG, "ibp_smooth_gaussian: null argument");
+    if (planes < 1 || planes > 65535 || img_h < 1 || img_w < 1) return fail(IBP_ERR_SHAPE, "ibp_smooth_gaussian: bad shape");
+    if (ksize < 1 || ksize > kGsMaxK || !(ksize & 1) || !(sigma > 0.f)) return fail(IBP_ERR_ARG, "ibp_smooth_gaussian: odd kernel size 1..%d and sigma > 0", kGsMaxK);
+    if (img_h <= ksize / 2 || img_w <= ksize / 2) return fail(IBP_ERR_SHAPE, "ibp_smooth_gaussian: the mirrored border needs a map larger than half the kernel");
+    CU(cudaSetDevice(h->device));
+    GaussArgs a;
+    memset(&a, 0, sizeof(a));
+    a.src = maps;
+    a.dst = out;
+    a.H = img_h;
+    a.W = img_w;
+    a.ksize = ksize;
+    // utils/util.py:131-146 in float32 like torch: g[i] = 1 / (sigma sqrt(2 pi)) exp(-((i - mean) / sigma)^2 / 2), the 2-D kernel is the
+    // outer product divided by its sum = the product of the two normalised 1-D kernels
+    {
+        const float mean = (float)(ksize - 1) / 2.0f;
+        float g[kGsMaxK], sum = 0.f;
+        for (int i = 0; i < ksize; i++) {
+            const float z = ((float)i - mean) / sigma;
+            g[i] = 1.0f / (sigma * sqrtf(2.0f * 3.14159265358979323846f)) * expf(-(z * z) / 2.0f);
+            sum += g[i];
+        }
+        for (int i = 0; i < ksize; i++) a.g[i] = g[i] / sum;
+    }
+    const int p = ksize / 2;
+    const size_t smem = ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 2 * p) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float);
+    static std::once_flag once;
+    std::call_once(once, [] { cudaFuncSetAttribute(gauss_smooth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); });
+    const dim3 grid((img_w + kGsTileX - 1) / kGsTileX, (img_h + kGsTileY - 1) / kGsTileY, planes);
+    {
+        StageTimer t(h, IBP_STAGE_SMOOTH, (cudaStream_t)stream);
+        gauss_smooth_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(a);
     }
     h->launches++;
     CU(cudaGetLastError());

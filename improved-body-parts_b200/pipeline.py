@@ -138,10 +138,11 @@ class PostProcessor:
                                   _stream_ptr(self.device))
         return fused
 
-    def fuse_multiscale(self, net_outs, scaled_sizes, img_h, img_w, flip_avg=True, want_heat32=True):
+    def fuse_multiscale(self, net_outs, scaled_sizes, img_h, img_w, flip_avg=True, want_heat32=True, interp="cubic"):
         """predict()'s fusion (utils/parse_skeletons.py:232-281) for a batch: net_outs = one (B,2,50,h_s,w_s) float32
         CUDA tensor per scale, scaled_sizes = [(sh,sw)] the scaled image sizes before padding.
-        -> (fused (B,50,img_h,img_w) float64 planar [0,30) limb / [30,50) keypoint, heat32 (B,18,img_h,img_w) or None)."""
+        -> (fused (B,50,img_h,img_w) float64 planar [0,30) limb / [30,50) keypoint, heat32 (B,18,img_h,img_w) or None).
+        interp="linear": the second operator mode (bilinear in both resizes; not the reference's operator)."""
         ts = [t.to(self.device, torch.float32).contiguous() for t in net_outs]
         B = ts[0].shape[0]
         out = torch.empty((B, _lib.NUM_LAYERS, img_h, img_w), dtype=torch.float64, device=self.device)
@@ -149,9 +150,19 @@ class PostProcessor:
         scales = [(t.data_ptr(), t.shape[3], t.shape[4], sh, sw) for t, (sh, sw) in zip(ts, scaled_sizes)]
         with torch.cuda.device(self.device):
             self.handle.fuse_multiscale(scales, B, img_h, img_w, out.data_ptr(), heat32.data_ptr() if want_heat32 else None,
-                                        flip_avg, _stream_ptr(self.device))
+                                        flip_avg, _stream_ptr(self.device), interp)
         self._keep_ms = ts
         return out, heat32
+
+    def smooth_gaussian(self, maps, ksize=5, sigma=1.0):
+        """Second operator mode: GaussianSmoothing(C, ksize, sigma) of utils/util.py:103-174 on F.pad(maps, reflect) —
+        (B,C,H,W) float32 planar CUDA tensor -> smoothed tensor of the same shape."""
+        maps = maps.to(self.device, torch.float32).contiguous()
+        B, Cn, H, W = maps.shape
+        out = torch.empty_like(maps)
+        with torch.cuda.device(self.device):
+            self.handle.smooth_gaussian(maps.data_ptr(), out.data_ptr(), B * Cn, H, W, ksize, sigma, _stream_ptr(self.device))
+        return out
 
     def original_route(self, net_outs, scaled_sizes, img_h, img_w, test_cfg=None, flip_avg=True):
         """The reference's ORIGINAL route for a batch, device resident end to end (evaluate.py:82-90 without flags):
@@ -162,10 +173,14 @@ class PostProcessor:
         B = self.enqueue_original_route(net_outs, scaled_sizes, img_h, img_w, test_cfg, flip_avg)
         return self.fetch_original_route(B)
 
-    def enqueue_original_route(self, net_outs, scaled_sizes, img_h, img_w, test_cfg=None, flip_avg=True):
-        """Launch the four kernels of the original route on the current stream; results stay on the device."""
-        fused, heat32 = self.fuse_multiscale(net_outs, scaled_sizes, img_h, img_w, flip_avg, want_heat32=True)
+    def enqueue_original_route(self, net_outs, scaled_sizes, img_h, img_w, test_cfg=None, flip_avg=True, interp="cubic", smooth=None):
+        """Launch the four kernels of the original route on the current stream; results stay on the device.
+        interp="linear" and smooth=(ksize, sigma) select the second operator mode (bilinear fusion, Gaussian-smoothed
+        keypoint maps before the 3x3 max-suppression); the defaults are the reference's operators."""
+        fused, heat32 = self.fuse_multiscale(net_outs, scaled_sizes, img_h, img_w, flip_avg, want_heat32=True, interp=interp)
         B = fused.shape[0]
+        if smooth is not None:
+            heat32 = self.smooth_gaussian(heat32, smooth[0], smooth[1])
         params = _lib.py_params(test_cfg)
         with torch.cuda.device(self.device):
             st = _stream_ptr(self.device)

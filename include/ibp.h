@@ -175,6 +175,23 @@ typedef struct ibp_scale_input {
 int ibp_fuse_multiscale(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w,
                         int flip_avg, double *out, float *heat32, void *stream);
 
+/* Second operator mode (the operators BASELINE.json's north_star names where the reference's live
+ * path uses others).  NOT what utils/parse_skeletons.py computes: the same scale-search / flip fusion as above
+ * (l.180-283) with cv2.INTER_LINEAR in place of INTER_CUBIC in both resizes (l.252-263, l.276-277), the two bilinear
+ * resizes composed into one <= 3 x 3 tap operator on the feature maps.  Same arguments and outputs as
+ * ibp_fuse_multiscale; feature maps of at least 3 x 3.  Checked against its own CPU oracle (oracle/np_oracle.py:
+ * predict_fuse_linear, which is held to cv2.resize) to 1e-4 relative, not bit for bit. */
+int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int n_scales, int batch, int img_h, int img_w,
+                               int flip_avg, double *out, float *heat32, void *stream);
+
+/* Second operator mode, smoothing: utils/util.py:103-174 (GaussianSmoothing, unused by the reference's live path) applied
+ * the way its docstring says, to F.pad(x, (p,p,p,p), mode='reflect') with p = ksize / 2: separable Gaussian of `planes`
+ * planar (img_h,img_w) float32 maps, odd ksize <= 15.  The smoothed maps then go through ibp_find_peaks (flavour 1:
+ * 3x3 max-suppression into per-channel candidate lists).  Oracle: oracle/np_oracle.py:gaussian_smooth, pinned by the
+ * reference class's own weights (tests/golden/modes_12x.npz); tolerance 1e-5 absolute. */
+int ibp_smooth_gaussian(ibp_handle *h, const float *maps, float *out, int planes, int img_h, int img_w, int ksize, float sigma,
+                        void *stream);
+
 /* A4 — limb-map up-sampling: evaluate.py:77-80 / demo_image.py:94-97, cv2.resize(pafs, fx=up, fy=up, INTER_CUBIC).
  * fused (batch,chan_stride,h,w) planar, limb channels first; out (batch, h*up, w*up, 30) HWC float32. */
 int ibp_upsample_limbs(ibp_handle *h, const float *fused, int chan_stride, int batch, int fh, int fw, int up,
@@ -329,7 +346,8 @@ int64_t ibp_launch_count(const ibp_handle *h);
 #define IBP_STAGE_LIMBS 3
 #define IBP_STAGE_GROUP 4
 #define IBP_STAGE_UPSAMPLE 5
-#define IBP_NUM_STAGES 6
+#define IBP_STAGE_SMOOTH 6
+#define IBP_NUM_STAGES 7
 int ibp_set_profiling(ibp_handle *h, int on);
 int ibp_get_stage_ms(ibp_handle *h, float *ms /* [IBP_NUM_STAGES] */);
 

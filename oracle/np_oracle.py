@@ -568,3 +568,77 @@ def coco_rows(peak_xy, humans):
         rows[k, :51] = cmu[ORDER_COCO, :].reshape(51)
         rows[k, 51] = score
     return rows
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Second operator mode (the operators BASELINE.json names where the reference uses others).
+# NOT on the reference's live path: predict() with cv2.INTER_LINEAR in both resizes, and GaussianSmoothing of
+# utils/util.py:103-174 (unused by the reference) applied to a mirror-padded map as its docstring says.
+# Pinned by: cv_resize_linear == cv2.resize(INTER_LINEAR) (tests/test_operator_modes.py), gaussian_smooth ==
+# F.conv2d with the reference class's own weight (tests/golden/modes_12x.npz, made by make_golden_modes.py).
+# ----------------------------------------------------------------------------------------------------------
+def _cv_linear_axis(n_src, n_dst, scale):
+    """cv2 INTER_LINEAR tap set-up of one axis (resize.cpp, generic path): -> (i0, i1, a0, a1) float32 weights."""
+    d = np.arange(n_dst, dtype=np.float64)
+    f = ((d + 0.5) * scale - 0.5).astype(np.float32)
+    s = np.floor(f).astype(np.int64)
+    f = (f - s.astype(np.float32)).astype(np.float32)
+    lo = s < 0
+    f[lo], s[lo] = 0.0, 0
+    hi = s >= n_src - 1
+    f[hi], s[hi] = 0.0, n_src - 1
+    return s, np.minimum(s + 1, n_src - 1), (np.float32(1.0) - f).astype(np.float32), f
+
+
+def cv_resize_linear(src, dst_h, dst_w, scale_y=None, scale_x=None):
+    """cv2.resize(src (h,w,C) float32, (dst_w,dst_h), interpolation=cv2.INTER_LINEAR): horizontal pass
+    S[x0]*a0 + S[x1]*a1, then vertical pass S0*b0 + S1*b1, float32 throughout."""
+    src = np.ascontiguousarray(src, dtype=np.float32)
+    h, w = src.shape[:2]
+    sy = scale_y if scale_y is not None else 1.0 / (dst_h / h)
+    sx = scale_x if scale_x is not None else 1.0 / (dst_w / w)
+    x0, x1, a0, a1 = _cv_linear_axis(w, dst_w, sx)
+    y0, y1, b0, b1 = _cv_linear_axis(h, dst_h, sy)
+    rows = src[:, x0, :] * a0[None, :, None] + src[:, x1, :] * a1[None, :, None]
+    return (rows[y0] * b0[:, None, None] + rows[y1] * b1[:, None, None]).astype(np.float32)
+
+
+def predict_fuse_linear(net_outs, img_h, img_w, scales, stride=4, max_downsample=64, flip_avg=True):
+    """predict_fuse with INTER_LINEAR in both resizes (the second operator mode of ibp_fuse_multiscale_linear)."""
+    heatmap_avg = np.zeros((img_h, img_w, NUM_HEATMAPS))
+    paf_avg = np.zeros((img_h, img_w, NUM_PAFS))
+    n = len(scales)
+    for out, scale in zip(net_outs, scales):
+        sh, sw = scaled_size(img_h, img_w, scale)
+        pad_h, pad_w = padded_size(sh, sw, max_downsample)
+        assert out.shape[2] * stride == pad_h and out.shape[3] * stride == pad_w, (out.shape, pad_h, pad_w)
+        heat, paf = fuse_flip(out, flip_avg)
+        heat = cv_resize_linear(heat, pad_h, pad_w, 1.0 / stride, 1.0 / stride)
+        paf = cv_resize_linear(paf, pad_h, pad_w, 1.0 / stride, 1.0 / stride)
+        heat, paf = heat[:sh, :sw, :], paf[:sh, :sw, :]
+        heat = cv_resize_linear(heat, img_h, img_w)
+        paf = cv_resize_linear(paf, img_h, img_w)
+        heatmap_avg = heatmap_avg + heat / n
+        paf_avg = paf_avg + paf / n
+    return heatmap_avg, paf_avg
+
+
+def gaussian_kernel1d(ksize, sigma):
+    """utils/util.py:131-146 for one axis, float32 like torch: the 2-D kernel of GaussianSmoothing is the outer product
+    of two of these divided by its sum, i.e. the outer product of the normalised 1-D kernels."""
+    i = np.arange(ksize, dtype=np.float32)
+    mean = np.float32((ksize - 1) / 2)
+    g = (np.float32(1.0) / (np.float32(sigma) * np.float32(np.sqrt(2 * np.pi)))) * np.exp(-(((i - mean) / np.float32(sigma)) ** 2) / 2).astype(np.float32)
+    return (g / g.sum(dtype=np.float32)).astype(np.float32)
+
+
+def gaussian_smooth(maps, ksize=5, sigma=1.0):
+    """GaussianSmoothing(C, ksize, sigma)(F.pad(maps, (p,p,p,p), mode='reflect')) for maps (C,H,W) float32 -> (C,H,W)."""
+    maps = np.asarray(maps, dtype=np.float32)
+    p = ksize // 2
+    g = gaussian_kernel1d(ksize, sigma).astype(np.float64)
+    x = np.pad(maps, ((0, 0), (p, p), (p, p)), mode="reflect").astype(np.float64)
+    H, W = maps.shape[1:]
+    tmp = sum(g[k] * x[:, :, k:k + W] for k in range(ksize))
+    out = sum(g[k] * tmp[:, k:k + H, :] for k in range(ksize))
+    return out.astype(np.float32)
