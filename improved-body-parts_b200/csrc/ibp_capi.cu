@@ -927,26 +927,59 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     a.W = W;
     a.out = out;
     a.heat32 = heat32;
-    // rows per warp: enough chains for ~8 waves of 16 resident CTAs per SM, at least 32 rows each (a chain start costs three feature rows)
+    // rows per CTA: enough chains for ~8 waves of 8 resident CTAs per SM, whole segments, at least 32 rows each (a chain start
+    // costs three feature rows per scale)
     const long long cols = (W + kLinThreads - 1) / kLinThreads;
     const long long per_chain = cols * kLayers * batch;
-    const long long want = 8LL * 16 * h->sm_count;
+    const long long want = 8LL * 8 * h->sm_count;
     const long long chains = std::max(1LL, std::min((long long)(H + 31) / 32, (want + per_chain - 1) / per_chain));
     a.chain_rows = (int)((H + chains - 1) / chains);
+    a.chain_rows = (a.chain_rows + kLinSeg - 1) / kLinSeg * kLinSeg;
+    // exact capacities of the staging buffers for this launch plan, from the (cached) host copy of the tables
+    {
+        const LinTap *tab = h->h_lin_tab;
+        int off = 0;
+        for (int s = 0; s < ns; s++) {
+            const LinTap *xt = tab + (size_t)s * (W + H), *yt = xt + W;
+            int nc = 1, maxr = 1;
+            for (int X0 = 0; X0 < W; X0 += kLinThreads) nc = std::max(nc, xt[std::min(X0 + kLinThreads - 1, W - 1)].base + 2 - xt[X0].base + 1);
+            for (int Yc = 0; Yc < H; Yc += a.chain_rows) {
+                int loaded = yt[Yc].base - 1;
+                for (int Ya = Yc; Ya < std::min(Yc + a.chain_rows, H); Ya += kLinSeg) {
+                    const int f_hi = yt[std::min(std::min(Ya + kLinSeg, Yc + a.chain_rows), H) - 1].base + 2;
+                    maxr = std::max(maxr, f_hi - loaded);
+                    loaded = std::max(loaded, f_hi);
+                }
+            }
+            a.nc[s] = nc;
+            a.maxr[s] = maxr;
+            a.off[s] = off;
+            off += 2 * nc * maxr;
+        }
+        a.buf_floats = (off + 3) & ~3;
+    }
+    const size_t smem = 2 * (size_t)a.buf_floats * sizeof(float) + 2 * (size_t)ns * kLinSeg * sizeof(LinTap);
+    if (smem > 96 * 1024) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: staging buffers of %zu B", smem);
     const dim3 grid((unsigned)cols, (unsigned)((H + a.chain_rows - 1) / a.chain_rows), (unsigned)batch * kLayers);
+#define IBP_LIN_LAUNCH(N)                                                                                          \
+    do {                                                                                                           \
+        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(fuse_linear_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
+        fuse_linear_kernel<N><<<grid, kLinThreads, smem, st>>>(a);                                                 \
+    } while (0)
     {
         StageTimer t(h, IBP_STAGE_FUSE, st);
         switch (ns) {
-            case 1: fuse_linear_kernel<1><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 2: fuse_linear_kernel<2><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 3: fuse_linear_kernel<3><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 4: fuse_linear_kernel<4><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 5: fuse_linear_kernel<5><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 6: fuse_linear_kernel<6><<<grid, kLinThreads, 0, st>>>(a); break;
-            case 7: fuse_linear_kernel<7><<<grid, kLinThreads, 0, st>>>(a); break;
-            default: fuse_linear_kernel<8><<<grid, kLinThreads, 0, st>>>(a); break;
+            case 1: IBP_LIN_LAUNCH(1); break;
+            case 2: IBP_LIN_LAUNCH(2); break;
+            case 3: IBP_LIN_LAUNCH(3); break;
+            case 4: IBP_LIN_LAUNCH(4); break;
+            case 5: IBP_LIN_LAUNCH(5); break;
+            case 6: IBP_LIN_LAUNCH(6); break;
+            case 7: IBP_LIN_LAUNCH(7); break;
+            default: IBP_LIN_LAUNCH(8); break;
         }
     }
+#undef IBP_LIN_LAUNCH
     h->launches++;
     CU(cudaGetLastError());
     return IBP_OK;
@@ -980,11 +1013,16 @@ int ibp_smooth_gaussian(ibp_handle *h, const float *maps, float *out, int planes
     const int p = ksize / 2;
     const size_t smem = ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 2 * p) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float);
     static std::once_flag once;
-    std::call_once(once, [] { cudaFuncSetAttribute(gauss_smooth_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); });
+    std::call_once(once, [] { cudaFuncSetAttribute(gauss_smooth_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); });
     const dim3 grid((img_w + kGsTileX - 1) / kGsTileX, (img_h + kGsTileY - 1) / kGsTileY, planes);
     {
         StageTimer t(h, IBP_STAGE_SMOOTH, (cudaStream_t)stream);
-        gauss_smooth_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(a);
+        switch (ksize) {
+            case 3: gauss_smooth_kernel<3><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
+            case 5: gauss_smooth_kernel<5><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
+            case 7: gauss_smooth_kernel<7><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
+            default: gauss_smooth_kernel<0><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
+        }
     }
     h->launches++;
     CU(cudaGetLastError());
