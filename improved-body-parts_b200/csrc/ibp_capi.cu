@@ -880,22 +880,28 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     std::vector<int> key = {H, W, ns};
     for (int s = 0; s < ns; s++) {
         const ibp_scale_input &in = scales[s];
-        if (!in.net_out || in.fh < 3 || in.fw < 3 || in.sh < 1 || in.sw < 1 || in.sh > in.fh * 4 || in.sw > in.fw * 4)
+        if (!in.net_out || in.fh < 3 || in.fw < 4 || in.sh < 1 || in.sw < 1 || in.sh > in.fh * 4 || in.sw > in.fw * 4)
             return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d: feature (%d,%d), scaled image (%d,%d)", s, in.fh, in.fw, in.sh, in.sw);
+        if ((in.fw & 3) || (((uintptr_t)in.net_out) & 15))  // the rows are staged in 16-byte pieces; every map the reference pads to x64 qualifies
+            return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d: feature width %d must be a multiple of 4 and the map 16-byte aligned", s, in.fw);
         key.insert(key.end(), {in.fh, in.fw, in.sh, in.sw});
     }
-    const size_t n_tab = (size_t)ns * (W + H);
+    const int n_seg_all = (H + kLinSeg - 1) / kLinSeg;
+    const size_t per_scale = (size_t)W + H + (n_seg_all + 3) / 4;  // taps of the columns, of the rows, then the segments' last feature rows (ints)
+    const size_t n_tab = (size_t)ns * per_scale;
     if (key != h->lin_tab_key) {
         std::vector<LinTap> tab(n_tab);
         const float fold = 1.0f / (float)ns;  // "/ n_scales" of parse_skeletons.py:280-281, folded into the row weights
         for (int s = 0; s < ns; s++) {
             const ibp_scale_input &in = scales[s];
             const double sx = 1.0 / ((double)W / (double)in.sw), sy = 1.0 / ((double)H / (double)in.sh);
-            LinTap *xt = &tab[(size_t)s * (W + H)], *yt = xt + W;
+            LinTap *xt = &tab[(size_t)s * per_scale], *yt = xt + W;
             for (int X = 0; X < W; X++)
                 if (!lin_compose(X, sx, in.sw, in.fw, 1.0f, &xt[X])) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: taps of column %d span more than three", X);
             for (int Y = 0; Y < H; Y++)
                 if (!lin_compose(Y, sy, in.sh, in.fh, fold, &yt[Y])) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: taps of row %d span more than three", Y);
+            int *seg_hi = reinterpret_cast<int *>(yt + H);
+            for (int g = 0; g < n_seg_all; g++) seg_hi[g] = yt[std::min((g + 1) * kLinSeg, H) - 1].base + 2;
         }
         if (h->lin_tab_cap < n_tab) {
             CU(cudaDeviceSynchronize());
@@ -918,8 +924,9 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
         a.sc[s].src = scales[s].net_out;
         a.sc[s].h = scales[s].fh;
         a.sc[s].w = scales[s].fw;
-        a.sc[s].xtab = h->d_lin_tab + (size_t)s * (W + H);
+        a.sc[s].xtab = h->d_lin_tab + (size_t)s * per_scale;
         a.sc[s].ytab = a.sc[s].xtab + W;
+        a.sc[s].seg_hi = reinterpret_cast<const int *>(a.sc[s].ytab + H);
     }
     a.n_scales = ns;
     a.flip = flip_avg ? 1 : 0;
@@ -929,20 +936,22 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     a.heat32 = heat32;
     // rows per CTA: enough chains for ~8 waves of 8 resident CTAs per SM, whole segments, at least 32 rows each (a chain start
     // costs three feature rows per scale)
-    const long long cols = (W + kLinThreads - 1) / kLinThreads;
+    const long long cols = (W + kLinCols - 1) / kLinCols;
     const long long per_chain = cols * kLayers * batch;
     const long long want = 8LL * 8 * h->sm_count;
     const long long chains = std::max(1LL, std::min((long long)(H + 31) / 32, (want + per_chain - 1) / per_chain));
     a.chain_rows = (int)((H + chains - 1) / chains);
-    a.chain_rows = (a.chain_rows + kLinSeg - 1) / kLinSeg * kLinSeg;
+    a.chain_rows = std::min((a.chain_rows + kLinSeg - 1) / kLinSeg * kLinSeg, kLinSeg * kLinMaxSegs);
     // exact capacities of the staging buffers for this launch plan, from the (cached) host copy of the tables
     {
         const LinTap *tab = h->h_lin_tab;
         int off = 0;
         for (int s = 0; s < ns; s++) {
-            const LinTap *xt = tab + (size_t)s * (W + H), *yt = xt + W;
+            const LinTap *xt = tab + (size_t)s * per_scale, *yt = xt + W;
             int nc = 1, maxr = 1;
-            for (int X0 = 0; X0 < W; X0 += kLinThreads) nc = std::max(nc, xt[std::min(X0 + kLinThreads - 1, W - 1)].base + 2 - xt[X0].base + 1);
+            // staged columns of a CTA: from its first tap rounded down to a 16-byte boundary, whole 16-byte groups
+            for (int X0 = 0; X0 < W; X0 += kLinCols) nc = std::max(nc, ((xt[std::min(X0 + kLinCols - 1, W - 1)].base + 2 - (xt[X0].base & ~3) + 1) + 3) & ~3);
+            if (nc / 4 > kLinThreads) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d shrinks by more than a factor of ~7.9", s);
             for (int Yc = 0; Yc < H; Yc += a.chain_rows) {
                 int loaded = yt[Yc].base - 1;
                 for (int Ya = Yc; Ya < std::min(Yc + a.chain_rows, H); Ya += kLinSeg) {

@@ -21,6 +21,8 @@ namespace ibp {
 
 constexpr int kLinMaxScales = 8;
 constexpr int kLinThreads = 128;
+constexpr int kLinSeg = 8;        // output rows per staging step
+constexpr int kLinMaxSegs = 64;   // staging steps of one CTA (chain_rows <= 512)
 
 struct __align__(16) LinTap {  // one axis, one destination index, one scale
     int base;                  // first of three consecutive feature indices (base + 2 is inside the map)
@@ -30,6 +32,7 @@ struct LinScale {
     const float *src;    // (batch, 2, 50, h, w)
     const LinTap *xtab;  // [W]
     const LinTap *ytab;  // [H]
+    const int *seg_hi;   // [ceil(H / kLinSeg)]: last feature row the output rows of a segment touch
     int h, w;
 };
 struct LinArgs {
@@ -43,7 +46,7 @@ struct LinArgs {
     double *out;
     float *heat32;
 };
-constexpr int kLinSeg = 16;  // output rows per staging step
+constexpr int kLinCols = 256;  // output columns of a CTA: a thread owns two adjacent ones (packed float32x2 arithmetic)
 
 __device__ __forceinline__ void lin_cp4(void *dst_smem, const void *src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
@@ -52,42 +55,57 @@ __device__ __forceinline__ void lin_cp16(void *dst_smem, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
 
-// A CTA owns 128 output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  The feature rows a
+// A CTA owns 256 output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  The feature rows a
 // segment adds to the windows (and the row taps of its output rows) are copied to shared memory with cp.async one
 // segment AHEAD, all requests independent, so HBM latency is paid once per segment and under the previous segment's
-// arithmetic; the walk itself only reads shared memory.
+// arithmetic; the walk itself only reads shared memory.  The four scales of a pixel are summed in float32 and widened
+// once (this mode is held to a tolerance, not to the bits of a float64 running sum).
 template <int NS>
-__global__ void __launch_bounds__(kLinThreads) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
+__global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
     extern __shared__ __align__(16) float lin_smem[];
     const int tid = threadIdx.x;
-    const int X0 = blockIdx.x * kLinThreads, X = X0 + tid;
-    const int Xl = min(X, a.W - 1);
+    const int X0 = blockIdx.x * kLinCols, X = X0 + 2 * tid;
     const int chan = blockIdx.z % kLayers, img = blockIdx.z / kLayers;
     const int Y0 = blockIdx.y * a.chain_rows, Y1 = min(Y0 + a.chain_rows, a.H);
     const bool flip = a.flip != 0;
+    const bool warp_active = X0 + 2 * (tid & ~31) < a.W;  // a warp entirely right of the image only helps with the copies
     LinTap *YT = reinterpret_cast<LinTap *>(lin_smem + 2 * a.buf_floats);  // [2][NS][kLinSeg]
     __shared__ int s_flo[2][kLinMaxScales];                                  // first feature row held by each buffer
+    __shared__ int s_hi[kLinMaxScales][kLinMaxSegs];                         // last feature row of each segment of this CTA
+    const int n_segs = (Y1 - Y0 + kLinSeg - 1) / kLinSeg;
 
-    float c0[NS], c1[NS], c2[NS];  // the lane's column taps
-    int col[NS];                   // its first feature column, relative to the CTA's first
-    int c_lo[NS];                  // the CTA's first feature column
-    const float *upr[NS], *twin[NS];
-    float w0[NS], w1[NS], w2[NS];  // horizontal sums of feature rows top, top + 1, top + 2
-    int top[NS], loaded[NS];       // window position; last feature row requested so far
+    float2 c0[NS], c1[NS], c2[NS];  // column taps of the thread's two columns
+    int colA[NS], colB[NS];         // their first feature columns, relative to the first staged one
+    const float *gsrc[NS];          // what this thread copies per feature row: 16 bytes of the upright plane (and of the twin) ...
+    int sdst[NS];                   // ... to this float offset of a staged row (-1: nothing)
+    int gtwin[NS];                  // float offset from the upright piece to the twin piece (the same for the whole CTA)
+    int nc4[NS];                    // staged columns of this CTA (a multiple of four)
+    float2 w0[NS], w1[NS], w2[NS];  // horizontal sums of feature rows top, top + 1, top + 2 (both columns)
+    int top[NS], loaded[NS];        // window position; last feature row requested so far
 #pragma unroll
     for (int s = 0; s < NS; s++) {
         const LinScale &S = a.sc[s];
-        const LinTap t = S.xtab[Xl];
-        c_lo[s] = __ldg(&S.xtab[X0].base);
-        col[s] = t.base - c_lo[s];
-        c0[s] = t.c[0], c1[s] = t.c[1], c2[s] = t.c[2];
+        const LinTap ta = S.xtab[min(X, a.W - 1)], tb = S.xtab[min(X + 1, a.W - 1)];
+        const int c_lo = __ldg(&S.xtab[X0].base) & ~3;  // staged columns start on a 16-byte boundary
+        nc4[s] = min(a.nc[s], S.w - c_lo);
+        colA[s] = ta.base - c_lo, colB[s] = tb.base - c_lo;
+        c0[s] = make_float2(ta.c[0], tb.c[0]), c1[s] = make_float2(ta.c[1], tb.c[1]), c2[s] = make_float2(ta.c[2], tb.c[2]);
         const size_t hw = (size_t)S.h * S.w;
         const float *base = S.src + (size_t)img * 2 * kLayers * hw;
-        upr[s] = base + (size_t)chan * hw;
-        twin[s] = base + (size_t)(kLayers + c_flip_src[chan]) * hw;
+        // thread t < nc4 / 4 copies, per feature row, 16 bytes of the upright plane (columns c_lo + 4t ..) and 16 bytes of the
+        // twin plane from the range that mirrors the staged one, [w - c_lo - nc4, w - c_lo), in its own order (read back mirrored)
+        if (tid < (nc4[s] >> 2)) {
+            gsrc[s] = base + (size_t)chan * hw + c_lo + 4 * tid;
+            sdst[s] = a.off[s] + 4 * tid;
+        } else {
+            gsrc[s] = base;
+            sdst[s] = -1;
+        }
+        gtwin[s] = (int)((size_t)(kLayers + c_flip_src[chan] - chan) * hw) + S.w - 2 * c_lo - nc4[s];
+        for (int g = tid; g < n_segs; g += kLinThreads) s_hi[s][g] = __ldg(&S.seg_hi[Y0 / kLinSeg + g]);
         top[s] = __ldg(&S.ytab[Y0].base) - 3;  // the first output row pulls three rows into the window
         loaded[s] = top[s] + 2;
-        w0[s] = w1[s] = w2[s] = 0.f;
+        w0[s] = w1[s] = w2[s] = make_float2(0.f, 0.f);
     }
 
     // requests of the segment that starts at row Ya into buffer b
@@ -97,15 +115,15 @@ __global__ void __launch_bounds__(kLinThreads) fuse_linear_kernel(const __grid_c
 #pragma unroll
         for (int s = 0; s < NS; s++) {
             const LinScale &S = a.sc[s];
-            const int f_hi = __ldg(&S.ytab[Yb - 1].base) + 2, f_lo = loaded[s] + 1;
+            const int f_hi = s_hi[s][(Ya - Y0) / kLinSeg], f_lo = loaded[s] + 1;
             if (tid == 0) s_flo[b][s] = f_lo;
-            for (int t = tid; t < a.nc[s]; t += kLinThreads) {
-                const int c = min(c_lo[s] + t, S.w - 1);
-                float *du = buf + a.off[s] + t, *dt = du + a.maxr[s] * a.nc[s];
-                for (int fr = f_lo; fr <= f_hi; fr++) {
-                    lin_cp4(du, upr[s] + (size_t)fr * S.w + c);
-                    if (flip) lin_cp4(dt, twin[s] + (size_t)fr * S.w + (S.w - 1 - c));
-                    du += a.nc[s], dt += a.nc[s];
+            if (sdst[s] >= 0) {
+                const float *g = gsrc[s] + (size_t)f_lo * S.w;
+                float *d = buf + sdst[s];
+                const int dtw = a.maxr[s] * a.nc[s];
+                for (int fr = f_lo; fr <= f_hi; fr++, g += S.w, d += a.nc[s]) {
+                    lin_cp16(d, g);
+                    if (flip) lin_cp16(d + dtw, g + gtwin[s]);
                 }
             }
             loaded[s] = max(loaded[s], f_hi);
@@ -116,6 +134,8 @@ __global__ void __launch_bounds__(kLinThreads) fuse_linear_kernel(const __grid_c
 
     double *out = a.out + ((size_t)img * kLayers + chan) * (size_t)a.H * a.W;
     float *h32 = (a.heat32 && chan >= kLimbs && chan < kLimbs + kParts) ? a.heat32 + ((size_t)img * kParts + (chan - kLimbs)) * (size_t)a.H * a.W : nullptr;
+    const bool two = X + 1 < a.W, wide = two && ((a.W & 1) == 0);  // X is even: aligned pairs when the row length is even
+    __syncthreads();  // s_hi
     request(Y0, 0);
     int b = 0;
     for (int Ya = Y0; Ya < Y1; Ya += kLinSeg, b ^= 1) {
@@ -126,33 +146,64 @@ __global__ void __launch_bounds__(kLinThreads) fuse_linear_kernel(const __grid_c
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const float *buf = lin_smem + b * a.buf_floats;
-        const int Yb = min(Ya + kLinSeg, Y1);
-        for (int Y = Ya; Y < Yb; Y++) {
-            double acc = 0.0;
+        if (warp_active) {
+            const float *buf = lin_smem + b * a.buf_floats;
+            const int Yb = min(Ya + kLinSeg, Y1);
+            const float *rowp[NS];  // the row a window takes in next (top + 3), at the CTA's first column
+            int tstride[NS];
 #pragma unroll
             for (int s = 0; s < NS; s++) {
-                const float4 e = *reinterpret_cast<const float4 *>(&YT[(b * NS + s) * kLinSeg + (Y - Ya)]);  // base, c0, c1, c2 of the row
-                const int ebase = __float_as_int(e.x);
-                while (top[s] < ebase) {  // the window moves down one feature row
-                    top[s]++;
-                    const float *pu = buf + a.off[s] + (top[s] + 2 - s_flo[b][s]) * a.nc[s] + col[s];
-                    float f0 = pu[0], f1 = pu[1], f2 = pu[2];
-                    if (flip) {
-                        const float *pt = pu + a.maxr[s] * a.nc[s];
-                        f0 = avg_like_numpy(f0, pt[0]), f1 = avg_like_numpy(f1, pt[1]), f2 = avg_like_numpy(f2, pt[2]);
-                    }
-                    w0[s] = w1[s];
-                    w1[s] = w2[s];
-                    w2[s] = __fmaf_rn(c2[s], f2, __fmaf_rn(c1[s], f1, __fmul_rn(c0[s], f0)));
-                }
-                const float v = __fmaf_rn(e.w, w2[s], __fmaf_rn(e.z, w1[s], __fmul_rn(e.y, w0[s])));
-                acc = __dadd_rn(acc, (double)v);
+                rowp[s] = buf + a.off[s] + (top[s] + 3 - s_flo[b][s]) * a.nc[s];
+                tstride[s] = a.maxr[s] * a.nc[s];
             }
-            if (X < a.W) {
-                const size_t o = (size_t)Y * a.W + X;
-                out[o] = acc;
-                if (h32) h32[o] = __double2float_rn(acc);
+            const LinTap *yt = YT + b * NS * kLinSeg;
+            float4 e[NS];  // base, c0, c1, c2 of the row, all scales requested together (and the next row's before this row's sums)
+#pragma unroll
+            for (int s = 0; s < NS; s++) e[s] = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);
+            for (int Y = Ya; Y < Yb; Y++) {
+                yt++;
+                float4 en[NS];
+#pragma unroll
+                for (int s = 0; s < NS; s++) en[s] = *reinterpret_cast<const float4 *>(yt + s * kLinSeg - (Y + 1 < Yb ? 0 : 1));
+                float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int s = 0; s < NS; s++) {
+                    const int ebase = __float_as_int(e[s].x);
+                    while (top[s] < ebase) {  // the window moves down one feature row
+                        top[s]++;
+                        const float *pa = rowp[s] + colA[s], *pb = rowp[s] + colB[s];
+                        float2 f0 = make_float2(pa[0], pb[0]), f1 = make_float2(pa[1], pb[1]), f2 = make_float2(pa[2], pb[2]);
+                        if (flip) {  // the twin row is staged in its own order: feature column c sits at nc4 - 1 - c
+                            const float *qa = rowp[s] + tstride[s] + (nc4[s] - 1 - colA[s]), *qb = rowp[s] + tstride[s] + (nc4[s] - 1 - colB[s]);
+                            const float2 half2 = make_float2(0.5f, 0.5f);
+                            f0 = __fmul2_rn(__fadd2_rn(f0, make_float2(qa[0], qb[0])), half2);
+                            f1 = __fmul2_rn(__fadd2_rn(f1, make_float2(qa[-1], qb[-1])), half2);
+                            f2 = __fmul2_rn(__fadd2_rn(f2, make_float2(qa[-2], qb[-2])), half2);
+                        }
+                        w0[s] = w1[s];
+                        w1[s] = w2[s];
+                        w2[s] = __ffma2_rn(c2[s], f2, __ffma2_rn(c1[s], f1, __fmul2_rn(c0[s], f0)));
+                        rowp[s] += a.nc[s];
+                    }
+                    const float2 v = __ffma2_rn(make_float2(e[s].w, e[s].w), w2[s],
+                                                __ffma2_rn(make_float2(e[s].z, e[s].z), w1[s], __fmul2_rn(make_float2(e[s].y, e[s].y), w0[s])));
+                    acc = __fadd2_rn(acc, v);
+                    e[s] = en[s];
+                }
+                if (X < a.W) {
+                    const size_t o = (size_t)Y * a.W + X;
+                    if (wide) {
+                        *reinterpret_cast<double2 *>(out + o) = make_double2((double)acc.x, (double)acc.y);
+                        if (h32) *reinterpret_cast<float2 *>(h32 + o) = acc;
+                    } else {
+                        out[o] = (double)acc.x;
+                        if (two) out[o + 1] = (double)acc.y;
+                        if (h32) {
+                            h32[o] = acc.x;
+                            if (two) h32[o + 1] = acc.y;
+                        }
+                    }
+                }
             }
         }
         __syncthreads();  // buffer b is free for the segment after next
