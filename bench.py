@@ -66,6 +66,9 @@ def workload_text(name, batch):
         "configs1": "configs[1]: synthetic batch %d, 512x512 input, stride-4 128x128x50 maps, flip twin, 1-10 people/image" % batch,
         "configs2": "configs[2]: flip + 4-scale fusion (0.5/1/1.5/2 x 512/480: maps 64x96..256x352) up-sampled to 640x480, "
                     "batch %d distinct images, 1-12 people/image" % batch,
+        "configs2_second_mode": "configs[2] inputs (flip + 4-scale fusion to 640x480, batch %d) through the SECOND operator mode — the "
+                                "north_star's operators, not the reference's: bilinear in both resizes, 5-tap Gaussian (sigma 1) in "
+                                "front of the 3x3 max-suppression" % batch,
         "configs3": "configs[3]: crowd stress, synthetic batch %d, 128x128x50 maps, flip twin, 40-60 people/image" % batch,
         "configs4": "configs[4]: image sweep fed in-stream by the random-init IMHN forward (fp16 autocast), %d images x 2 flips "
                     "per forward, 512x512 input" % batch,
@@ -75,8 +78,9 @@ def workload_text(name, batch):
 ROUTES = {"configs1": "refactored + C++ (predict_refactor, heatmap_nms, process_paf)",
           "configs3": "refactored + C++ (predict_refactor, heatmap_nms, process_paf)",
           "configs2": "original (predict, find_peaks, find_connections, find_humans)",
+          "configs2_second_mode": "original route with ibp_fuse_multiscale_linear + ibp_smooth_gaussian (second operator mode, own oracle, 1e-4)",
           "configs4": "IMHN forward -> refactored + C++ (predict_refactor, heatmap_nms, process_paf), fetch_coco"}
-DEFAULT_BATCH = {"configs1": BATCH, "configs2": 64, "configs3": BATCH, "configs4": 16}
+DEFAULT_BATCH = {"configs1": BATCH, "configs2": 64, "configs2_second_mode": 64, "configs3": BATCH, "configs4": 16}
 
 
 def config_of(name, world, batch, depth):
@@ -174,14 +178,18 @@ def cpu_baseline_refactored(sample, passes=None):
                       "(oracle/cpu_path.py)" % (n, passes, procs, cpp_stage_text())}
 
 
-def cpu_baseline_original(cases_by_scale, n_images):
+def cpu_baseline_original(cases_by_scale, n_images, second_mode=False):
     """The reference's ORIGINAL route on the host (configs[2]): predict's fusion with the reference's cv2.resize calls,
     find_peaks, find_connections, find_humans in numpy/Python (oracle/cpu_path.original_route_image)."""
     from improved_body_parts_b200 import synth
     from oracle import cpu_path
     shapes = synth.multiscale_shapes(MS_H, MS_W, MS_SS)
     cases = [[cases_by_scale[s][i] for s in range(len(MS_SS))] for i in range(n_images)]
-    secs, procs = cpu_path.time_original_route(cases, MS_H, MS_W, [s[0] for s in shapes])
+    secs, procs = cpu_path.time_original_route(cases, MS_H, MS_W, [s[0] for s in shapes], second_mode=second_mode)
+    if second_mode:
+        return {"value": n_images / secs, "unit": UNIT, "cores": procs, "kind": "port",
+                "kind_detail": "the same route with cv2.INTER_LINEAR in predict's resizes and a numpy 5-tap Gaussian (sigma 1) in front of find_peaks",
+                "sample": "%d images of the same workload, one pass after a warm-up image per process, %d processes x 1 thread" % (n_images, procs)}
     return {"value": n_images / secs, "unit": UNIT, "cores": procs, "kind": "port",
             "kind_detail": "restated Python issuing the reference's cv2.resize calls (the route has no C++ stage)",
             "sample": "%d images of the same workload, one pass after a warm-up image per process, %d processes x 1 thread: "
@@ -435,11 +443,13 @@ class MultiScale:
     find_connections -> find_humans, Python semantics in float64): four kernels."""
     H, W, SS = MS_H, MS_W, MS_SS
 
-    def __init__(self, name, args, dev, by_scale, rank=0):
+    def __init__(self, name, args, dev, by_scale, rank=0, route_kw=None):
         import torch
         from improved_body_parts_b200 import synth
         from improved_body_parts_b200.pipeline import PostProcessor
         self.name = name
+        # {} = the reference's operators; {"interp": "linear", "smooth": (5, 1.0)} = the second operator mode
+        self.route_kw = route_kw or {}
         self.by_scale = by_scale
         self.batch = by_scale[0].shape[0]
         self.shapes = synth.multiscale_shapes(self.H, self.W, self.SS)
@@ -456,7 +466,7 @@ class MultiScale:
         self.torch = torch
         self.in_bytes = sum(h.numel() * 4 for h in self.host)
         px = self.H * self.W
-        self.algo_bytes = {"fuse": self.in_bytes // self.batch + 50 * px * 8 + 18 * px * 4, "peaks": 18 * px * 4}
+        self.algo_bytes = {"fuse": self.in_bytes // self.batch + 50 * px * 8 + 18 * px * 4, "peaks": 18 * px * 4, "smooth": 2 * 18 * px * 4}
         self.e2e_note = ("each step uploads one full input set from pinned host memory; the upload of step k+1 runs on a copy "
                          "stream under the kernels of step k and step k does not end before it has")
         self.dev_obj = dev
@@ -465,15 +475,15 @@ class MultiScale:
 
     def step_dev(self, s):
         if self.depth == 1 or self.one_at_a_time:
-            self.pp.enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W)
+            self.pp.enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W, **self.route_kw)
             return
         k = s % self.depth
         self.streams[k].wait_stream(self.torch.cuda.current_stream(self.dev_obj))
         with self.torch.cuda.stream(self.streams[k]):
-            self.pps[k].enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W)
+            self.pps[k].enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W, **self.route_kw)
 
     def step_one(self, s):
-        self.pp.enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W)
+        self.pp.enqueue_original_route(self.dev[s % 2], self.sizes, self.H, self.W, **self.route_kw)
 
     def join(self):
         for st in self.streams:
@@ -501,7 +511,7 @@ class MultiScale:
             self.inflight = self._upload(0)
         k, ev = self.inflight
         cur.wait_event(ev)
-        self.pp.enqueue_original_route(self.dev[k], self.sizes, self.H, self.W)
+        self.pp.enqueue_original_route(self.dev[k], self.sizes, self.H, self.W, **self.route_kw)
         self.inflight = self._upload(1 - k)
         cur.wait_event(self.inflight[1])
         self.last = self.pp.fetch_original_route(self.batch)
@@ -521,7 +531,7 @@ class MultiScale:
 
     def cpu_baseline(self, args):
         n = min(args.cpu_sample or max(4, os.cpu_count() or 1), self.batch)
-        return cpu_baseline_original(self.by_scale, n)
+        return cpu_baseline_original(self.by_scale, n, second_mode=bool(self.route_kw))
 
     def release(self):
         del self.pps, self.pp, self.dev, self.host
@@ -619,7 +629,8 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
     # dram bytes read + written per launch of each kernel, from the committed `ncu --set full` captures: per launch, so only
     # meaningful at the batch size it was captured on (profiles/r2_traffic.json: {"<workload>@<batch>": {kernel: {...}}})
     traffic = None
-    key = "%s@%d" % (wl.name, batch)
+    key = "%s@%d" % (wl.name.replace("_second_mode", ""), batch)
+    alias = {"fuse": "fuse_linear"} if getattr(wl, "route_kw", None) else {}  # the stage timer is shared, the kernel is not
     tfile = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.exists(tfile):
         traffic = json.load(open(tfile)).get(key)
@@ -629,7 +640,8 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
             traffic = json.load(open(tfile))["kernels"]
     dominant = max((k for k in stage_ms if k in algo), key=lambda k: stage_ms[k])
     achieved = algo[dominant] * batch / (stage_ms[dominant] * 1e-3) / 1e9
-    traffic_bytes = (traffic[dominant]["dram_bytes_read"] + traffic[dominant]["dram_bytes_write"]) if traffic and dominant in traffic else None
+    tdom = alias.get(dominant, dominant)
+    traffic_bytes = (traffic[tdom]["dram_bytes_read"] + traffic[tdom]["dram_bytes_write"]) if traffic and tdom in traffic else None
     out = {"value": world * batch * args.steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / args.steps,
            "repeats": len(regions), "timed_regions_ms": [round(r, 4) for r in regions],
            "dtype": wl.dtype,
@@ -726,6 +738,8 @@ def run_ours(args, rank, world, local_rank, inputs):
     def build(nm):
         if nm == "configs2":
             return MultiScale(nm, args, dev, inputs[nm], rank)
+        if nm == "configs2_second_mode":  # same inputs, the north_star's operators (bilinear fusion, Gaussian-smoothed peaks)
+            return MultiScale(nm, args, dev, inputs["configs2"], rank, route_kw={"interp": "linear", "smooth": (5, 1.0)})
         if nm == "configs4":
             import copy
             import sweep
@@ -761,8 +775,8 @@ def run_ours(args, rank, world, local_rank, inputs):
         extras = {}
         import sweep
         have_model = sweep.model_available()
-        for nm in ("configs2", "configs3", "configs4"):
-            if (nm not in inputs and nm != "configs4") or (nm == "configs4" and not have_model):
+        for nm in ("configs2", "configs2_second_mode", "configs3", "configs4"):
+            if (nm.split("_")[0] not in inputs and nm != "configs4") or (nm == "configs4" and not have_model):
                 continue
             t0 = time.perf_counter()
             try:

@@ -83,22 +83,23 @@ def postprocess_image(net_out, img_h=512, up=4):
     return humans
 
 
-def predict_fuse_cv2(net_outs, img_h, img_w, scales, stride=4, flip_avg=True):
+def predict_fuse_cv2(net_outs, img_h, img_w, scales, stride=4, flip_avg=True, interp=None):
     """parse_skeletons.py:232-281 (everything predict() does after the model calls) with the reference's own cv2.resize
     calls; net_outs[i] = (2,50,h_i,w_i) network output of scale scales[i].  -> heatmap_avg (H,W,20), paf_avg (H,W,30)
     float64.  Equal to np_oracle.predict_fuse bit for bit (tests/test_multiscale.py holds the two together)."""
     import cv2
+    interp = cv2.INTER_CUBIC if interp is None else interp  # the reference's operator; INTER_LINEAR = the second operator mode
     heatmap_avg = np.zeros((img_h, img_w, O.NUM_HEATMAPS))
     paf_avg = np.zeros((img_h, img_w, O.NUM_PAFS))
     n = len(scales)
     for out, scale in zip(net_outs, scales):
         sh, sw = O.scaled_size(img_h, img_w, scale)
         heat, paf = O.fuse_flip(out, flip_avg)                                                    # l.232-248
-        heat = cv2.resize(heat, (0, 0), fx=stride, fy=stride, interpolation=cv2.INTER_CUBIC)      # l.252-256
-        paf = cv2.resize(paf, (0, 0), fx=stride, fy=stride, interpolation=cv2.INTER_CUBIC)        # l.259-263
+        heat = cv2.resize(heat, (0, 0), fx=stride, fy=stride, interpolation=interp)               # l.252-256
+        paf = cv2.resize(paf, (0, 0), fx=stride, fy=stride, interpolation=interp)                 # l.259-263
         heat, paf = heat[:sh, :sw, :], paf[:sh, :sw, :]                                           # l.272-273
-        heat = cv2.resize(heat, (img_w, img_h), interpolation=cv2.INTER_CUBIC)                    # l.276
-        paf = cv2.resize(paf, (img_w, img_h), interpolation=cv2.INTER_CUBIC)                      # l.277
+        heat = cv2.resize(heat, (img_w, img_h), interpolation=interp)                             # l.276
+        paf = cv2.resize(paf, (img_w, img_h), interpolation=interp)                               # l.277
         heatmap_avg = heatmap_avg + heat / n                                                      # l.280
         paf_avg = paf_avg + paf / n                                                               # l.281
     return heatmap_avg, paf_avg
@@ -109,7 +110,12 @@ def original_route_image(net_outs, img_h, img_w, scales):
     fusion (cv2), find_peaks (3x3 NMS + centroid refine; the reference does the NMS with torch on the GPU,
     util.py:177-185 — here numpy), find_connections, find_humans (pure Python/numpy, as in the reference).
     -> number of people."""
-    heat, paf = predict_fuse_cv2(net_outs, img_h, img_w, scales)
+    if _shared.get("second_mode"):  # bilinear fusion + Gaussian-smoothed keypoint maps (5 taps, sigma 1), then the same steps
+        import cv2
+        heat, paf = predict_fuse_cv2(net_outs, img_h, img_w, scales, interp=cv2.INTER_LINEAR)
+        heat = O.gaussian_smooth(heat[:, :, :18].astype(np.float32).transpose(2, 0, 1), 5, 1.0).transpose(1, 2, 0)
+    else:
+        heat, paf = predict_fuse_cv2(net_outs, img_h, img_w, scales)
     peaks = O.find_peaks(heat, 0.1, 2)
     cl, sp = O.find_connections(peaks, paf, img_h)
     assoc, _ = O.find_humans(cl, sp, peaks)
@@ -135,13 +141,14 @@ def _worker_orig(args):
     return [original_route_image(cases[i], img_h, img_w, scales) for i in idx]
 
 
-def time_original_route(cases, img_h, img_w, scales, procs=None):
+def time_original_route(cases, img_h, img_w, scales, procs=None, second_mode=False):
     """Seconds to run the original route over `cases` (list over images of per-scale network outputs) once on `procs`
     host processes; returns (seconds, procs)."""
     import multiprocessing as mp
     import time
     procs = max(1, min(procs or os.cpu_count() or 1, len(cases)))
     _shared["cases"] = cases
+    _shared["second_mode"] = bool(second_mode)
     if procs == 1:
         t0 = time.perf_counter()
         _worker_orig((list(range(len(cases))), img_h, img_w, scales))

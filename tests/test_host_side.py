@@ -183,7 +183,9 @@ def test_no_contracted_packed_multiply_add():
     if not os.path.exists(tool) or not os.path.exists(_lib.LIB_PATH):
         pytest.skip("cuobjdump or the library is not available")
     sass = subprocess.run([tool, "-sass", _lib.LIB_PATH], capture_output=True, text=True).stdout
-    packed = re.findall(r"\bFFMA2\s+([^;]*);", sass)
+    # the second operator mode (fuse_linear_kernel, gauss_smooth_kernel) is held to a tolerance and fuses on purpose
+    exact = "".join(f for f in sass.split("Function :") if not re.match(r"\s*\S*(fuse_linear|gauss_smooth)", f))
+    packed = re.findall(r"\bFFMA2\s+([^;]*);", exact)
     assert len(packed) > 50, "the multi-scale kernel is expected to use packed float32x2 arithmetic"
     bad = [p for p in packed if not re.match(r"R\d+, R\d+(\.reuse)?\.F32x2\.HI_LO, UR\d+\.F32, R\d+(\.reuse)?\.F32x2\.HI_LO\s*$", p.strip())]
     assert not bad, "fused packed multiply-add in the library: %s" % bad[:3]

@@ -17,11 +17,12 @@ for w in $which; do
     rep=/tmp/${tag}_${w}.ncu-rep
     timeout 900 ncu --set full --clock-control none --import-source on -o ${rep%.ncu-rep} -f python tools/profile_driver.py $w > $O/${tag}_ncu_${w}.log 2>&1
     echo "ncu full $w rc=$?"
-    specs="$specs $rep"
+    case $w in configs1) key=configs1@64 ;; configs3) key=configs3@64 ;; configs2) key=configs2@64 ;; esac
+    specs="$specs $rep:$key"
     case $w in
         configs1) ks="peaks_stream_kernel index_bands_kernel limbs_stream_kernel" ;;
         configs3) ks="peaks_kernel limbs_kernel" ;;
-        configs2) ks="fuse_multiscale py_connections_kernel py_humans_kernel" ;;
+        configs2) ks="fuse_multiscale fuse_linear gauss_smooth py_connections_kernel py_humans_kernel" ;;
     esac
     for k in $ks; do
         python tools/ncu_lines.py $rep $k 60 > $O/${tag}_${k}_source_lines.txt 2>&1
