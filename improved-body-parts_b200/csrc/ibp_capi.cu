@@ -1020,16 +1020,23 @@ int ibp_smooth_gaussian(ibp_handle *h, const float *maps, float *out, int planes
         for (int i = 0; i < ksize; i++) a.g[i] = g[i] / sum;
     }
     const int p = ksize / 2;
-    const size_t smem = ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 2 * p) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float);
+    // the 128-bit variant: sizes 3..9, rows that are 16-byte multiples on a 16-byte aligned map
+    const bool vec = ksize >= 3 && ksize <= 9 && (img_w & 3) == 0 && (((uintptr_t)maps | (uintptr_t)out) & 15) == 0;
+    const size_t smem = vec ? ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 8) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float)
+                            : ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 2 * p) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float);
     static std::once_flag once;
-    std::call_once(once, [] { cudaFuncSetAttribute(gauss_smooth_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024); });
+    std::call_once(once, [] {
+        cudaFuncSetAttribute(gauss_smooth_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+        cudaFuncSetAttribute(gauss_smooth_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    });
     const dim3 grid((img_w + kGsTileX - 1) / kGsTileX, (img_h + kGsTileY - 1) / kGsTileY, planes);
     {
         StageTimer t(h, IBP_STAGE_SMOOTH, (cudaStream_t)stream);
-        switch (ksize) {
+        switch (vec ? ksize : 0) {
             case 3: gauss_smooth_kernel<3><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
             case 5: gauss_smooth_kernel<5><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
             case 7: gauss_smooth_kernel<7><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
+            case 9: gauss_smooth_kernel<9><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
             default: gauss_smooth_kernel<0><<<grid, 256, smem, (cudaStream_t)stream>>>(a); break;
         }
     }

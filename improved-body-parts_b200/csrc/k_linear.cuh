@@ -228,63 +228,130 @@ __device__ __forceinline__ int reflect_idx(int i, int n) {  // torch 'reflect': 
     if (i >= n) i = 2 * n - 2 - i;
     return i;
 }
-// K = kernel size as a compile-time constant (0: run-time size, any odd K <= kGsMaxK)
+// K = kernel size as a compile-time constant (0: run-time size, any odd K <= kGsMaxK; the generic, scalar variant).
+// K = 3, 5, 7, 9 with a row length that is a multiple of four: everything in 128-bit pieces — the tile comes in as
+// float4 (a 4-column halo on either side keeps the pieces aligned), a thread makes four adjacent outputs of the
+// horizontal pass from three float4 loads, and four adjacent columns of the vertical pass with a sliding window down
+// four rows.
 template <int K>
 __global__ void __launch_bounds__(256) gauss_smooth_kernel(const __grid_constant__ GaussArgs a) {
     extern __shared__ __align__(16) float gs_smem[];
-    const int ksize = K ? K : a.ksize;
-    const int p = ksize >> 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int X0 = blockIdx.x * kGsTileX, Y0 = blockIdx.y * kGsTileY;
     const float *src = a.src + (size_t)blockIdx.z * a.H * a.W;
     float *dst = a.dst + (size_t)blockIdx.z * a.H * a.W;
-    const int in_w = kGsTileX + 2 * p, in_h = kGsTileY + 2 * p;
-    float *tin = gs_smem;                 // [in_h][in_w]
-    float *tmid = gs_smem + in_h * in_w;  // [in_h][kGsTileX]
-    float g[K ? K : kGsMaxK];
+    if constexpr (K != 0) {
+        constexpr int P = K / 2;
+        constexpr int IW = kGsTileX + 8, IH = kGsTileY + 2 * P;  // staged tile: 4 halo columns each side (P <= 4), P halo rows
+        float *tin = gs_smem;              // [IH][IW]
+        float *tmid = gs_smem + IH * IW;   // [IH][kGsTileX]
+        float g[K];
 #pragma unroll
-    for (int k = 0; k < (K ? K : kGsMaxK); k++) g[k] = k < ksize ? a.g[k] : 0.f;
-    // tile + mirrored halo: a warp per row, lanes along the row
-    for (int r = warp; r < in_h; r += 8) {
-        const int y = reflect_idx(min(Y0 + r - p, a.H - 1 + p), a.H);
-        const float *row = src + (size_t)y * a.W;
-        for (int c = lane; c < in_w; c += 32) tin[r * in_w + c] = __ldg(row + reflect_idx(min(X0 + c - p, a.W - 1 + p), a.W));
-    }
-    __syncthreads();
-    // horizontal pass: a warp per row, a lane four columns 32 apart
-    for (int r = warp; r < in_h; r += 8) {
-        const float *q = tin + r * in_w + lane;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
-#pragma unroll
-        for (int k = 0; k < (K ? K : kGsMaxK); k++) {
-            if (!K && k >= ksize) break;
-            v0 = __fmaf_rn(g[k], q[k], v0);
-            v1 = __fmaf_rn(g[k], q[k + 32], v1);
-            v2 = __fmaf_rn(g[k], q[k + 64], v2);
-            v3 = __fmaf_rn(g[k], q[k + 96], v3);
+        for (int k = 0; k < K; k++) g[k] = a.g[k];
+        // tile + mirrored halo as float4 pieces; a piece that crosses the edge of the map is put together element by element
+        for (int i = threadIdx.x; i < IH * (IW / 4); i += 256) {
+            const int r = i / (IW / 4), q = i - r * (IW / 4);
+            const int y = reflect_idx(min(Y0 + r - P, a.H - 1 + P), a.H);
+            const int x = X0 - 4 + 4 * q;
+            const float *row = src + (size_t)y * a.W;
+            float4 v;
+            if (x >= 0 && x + 3 < a.W) {
+                v = __ldg(reinterpret_cast<const float4 *>(row + x));
+            } else {
+                v.x = __ldg(row + reflect_idx(min(x, a.W - 1 + P), a.W));
+                v.y = __ldg(row + reflect_idx(min(x + 1, a.W - 1 + P), a.W));
+                v.z = __ldg(row + reflect_idx(min(x + 2, a.W - 1 + P), a.W));
+                v.w = __ldg(row + reflect_idx(min(x + 3, a.W - 1 + P), a.W));
+            }
+            *reinterpret_cast<float4 *>(tin + r * IW + 4 * q) = v;
         }
-        float *o = tmid + r * kGsTileX + lane;
-        o[0] = v0, o[32] = v1, o[64] = v2, o[96] = v3;
-    }
-    __syncthreads();
-    // vertical pass: a warp per output row
-    for (int r = warp; r < kGsTileY; r += 8) {
-        if (Y0 + r >= a.H) break;
-        const float *q = tmid + r * kGsTileX + lane;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+        __syncthreads();
+        // horizontal pass: four adjacent outputs from the three float4 around them
+        for (int i = threadIdx.x; i < IH * (kGsTileX / 4); i += 256) {
+            const int r = i >> 5, q = i & 31;
+            const float4 *p = reinterpret_cast<const float4 *>(tin + r * IW + 4 * q);
+            const float4 l = p[0], m = p[1], h = p[2];
+            const float in[12] = {l.x, l.y, l.z, l.w, m.x, m.y, m.z, m.w, h.x, h.y, h.z, h.w};
+            float o[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int k = 0; k < (K ? K : kGsMaxK); k++) {
-            if (!K && k >= ksize) break;
-            v0 = __fmaf_rn(g[k], q[k * kGsTileX], v0);
-            v1 = __fmaf_rn(g[k], q[k * kGsTileX + 32], v1);
-            v2 = __fmaf_rn(g[k], q[k * kGsTileX + 64], v2);
-            v3 = __fmaf_rn(g[k], q[k * kGsTileX + 96], v3);
+            for (int k = 0; k < K; k++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) o[j] = __fmaf_rn(g[k], in[4 - P + j + k], o[j]);
+            }
+            *reinterpret_cast<float4 *>(tmid + r * kGsTileX + 4 * q) = make_float4(o[0], o[1], o[2], o[3]);
         }
-        float *o = dst + (size_t)(Y0 + r) * a.W + X0 + lane;
-        if (X0 + lane < a.W) o[0] = v0;
-        if (X0 + lane + 32 < a.W) o[32] = v1;
-        if (X0 + lane + 64 < a.W) o[64] = v2;
-        if (X0 + lane + 96 < a.W) o[96] = v3;
+        __syncthreads();
+        // vertical pass: a thread = four adjacent columns x four rows, window of K rows in registers
+        {
+            const int q = lane, r0 = warp * 4;  // 8 warps x 4 rows = the 32 rows of the tile
+            float4 win[K + 3];
+#pragma unroll
+            for (int k = 0; k < K + 3; k++) win[k] = *reinterpret_cast<const float4 *>(tmid + (r0 + k) * kGsTileX + 4 * q);
+            const bool cols_ok = X0 + 4 * q + 3 < a.W;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    o.x = __fmaf_rn(g[k], win[j + k].x, o.x);
+                    o.y = __fmaf_rn(g[k], win[j + k].y, o.y);
+                    o.z = __fmaf_rn(g[k], win[j + k].z, o.z);
+                    o.w = __fmaf_rn(g[k], win[j + k].w, o.w);
+                }
+                const int y = Y0 + r0 + j;
+                if (y < a.H) {
+                    float *d = dst + (size_t)y * a.W + X0 + 4 * q;
+                    if (cols_ok) *reinterpret_cast<float4 *>(d) = o;
+                    else {
+                        if (X0 + 4 * q < a.W) d[0] = o.x;
+                        if (X0 + 4 * q + 1 < a.W) d[1] = o.y;
+                        if (X0 + 4 * q + 2 < a.W) d[2] = o.z;
+                    }
+                }
+            }
+        }
+    } else {
+        const int ksize = a.ksize, p = ksize >> 1;
+        const int in_w = kGsTileX + 2 * p, in_h = kGsTileY + 2 * p;
+        float *tin = gs_smem;                 // [in_h][in_w]
+        float *tmid = gs_smem + in_h * in_w;  // [in_h][kGsTileX]
+        for (int r = warp; r < in_h; r += 8) {
+            const int y = reflect_idx(min(Y0 + r - p, a.H - 1 + p), a.H);
+            const float *row = src + (size_t)y * a.W;
+            for (int c = lane; c < in_w; c += 32) tin[r * in_w + c] = __ldg(row + reflect_idx(min(X0 + c - p, a.W - 1 + p), a.W));
+        }
+        __syncthreads();
+        for (int r = warp; r < in_h; r += 8) {
+            const float *q = tin + r * in_w + lane;
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+            for (int k = 0; k < ksize; k++) {
+                const float gk = a.g[k];
+                v0 = __fmaf_rn(gk, q[k], v0);
+                v1 = __fmaf_rn(gk, q[k + 32], v1);
+                v2 = __fmaf_rn(gk, q[k + 64], v2);
+                v3 = __fmaf_rn(gk, q[k + 96], v3);
+            }
+            float *o = tmid + r * kGsTileX + lane;
+            o[0] = v0, o[32] = v1, o[64] = v2, o[96] = v3;
+        }
+        __syncthreads();
+        for (int r = warp; r < kGsTileY; r += 8) {
+            if (Y0 + r >= a.H) break;
+            const float *q = tmid + r * kGsTileX + lane;
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f;
+            for (int k = 0; k < ksize; k++) {
+                const float gk = a.g[k];
+                v0 = __fmaf_rn(gk, q[k * kGsTileX], v0);
+                v1 = __fmaf_rn(gk, q[k * kGsTileX + 32], v1);
+                v2 = __fmaf_rn(gk, q[k * kGsTileX + 64], v2);
+                v3 = __fmaf_rn(gk, q[k * kGsTileX + 96], v3);
+            }
+            float *o = dst + (size_t)(Y0 + r) * a.W + X0 + lane;
+            if (X0 + lane < a.W) o[0] = v0;
+            if (X0 + lane + 32 < a.W) o[32] = v1;
+            if (X0 + lane + 64 < a.W) o[64] = v2;
+            if (X0 + lane + 96 < a.W) o[96] = v3;
+        }
     }
 }
 

@@ -127,6 +127,18 @@ def test_gpu_smooth_gaussian(path):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("shape,k,sigma", [((3, 96, 70), 5, 1.0), ((2, 50, 131), 3, 0.7), ((4, 77, 96), 11, 2.0), ((1, 200, 260), 9, 1.7)])
+def test_gpu_smooth_gaussian_other_shapes(shape, k, sigma):
+    """Row lengths that are not 16-byte multiples and kernel sizes outside 3..9 take the scalar variant; partial tiles."""
+    import torch
+    from improved_body_parts_b200.pipeline import PostProcessor
+    x = np.random.default_rng(k).random(shape, dtype=np.float32)
+    pp = PostProcessor(device=0, max_batch=1)
+    got = pp.smooth_gaussian(torch.from_numpy(x[None]).cuda(), k, sigma).cpu().numpy()[0]
+    np.testing.assert_allclose(got, O.gaussian_smooth(x, k, sigma), rtol=RTOL, atol=1e-5)
+
+
+@pytest.mark.gpu
 def test_gpu_second_mode_route_end_to_end():
     """Bilinear fusion -> Gaussian smoothing -> 3x3 max-suppression + centroid -> connections -> people, device resident,
     against the same chain of oracles (peak positions identical, scores to the mode's tolerance)."""
