@@ -1022,7 +1022,7 @@ int ibp_smooth_gaussian(ibp_handle *h, const float *maps, float *out, int planes
     const int p = ksize / 2;
     // the 128-bit variant: sizes 3..9, rows that are 16-byte multiples on a 16-byte aligned map
     const bool vec = ksize >= 3 && ksize <= 9 && (img_w & 3) == 0 && (((uintptr_t)maps | (uintptr_t)out) & 15) == 0;
-    const size_t smem = vec ? ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 8) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float)
+    const size_t smem = vec ? (size_t)(kGsTileY + 2 * p) * kGsTileX * sizeof(float)
                             : ((size_t)(kGsTileY + 2 * p) * (kGsTileX + 2 * p) + (size_t)(kGsTileY + 2 * p) * kGsTileX) * sizeof(float);
     static std::once_flag once;
     std::call_once(once, [] {

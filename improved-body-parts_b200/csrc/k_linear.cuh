@@ -212,11 +212,11 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
 
 // ---------------------------------------------------------------------------------------------------------------
 // Separable Gaussian smoothing with a mirrored border: GaussianSmoothing(channels, ksize, sigma) applied to
-// F.pad(x, (p, p, p, p), mode='reflect') — utils/util.py:103-174 and its docstring.  One CTA = a 128 x 32 tile of one
+// F.pad(x, (p, p, p, p), mode='reflect') — utils/util.py:103-174 and its docstring.  One CTA = a 128 x 64 tile of one
 // plane: tile + halo to shared memory, horizontal pass into a second buffer, vertical pass to HBM.  Reads and writes
 // every pixel once: bound by HBM.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int kGsTileX = 128, kGsTileY = 32, kGsMaxK = 15;
+constexpr int kGsTileX = 128, kGsTileY = 64, kGsMaxK = 15;
 struct GaussArgs {
     const float *src;
     float *dst;
@@ -242,35 +242,28 @@ __global__ void __launch_bounds__(256) gauss_smooth_kernel(const __grid_constant
     float *dst = a.dst + (size_t)blockIdx.z * a.H * a.W;
     if constexpr (K != 0) {
         constexpr int P = K / 2;
-        constexpr int IW = kGsTileX + 8, IH = kGsTileY + 2 * P;  // staged tile: 4 halo columns each side (P <= 4), P halo rows
-        float *tin = gs_smem;              // [IH][IW]
-        float *tmid = gs_smem + IH * IW;   // [IH][kGsTileX]
+        constexpr int IH = kGsTileY + 2 * P;
+        float *tmid = gs_smem;  // [IH][kGsTileX]: the horizontal pass of the tile and its P halo rows
         float g[K];
 #pragma unroll
         for (int k = 0; k < K; k++) g[k] = a.g[k];
-        // tile + mirrored halo as float4 pieces; a piece that crosses the edge of the map is put together element by element
-        for (int i = threadIdx.x; i < IH * (IW / 4); i += 256) {
-            const int r = i / (IW / 4), q = i - r * (IW / 4);
-            const int y = reflect_idx(min(Y0 + r - P, a.H - 1 + P), a.H);
-            const int x = X0 - 4 + 4 * q;
-            const float *row = src + (size_t)y * a.W;
+        // horizontal pass straight from global memory (neighbouring threads share their pieces through L1): four adjacent
+        // outputs from the three float4 around them; a piece that crosses the edge of the map is put together element by
+        // element through the mirror
+        auto piece = [&](const float *row, int x) {
+            if (x >= 0 && x + 3 < a.W) return __ldg(reinterpret_cast<const float4 *>(row + x));
             float4 v;
-            if (x >= 0 && x + 3 < a.W) {
-                v = __ldg(reinterpret_cast<const float4 *>(row + x));
-            } else {
-                v.x = __ldg(row + reflect_idx(min(x, a.W - 1 + P), a.W));
-                v.y = __ldg(row + reflect_idx(min(x + 1, a.W - 1 + P), a.W));
-                v.z = __ldg(row + reflect_idx(min(x + 2, a.W - 1 + P), a.W));
-                v.w = __ldg(row + reflect_idx(min(x + 3, a.W - 1 + P), a.W));
-            }
-            *reinterpret_cast<float4 *>(tin + r * IW + 4 * q) = v;
-        }
-        __syncthreads();
-        // horizontal pass: four adjacent outputs from the three float4 around them
+            v.x = __ldg(row + reflect_idx(min(x, a.W - 1 + P), a.W));
+            v.y = __ldg(row + reflect_idx(min(x + 1, a.W - 1 + P), a.W));
+            v.z = __ldg(row + reflect_idx(min(x + 2, a.W - 1 + P), a.W));
+            v.w = __ldg(row + reflect_idx(min(x + 3, a.W - 1 + P), a.W));
+            return v;
+        };
         for (int i = threadIdx.x; i < IH * (kGsTileX / 4); i += 256) {
             const int r = i >> 5, q = i & 31;
-            const float4 *p = reinterpret_cast<const float4 *>(tin + r * IW + 4 * q);
-            const float4 l = p[0], m = p[1], h = p[2];
+            const int y = reflect_idx(min(Y0 + r - P, a.H - 1 + P), a.H), x = X0 + 4 * q;
+            const float *row = src + (size_t)y * a.W;
+            const float4 l = piece(row, x - 4), m = piece(row, x), h = piece(row, x + 4);
             const float in[12] = {l.x, l.y, l.z, l.w, m.x, m.y, m.z, m.w, h.x, h.y, h.z, h.w};
             float o[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -282,8 +275,9 @@ __global__ void __launch_bounds__(256) gauss_smooth_kernel(const __grid_constant
         }
         __syncthreads();
         // vertical pass: a thread = four adjacent columns x four rows, window of K rows in registers
-        {
-            const int q = lane, r0 = warp * 4;  // 8 warps x 4 rows = the 32 rows of the tile
+        for (int r0 = warp * 4; r0 < kGsTileY; r0 += 32) {  // 8 warps x 4 rows per round
+            if (Y0 + r0 >= a.H) break;
+            const int q = lane;
             float4 win[K + 3];
 #pragma unroll
             for (int k = 0; k < K + 3; k++) win[k] = *reinterpret_cast<const float4 *>(tmid + (r0 + k) * kGsTileX + 4 * q);
