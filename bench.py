@@ -369,6 +369,10 @@ class Refactored:
         self.e2e_mode = False
         self.dtype = "f32"
         fb = 2 * FEAT * FEAT * 4
+        self.e2e_note = ("the caller hands over the whole (B,2,50,h,w) pinned host tensor; h2d_bytes_per_step is what crosses the bus: the 36 "
+                         "keypoint planes per image by cudaMemcpy2DAsync plus the limb rows the limb kernel pulls straight from the pinned "
+                         "buffer (rows between the extreme peaks of a limb's joint types, counted from the fetched peaks); "
+                         "h2d_bytes_offered_per_step = the 96 limb + keypoint planes per image a full copy would move")
         self.algo_bytes = {"peaks": 18 * fb, "limbs": 30 * fb}  # planes of the upright and the flipped output, read once
 
     def step_dev(self, s):
@@ -411,9 +415,39 @@ class Refactored:
             self.last = res[-1]
         self.e2e_mode = False
 
-    def h2d(self):
-        # ibp_postprocess_batch uploads the 48 limb + keypoint planes of each half; the 2 background planes stay behind
-        return self.host_sets[0].numel() * self.host_sets[0].element_size() // 50 * 48
+    def h2d(self, esz=4):
+        """Bytes that cross the bus per step.  ibp_postprocess_batch copies the 18 keypoint planes of each half; the limb
+        kernel pulls the limb rows it needs straight out of the pinned host buffer (zero copy) — for limb l of an image the
+        feature rows between the extreme peaks of its two joint types plus the bicubic support (the formula of
+        index_bands_kernel, csrc/k_peaks.cuh), of the upright and of the twin plane.  Counted here from the fetched peaks,
+        averaged over the two input sets; the 2 background planes never move.  With IBP_NO_ZEROCOPY the 48 planes are copied."""
+        full = self.host_sets[0].numel() * esz // 50
+        if os.environ.get("IBP_NO_ZEROCOPY"):
+            return full * 48
+        if not hasattr(self, "_limb_rows"):
+            from improved_body_parts_b200.config import LIMBS
+            rows = []
+            for d in self.dev_sets:
+                self.pp.enqueue(d, IMG)
+                res = self.pp.fetch(self.batch)
+                n = 0
+                for b in range(self.batch):
+                    pk = res.peaks[b]
+                    lo, hi, cnt = {}, {}, {}
+                    for part in range(18):
+                        ys = pk["y"][pk["part"] == part]
+                        cnt[part] = len(ys)
+                        if len(ys):
+                            lo[part], hi[part] = int(ys.min()), int(ys.max())
+                    for pa, pb in LIMBS:
+                        pa, pb = int(pa), int(pb)
+                        if cnt[pa] and cnt[pb]:
+                            r0 = max(0, ((min(lo[pa], lo[pb]) - 2) >> 2) - 2)
+                            r1 = min(FEAT, ((max(hi[pa], hi[pb]) - 2) >> 2) + 4)
+                            n += r1 - r0
+                rows.append(n)
+            self._limb_rows = float(np.mean(rows))
+        return int(full * 18 + 2 * self._limb_rows * FEAT * esz)
 
     def d2h(self):
         # ibp_fetch_coco: offsets + status + one 52-float row per human of the batch
@@ -650,6 +684,7 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
                    "h2d_bytes_per_step": world * wl.h2d(), "d2h_bytes_per_step": world * wl.d2h(),
                    "ms_per_step": ms_e2e / args.steps, "repeats": len(regions_e2e),
                    "h2d_gbs_per_rank": wl.h2d() / (ms_e2e / args.steps * 1e-3) / 1e9,
+                   **({"h2d_bytes_offered_per_step": world * wl.host_sets[0].numel() * 4 // 50 * 48} if hasattr(wl, "host_sets") else {}),
                    **({"note": wl.e2e_note} if hasattr(wl, "e2e_note") else {})},
            "gpu_launches": int(launches),
            "roofline": {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -666,7 +701,7 @@ def measure(wl, args, dev, world, rank, traffic_key=None):
                             "note": "device-resident float16 network output (the reference's amp O1 default), same streaming kernels"}
     if ms_e2e16:
         out["e2e_f16"] = {"value": world * batch * args.steps / (ms_e2e16 * 1e-3), "unit": UNIT,
-                          "h2d_bytes_per_step": world * wl.h2d() // 2,
+                          "h2d_bytes_per_step": world * wl.h2d(2),
                           "note": "same call, float16 network output (the reference's amp O1 default, parse_skeletons.py:75-80)"}
     return out
 

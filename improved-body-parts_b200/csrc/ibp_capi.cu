@@ -1510,25 +1510,45 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
     const size_t image_stride = (size_t)2 * kLayers * fh * fw;
     const size_t elems = (size_t)batch * image_stride;
     const void *dev_in = net_out;
+    const void *limb_in = nullptr;  // where the limb kernel reads the limb planes from (default: the same place as the peak kernel)
+    const size_t plane_bytes = (size_t)fh * fw * 4;
+    const bool direct = plane_bytes <= kLimbPlaneMaxBytes && limb_smem_bytes(h, plane_bytes) <= kMaxDynSmem;
     if (on_host) {
         const size_t bytes = elems * (dtype == IBP_F16 ? 2 : 4);
         int rc = ensure_stage(h, bytes, st);
         if (rc != IBP_OK) return rc;
-        // the path reads the 30 limb and 18 keypoint planes of each half (parse_skeletons.py:137 skips the two background
-        // channels): only those cross the bus, 4 % fewer bytes on a copy that is 98 % of the end-to-end step
         const size_t half_bytes = bytes / ((size_t)batch * 2);
-        const size_t used_bytes = half_bytes / kLayers * (kLimbs + kParts);
-        CU(cudaMemcpy2DAsync(h->d_stage, half_bytes, net_out, half_bytes, used_bytes, (size_t)batch * 2, cudaMemcpyHostToDevice, st));
+        // Pinned (page-locked, device-mapped) host buffers: only the 18 keypoint planes of each half are copied — the peak
+        // kernel reads all of them — while the limb kernel pulls the limb rows it needs STRAIGHT from the host buffer with its
+        // bulk copies: a limb item touches only the rows between the extreme peaks of its two joint types (~43 % of a plane
+        // on the benchmark images), and which rows is only known on the device.  36 % fewer bytes cross the bus on a step
+        // that is 98 % bus time.  The caller's buffer must stay unchanged until the batch has been fetched.
+        static const bool no_zero_copy = getenv("IBP_NO_ZEROCOPY") != nullptr;
+        cudaPointerAttributes pa;
+        void *mapped = nullptr;
+        if (direct && !no_zero_copy && cudaPointerGetAttributes(&pa, net_out) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+            mapped = pa.devicePointer;
+        else
+            cudaGetLastError();  // a pageable pointer is not an error here
+        if (mapped) {
+            const size_t kp_off = half_bytes / kLayers * kLimbs, kp_bytes = half_bytes / kLayers * kParts;
+            CU(cudaMemcpy2DAsync((char *)h->d_stage + kp_off, half_bytes, (const char *)net_out + kp_off, half_bytes, kp_bytes, (size_t)batch * 2,
+                                 cudaMemcpyHostToDevice, st));
+            limb_in = mapped;
+        } else {
+            // the path reads the 30 limb and 18 keypoint planes of each half (parse_skeletons.py:137 skips the two background
+            // channels): only those cross the bus
+            const size_t used_bytes = half_bytes / kLayers * (kLimbs + kParts);
+            CU(cudaMemcpy2DAsync(h->d_stage, half_bytes, net_out, half_bytes, used_bytes, (size_t)batch * 2, cudaMemcpyHostToDevice, st));
+        }
         dev_in = h->d_stage;
     }
-    const size_t plane_bytes = (size_t)fh * fw * 4;
-    const bool direct = plane_bytes <= kLimbPlaneMaxBytes && limb_smem_bytes(h, plane_bytes) <= kMaxDynSmem;
     if (direct) {
         // two kernels, the network output is read once and nothing intermediate is written: the flip average
         // happens while each keypoint band / limb plane is staged in shared memory
         int rc = launch_peaks(h, dev_in, dtype, image_stride, kLimbs, kLayers, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, st, /*may_defer=*/true);
         if (rc != IBP_OK) return rc;
-        return launch_limbs(h, dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st);
+        return launch_limbs(h, limb_in ? limb_in : dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st);
     }
     // limb planes too large for shared memory: materialise the fused float32 maps, sample them through L2
     int rc = ensure_fused(h, (size_t)batch * kLayers * fh * fw);

@@ -217,8 +217,11 @@ int ibp_assign(ibp_handle *h, const float *limb_src, int mode, int batch, int di
 
 /* ---------------------------------------------------------------------------------------------------------------
  * 3. Batched pipeline: everything evaluate.py:75-129 does after the model call, for `batch` images.
- *    net_out (batch,2,50,h,w); on_host != 0 means a HOST pointer (pinned or pageable) that is copied in-stream: the 48
- *    limb + keypoint planes of each half only, the two background planes are never read on this path.
+ *    net_out (batch,2,50,h,w); on_host != 0 means a HOST pointer.  Pageable: the 48 limb + keypoint planes of each half are
+ *    copied in-stream (the two background planes are never read on this path).  Pinned (page-locked, as cudaHostAlloc /
+ *    torch pin_memory give it): only the 18 keypoint planes of each half are copied; the limb kernel reads the limb rows it
+ *    needs straight out of the caller's buffer over the bus (about 36 % fewer bytes), so that buffer must stay unchanged
+ *    until ibp_fetch / ibp_fetch_coco has returned for this batch (IBP_NO_ZEROCOPY=1 in the environment forces the copy).
  *    ibp_fetch waits for the stream, copies the packed results to the handle's pinned buffers and fills `view`.
  * ------------------------------------------------------------------------------------------------------------- */
 int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int dtype, int batch, int fh, int fw,
