@@ -370,8 +370,8 @@ class Refactored:
         self.dtype = "f32"
         fb = 2 * FEAT * FEAT * 4
         self.e2e_note = ("the caller hands over the whole (B,2,50,h,w) pinned host tensor; h2d_bytes_per_step is what crosses the bus: the 36 "
-                         "keypoint planes per image by cudaMemcpy2DAsync plus the limb rows the limb kernel pulls straight from the pinned "
-                         "buffer (rows between the extreme peaks of a limb's joint types, counted from the fetched peaks); "
+                         "keypoint planes per image by cudaMemcpy2DAsync plus the limb boxes the limb kernel pulls straight from the pinned "
+                         "buffer (rows x columns between the extreme peaks of a limb's joint types, counted from the fetched peaks); "
                          "h2d_bytes_offered_per_step = the 96 limb + keypoint planes per image a full copy would move")
         self.algo_bytes = {"peaks": 18 * fb, "limbs": 30 * fb}  # planes of the upright and the flipped output, read once
 
@@ -418,13 +418,13 @@ class Refactored:
     def h2d(self, esz=4):
         """Bytes that cross the bus per step.  ibp_postprocess_batch copies the 18 keypoint planes of each half; the limb
         kernel pulls the limb rows it needs straight out of the pinned host buffer (zero copy) — for limb l of an image the
-        feature rows between the extreme peaks of its two joint types plus the bicubic support (the formula of
-        index_bands_kernel, csrc/k_peaks.cuh), of the upright and of the twin plane.  Counted here from the fetched peaks,
+        box of feature rows x columns between the extreme peaks of its two joint types plus the bicubic support (the
+        formula of index_bands_kernel, csrc/k_peaks.cuh), of the upright and of the twin plane.  Counted here from the fetched peaks,
         averaged over the two input sets; the 2 background planes never move.  With IBP_NO_ZEROCOPY the 48 planes are copied."""
         full = self.host_sets[0].numel() * esz // 50
         if os.environ.get("IBP_NO_ZEROCOPY"):
             return full * 48
-        if not hasattr(self, "_limb_rows"):
+        if not hasattr(self, "_limb_elems"):
             from improved_body_parts_b200.config import LIMBS
             rows = []
             for d in self.dev_sets:
@@ -433,21 +433,24 @@ class Refactored:
                 n = 0
                 for b in range(self.batch):
                     pk = res.peaks[b]
-                    lo, hi, cnt = {}, {}, {}
+                    lo, hi, xl, xh, cnt = {}, {}, {}, {}, {}
                     for part in range(18):
-                        ys = pk["y"][pk["part"] == part]
+                        sel = pk["part"] == part
+                        ys, xs = pk["y"][sel], pk["x"][sel]
                         cnt[part] = len(ys)
                         if len(ys):
-                            lo[part], hi[part] = int(ys.min()), int(ys.max())
+                            lo[part], hi[part], xl[part], xh[part] = int(ys.min()), int(ys.max()), int(xs.min()), int(xs.max())
                     for pa, pb in LIMBS:
                         pa, pb = int(pa), int(pb)
                         if cnt[pa] and cnt[pb]:
                             r0 = max(0, ((min(lo[pa], lo[pb]) - 2) >> 2) - 2)
                             r1 = min(FEAT, ((max(hi[pa], hi[pb]) - 2) >> 2) + 4)
-                            n += r1 - r0
+                            c0 = max(0, ((min(xl[pa], xl[pb]) - 2) >> 2) - 2) & ~7
+                            c1 = min(FEAT, (((max(xh[pa], xh[pb]) - 2) >> 2) + 4 + 7) & ~7)
+                            n += (r1 - r0) * (c1 - c0)
                 rows.append(n)
-            self._limb_rows = float(np.mean(rows))
-        return int(full * 18 + 2 * self._limb_rows * FEAT * esz)
+            self._limb_elems = float(np.mean(rows))
+        return int(full * 18 + 2 * self._limb_elems * esz)
 
     def d2h(self):
         # ibp_fetch_coco: offsets + status + one 52-float row per human of the batch

@@ -139,7 +139,7 @@ struct ibp_handle {
     int order_batch = 0;           // batch size d_order is valid for (0: not valid)
     int defer_bands = 0;           // > 0: the last peak launch left its band lists unpacked (this many bands per plane)
     int defer_batch = 0;
-    int *d_yext = nullptr;         // [max_batch][18][2] y extent of each part's peaks, kept "empty" between launches
+    int *d_yext = nullptr;         // [max_batch][18][4] y and x extent of each part's peaks, kept "empty" between launches
     int4 *d_item_meta = nullptr;   // [max_batch*30] limb items in heaviest-image-first order (index_bands_kernel)
     unsigned *d_lb_work = nullptr; // work counter of the streaming limb kernel, never reset ...
     unsigned lb_work_base = 0;     // ... its value before the next launch
@@ -465,12 +465,14 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMalloc(&h->d_order, B * sizeof(int)));
         CU(cudaMalloc(&h->d_partbase, B * (kParts + 1) * sizeof(int)));
         CU(cudaMalloc(&h->d_item_meta, B * (kLimbs + 1) * sizeof(int4)));
-        CU(cudaMalloc(&h->d_yext, B * kParts * 2 * sizeof(int)));
-        CU(cudaMemset(h->d_yext, 0x80, B * kParts * 2 * sizeof(int)));  // 0x80808080: below every -y
+        CU(cudaMalloc(&h->d_yext, B * kParts * 4 * sizeof(int)));
+        CU(cudaMemset(h->d_yext, 0x80, B * kParts * 4 * sizeof(int)));  // 0x80808080: below every -y
         CU(cudaMalloc(&h->d_lb_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_lb_work, 0, sizeof(unsigned)));
         CU(cudaFuncSetAttribute(limbs_stream_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_stream_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaMalloc(&h->d_pk_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_pk_work, 0, sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
@@ -1225,6 +1227,7 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
             ia.item_meta = h->d_item_meta;
             ia.yext = h->d_yext;
             ia.h = fh;
+            ia.w = fw;
             ia.up = h->P.upsample;
             ia.status = h->d_status;
             CU(launch_dependent(index_bands_kernel, dim3(batch), dim3(32), 0, st, ia));
@@ -1339,7 +1342,7 @@ int set_peaks_impl(ibp_handle *h, int image, const float *host_peaks, int n, int
 // ------------------------------------------------------------------------------------------------ K3 + K4
 namespace {
 int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int twin_base, size_t image_stride, int batch, int dim0, int dim1,
-                 int dim2, int min_img_size, cudaStream_t st) {
+                 int dim2, int min_img_size, cudaStream_t st, bool src_over_bus = false) {
     if (batch < 1 || batch > h->L.max_batch) return fail(IBP_ERR_ARG, "assign: batch %d exceeds limit %d", batch, h->L.max_batch);
     if (dim0 < 1 || dim1 < 1 || dim2 < kLimbs) return fail(IBP_ERR_SHAPE, "assign: bad shape (%d,%d,%d)", dim0, dim1, dim2);
     if (mode != IBP_LIMB_FULLRES_HWC && mode != IBP_LIMB_FEAT_PLANAR) return fail(IBP_ERR_ARG, "assign: mode %d", mode);
@@ -1454,7 +1457,8 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         a.work_base = h->lb_work_base;
         a.plane_bytes = (int)plane_s_bytes;
         a.smem_bytes = (int)smem_s;
-        void (*kern)(LimbArgs) = dtype == IBP_F16 ? limbs_stream_kernel<__half> : limbs_stream_kernel<float>;
+        void (*kern)(LimbArgs) = src_over_bus ? (dtype == IBP_F16 ? limbs_stream_kernel<__half, true> : limbs_stream_kernel<float, true>)
+                                              : (dtype == IBP_F16 ? limbs_stream_kernel<__half> : limbs_stream_kernel<float>);
         const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
         if (h->lb_occ_smem != smem_s || h->lb_occ_kern != (const void *)kern) {  // every CTA of the grid must be resident (queue items wait for one another)
             int per_sm = 0;
@@ -1548,7 +1552,8 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
         // happens while each keypoint band / limb plane is staged in shared memory
         int rc = launch_peaks(h, dev_in, dtype, image_stride, kLimbs, kLayers, batch, fh, fw, IBP_PEAKS_CROSS_REFINE, st, /*may_defer=*/true);
         if (rc != IBP_OK) return rc;
-        return launch_limbs(h, limb_in ? limb_in : dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st);
+        return launch_limbs(h, limb_in ? limb_in : dev_in, dtype, IBP_LIMB_FEAT_PLANAR, kLayers, image_stride, batch, fh, fw, kLayers, min_img_size, st,
+                            /*src_over_bus=*/limb_in != nullptr);
     }
     // limb planes too large for shared memory: materialise the fused float32 maps, sample them through L2
     int rc = ensure_fused(h, (size_t)batch * kLayers * fh * fw);

@@ -646,7 +646,9 @@ __global__ void __launch_bounds__(kLimbThreads) limbs_kernel(LimbArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kLimbStreamThreads = 256;
 
-template <typename T>
+// BOX: stage only the columns an item's samples can touch (the source is host memory read over the bus); from device memory
+// whole rows are staged — one bulk copy per item beats a copy per row there.
+template <typename T, bool BOX = false>
 __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(LimbArgs a) {
     constexpr int kLimbThreads = kLimbStreamThreads;
     constexpr int V = 16 / (int)sizeof(T);  // elements per 16-byte vector
@@ -708,17 +710,32 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     auto twin_of = [&](int img, int limb) {  // flipped image: channel flip_paf_ord[limb] of its block (config/config.py:150-152)
         return reinterpret_cast<const T *>(a.src) + (size_t)img * a.image_stride + (size_t)(a.twin_base + c_flip_src[limb]) * hw;
     };
-    // Only the feature rows [r0, r1) that a sample of the item can touch are staged (at their own place in the buffer).
-    auto has_pairs = [](const int4 &it) { return (it.y & 0xffff) > 0 && (it.y >> 16) > 0 && it.z < kLimbs; };
-    auto twin_chunk = [&](const T *twin, int r0, int r1, int c) {  // one thread: chunk c of the twin rows into its ring slot
+    // Only the box of feature rows [r0, r1) x columns [c0, c1) that a sample of the item can touch is staged (at its own place in
+    // the buffer): item.w = r0 | r1 << 16, item.z = limb | (c0 / 4) << 8 | (c1 / 4) << 20 (index_bands_kernel).
+    auto item_limb = [](const int4 &it) { return it.z & 0xff; };
+    auto item_c0 = [&](const int4 &it) { return BOX ? ((it.z >> 8) & 0xfff) << 2 : 0; };
+    auto item_c1 = [&](const int4 &it) { return BOX ? (int)((unsigned)it.z >> 20) << 2 : a.w; };
+    auto has_pairs = [&](const int4 &it) { return (it.y & 0xffff) > 0 && (it.y >> 16) > 0 && item_limb(it) < kLimbs; };
+    // one thread: `rows` rows of columns [col0, col0 + ncols) from src to dst (both with a row pitch of a.w elements)
+    auto bulk_box = [&](T *dst, const T *src, int rows, int col0, int ncols, uint64_t *bar) {
+        if (!BOX || ncols == a.w) {
+            bulk_rows(dst, src, (uint32_t)rows * a.w * (uint32_t)sizeof(T), bar);
+            return;
+        }
+        const uint32_t row_bytes = (uint32_t)ncols * (uint32_t)sizeof(T);
+        mbar_expect_tx(bar, (uint32_t)rows * row_bytes);
+        for (int r = 0; r < rows; r++) bulk_g2s(dst + (size_t)r * a.w + col0, src + (size_t)r * a.w + col0, row_bytes, bar);
+    };
+    // one thread: chunk c of the twin rows into its ring slot; the twin is mirrored, the box's columns [c0, c1) are its [w - c1, w - c0)
+    auto twin_chunk = [&](const T *twin, int r0, int r1, int c0, int c1, int c) {
         const int s = c % kLimbRing, first = r0 + c * slot_rows;
         const int rows = min(slot_rows, r1 - first);
-        bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * a.w * (uint32_t)sizeof(T), &bars[1 + s]);
+        bulk_box(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, rows, a.w - c1, c1 - c0, &bars[1 + s]);
     };
-    auto upright_rows = [&](const int4 &it) {  // one thread: the upright rows of a limb item straight to their place
+    auto upright_rows = [&](const int4 &it) {  // one thread: the upright box of a limb item straight to its place
         if (!has_pairs(it)) return;
         const int r0 = it.w & 0xffff, r1 = it.w >> 16;
-        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, it.z) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * (uint32_t)sizeof(T), &bars[0]);
+        bulk_box(plane_s + (size_t)r0 * a.w, upright_of(it.x, item_limb(it)) + (size_t)r0 * a.w, r1 - r0, item_c0(it), item_c1(it) - item_c0(it), &bars[0]);
     };
 
     pdl_wait();  // launched as a programmatic dependent: the work queue and the band lists come from the kernels before
@@ -737,8 +754,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
     for (;;) {
         const int4 cur = s_next;
         if (cur.x < 0) break;
-        const int img = cur.x, nA = cur.y & 0xffff, nB = cur.y >> 16, limb = cur.z;
-        const int r0 = cur.w & 0xffff, r1 = cur.w >> 16;
+        const int img = cur.x, nA = cur.y & 0xffff, nB = cur.y >> 16, limb = item_limb(cur);
+        const int r0 = cur.w & 0xffff, r1 = cur.w >> 16, c0 = item_c0(cur), c1 = item_c1(cur);
         unsigned claimed = 0;
         int4 nmeta = make_int4(-1, 0, 0, 0);
         // thread 0: who is next (one load, issued early), and — once the plane is dead — start its upright plane
@@ -793,7 +810,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             claimed = atomicAdd(a.work_counter, 1u);
             if (pairs) {
                 fence_proxy_async();  // the previous round's generic-proxy use of the ring region comes first
-                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(twin, r0, r1, c);
+                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(twin, r0, r1, c0, c1, c);
             }
         }
         limb_stamp(a, img, limb, 0);
@@ -860,7 +877,8 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             up_uses++;
             {
                 const int wv = a.w / V;
-                const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
+                const int v0 = c0 / V, nv = (c1 - c0) / V;  // the box in 16-byte vectors
+                const int shift = ((nv & (nv - 1)) == 0) ? (__ffs(nv) - 1) : -1;
                 Vec *d4 = reinterpret_cast<Vec *>(plane_s);
                 for (int c = 0; c < nchunks; c++) {
                     const int s = c % kLimbRing;
@@ -870,18 +888,28 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
                     const int rows = min(slot_rows, r1 - first);
                     const Vec *r4 = reinterpret_cast<const Vec *>(ring + (size_t)s * slot_rows * a.w);
                     Vec *o4 = d4 + (size_t)first * wv;
-                    for (int i = tid; i < rows * wv; i += kLimbThreads) {
-                        const int r = (shift >= 0) ? (i >> shift) : (i / wv);
-                        const int col = i - r * wv;
-                        Vec v = o4[i];
-                        fold_mirrored(v, r4[r * wv + (wv - 1 - col)]);
-                        o4[i] = v;
+                    if (!BOX || nv == wv) {  // whole rows
+                        for (int i = tid; i < rows * wv; i += kLimbThreads) {
+                            const int r = (shift >= 0) ? (i >> shift) : (i / wv);
+                            const int col = i - r * wv;
+                            Vec v = o4[i];
+                            fold_mirrored(v, r4[r * wv + (wv - 1 - col)]);
+                            o4[i] = v;
+                        }
+                    } else {
+                        for (int i = tid; i < rows * nv; i += kLimbThreads) {
+                            const int r = (shift >= 0) ? (i >> shift) : (i / nv);
+                            const int col = v0 + i - r * nv;
+                            Vec v = o4[r * wv + col];
+                            fold_mirrored(v, r4[r * wv + (wv - 1 - col)]);
+                            o4[r * wv + col] = v;
+                        }
                     }
                     if (c + kLimbRing < nchunks) {
                         __syncthreads();  // everybody has read slot s
                         if (tid == 0) {
                             fence_proxy_async();
-                            twin_chunk(twin, r0, r1, c + kLimbRing);
+                            twin_chunk(twin, r0, r1, c0, c1, c + kLimbRing);
                         }
                     }
                 }

@@ -61,7 +61,7 @@ struct PeakArgs {
     unsigned long long *timeline;  // experiments only: (batch, 18, nbands, 6) %globaltimer stamps, or null
     int *order;           // (batch) images sorted by descending number of peaks, written by the last CTA of the launch
     int batch;
-    int *yext;               // (batch, 18, 2) or null, defer_pack only: running {max(-y), max(y)} of each part's peaks;
+    int *yext;               // (batch, 18, 4) or null, defer_pack only: running {max(-y), max(y), max(-x), max(x)} of each part's peaks;
                              // "nothing yet" is any value below -2^30 (the index kernel resets the entries it read)
     int defer_pack;          // streaming kernel: 1 = leave the band lists as they are (no tickets, no pack, no order): the
                              // limb kernel gathers them itself; only n_raw[img] += peaks of the band
@@ -296,9 +296,11 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = best;
                 p.id = k;
                 out[k] = p;
-                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                if (yext) {  // extent of this part's peaks (up-sampled pixels): {max of -y, max of y, max of -x, max of x}
                     atomicMax(yext, -p.y);
                     atomicMax(yext + 1, p.y);
+                    atomicMax(yext + 2, -p.x);
+                    atomicMax(yext + 3, p.x);
                 }
             }
             __syncwarp();
@@ -381,9 +383,11 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = best;
                 p.id = k;
                 out[k] = p;
-                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                if (yext) {  // extent of this part's peaks (up-sampled pixels): {max of -y, max of y, max of -x, max of x}
                     atomicMax(yext, -p.y);
                     atomicMax(yext + 1, p.y);
+                    atomicMax(yext + 2, -p.x);
+                    atomicMax(yext + 3, p.x);
                 }
             }
             __syncwarp();
@@ -438,9 +442,11 @@ __device__ __forceinline__ void peaks_refine(const Acc &B, const PeakArgs &a, in
                 p.score = sc;
                 p.id = k;
                 out[k] = p;
-                if (yext) {  // extent of this part's peaks in y (up-sampled pixels): {max of -y, max of y}
+                if (yext) {  // extent of this part's peaks (up-sampled pixels): {max of -y, max of y, max of -x, max of x}
                     atomicMax(yext, -p.y);
                     atomicMax(yext + 1, p.y);
+                    atomicMax(yext + 2, -p.x);
+                    atomicMax(yext + 3, p.x);
                 }
                 if (a.band_subpix) {
                     double *sp = a.band_subpix + (slot_base + k) * 2;
@@ -847,7 +853,7 @@ __global__ void __launch_bounds__(kPeakThreads, kPeakStreamCtasPerSm) peaks_stre
         workers_sync();
         const size_t slot_base = (size_t)item * a.cap;  // == ((img*18 + part)*nbands + band) * cap
         peaks_refine<FLAVOUR>(B, a, n, sc.sorted, a.band_peaks + slot_base, slot_base, sc.hbuf_all + wwarp * sc.hbuf_per_warp, tab4, wwarp, nworkers,
-                              (a.defer_pack && a.yext) ? a.yext + ((size_t)it.img * kParts + it.part) * 2 : nullptr);
+                              (a.defer_pack && a.yext) ? a.yext + ((size_t)it.img * kParts + it.part) * 4 : nullptr);
         if (wtid == 0) {
             a.band_count[item] = n;
             if (n_raw > a.cap) atomicOr(a.status + it.img, IBP_ST_PEAK_OVERFLOW);
@@ -876,11 +882,12 @@ struct IndexArgs {
     int *partbase;          // (batch, 19)
     int *n_peaks;           // (batch)
     int *order;             // (batch)
-    int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel, images by rank (0 = most peaks):
+    int4 *item_meta;        // (batch*31) or null: work queue of the streaming limb kernel, images by rank (0 = most peaks); z = limb | (c0/4) << 8 | (c1/4) << 20:
                             // {image, nA | nB << 16, limb, r0 | r1 << 16} for the 30 limbs of an image — [r0, r1) = the
                             // feature rows any sample of the limb can touch — and {image, 0, 30, 0} = "group it",
                             // queued kGroupLag images after its limbs
-    int *yext;              // (batch, 18, 2) from the peak kernel, reset here
+    int *yext;              // (batch, 18, 4) from the peak kernel ({max -y, max y, max -x, max x} per part), reset here
+    int w;                  // feature width
     int h, up;              // feature rows, up-sampling factor
     uint32_t *status;       // (batch)
 };
@@ -896,11 +903,13 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
     int cv[kRounds];
 #pragma unroll
     for (int r = 0; r < kRounds; r++) cv[r] = (r * 32 + lane < items) ? bc[r * 32 + lane] : 0;
-    int ext_lo = 0, ext_hi = 0;  // y extent of part `lane`
+    int ext_lo = 0, ext_hi = 0, ext_xlo = 0, ext_xhi = 0;  // y and x extent of part `lane`
     if (a.item_meta && lane < kParts) {
-        const int *e = a.yext + ((size_t)img * kParts + lane) * 2;
+        const int *e = a.yext + ((size_t)img * kParts + lane) * 4;
         ext_lo = e[0];
         ext_hi = e[1];
+        ext_xlo = e[2];
+        ext_xhi = e[3];
     }
     const int mine = a.n_raw[img];
     int rank = 0;
@@ -941,19 +950,21 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
     }
     if (a.item_meta) {
         // y extent of each part's peaks (up-sampled pixels)
-        __shared__ int ylo[kParts], yhi[kParts];
+        __shared__ int ylo[kParts], yhi[kParts], xlo[kParts], xhi[kParts];
         if (lane < kParts) {
-            int *e = a.yext + ((size_t)img * kParts + lane) * 2;
+            int *e = a.yext + ((size_t)img * kParts + lane) * 4;
             ylo[lane] = -ext_lo;
             yhi[lane] = ext_hi;
-            e[0] = e[1] = INT_MIN;  // ready for the next launch
+            xlo[lane] = -ext_xlo;
+            xhi[lane] = ext_xhi;
+            e[0] = e[1] = e[2] = e[3] = INT_MIN;  // ready for the next launch
         }
         __syncwarp();
         if (lane < kLimbs) {
             const int pa = c_limb_a[lane], pb = c_limb_b[lane];
             const int na = min(offs[(pa + 1) * a.nbands] - offs[pa * a.nbands], a.cap);
             const int nb = min(offs[(pb + 1) * a.nbands] - offs[pb * a.nbands], a.cap);
-            int r0 = 0, r1 = a.h;
+            int r0 = 0, r1 = a.h, c0 = 0, c1 = a.w;
             if (a.up == 4 && na > 0 && nb > 0) {
                 // samples lie between the two end points (pafprocess.cpp:319-320); the x4 bicubic of an up-sampled row Y
                 // reads feature rows ((Y-2)>>2)-1 .. ((Y-2)>>2)+2 (ibp_device.cuh cubic_sample4); one more row either side
@@ -961,9 +972,14 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
                 r0 = max(0, ((lo - 2) >> 2) - 2);
                 r1 = min(a.h, ((hi - 2) >> 2) + 4);
                 if (r1 <= r0) { r0 = 0; r1 = a.h; }
+                // the same for the columns, widened to whole 32-byte pieces (the rows of the box are staged one by one)
+                const int xl = min(xlo[pa], xlo[pb]), xh = max(xhi[pa], xhi[pb]);
+                c0 = max(0, ((xl - 2) >> 2) - 2) & ~7;
+                c1 = min(a.w, (((xh - 2) >> 2) + 4 + 7) & ~7);
+                if (c1 <= c0 || (a.w & 3) || a.w > 16380) { c0 = 0; c1 = a.w; }
             }
             // queue position: the 30 limbs of rank r follow those of rank r-1 and the "group it" items of ranks < r - lag
-            a.item_meta[rank * kLimbs + lane + max(0, rank - kGroupLag)] = make_int4(img, na | (nb << 16), lane, r0 | (r1 << 16));
+            a.item_meta[rank * kLimbs + lane + max(0, rank - kGroupLag)] = make_int4(img, na | (nb << 16), lane | ((c0 >> 2) << 8) | ((c1 >> 2) << 20), r0 | (r1 << 16));
         }
         // "group image of rank q" is queued kGroupLag images later (by then its limbs are finished and whoever claims it
         // does not have to wait), the last ones at the very end
