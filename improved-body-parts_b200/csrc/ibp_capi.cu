@@ -1530,7 +1530,15 @@ int ibp_postprocess_batch(ibp_handle *h, const void *net_out, int on_host, int d
         static const bool no_zero_copy = getenv("IBP_NO_ZEROCOPY") != nullptr;
         cudaPointerAttributes pa;
         void *mapped = nullptr;
-        if (direct && !no_zero_copy && cudaPointerGetAttributes(&pa, net_out) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer)
+        // only when the streaming limb kernel will run (it alone stages a box per item; the one-CTA-per-item kernel of the crowd
+        // handles stages whole planes and is better fed from device memory)
+        const size_t esz_in = dtype == IBP_F16 ? 2 : 4;
+        const size_t plane_in = (((size_t)fh * fw * esz_in) + 15) & ~(size_t)15;
+        const bool will_stream = h->L.max_peaks_per_part <= 128 && ((size_t)fw * esz_in) % 16 == 0 &&
+                                 limb_phase_bytes(h, plane_in) >= group_phase_bytes(h) &&
+                                 limb_smem_bytes(h, plane_in) - plane_in >= group_phase_bytes(h) && limb_smem_bytes(h, plane_in) <= kMaxDynSmem;
+        if (direct && will_stream && !no_zero_copy && cudaPointerGetAttributes(&pa, net_out) == cudaSuccess && pa.type == cudaMemoryTypeHost &&
+            pa.devicePointer)
             mapped = pa.devicePointer;
         else
             cudaGetLastError();  // a pageable pointer is not an error here
