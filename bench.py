@@ -422,7 +422,7 @@ class Refactored:
         formula of index_bands_kernel, csrc/k_peaks.cuh), of the upright and of the twin plane.  Counted here from the fetched peaks,
         averaged over the two input sets; the 2 background planes never move.  With IBP_NO_ZEROCOPY the 48 planes are copied."""
         full = self.host_sets[0].numel() * esz // 50
-        if os.environ.get("IBP_NO_ZEROCOPY"):
+        if os.environ.get("IBP_NO_ZEROCOPY") or self.crowd:  # the crowd handle runs the one-CTA-per-item limb kernel: staged copy
             return full * 48
         if not hasattr(self, "_limb_elems"):
             from improved_body_parts_b200.config import LIMBS
