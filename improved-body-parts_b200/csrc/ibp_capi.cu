@@ -947,7 +947,8 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     // exact capacities of the staging buffers for this launch plan, from the (cached) host copy of the tables
     {
         const LinTap *tab = h->h_lin_tab;
-        int off = 0;
+        int off = 0, hoff = 0;
+        a.step1 = 1;
         for (int s = 0; s < ns; s++) {
             const LinTap *xt = tab + (size_t)s * per_scale, *yt = xt + W;
             int nc = 1, maxr = 1;
@@ -962,19 +963,25 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
                     loaded = std::max(loaded, f_hi);
                 }
             }
+            for (int X = 0; X + 1 < W; X++)
+                if (xt[X + 1].base - xt[X].base > 1) a.step1 = 0;
+            nc += 4;  // the four-load form of the horizontal pass reads one column past a thread's last tap
             a.nc[s] = nc;
             a.maxr[s] = maxr;
             a.off[s] = off;
             off += 2 * nc * maxr;
+            a.hoff[s] = hoff;
+            hoff += (maxr + 3) * kLinCols;
         }
         a.buf_floats = (off + 3) & ~3;
+        a.hr_floats = hoff;
     }
-    const size_t smem = 2 * (size_t)a.buf_floats * sizeof(float) + 2 * (size_t)ns * kLinSeg * sizeof(LinTap);
-    if (smem > 96 * 1024) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: staging buffers of %zu B", smem);
+    const size_t smem = ((size_t)a.buf_floats + a.hr_floats) * sizeof(float) + 2 * (size_t)ns * kLinSeg * sizeof(LinTap);
+    if (smem > 160 * 1024) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: staging buffers of %zu B", smem);
     const dim3 grid((unsigned)cols, (unsigned)((H + a.chain_rows - 1) / a.chain_rows), (unsigned)batch * kLayers);
 #define IBP_LIN_LAUNCH(N)                                                                                          \
     do {                                                                                                           \
-        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(fuse_linear_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
+        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(fuse_linear_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); \
         fuse_linear_kernel<N><<<grid, kLinThreads, smem, st>>>(a);                                                 \
     } while (0)
     {

@@ -37,10 +37,13 @@ struct LinScale {
 };
 struct LinArgs {
     LinScale sc[kLinMaxScales];
-    int nc[kLinMaxScales];    // feature columns a CTA's 128 output columns can touch (capacity of a staged row)
-    int maxr[kLinMaxScales];  // feature rows a segment can add (capacity of a staging buffer)
-    int off[kLinMaxScales];   // float offset of the scale's rows inside a staging buffer: upright rows, then twin rows
-    int buf_floats;           // floats per staging buffer (there are two)
+    int nc[kLinMaxScales];    // feature columns a CTA's 256 output columns can touch (capacity of a staged row)
+    int maxr[kLinMaxScales];  // feature rows a segment can add (capacity of the raw staging buffer)
+    int off[kLinMaxScales];   // float offset of the scale's raw rows in the staging buffer: upright rows, then twin rows
+    int hoff[kLinMaxScales];  // float offset of the scale's horizontal sums: (maxr + 3) rows of kLinCols floats
+    int buf_floats;           // floats of the raw staging buffer
+    int hr_floats;            // floats of the horizontal sums of all scales
+    int step1;                // the taps of two adjacent output columns start at most one feature column apart (every scale <= 4)
     int n_scales, flip, H, W;
     int chain_rows;           // output rows one CTA walks (multiple of kLinSeg)
     double *out;
@@ -48,20 +51,21 @@ struct LinArgs {
 };
 constexpr int kLinCols = 256;  // output columns of a CTA: a thread owns two adjacent ones (packed float32x2 arithmetic)
 
-__device__ __forceinline__ void lin_cp4(void *dst_smem, const void *src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
 __device__ __forceinline__ void lin_cp16(void *dst_smem, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
 
-// A CTA owns 256 output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  The feature rows a
-// segment adds to the windows (and the row taps of its output rows) are copied to shared memory with cp.async one
-// segment AHEAD, all requests independent, so HBM latency is paid once per segment and under the previous segment's
-// arithmetic; the walk itself only reads shared memory.  The four scales of a pixel are summed in float32 and widened
-// once (this mode is held to a tolerance, not to the bits of a float64 running sum).
+// A CTA owns 256 output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  Per segment:
+//   1. the feature rows the segment adds (and the row taps of its output rows) have been copied to shared memory with
+//      16-byte cp.async while the PREVIOUS segment was computed: HBM latency is paid once per segment, under arithmetic;
+//   2. horizontal pass: every thread turns the new raw rows into the three-tap sums of its two columns (flip average on
+//      the way) and appends them to its own column of the HR table — thread-private shared memory, no barrier;
+//   3. the raw buffer is free: the next segment's rows are requested;
+//   4. vertical pass, straight-line: per output row and scale one uniform 128-bit load of the row's taps, three loads
+//      from HR at immediate offsets, three packed multiply-adds.  The scales of a pixel are summed in float32 and
+//      widened once (this mode is held to a tolerance, not to the bits of a float64 running sum).
 template <int NS>
-__global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
+__global__ void __launch_bounds__(kLinThreads, 3) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
     extern __shared__ __align__(16) float lin_smem[];
     const int tid = threadIdx.x;
     const int X0 = blockIdx.x * kLinCols, X = X0 + 2 * tid;
@@ -69,9 +73,10 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
     const int Y0 = blockIdx.y * a.chain_rows, Y1 = min(Y0 + a.chain_rows, a.H);
     const bool flip = a.flip != 0;
     const bool warp_active = X0 + 2 * (tid & ~31) < a.W;  // a warp entirely right of the image only helps with the copies
-    LinTap *YT = reinterpret_cast<LinTap *>(lin_smem + 2 * a.buf_floats);  // [2][NS][kLinSeg]
-    __shared__ int s_flo[2][kLinMaxScales];                                  // first feature row held by each buffer
-    __shared__ int s_hi[kLinMaxScales][kLinMaxSegs];                         // last feature row of each segment of this CTA
+    float *RAW = lin_smem;
+    float *HR = lin_smem + a.buf_floats;
+    LinTap *YT = reinterpret_cast<LinTap *>(HR + a.hr_floats);  // [2][NS][kLinSeg]
+    __shared__ int s_hi[kLinMaxScales][kLinMaxSegs];            // last feature row of each segment of this CTA
     const int n_segs = (Y1 - Y0 + kLinSeg - 1) / kLinSeg;
 
     float2 c0[NS], c1[NS], c2[NS];  // column taps of the thread's two columns
@@ -80,8 +85,8 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
     int sdst[NS];                   // ... to this float offset of a staged row (-1: nothing)
     int gtwin[NS];                  // float offset from the upright piece to the twin piece (the same for the whole CTA)
     int nc4[NS];                    // staged columns of this CTA (a multiple of four)
-    float2 w0[NS], w1[NS], w2[NS];  // horizontal sums of feature rows top, top + 1, top + 2 (both columns)
-    int top[NS], loaded[NS];        // window position; last feature row requested so far
+    int loaded[NS];                 // last feature row requested so far
+    int hbase[NS], cnt[NS];         // HR row j of the thread's column = feature row hbase + j; rows 0 .. cnt + 2 are valid
 #pragma unroll
     for (int s = 0; s < NS; s++) {
         const LinScale &S = a.sc[s];
@@ -103,23 +108,25 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
         }
         gtwin[s] = (int)((size_t)(kLayers + c_flip_src[chan] - chan) * hw) + S.w - 2 * c_lo - nc4[s];
         for (int g = tid; g < n_segs; g += kLinThreads) s_hi[s][g] = __ldg(&S.seg_hi[Y0 / kLinSeg + g]);
-        top[s] = __ldg(&S.ytab[Y0].base) - 3;  // the first output row pulls three rows into the window
-        loaded[s] = top[s] + 2;
-        w0[s] = w1[s] = w2[s] = make_float2(0.f, 0.f);
+        loaded[s] = __ldg(&S.ytab[Y0].base) - 1;  // the first segment brings in everything from the first row's window on
+        hbase[s] = loaded[s] - 2;
+        cnt[s] = 0;
     }
+    __syncthreads();  // s_hi
 
-    // requests of the segment that starts at row Ya into buffer b
-    auto request = [&](int Ya, int b) {
-        const int Yb = min(Ya + kLinSeg, Y1);
-        float *buf = lin_smem + b * a.buf_floats;
+    int req_lo[NS], req_n[NS];  // what the last request brought: feature rows req_lo .. req_lo + req_n - 1, raw rows 0 ..
+    // requests of segment k (rows Y0 + k * kLinSeg ..): the feature rows it adds into RAW, its row taps into YT[k & 1]
+    auto request = [&](int k) {
+        const int Ya = Y0 + k * kLinSeg, Yb = min(Ya + kLinSeg, Y1);
 #pragma unroll
         for (int s = 0; s < NS; s++) {
             const LinScale &S = a.sc[s];
-            const int f_hi = s_hi[s][(Ya - Y0) / kLinSeg], f_lo = loaded[s] + 1;
-            if (tid == 0) s_flo[b][s] = f_lo;
+            const int f_hi = s_hi[s][k], f_lo = loaded[s] + 1;
+            req_lo[s] = f_lo;
+            req_n[s] = max(f_hi - f_lo + 1, 0);
             if (sdst[s] >= 0) {
                 const float *g = gsrc[s] + (size_t)f_lo * S.w;
-                float *d = buf + sdst[s];
+                float *d = RAW + sdst[s];
                 const int dtw = a.maxr[s] * a.nc[s];
                 for (int fr = f_lo; fr <= f_hi; fr++, g += S.w, d += a.nc[s]) {
                     lin_cp16(d, g);
@@ -127,7 +134,7 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
                 }
             }
             loaded[s] = max(loaded[s], f_hi);
-            if (tid < Yb - Ya) lin_cp16(&YT[(b * NS + s) * kLinSeg + tid], &S.ytab[Ya + tid]);
+            if (tid < Yb - Ya) lin_cp16(&YT[((k & 1) * NS + s) * kLinSeg + tid], &S.ytab[Ya + tid]);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -135,60 +142,66 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
     double *out = a.out + ((size_t)img * kLayers + chan) * (size_t)a.H * a.W;
     float *h32 = (a.heat32 && chan >= kLimbs && chan < kLimbs + kParts) ? a.heat32 + ((size_t)img * kParts + (chan - kLimbs)) * (size_t)a.H * a.W : nullptr;
     const bool two = X + 1 < a.W, wide = two && ((a.W & 1) == 0);  // X is even: aligned pairs when the row length is even
-    __syncthreads();  // s_hi
-    request(Y0, 0);
-    int b = 0;
-    for (int Ya = Y0; Ya < Y1; Ya += kLinSeg, b ^= 1) {
-        if (Ya + kLinSeg < Y1) {
-            request(Ya + kLinSeg, b ^ 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
+    constexpr int HP = kLinCols / 2;  // row pitch of HR in float2
+    request(0);
+    for (int k = 0; k < n_segs; k++) {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
+        // ---- horizontal pass: the new raw rows -> three-tap sums of the thread's two columns, appended to its HR column ----
         if (warp_active) {
-            const float *buf = lin_smem + b * a.buf_floats;
-            const int Yb = min(Ya + kLinSeg, Y1);
-            const float *rowp[NS];  // the row a window takes in next (top + 3), at the CTA's first column
-            int tstride[NS];
 #pragma unroll
             for (int s = 0; s < NS; s++) {
-                rowp[s] = buf + a.off[s] + (top[s] + 3 - s_flo[b][s]) * a.nc[s];
-                tstride[s] = a.maxr[s] * a.nc[s];
+                const int n = req_n[s];
+                if (n > 0) {
+                    float2 *hr = reinterpret_cast<float2 *>(HR + a.hoff[s]) + tid;
+                    const int old = cnt[s];
+#pragma unroll
+                    for (int i = 0; i < 3; i++) hr[i * HP] = hr[(old + i) * HP];  // the last three rows stay: a window may start there
+                    const int nc = a.nc[s], tstride = a.maxr[s] * nc;
+                    const float *pa = RAW + a.off[s] + colA[s];
+                    const float *qa = RAW + a.off[s] + tstride + (nc4[s] - 1 - colA[s]);
+                    const int d = colB[s] - colA[s];  // the second column's taps start 0 or 1 to the right (a.step1), else anywhere
+                    for (int i = 0; i < n; i++, pa += nc, qa += nc) {
+                        float2 f0, f1, f2;
+                        if (a.step1) {  // four loads cover both columns
+                            float u0 = pa[0], u1 = pa[1], u2 = pa[2], u3 = pa[3];
+                            if (flip) {  // the twin row is staged in its own order: feature column c sits at nc4 - 1 - c
+                                u0 = avg_like_numpy(u0, qa[0]), u1 = avg_like_numpy(u1, qa[-1]), u2 = avg_like_numpy(u2, qa[-2]), u3 = avg_like_numpy(u3, qa[-3]);
+                            }
+                            f0 = make_float2(u0, d ? u1 : u0), f1 = make_float2(u1, d ? u2 : u1), f2 = make_float2(u2, d ? u3 : u2);
+                        } else {
+                            f0 = make_float2(pa[0], pa[d]), f1 = make_float2(pa[1], pa[d + 1]), f2 = make_float2(pa[2], pa[d + 2]);
+                            if (flip) {
+                                const float2 half2 = make_float2(0.5f, 0.5f);
+                                f0 = __fmul2_rn(__fadd2_rn(f0, make_float2(qa[0], qa[-d])), half2);
+                                f1 = __fmul2_rn(__fadd2_rn(f1, make_float2(qa[-1], qa[-d - 1])), half2);
+                                f2 = __fmul2_rn(__fadd2_rn(f2, make_float2(qa[-2], qa[-d - 2])), half2);
+                            }
+                        }
+                        hr[(3 + i) * HP] = __ffma2_rn(c2[s], f2, __ffma2_rn(c1[s], f1, __fmul2_rn(c0[s], f0)));
+                    }
+                    cnt[s] = n;
+                    hbase[s] = req_lo[s] - 3;
+                }
             }
-            const LinTap *yt = YT + b * NS * kLinSeg;
-            float4 e[NS];  // base, c0, c1, c2 of the row, all scales requested together (and the next row's before this row's sums)
+        }
+        __syncthreads();  // the raw rows are consumed
+        if (k + 1 < n_segs) request(k + 1);
+        // ---- vertical pass of the segment's rows: straight-line ----
+        if (warp_active) {
+            const int Ya = Y0 + k * kLinSeg, Yb = min(Ya + kLinSeg, Y1);
+            const LinTap *yt = YT + (k & 1) * NS * kLinSeg;
+            const float2 *hrs[NS];
 #pragma unroll
-            for (int s = 0; s < NS; s++) e[s] = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);
-            for (int Y = Ya; Y < Yb; Y++) {
-                yt++;
-                float4 en[NS];
-#pragma unroll
-                for (int s = 0; s < NS; s++) en[s] = *reinterpret_cast<const float4 *>(yt + s * kLinSeg - (Y + 1 < Yb ? 0 : 1));
+            for (int s = 0; s < NS; s++) hrs[s] = reinterpret_cast<const float2 *>(HR + a.hoff[s]) + tid;
+            for (int Y = Ya; Y < Yb; Y++, yt++) {
                 float2 acc = make_float2(0.f, 0.f);
 #pragma unroll
                 for (int s = 0; s < NS; s++) {
-                    const int ebase = __float_as_int(e[s].x);
-                    while (top[s] < ebase) {  // the window moves down one feature row
-                        top[s]++;
-                        const float *pa = rowp[s] + colA[s], *pb = rowp[s] + colB[s];
-                        float2 f0 = make_float2(pa[0], pb[0]), f1 = make_float2(pa[1], pb[1]), f2 = make_float2(pa[2], pb[2]);
-                        if (flip) {  // the twin row is staged in its own order: feature column c sits at nc4 - 1 - c
-                            const float *qa = rowp[s] + tstride[s] + (nc4[s] - 1 - colA[s]), *qb = rowp[s] + tstride[s] + (nc4[s] - 1 - colB[s]);
-                            const float2 half2 = make_float2(0.5f, 0.5f);
-                            f0 = __fmul2_rn(__fadd2_rn(f0, make_float2(qa[0], qb[0])), half2);
-                            f1 = __fmul2_rn(__fadd2_rn(f1, make_float2(qa[-1], qb[-1])), half2);
-                            f2 = __fmul2_rn(__fadd2_rn(f2, make_float2(qa[-2], qb[-2])), half2);
-                        }
-                        w0[s] = w1[s];
-                        w1[s] = w2[s];
-                        w2[s] = __ffma2_rn(c2[s], f2, __ffma2_rn(c1[s], f1, __fmul2_rn(c0[s], f0)));
-                        rowp[s] += a.nc[s];
-                    }
-                    const float2 v = __ffma2_rn(make_float2(e[s].w, e[s].w), w2[s],
-                                                __ffma2_rn(make_float2(e[s].z, e[s].z), w1[s], __fmul2_rn(make_float2(e[s].y, e[s].y), w0[s])));
+                    const float4 e = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);  // base, c0, c1, c2 of the row (uniform)
+                    const float2 *p = hrs[s] + (__float_as_int(e.x) - hbase[s]) * HP;
+                    const float2 v = __ffma2_rn(make_float2(e.w, e.w), p[2 * HP], __ffma2_rn(make_float2(e.z, e.z), p[HP], __fmul2_rn(make_float2(e.y, e.y), p[0])));
                     acc = __fadd2_rn(acc, v);
-                    e[s] = en[s];
                 }
                 if (X < a.W) {
                     const size_t o = (size_t)Y * a.W + X;
@@ -206,7 +219,6 @@ __global__ void __launch_bounds__(kLinThreads, 4) fuse_linear_kernel(const __gri
                 }
             }
         }
-        __syncthreads();  // buffer b is free for the segment after next
     }
 }
 
