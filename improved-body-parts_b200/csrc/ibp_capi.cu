@@ -938,6 +938,9 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     a.heat32 = heat32;
     // rows per CTA: enough chains for ~8 waves of 8 resident CTAs per SM, whole segments, at least 32 rows each (a chain start
     // costs three feature rows per scale)
+    // 256 or 128 output columns per CTA: what wastes fewer columns right of the image (640 = 5 x 128)
+    const int lin_threads = (((W + 255) / 256) * 256 - W > ((W + 127) / 128) * 128 - W) ? 64 : 128;
+    const int kLinCols = 2 * lin_threads;
     const long long cols = (W + kLinCols - 1) / kLinCols;
     const long long per_chain = cols * kLayers * batch;
     const long long want = 8LL * 8 * h->sm_count;
@@ -954,7 +957,7 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
             int nc = 1, maxr = 1;
             // staged columns of a CTA: from its first tap rounded down to a 16-byte boundary, whole 16-byte groups
             for (int X0 = 0; X0 < W; X0 += kLinCols) nc = std::max(nc, ((xt[std::min(X0 + kLinCols - 1, W - 1)].base + 2 - (xt[X0].base & ~3) + 1) + 3) & ~3);
-            if (nc / 4 > kLinThreads) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d shrinks by more than a factor of ~7.9", s);
+            if (nc / 4 > lin_threads) return fail(IBP_ERR_SHAPE, "ibp_fuse_multiscale_linear: scale %d shrinks by more than a factor of ~7.9", s);
             for (int Yc = 0; Yc < H; Yc += a.chain_rows) {
                 int loaded = yt[Yc].base - 1;
                 for (int Ya = Yc; Ya < std::min(Yc + a.chain_rows, H); Ya += kLinSeg) {
@@ -981,8 +984,12 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     const dim3 grid((unsigned)cols, (unsigned)((H + a.chain_rows - 1) / a.chain_rows), (unsigned)batch * kLayers);
 #define IBP_LIN_LAUNCH(N)                                                                                          \
     do {                                                                                                           \
-        if (smem > 48 * 1024) CU(cudaFuncSetAttribute(fuse_linear_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); \
-        fuse_linear_kernel<N><<<grid, kLinThreads, smem, st>>>(a);                                                 \
+        if (smem > 48 * 1024) {                                                                                    \
+            CU(cudaFuncSetAttribute(fuse_linear_kernel<N, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));  \
+            CU(cudaFuncSetAttribute(fuse_linear_kernel<N, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); \
+        }                                                                                                          \
+        if (lin_threads == 64) fuse_linear_kernel<N, 64><<<grid, 64, smem, st>>>(a);                               \
+        else fuse_linear_kernel<N, 128><<<grid, 128, smem, st>>>(a);                                               \
     } while (0)
     {
         StageTimer t(h, IBP_STAGE_FUSE, st);

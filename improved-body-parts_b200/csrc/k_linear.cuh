@@ -20,7 +20,7 @@
 namespace ibp {
 
 constexpr int kLinMaxScales = 8;
-constexpr int kLinThreads = 128;
+constexpr int kLinThreads = 128;   // threads of a CTA (the wide form; the narrow form has 64), a thread owns two adjacent output columns
 constexpr int kLinSeg = 8;        // output rows per staging step
 constexpr int kLinMaxSegs = 64;   // staging steps of one CTA (chain_rows <= 512)
 
@@ -49,13 +49,12 @@ struct LinArgs {
     double *out;
     float *heat32;
 };
-constexpr int kLinCols = 256;  // output columns of a CTA: a thread owns two adjacent ones (packed float32x2 arithmetic)
 
 __device__ __forceinline__ void lin_cp16(void *dst_smem, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
 }
 
-// A CTA owns 256 output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  Per segment:
+// A CTA owns 256 (or 128) output columns of one channel and walks down `chain_rows` rows, kLinSeg at a time.  Per segment:
 //   1. the feature rows the segment adds (and the row taps of its output rows) have been copied to shared memory with
 //      16-byte cp.async while the PREVIOUS segment was computed: HBM latency is paid once per segment, under arithmetic;
 //   2. horizontal pass: every thread turns the new raw rows into the three-tap sums of its two columns (flip average on
@@ -64,8 +63,10 @@ __device__ __forceinline__ void lin_cp16(void *dst_smem, const void *src) {
 //   4. vertical pass, straight-line: per output row and scale one uniform 128-bit load of the row's taps, three loads
 //      from HR at immediate offsets, three packed multiply-adds.  The scales of a pixel are summed in float32 and
 //      widened once (this mode is held to a tolerance, not to the bits of a float64 running sum).
-template <int NS>
-__global__ void __launch_bounds__(kLinThreads, 3) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
+// THREADS = 128 or 64: 256 or 128 output columns per CTA, whichever tiles the image width with less waste.
+template <int NS, int THREADS>
+__global__ void __launch_bounds__(THREADS, 384 / THREADS) fuse_linear_kernel(const __grid_constant__ LinArgs a) {
+    constexpr int kLinCols = 2 * THREADS;
     extern __shared__ __align__(16) float lin_smem[];
     const int tid = threadIdx.x;
     const int X0 = blockIdx.x * kLinCols, X = X0 + 2 * tid;
@@ -107,7 +108,7 @@ __global__ void __launch_bounds__(kLinThreads, 3) fuse_linear_kernel(const __gri
             sdst[s] = -1;
         }
         gtwin[s] = (int)((size_t)(kLayers + c_flip_src[chan] - chan) * hw) + S.w - 2 * c_lo - nc4[s];
-        for (int g = tid; g < n_segs; g += kLinThreads) s_hi[s][g] = __ldg(&S.seg_hi[Y0 / kLinSeg + g]);
+        for (int g = tid; g < n_segs; g += THREADS) s_hi[s][g] = __ldg(&S.seg_hi[Y0 / kLinSeg + g]);
         loaded[s] = __ldg(&S.ytab[Y0].base) - 1;  // the first segment brings in everything from the first row's window on
         hbase[s] = loaded[s] - 2;
         cnt[s] = 0;
