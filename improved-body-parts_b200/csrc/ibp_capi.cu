@@ -951,7 +951,7 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
     {
         const LinTap *tab = h->h_lin_tab;
         int off = 0, hoff = 0;
-        a.step1 = 1;
+        a.step1 = a.ystep1 = 1;
         for (int s = 0; s < ns; s++) {
             const LinTap *xt = tab + (size_t)s * per_scale, *yt = xt + W;
             int nc = 1, maxr = 1;
@@ -968,13 +968,15 @@ int ibp_fuse_multiscale_linear(ibp_handle *h, const ibp_scale_input *scales, int
             }
             for (int X = 0; X + 1 < W; X++)
                 if (xt[X + 1].base - xt[X].base > 1) a.step1 = 0;
+            for (int Y = 0; Y + 1 < H; Y++)
+                if (yt[Y + 1].base - yt[Y].base > 1) a.ystep1 = 0;
             nc += 4;  // the four-load form of the horizontal pass reads one column past a thread's last tap
             a.nc[s] = nc;
             a.maxr[s] = maxr;
             a.off[s] = off;
             off += 2 * nc * maxr;
             a.hoff[s] = hoff;
-            hoff += (maxr + 3) * kLinCols;
+            hoff += (maxr + 4) * kLinCols;  // three rows kept from the segment before, one row of slack for the paired vertical pass
         }
         a.buf_floats = (off + 3) & ~3;
         a.hr_floats = hoff;

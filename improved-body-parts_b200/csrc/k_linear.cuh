@@ -40,10 +40,11 @@ struct LinArgs {
     int nc[kLinMaxScales];    // feature columns a CTA's 256 output columns can touch (capacity of a staged row)
     int maxr[kLinMaxScales];  // feature rows a segment can add (capacity of the raw staging buffer)
     int off[kLinMaxScales];   // float offset of the scale's raw rows in the staging buffer: upright rows, then twin rows
-    int hoff[kLinMaxScales];  // float offset of the scale's horizontal sums: (maxr + 3) rows of kLinCols floats
+    int hoff[kLinMaxScales];  // float offset of the scale's horizontal sums: (maxr + 4) rows of the CTA's columns
     int buf_floats;           // floats of the raw staging buffer
     int hr_floats;            // floats of the horizontal sums of all scales
     int step1;                // the taps of two adjacent output columns start at most one feature column apart (every scale <= 4)
+    int ystep1;               // the same for two adjacent output rows
     int n_scales, flip, H, W;
     int chain_rows;           // output rows one CTA walks (multiple of kLinSeg)
     double *out;
@@ -195,28 +196,54 @@ __global__ void __launch_bounds__(THREADS, 384 / THREADS) fuse_linear_kernel(con
             const float2 *hrs[NS];
 #pragma unroll
             for (int s = 0; s < NS; s++) hrs[s] = reinterpret_cast<const float2 *>(HR + a.hoff[s]) + tid;
-            for (int Y = Ya; Y < Yb; Y++, yt++) {
-                float2 acc = make_float2(0.f, 0.f);
-#pragma unroll
-                for (int s = 0; s < NS; s++) {
-                    const float4 e = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);  // base, c0, c1, c2 of the row (uniform)
-                    const float2 *p = hrs[s] + (__float_as_int(e.x) - hbase[s]) * HP;
-                    const float2 v = __ffma2_rn(make_float2(e.w, e.w), p[2 * HP], __ffma2_rn(make_float2(e.z, e.z), p[HP], __fmul2_rn(make_float2(e.y, e.y), p[0])));
-                    acc = __fadd2_rn(acc, v);
-                }
-                if (X < a.W) {
-                    const size_t o = (size_t)Y * a.W + X;
-                    if (wide) {
-                        *reinterpret_cast<double2 *>(out + o) = make_double2((double)acc.x, (double)acc.y);
-                        if (h32) *reinterpret_cast<float2 *>(h32 + o) = acc;
-                    } else {
-                        out[o] = (double)acc.x;
-                        if (two) out[o + 1] = (double)acc.y;
-                        if (h32) {
-                            h32[o] = acc.x;
-                            if (two) h32[o + 1] = acc.y;
-                        }
+            auto store_row = [&](int Y, float2 acc) {
+                const size_t o = (size_t)Y * a.W + X;
+                if (wide) {
+                    *reinterpret_cast<double2 *>(out + o) = make_double2((double)acc.x, (double)acc.y);
+                    if (h32) *reinterpret_cast<float2 *>(h32 + o) = acc;
+                } else {
+                    out[o] = (double)acc.x;
+                    if (two) out[o + 1] = (double)acc.y;
+                    if (h32) {
+                        h32[o] = acc.x;
+                        if (two) h32[o + 1] = acc.y;
                     }
+                }
+            };
+            if (a.ystep1) {
+                // two output rows at a time: their windows start on the same feature row or one apart, so four loads from HR
+                // serve both (the second row's three are picked with the warp-uniform step)
+                for (int Y = Ya; Y < Yb; Y += 2, yt += 2) {
+                    const bool has2 = Y + 1 < Yb;
+                    float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int s = 0; s < NS; s++) {
+                        const float4 e0 = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);
+                        const float4 e1 = *reinterpret_cast<const float4 *>(yt + s * kLinSeg + (has2 ? 1 : 0));
+                        const int b0 = __float_as_int(e0.x);
+                        const bool step = __float_as_int(e1.x) != b0;
+                        const float2 *p = hrs[s] + (b0 - hbase[s]) * HP;
+                        const float2 h0 = p[0], h1 = p[HP], h2 = p[2 * HP], h3 = p[3 * HP];
+                        acc0 = __fadd2_rn(acc0, __ffma2_rn(make_float2(e0.w, e0.w), h2, __ffma2_rn(make_float2(e0.z, e0.z), h1, __fmul2_rn(make_float2(e0.y, e0.y), h0))));
+                        const float2 g0 = step ? h1 : h0, g1 = step ? h2 : h1, g2 = step ? h3 : h2;
+                        acc1 = __fadd2_rn(acc1, __ffma2_rn(make_float2(e1.w, e1.w), g2, __ffma2_rn(make_float2(e1.z, e1.z), g1, __fmul2_rn(make_float2(e1.y, e1.y), g0))));
+                    }
+                    if (X < a.W) {
+                        store_row(Y, acc0);
+                        if (has2) store_row(Y + 1, acc1);
+                    }
+                }
+            } else {
+                for (int Y = Ya; Y < Yb; Y++, yt++) {
+                    float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int s = 0; s < NS; s++) {
+                        const float4 e = *reinterpret_cast<const float4 *>(yt + s * kLinSeg);  // base, c0, c1, c2 of the row (uniform)
+                        const float2 *p = hrs[s] + (__float_as_int(e.x) - hbase[s]) * HP;
+                        const float2 v = __ffma2_rn(make_float2(e.w, e.w), p[2 * HP], __ffma2_rn(make_float2(e.z, e.z), p[HP], __fmul2_rn(make_float2(e.y, e.y), p[0])));
+                        acc = __fadd2_rn(acc, v);
+                    }
+                    if (X < a.W) store_row(Y, acc);
                 }
             }
         }
