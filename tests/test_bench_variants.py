@@ -131,6 +131,33 @@ def test_bench_configs1_batch64_pinned_host_exact(oracle):
         assert coco[b].shape == want_rows.shape and np.array_equal(coco[b], want_rows)
 
 
+@pytest.mark.parametrize("dtype", ["float32", "float16"])
+@pytest.mark.parametrize("shape", [(512, 512), (384, 640)])
+def test_pinned_host_zero_copy_equals_device_and_pageable(dtype, shape):
+    """Round 2: from a PINNED host buffer only the keypoint planes are copied and the limb kernel pulls the box of rows x
+    columns it needs straight out of the caller's buffer (include/ibp.h §3).  The same batch as a device tensor (whole rows
+    staged from HBM) and as a pageable numpy array (staged copy of the 48 planes) must give the same bits, for both
+    element types and a non-square map; people near the image border make boxes that start at column 0 / end at w."""
+    import torch
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    n = 12
+    batch = synth.make_batch(2600, n, people=(1, 9), height=shape[0], width=shape[1])
+    t = torch.from_numpy(batch)
+    if dtype == "float16":
+        t = t.half()
+    pp = PostProcessor(device=0, max_batch=n)
+    ref = pp(t.cuda(), shape[0])
+    got_pinned = pp(t.pin_memory(), shape[0])
+    got_pageable = pp(t.numpy().copy() if dtype == "float32" else t.clone(), shape[0])
+    for got in (got_pinned, got_pageable):
+        assert np.array_equal(got.n_peaks, ref.n_peaks) and np.array_equal(got.n_humans, ref.n_humans)
+        for b in range(n):
+            assert np.array_equal(got.peaks[b], ref.peaks[b])
+            assert np.array_equal(got.humans[b], ref.humans[b])
+    assert ref.n_humans.sum() >= n
+
+
 def test_configs2_batch_two_lanes_exact():
     """bench.py --workload configs2: 640x480, flip + 4 scales, DISTINCT images at batch 8, two handles on two streams
     (MultiScale.step_dev), every image against the oracle chain.  The fusion oracle here issues the reference's own
