@@ -19,6 +19,7 @@
 #include "k_fuse.cuh"
 #include "k_glue.cuh"
 #include "k_limbs.cuh"
+#include "k_limbs3.cuh"
 #include "k_multiscale.cuh"
 #include "k_msstrip.cuh"
 #include "k_linear.cuh"
@@ -72,6 +73,7 @@ constexpr size_t kMaxDynSmem = 220 * 1024;  // opt-in dynamic shared memory we a
 constexpr size_t kPeakBandTarget = 16 * 1024;  // owned rows of one band (the CTA also stages 2*halo rows around them)
 constexpr size_t kPeakBandTargetStream = 24 * 1024;
 constexpr size_t kLimbPlaneMaxBytes = 96 * 1024;
+constexpr int kL3MaxCtasPerSm = 4;  // limbs_stream3_kernel: CTAs per SM its global scratch is sized for
 
 // bytes of one staged band: the streaming kernel (two buffer sets per CTA, few fat items) likes them larger than the
 // one-CTA-per-band kernel (five CTAs per SM)
@@ -146,6 +148,10 @@ struct ibp_handle {
     const void *lb_occ_kern = nullptr;
     size_t lb_occ_smem = 0;        // occupancy of the streaming limb kernel, cached per (instantiation, shared-memory size)
     int lb_occ = 0;
+    const void *l3_occ_kern = nullptr;  // the same for limbs_stream3_kernel
+    size_t l3_occ_smem = 0;
+    int l3_occ = 0;
+    unsigned char *d_l3_scratch = nullptr;  // per-CTA global scratch of limbs_stream3_kernel (kL3MaxCtasPerSm CTAs per SM)
     int *d_partbase = nullptr;     // [max_batch][19] first id of each part + image total (index_bands_kernel)
     int *d_n_raw = nullptr;        // [max_batch] peaks per image, accumulated by the streaming peak kernel (lives after d_status)
     unsigned long long *d_timeline = nullptr;  // experiments only (IBP_DEBUG & 8)
@@ -262,6 +268,7 @@ void destroy_buffers(ibp_handle *h) {
     free_dev(h->d_item_meta);
     free_dev(h->d_yext);
     free_dev(h->d_lb_work);
+    free_dev(h->d_l3_scratch);
     free_dev(h->d_score64);
     free_dev(h->d_py_conn);
     free_dev(h->d_py_conn_count);
@@ -497,6 +504,10 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(peaks_stream_kernel<IBP_PEAKS_BOX_CENTROID, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device));
+        CU(cudaFuncSetAttribute(limbs_stream3_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream3_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        if (h->L.max_peaks_per_part <= 128)  // the handles the streaming limb kernels serve
+            CU(cudaMalloc(&h->d_l3_scratch, (size_t)kL3MaxCtasPerSm * h->sm_count * l3_global_scratch_bytes(h->L.max_candidates_per_limb)));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -1419,6 +1430,8 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
     a.batch = batch;
     a.peaks_out = h->d_peaks;
     a.line_out = h->d_line;
+    a.cta_scratch = nullptr;
+    a.cta_scratch_bytes = 0;
     if (h->defer_bands > 0) {
         if (h->defer_batch != batch) return fail(IBP_ERR_ARG, "assign: %d images, but the pending peak lists are of %d", batch, h->defer_batch);
         a.band_peaks = h->d_band_peaks;
@@ -1476,6 +1489,33 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         void (*kern)(LimbArgs) = src_over_bus ? (dtype == IBP_F16 ? limbs_stream_kernel<__half, true> : limbs_stream_kernel<float, true>)
                                               : (dtype == IBP_F16 ? limbs_stream_kernel<__half> : limbs_stream_kernel<float>);
         const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
+        // Device-resident source, opt-in (IBP_LIMBS_STREAM3=1, read once per process): the three-CTAs-per-SM form of
+        // k_limbs3.cuh.  Measured on the B200 it is no faster than the kernel above, so it is not the default.
+        static const bool no_l3 = !(getenv("IBP_LIMBS_STREAM3") && atoi(getenv("IBP_LIMBS_STREAM3")) != 0);
+        const size_t smem_3 = plane_s_bytes + l3_scratch_bytes(a.cap);
+        if (!src_over_bus && !no_l3 && h->d_l3_scratch && a.max_steps <= 32 && a.nbands <= kL3MaxBands && smem_3 >= group_phase_bytes(h) && smem_3 <= kMaxDynSmem) {
+            void (*kern3)(LimbArgs) = dtype == IBP_F16 ? limbs_stream3_kernel<__half> : limbs_stream3_kernel<float>;
+            if (h->l3_occ_smem != smem_3 || h->l3_occ_kern != (const void *)kern3) {
+                int per_sm = 0;
+                CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern3, kL3Threads, smem_3));
+                h->l3_occ = std::min(per_sm, kL3MaxCtasPerSm);
+                if (const char *cap_env = getenv("IBP_L3_OCC")) h->l3_occ = std::min(h->l3_occ, std::max(atoi(cap_env), 1));  // experiments
+                h->l3_occ_smem = smem_3;
+                h->l3_occ_kern = (const void *)kern3;
+            }
+            if (h->l3_occ >= 3 || getenv("IBP_L3_OCC")) {
+                a.smem_bytes = (int)smem_3;
+                a.cta_scratch = h->d_l3_scratch;
+                a.cta_scratch_bytes = l3_global_scratch_bytes(a.cand_cap);
+                const int grid = std::min(items, h->l3_occ * h->sm_count);
+                StageTimer t(h, IBP_STAGE_LIMBS, st);
+                CU(launch_dependent(kern3, dim3(grid), dim3(kL3Threads), smem_3, st, a));
+                h->lb_work_base += (unsigned)items;
+                h->launches++;
+                CU(cudaGetLastError());
+                return IBP_OK;
+            }
+        }
         if (h->lb_occ_smem != smem_s || h->lb_occ_kern != (const void *)kern) {  // every CTA of the grid must be resident (queue items wait for one another)
             int per_sm = 0;
             CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kLimbStreamThreads, smem_s));

@@ -75,6 +75,8 @@ struct LimbArgs {
     DevPeak *peaks_out;         // (batch, 18, cap)
     ibp_peak *line_out;         // (batch, line_stride)
     unsigned long long *timeline;  // experiments only: (batch, 31, 4) %globaltimer stamps, or null
+    unsigned char *cta_scratch;    // limbs_stream3_kernel: per-CTA global scratch (cta_scratch_bytes each) for what does not
+    size_t cta_scratch_bytes;      // fit its small shared memory: the candidates of a crowded limb, the introsort emulation
     GroupArgs group;
 };
 
@@ -171,13 +173,11 @@ __device__ __forceinline__ void limb_stamp(const LimbArgs &a, int img, int row, 
     }
 }
 
-// Scores every (a, b) pair of one limb from the staged plane, orders the accepted candidates and connects them
-// greedily (pafprocess.cpp:52-130).  All threads of the CTA; the number of connections written is returned on thread 0.
-// `plane_dead` is called by every thread once the last sample has been read (after a barrier): the streaming kernel starts
-// the next item's plane copy there, under the ordering / greedy tail.
-template <int kLimbThreads, class Smp, class PlaneDead>
-__device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Smp &smp, int img, int limb, int nA, int nB,
-                                              PlaneDead plane_dead) {
+// Orders the `ncand` accepted candidates of one limb (compacted in pair order in m.keys / m.cand_limb / m.cand_pair) and
+// connects them greedily (pafprocess.cpp:98-129).  All threads of the CTA; the number of connections written is returned
+// on thread 0.  The arrays may live in shared or in global memory.
+template <int kLimbThreads, int kRankMax = kRankSortMax>  // kRankMax: the caller's bound on ncand when it is below kRankSortMax
+__device__ __forceinline__ int order_and_link(const LimbArgs &a, const LimbSmem &m, int img, int limb, int nA, int nB, int ncand) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *emu = m.emu;
     DevPeak *sA = m.sA, *sB = m.sB;
@@ -186,10 +186,144 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
     uint64_t *keys = m.keys;
     float *cand_limb = m.cand_limb;
     uint32_t *cand_pair = m.cand_pair;
+    int n_links = 0;
+    if (ncand > a.cand_cap) {
+        if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
+        ncand = a.cand_cap;
+    }
+
+    if (ncand > 0) {
+        // ---- order: descending on (score, index); keys are distinct because they carry the index ----
+        if (ncand <= kRankMax) {
+            // rank sort: one pass, two barriers — the common case (a handful of candidates per limb)
+            uint64_t mine[kRankMax / kLimbThreads];
+            int rank[kRankMax / kLimbThreads];
+#pragma unroll
+            for (int q = 0; q < kRankMax / kLimbThreads; q++) {
+                const int i = tid + q * kLimbThreads;
+                mine[q] = (i < ncand) ? keys[i] : 0;
+                rank[q] = 0;
+            }
+            for (int j = 0; j < ncand; j++) {
+                const uint64_t kj = keys[j];
+#pragma unroll
+                for (int q = 0; q < kRankMax / kLimbThreads; q++) rank[q] += (kj > mine[q]);
+            }
+            __syncthreads();
+#pragma unroll
+            for (int q = 0; q < kRankMax / kLimbThreads; q++)
+                if (tid + q * kLimbThreads < ncand) keys[rank[q]] = mine[q];
+            __syncthreads();
+        } else {
+            int np2 = 1;
+            while (np2 < ncand) np2 <<= 1;
+            for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
+            __syncthreads();
+            for (int k = 2; k <= np2; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < np2; i += kLimbThreads) {
+                        const int l = i ^ j;
+                        if (l > i) {
+                            const uint64_t x = keys[i], y = keys[l];
+                            const bool desc = ((i & k) == 0);
+                            if (desc ? (x < y) : (x > y)) {
+                                keys[i] = y;
+                                keys[l] = x;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+        }
+        // duplicate keys?
+        bool dup = false;
+        for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
+        const bool emulate = __syncthreads_or(dup && ncand > 16);
+        if (emulate) {
+            // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
+            for (int i = tid; i < ncand; i += kLimbThreads) {
+                const uint64_t kv = keys[i];
+                const uint32_t idx = (uint32_t)kv;
+                emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
+                atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
+            }
+            __syncthreads();
+        }
+        const uint64_t *order = emulate ? emu : keys;
+
+        // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order.  Every lane prepares the
+        //      record of its own candidate first (in parallel); the serial part is one ballot and two shuffles per connection:
+        //      the leader's two peaks are broadcast and each lane strikes itself out if it shares one of them ----
+        if (warp == 0) {
+            const int max_links = min(nA, nB);
+            DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
+            int nl = 0;
+            for (int base = 0; base < ncand && nl < max_links; base += 32) {
+                const int i = base + lane;
+                bool valid = i < ncand;
+                int ia = -1, ib = -1;  // never equal to a leader's
+                DevLink rec;
+                rec.id_a = rec.id_b = 0;
+                rec.limb = rec.len = rec.gate = rec.pad = rec.score_a = rec.score_b = 0.f;
+                if (valid) {
+                    const int cidx = (int)(uint32_t)order[i];
+                    const uint32_t pr = cand_pair[cidx];
+                    const int ca = (int)(pr >> 16), cb = (int)(pr & 0xffffu);
+                    valid = !used_a[ca] && !used_b[cb];  // taken in an earlier step of 32
+                    if (valid) {
+                        ia = ca;
+                        ib = cb;
+                        const DevPeak A = sA[ia], B = sB[ib];
+                        rec.id_a = A.id;
+                        rec.id_b = B.id;
+                        rec.limb = cand_limb[cidx];
+                        rec.len = limb_length(A, B);
+                        rec.gate = length_gate(rec.len, a.group.len_rate);
+                        rec.score_a = line_a[ia];
+                        rec.score_b = line_b[ib];
+                    }
+                }
+                while (nl < max_links) {
+                    const uint32_t bal = __ballot_sync(0xffffffffu, valid);
+                    if (bal == 0) break;
+                    const int leader = __ffs(bal) - 1;
+                    const int la = __shfl_sync(0xffffffffu, ia, leader), lb = __shfl_sync(0xffffffffu, ib, leader);
+                    if (lane == leader) {
+                        used_a[ia] = 1;
+                        used_b[ib] = 1;
+                        out[nl] = rec;
+                    }
+                    valid = valid && ia != la && ib != lb;  // the leader itself included
+                    nl++;
+                }
+                __syncwarp();  // the flags, for the next 32
+            }
+            n_links = nl;
+        }
+    }
+    return n_links;
+}
+
+// Scores every (a, b) pair of one limb from the staged plane, orders the accepted candidates and connects them
+// greedily (pafprocess.cpp:52-130).  All threads of the CTA; the number of connections written is returned on thread 0.
+// `plane_dead` is called by every thread once the last sample has been read (after a barrier): the streaming kernel starts
+// the next item's plane copy there, under the ordering / greedy tail.
+template <int kLimbThreads, class Smp, class PlaneDead>
+__device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Smp &smp, int img, int limb, int nA, int nB,
+                                              PlaneDead plane_dead) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    DevPeak *sA = m.sA, *sB = m.sB;
+    uint64_t *keys = m.keys;
+    float *cand_limb = m.cand_limb;
+    uint32_t *cand_pair = m.cand_pair;
     PairGeo *geo = m.geo;
     float *vals = m.vals;
     int *wcnt = m.wcnt;
-    int n_links = 0;
     // ---- score all pairs; compact the accepted ones in pair order ----
     const int npairs = (a.debug & 2) ? 0 : nA * nB;
     int ncand = 0;
@@ -280,118 +414,7 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
     }
     plane_dead();
     limb_stamp(a, img, limb, 2);
-    if (ncand > a.cand_cap) {
-        if (tid == 0) atomicOr(a.status + img, IBP_ST_CAND_OVERFLOW);
-        ncand = a.cand_cap;
-    }
-
-    if (ncand > 0) {
-        // ---- order: descending on (score, index); keys are distinct because they carry the index ----
-        if (ncand <= kRankSortMax) {
-            // rank sort: one pass, two barriers — the common case (a handful of candidates per limb)
-            uint64_t mine[kRankSortMax / kLimbThreads];
-            int rank[kRankSortMax / kLimbThreads];
-#pragma unroll
-            for (int q = 0; q < kRankSortMax / kLimbThreads; q++) {
-                const int i = tid + q * kLimbThreads;
-                mine[q] = (i < ncand) ? keys[i] : 0;
-                rank[q] = 0;
-            }
-            for (int j = 0; j < ncand; j++) {
-                const uint64_t kj = keys[j];
-#pragma unroll
-                for (int q = 0; q < kRankSortMax / kLimbThreads; q++) rank[q] += (kj > mine[q]);
-            }
-            __syncthreads();
-#pragma unroll
-            for (int q = 0; q < kRankSortMax / kLimbThreads; q++)
-                if (tid + q * kLimbThreads < ncand) keys[rank[q]] = mine[q];
-            __syncthreads();
-        } else {
-            int np2 = 1;
-            while (np2 < ncand) np2 <<= 1;
-            for (int i = ncand + tid; i < np2; i += kLimbThreads) keys[i] = 0;  // below every real key
-            __syncthreads();
-            for (int k = 2; k <= np2; k <<= 1) {
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < np2; i += kLimbThreads) {
-                        const int l = i ^ j;
-                        if (l > i) {
-                            const uint64_t x = keys[i], y = keys[l];
-                            const bool desc = ((i & k) == 0);
-                            if (desc ? (x < y) : (x > y)) {
-                                keys[i] = y;
-                                keys[l] = x;
-                            }
-                        }
-                    }
-                    __syncthreads();
-                }
-            }
-        }
-        // duplicate keys?
-        bool dup = false;
-        for (int i = tid; i + 1 < ncand; i += kLimbThreads) dup |= ((uint32_t)(keys[i] >> 32) == (uint32_t)(keys[i + 1] >> 32));
-        const bool emulate = __syncthreads_or(dup && ncand > 16);
-        if (emulate) {
-            // rebuild the array in original (pair) order with raw float bits, then walk libstdc++'s steps on one thread
-            for (int i = tid; i < ncand; i += kLimbThreads) {
-                const uint64_t kv = keys[i];
-                const uint32_t idx = (uint32_t)kv;
-                emu[idx] = ((uint64_t)float_orderable_inv((uint32_t)(kv >> 32)) << 32) | idx;
-            }
-            __syncthreads();
-            if (tid == 0) {
-                const bool defined = ibp_sortemu::sort_like_libstdcxx(emu, ncand);
-                atomicOr(a.status + img, defined ? IBP_ST_TIE_EMULATED : (IBP_ST_TIE_EMULATED | IBP_ST_TIE_UNDEFINED));
-            }
-            __syncthreads();
-        }
-        const uint64_t *order = emulate ? emu : keys;
-
-        // ---- greedy connection (:111-129), warp 0: 32 candidates per step, leaders taken in order ----
-        if (warp == 0) {
-            const int max_links = min(nA, nB);
-            DevLink *out = a.links + ((size_t)img * kLimbs + limb) * a.cap;
-            int nl = 0;
-            for (int base = 0; base < ncand && nl < max_links; base += 32) {
-                const int i = base + lane;
-                bool valid = i < ncand;
-                int ia = 0, ib = 0, cidx = 0;
-                if (valid) {
-                    cidx = (int)(uint32_t)order[i];
-                    const uint32_t pr = cand_pair[cidx];
-                    ia = (int)(pr >> 16);
-                    ib = (int)(pr & 0xffffu);
-                }
-                while (nl < max_links) {
-                    const bool free_now = valid && !used_a[ia] && !used_b[ib];
-                    const uint32_t bal = __ballot_sync(0xffffffffu, free_now);
-                    if (bal == 0) break;
-                    const int leader = __ffs(bal) - 1;
-                    if (lane == leader) {
-                        used_a[ia] = 1;
-                        used_b[ib] = 1;
-                        DevLink l;
-                        l.id_a = sA[ia].id;
-                        l.id_b = sB[ib].id;
-                        l.limb = cand_limb[cidx];
-                        l.len = limb_length(sA[ia], sB[ib]);
-                        l.gate = length_gate(l.len, a.group.len_rate);
-                        l.pad = 0.f;
-                        l.score_a = line_a[ia];
-                        l.score_b = line_b[ib];
-                        out[nl] = l;
-                        valid = false;
-                    }
-                    nl++;
-                    __syncwarp();
-                }
-            }
-            n_links = nl;
-        }
-    }
-    return n_links;
+    return order_and_link<kLimbThreads>(a, m, img, limb, nA, nB, ncand);
 }
 
 template <typename T, int kLimbThreads>

@@ -72,9 +72,6 @@ __device__ __forceinline__ void ms_planes_raw(const float *src, int h, int w, in
     upr = base + (size_t)chan * hw;
     twin = base + (size_t)(kLayers + c_flip_src[chan]) * hw;
 }
-__device__ __forceinline__ void cp_async4(void *dst_smem, const void *src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float2 ss_pair(const float *p) { return *reinterpret_cast<const float2 *>(p); }

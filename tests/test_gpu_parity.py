@@ -220,3 +220,59 @@ def test_bench_workload_exact(oracle):
                 assert np.float32(ref.get_score(k)) == np.float32(score)
         total += len(humans)
     assert total > n  # the workload has people in it
+
+
+def test_crowded_limbs_on_default_limits(oracle):
+    """Default limits, images with more than 16 people: limbs with more than 256 pairs take the one-thread-per-pair
+    path of the streaming limb kernels (in the three-CTAs-per-SM form of csrc/k_limbs3.cuh: with the candidates in its
+    global scratch); mixed in one batch with ordinary images, twice (scratch and counters are re-used), against the oracle."""
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    B = 10
+    pp = PostProcessor(device=0, max_batch=B)
+    people = [22, 3, 18, 26, 1, 20, 9, 24, 0, 17]
+    batch = np.stack([synth.make_network_output(8100 + b, people[b])[0] for b in range(B)])
+    want = [_oracle_image(oracle, batch[b]) for b in range(B)]
+    crowded = 0
+    for rnd in range(2):
+        res = pp(batch, 512)
+        for b in range(B):
+            _, _, peaks, jl, humans = want[b]
+            assert res.n_peaks[b] == jl.shape[0], (rnd, b)
+            assert np.array_equal(res.peaks[b]["x"], jl[:, 0].astype(np.int32))
+            assert np.array_equal(res.peaks[b]["score"], jl[:, 2])
+            assert res.n_humans[b] == len(humans), (rnd, b)
+            for rec, (ids, score) in zip(res.humans[b], humans):
+                assert np.array_equal(rec["peak_id"], ids)
+                assert rec["score"] == score
+            assert res.status[b] & 0xF == 0
+            n = [len(p) for p in peaks]
+            crowded += any(n[a] * n[c] > 256 for a, c in zip(_limb_a(), _limb_b()))
+    assert crowded >= 6  # the batch does reach the path this test is about
+    assert pp.handle.launches == 2 * 3
+
+
+def _limb_a():
+    from improved_body_parts_b200 import config
+    return [l[0] for l in config.LIMBS]
+
+
+def _limb_b():
+    from improved_body_parts_b200 import config
+    return [l[1] for l in config.LIMBS]
+
+
+def test_three_ctas_per_sm_limb_kernel_in_subprocess():
+    """The opt-in form of the streaming limb kernel (csrc/k_limbs3.cuh, IBP_LIMBS_STREAM3=1, read once per process): the
+    streaming tests of this module once more on that kernel, in a process of its own."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("IBP_LIMBS_STREAM3"):
+        pytest.skip("already inside the run with the three-CTA kernel")
+    env = dict(os.environ, IBP_LIMBS_STREAM3="1")
+    res = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-k",
+                          "streaming_kernels or stress or crowded_limbs or bench_workload"],
+                         env=env, capture_output=True, text=True, timeout=1500)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert " passed" in res.stdout
