@@ -56,7 +56,7 @@ struct LimbArgs {
     uint32_t *status;       // (batch)
     unsigned *ticket;       // (batch) zero on entry, left zero on exit
     int smem_bytes;         // dynamic shared memory of the launch
-    int debug;              // experiments only (IBP_DEBUG): 1 = skip grouping, 2 = skip scoring
+    int debug;              // experiments only (IBP_DEBUG): 1 = skip grouping, 2 = skip scoring, 32 = publish a limb at once
     const int *order;       // (batch) image handled by grid row y, or null: identity
     // Band-list mode (band_peaks != null): the peak kernel left its per-band lists unpacked and index_bands_kernel
     // counted them (part_count, partbase, order).  Every CTA gathers the lists of its two joint types from the bands
@@ -774,6 +774,18 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
 
     uint32_t up_uses = 0;   // completed waits on bars[0] (one per item with pairs)
     uint32_t ring_par = 0;  // bit s: parity of the next wait on ring slot s
+    // Publishing a limb (fence, then +1 on the image's ticket) is put off until the stores it orders have had the time of
+    // the next item's first memory round trip to reach L2: issued right behind them, the fence holds the whole CTA for
+    // that long.  Nothing waits in between: a group item publishes what is pending before it starts to wait.
+    int pending_img = -1;
+    auto publish_pending = [&]() {
+        if (pending_img >= 0 && tid < 32) {
+            __threadfence();  // warp 0 wrote the connections and the count
+            __syncwarp();
+            if (tid == 0) atomicAdd(a.ticket + pending_img, 1u);
+        }
+        pending_img = -1;
+    };
     for (;;) {
         const int4 cur = s_next;
         if (cur.x < 0) break;
@@ -799,6 +811,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         };
         if (limb == kLimbs) {
             // ---- group the image (pafprocess.cpp:133-285) once its 30 limbs are in ----
+            publish_pending();
             if (tid == 0) {
                 unsigned seen = 0;
                 for (int spins = 0; spins < (1 << 22); spins++) {
@@ -843,6 +856,7 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
             if (tid <= kParts) s_partbase[tid] = a.partbase[img * (kParts + 1) + tid];
         }
         __syncthreads();
+        publish_pending();  // the limb this CTA finished before this one
         // k-th peak of part p = entry (band, k - first of band) of the band lists, with its running id
         auto gather_part = [&](int p, int k, DevPeak &out) {
             const int *bc = s_bc + p * a.nbands;
@@ -956,14 +970,12 @@ __global__ void __launch_bounds__(kLimbStreamThreads, 2) limbs_stream_kernel(Lim
         if (tid == 0) a.link_count[img * kLimbs + limb] = n_links;
         limb_stamp(a, img, limb, 3);
 
-        // ---- publish: connections and count of this limb are out (warp 0 wrote them); the image's group item counts 30 ----
-        if (tid < 32) {
-            __threadfence();
-            __syncwarp();
-            if (tid == 0) atomicAdd(a.ticket + img, 1u);
-        }
+        // ---- connections and count of this limb are out (warp 0 wrote them); the image's group item counts 30 tickets ----
+        pending_img = img;
+        if (a.debug & 32) publish_pending();  // experiments: publish at once
         __syncthreads();  // s_next, and every use of this round's shared data
     }
+    publish_pending();
 }
 
 }  // namespace ibp

@@ -133,6 +133,15 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
     uint32_t up_uses = 0;  // completed waits on the barrier (one per item with pairs)
     int bset = 0;          // the set of band counts in use
     int pre_img = -1;      // image whose counts are on their way into the other set (asynchronous copies), or -1
+    int pending_img = -1;  // image of the limb this CTA finished last and has not published yet (see limbs_stream_kernel)
+    auto publish_pending = [&]() {
+        if (pending_img >= 0 && tid < 32) {
+            __threadfence();  // warp 0 wrote the connections and the count
+            __syncwarp();
+            if (tid == 0) atomicAdd(a.ticket + pending_img, 1u);
+        }
+        pending_img = -1;
+    };
     for (;;) {
         const int4 cur = s_next;
         if (cur.x < 0) break;
@@ -163,6 +172,7 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
         if (limb == kLimbs) {
             // ---- group the image (pafprocess.cpp:133-285) once its 30 limbs are in; no plane copy is in flight: the tables
             //      take the whole allocation ----
+            publish_pending();
             if (tid == 0) {
                 unsigned seen = 0;
                 for (int spins = 0; spins < (1 << 22); spins++) {
@@ -205,6 +215,7 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
         pre_img = -1;
         const int *s_bc = s_bcnt[bset], *s_partbase = s_pbase[bset];
         __syncthreads();
+        publish_pending();  // the limb this CTA finished before this one
         // k-th peak of part p = entry (band, k - first of band) of the band lists, with its running id
         auto gather_part = [&](int p, int k, DevPeak &out) {
             const int *bc = s_bc + p * a.nbands;
@@ -431,14 +442,11 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
         if (tid == 0) a.link_count[img * kLimbs + limb] = n_links;
         limb_stamp(a, img, limb, 3);
 
-        // ---- publish: connections and count of this limb are out (warp 0 wrote them); the image's group item counts 30 ----
-        if (tid < 32) {
-            __threadfence();
-            __syncwarp();
-            if (tid == 0) atomicAdd(a.ticket + img, 1u);
-        }
+        // ---- connections and count of this limb are out (warp 0 wrote them); the image's group item counts 30 tickets ----
+        pending_img = img;
         __syncthreads();  // s_next, and every use of this round's shared data
     }
+    publish_pending();
 }
 
 }  // namespace ibp
