@@ -506,7 +506,7 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device));
         CU(cudaFuncSetAttribute(limbs_stream3_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_stream3_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        if (h->L.max_peaks_per_part <= 128)  // the handles the streaming limb kernels serve
+        if (h->L.max_peaks_per_part <= 128 && getenv("IBP_LIMBS_STREAM3") && atoi(getenv("IBP_LIMBS_STREAM3")) != 0)  // opt-in kernel only
             CU(cudaMalloc(&h->d_l3_scratch, (size_t)kL3MaxCtasPerSm * h->sm_count * l3_global_scratch_bytes(h->L.max_candidates_per_limb)));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
