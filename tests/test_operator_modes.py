@@ -162,3 +162,48 @@ def test_gpu_second_mode_route_end_to_end():
     assoc, _ = O.find_humans(cl, sp, peaks)
     assert people_g.shape == assoc.shape
     assert np.array_equal(people_g[:, :18, 0], assoc[:, :18, 0])  # the same peaks in the same people
+
+
+@pytest.mark.gpu
+def test_gpu_linear_fusion_is_linear_at_full_size():
+    """Size-independent property at the configs[2] size (640x480, flip + 4 scales): the bilinear fusion is a linear
+    operator, fuse(a x + b y) = a fuse(x) + b fuse(y) to the tolerance of this mode; a constant map fuses to that constant
+    (every composed tap set sums to 1 / n_scales per scale)."""
+    import torch
+    from improved_body_parts_b200 import synth
+    from improved_body_parts_b200.pipeline import PostProcessor
+    ss = (0.5, 1.0, 1.5, 2.0)
+    shapes = synth.multiscale_shapes(480, 640, ss)
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    xs = [torch.rand((1, 2, 50) + tuple(s[3]), device="cuda", generator=gen) for s in shapes]
+    ys = [torch.rand((1, 2, 50) + tuple(s[3]), device="cuda", generator=gen) for s in shapes]
+    pp = PostProcessor(device=0, max_batch=1)
+    sizes = [s[1] for s in shapes]
+    fx = pp.fuse_multiscale(xs, sizes, 480, 640, flip_avg=True, interp="linear")[0].clone()
+    fy = pp.fuse_multiscale(ys, sizes, 480, 640, flip_avg=True, interp="linear")[0].clone()
+    fz = pp.fuse_multiscale([0.25 * x + 0.5 * y for x, y in zip(xs, ys)], sizes, 480, 640, flip_avg=True, interp="linear")[0].clone()
+    np.testing.assert_allclose(fz.cpu().numpy(), (0.25 * fx + 0.5 * fy).cpu().numpy(), rtol=RTOL, atol=1e-5)
+    ones = [torch.full_like(x, 0.375) for x in xs]
+    fc = pp.fuse_multiscale(ones, sizes, 480, 640, flip_avg=True, interp="linear")[0]
+    np.testing.assert_allclose(fc.cpu().numpy(), 0.375, rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.gpu
+def test_gpu_gaussian_properties_at_full_size():
+    """18 planes of 640x480: a constant plane stays constant (the kernel sums to 1, reflect padding adds no mass), the
+    operator is linear and commutes with mirroring the plane (symmetric kernel, reflect border)."""
+    import torch
+    from improved_body_parts_b200.pipeline import PostProcessor
+    pp = PostProcessor(device=0, max_batch=1)
+    gen = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.rand((1, 18, 480, 640), device="cuda", generator=gen)
+    y = torch.rand((1, 18, 480, 640), device="cuda", generator=gen)
+    for k, sigma in [(5, 1.0), (9, 2.0)]:
+        sx = pp.smooth_gaussian(x, k, sigma).clone()
+        sy = pp.smooth_gaussian(y, k, sigma).clone()
+        sz = pp.smooth_gaussian(0.5 * x + 2.0 * y, k, sigma).clone()
+        np.testing.assert_allclose(sz.cpu().numpy(), (0.5 * sx + 2.0 * sy).cpu().numpy(), rtol=RTOL, atol=1e-5)
+        sm = pp.smooth_gaussian(torch.flip(x, dims=(3,)).contiguous(), k, sigma)
+        np.testing.assert_allclose(torch.flip(sm, dims=(3,)).cpu().numpy(), sx.cpu().numpy(), rtol=RTOL, atol=1e-6)
+        c = pp.smooth_gaussian(torch.full_like(x, 0.625), k, sigma)
+        np.testing.assert_allclose(c.cpu().numpy(), 0.625, rtol=1e-5, atol=1e-6)
