@@ -23,7 +23,7 @@ def _same(a, i, b, j):
 @pytest.fixture(scope="module")
 def batch64():
     from improved_body_parts_b200 import synth
-    return synth.make_batch(2000, 64, people=(1, 10), height=512, width=512, workers=0)  # bench.py's configs[1] images
+    return synth.make_batch(2000, 64, people=(1, 10), height=512, width=512)  # bench.py's configs[1] images
 
 
 @pytest.fixture(scope="module")
@@ -106,7 +106,7 @@ def test_crowd_batch_64_layout_independent():
     single images agree; invariants hold."""
     from improved_body_parts_b200 import synth
     from improved_body_parts_b200.pipeline import PostProcessor
-    batch = synth.make_batch(3000, 64, people=(40, 60), height=512, width=512, scale=(0.2, 0.45), workers=0)
+    batch = synth.make_batch(3000, 64, people=(40, 60), height=512, width=512, scale=(0.2, 0.45))
     pp = PostProcessor(device=0, max_batch=64, **CROWD_LIMITS)
     first = pp(batch, 512)
     rev = pp(batch[::-1].copy(), 512)
