@@ -2195,6 +2195,23 @@ private:
 };
 }  // namespace
 
+namespace {
+// Legacy entry point, limb map in pinned host memory: sample it in place over the bus instead of copying the rows between
+// the extreme peaks?  A sample costs a 32-byte read at a small fraction of the bus's streaming rate (taken as 1/8 here), the
+// copy moves the rows at full rate.
+bool legacy_sample_over_bus(const cudaPointerAttributes &attr, const int *counts, int max_steps, int f1, int f2, int f3, int y_lo, int y_hi) {
+    static const bool off = getenv("IBP_NO_ZEROCOPY") != nullptr;
+    if (off || attr.type != cudaMemoryTypeHost || !attr.devicePointer) return false;
+    static const int limb_a[kLimbs] = {1, 1, 1, 1, 1, 0, 0, 14, 15, 1, 2, 3, 1, 5, 6, 1, 8, 9, 1, 11, 12, 0, 0, 2, 8, 5, 11, 16, 17, 8};
+    static const int limb_b[kLimbs] = {0, 14, 15, 16, 17, 14, 15, 16, 17, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 2, 5, 8, 12, 11, 9, 2, 5, 11};
+    size_t samples = 0;
+    for (int l = 0; l < kLimbs; l++) samples += (size_t)counts[limb_a[l]] * counts[limb_b[l]] * (size_t)max_steps;
+    const int r0 = std::max(0, std::min(y_lo, f1 - 1) - 1), r1 = std::min(f1 - 1, std::max(y_hi, 0) + 1);
+    const size_t copy_bytes = (size_t)(r1 - r0 + 1) * f2 * f3 * sizeof(float);
+    return samples * 32 * 8 < copy_bytes;
+}
+}  // namespace
+
 int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, int f3, const float *pafmap, int min_img_size) {
     g_view_valid = false;
     if (!peaks || !pafmap) return fail(IBP_ERR_ARG, "process_paf: null array");
@@ -2251,6 +2268,10 @@ int ibp_process_paf(int p1, int p2, int p3, const float *peaks, int f1, int f2, 
         if (attr.type == cudaMemoryTypeDevice && attr.device != h->device)
             return fail(IBP_ERR_ARG, "process_paf: the limb map lives on device %d, the handle on device %d (IBP_DEVICE)", attr.device, h->device);
         dev_map = pafmap;
+    } else if (n > 0 && legacy_sample_over_bus(attr, counts, h->P.max_steps, f1, f2, f3, y_lo, y_hi)) {
+        // pinned / registered memory and few pairs: the kernel reads its samples (one 32-byte sector each) straight out
+        // of the caller's array over the bus; nothing is copied
+        dev_map = (const float *)attr.devicePointer;
     } else if (n > 0) {
         const size_t row_bytes = (size_t)f2 * f3 * sizeof(float);
         rc = ensure_stage(h, (size_t)f1 * row_bytes, st);
