@@ -331,6 +331,9 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
     // crowd): one thread per pair does its own samples — enough parallelism already, no staging, fewer barriers.
     const bool direct = npairs > kLimbThreads;
     const int chunk_size = direct ? kLimbThreads : kPairChunk;
+    const bool fastdiv = a.max_steps <= 32;
+    const unsigned rcp_steps = (1u << 20) / (unsigned)a.max_steps + 1u;
+    const double half_size = __dmul_rn(0.5, (double)a.min_img_size);
     for (int base = 0; base < npairs; base += chunk_size) {
         const int chunk = min(chunk_size, npairs - base);
         if (!direct) {
@@ -343,7 +346,8 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
             __syncthreads();
             // (1) samples, one thread per (pair, step)
             for (int it = tid; it < chunk * a.max_steps; it += kLimbThreads) {
-                const int q = it / a.max_steps, i = it - q * a.max_steps;
+                // it / max_steps: exact by multiply and shift for it < 4096 and max_steps <= 32 (error < 2^-8 < 1 / max_steps)
+                const int q = fastdiv ? (int)(((unsigned)it * rcp_steps) >> 20) : it / a.max_steps, i = it - q * a.max_steps;
                 const PairGeo g = geo[q];
                 if (i < g.steps) {
                     int px, py;
@@ -380,10 +384,15 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
                     sum = __fadd_rn(sum, vi);   // :85
                     above += (vi > a.thr);      // :87
                 }
-                // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
-                const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
-                const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
-                ls = __double2float_rn(__dadd_rn((double)__fdiv_rn(sum, __int2float_rn(g.steps)), pen));
+                // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment.  A limb shorter
+                // than half the image size pays no penalty: the exact quotient is above 1, so is the rounded one, the min is 0
+                // and the sum of a float and 0.0 narrows back to that float — no double division for the usual limb
+                ls = __fdiv_rn(sum, __int2float_rn(g.steps));
+                if (!((double)len < half_size)) {
+                    const double pen_raw = __dsub_rn(__ddiv_rn(half_size, (double)len), 1.0);
+                    const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
+                    ls = __double2float_rn(__dadd_rn((double)ls, pen));
+                }
                 const float need = __fmul_rn(__int2float_rn(g.steps), a.step_ratio);  // :91
                 if (__int2float_rn(above) > need && ls > 0.0f) {                      // :93
                     ok = true;
