@@ -477,9 +477,9 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaMalloc(&h->d_lb_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_lb_work, 0, sizeof(unsigned)));
         CU(cudaFuncSetAttribute(limbs_stream_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half, false, kLimbStreamThreadsHalf>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_stream_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+        CU(cudaFuncSetAttribute(limbs_stream_kernel<__half, true, kLimbStreamThreadsHalf>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaMalloc(&h->d_pk_work, sizeof(unsigned)));
         CU(cudaMemset(h->d_pk_work, 0, sizeof(unsigned)));
         CU(cudaMallocHost(&h->h_n_peaks, B * sizeof(int)));
@@ -1489,8 +1489,9 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         a.work_base = h->lb_work_base;
         a.plane_bytes = (int)plane_s_bytes;
         a.smem_bytes = (int)smem_s;
-        void (*kern)(LimbArgs) = src_over_bus ? (dtype == IBP_F16 ? limbs_stream_kernel<__half, true> : limbs_stream_kernel<float, true>)
-                                              : (dtype == IBP_F16 ? limbs_stream_kernel<__half> : limbs_stream_kernel<float>);
+        const int stream_threads = dtype == IBP_F16 ? kLimbStreamThreadsHalf : kLimbStreamThreads;
+        void (*kern)(LimbArgs) = src_over_bus ? (dtype == IBP_F16 ? limbs_stream_kernel<__half, true, kLimbStreamThreadsHalf> : limbs_stream_kernel<float, true>)
+                                              : (dtype == IBP_F16 ? limbs_stream_kernel<__half, false, kLimbStreamThreadsHalf> : limbs_stream_kernel<float>);
         const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
         // Device-resident source, opt-in (IBP_LIMBS_STREAM3=1, read once per process): the three-CTAs-per-SM form of
         // k_limbs3.cuh.  Measured on the B200 it is no faster than the kernel above, so it is not the default.
@@ -1521,7 +1522,7 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         }
         if (h->lb_occ_smem != smem_s || h->lb_occ_kern != (const void *)kern) {  // every CTA of the grid must be resident (queue items wait for one another)
             int per_sm = 0;
-            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kLimbStreamThreads, smem_s));
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, stream_threads, smem_s));
             h->lb_occ = per_sm;
             h->lb_occ_smem = smem_s;
             h->lb_occ_kern = (const void *)kern;
@@ -1529,7 +1530,7 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         if (h->lb_occ < 1) return fail(IBP_ERR_SHAPE, "assign: streaming limb kernel does not fit");
         const int grid = std::min(items, h->lb_occ * h->sm_count);
         StageTimer t(h, IBP_STAGE_LIMBS, st);
-        CU(launch_dependent(kern, dim3(grid), dim3(kLimbStreamThreads), smem_s, st, a));
+        CU(launch_dependent(kern, dim3(grid), dim3(stream_threads), smem_s, st, a));
         h->lb_work_base += (unsigned)items;  // once it runs, the kernel advances its counter by exactly this much
         h->launches++;
         CU(cudaGetLastError());
