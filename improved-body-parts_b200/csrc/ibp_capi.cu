@@ -506,7 +506,7 @@ int ibp_create(ibp_handle **out, int device, const ibp_params *params, const ibp
         CU(cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, h->device));
         CU(cudaFuncSetAttribute(limbs_stream3_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_stream3_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
-        if (h->L.max_peaks_per_part <= 128 && getenv("IBP_LIMBS_STREAM3") && atoi(getenv("IBP_LIMBS_STREAM3")) != 0)  // opt-in kernel only
+        if (h->L.max_peaks_per_part <= 128 && !getenv("IBP_LIMBS_NO_STREAM3"))  // the handles limbs_stream3_kernel serves
             CU(cudaMalloc(&h->d_l3_scratch, (size_t)kL3MaxCtasPerSm * h->sm_count * l3_global_scratch_bytes(h->L.max_candidates_per_limb)));
         CU(cudaFuncSetAttribute(limbs_kernel<float, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
         CU(cudaFuncSetAttribute(limbs_kernel<__half, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
@@ -1260,6 +1260,10 @@ int launch_peaks(ibp_handle *h, const void *src, int dtype, size_t image_stride,
             ia.w = fw;
             ia.up = h->P.upsample;
             ia.status = h->d_status;
+            {
+                static const int lag_env = getenv("IBP_GROUP_LAG") ? std::max(0, atoi(getenv("IBP_GROUP_LAG"))) : -1;  // experiments
+                ia.group_lag = lag_env >= 0 ? lag_env : kGroupLag;
+            }
             CU(launch_dependent(index_bands_kernel, dim3(batch), dim3(32), 0, st, ia));
             h->launches++;
             h->order_batch = batch;
@@ -1493,11 +1497,12 @@ int launch_limbs(ibp_handle *h, const void *limb_src, int dtype, int mode, int t
         void (*kern)(LimbArgs) = src_over_bus ? (dtype == IBP_F16 ? limbs_stream_kernel<__half, true, kLimbStreamThreadsHalf> : limbs_stream_kernel<float, true>)
                                               : (dtype == IBP_F16 ? limbs_stream_kernel<__half, false, kLimbStreamThreadsHalf> : limbs_stream_kernel<float>);
         const int items = batch * (kLimbs + 1);  // 30 limbs + the grouping of each image
-        // Device-resident source, opt-in (IBP_LIMBS_STREAM3=1, read once per process): the three-CTAs-per-SM form of
-        // k_limbs3.cuh.  Measured on the B200 it is no faster than the kernel above, so it is not the default.
-        static const bool no_l3 = !(getenv("IBP_LIMBS_STREAM3") && atoi(getenv("IBP_LIMBS_STREAM3")) != 0);
-        const size_t smem_3 = plane_s_bytes + l3_scratch_bytes(a.cap);
-        if (!src_over_bus && !no_l3 && h->d_l3_scratch && a.max_steps <= 32 && a.nbands <= kL3MaxBands && smem_3 >= group_phase_bytes(h) && smem_3 <= kMaxDynSmem) {
+        // Device-resident source: the three-CTAs-per-SM form of k_limbs3.cuh (664 k against 606 k img/s on configs[1],
+        // DESIGN.md section 5).  IBP_LIMBS_NO_STREAM3 (read once per process) keeps the two-CTA kernel, which host sources use anyway.
+        static const bool no_l3 = getenv("IBP_LIMBS_NO_STREAM3") != nullptr;
+        const size_t smem_3 = plane_s_bytes + l3_scratch_bytes(a.cap, a.max_steps);
+        if (!src_over_bus && !no_l3 && h->d_l3_scratch && smem_3 >= group_phase_bytes(h) && smem_3 <= kMaxDynSmem &&
+            l3_fallback_ring_bytes(a.max_steps) / kLimbRing >= (size_t)dim1 * esz) {
             void (*kern3)(LimbArgs) = dtype == IBP_F16 ? limbs_stream3_kernel<__half> : limbs_stream3_kernel<float>;
             if (h->l3_occ_smem != smem_3 || h->l3_occ_kern != (const void *)kern3) {
                 int per_sm = 0;

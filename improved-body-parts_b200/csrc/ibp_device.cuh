@@ -162,6 +162,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  : "memory");
 }
 
+__device__ __forceinline__ void cp_async4(void *dst_smem, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+
 // Cooperative "rows to shared": the bulk engine when source, destination and size are 16-byte aligned (every map
 // the reference pads to a multiple of 64 pixels is), plain coalesced loads otherwise.  Must be called by all
 // threads of the CTA; returns after the data is visible to all of them.  `phase` is the barrier's running parity.

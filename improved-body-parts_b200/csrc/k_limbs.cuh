@@ -313,7 +313,8 @@ __device__ __forceinline__ int order_and_link(const LimbArgs &a, const LimbSmem 
 // greedily (pafprocess.cpp:52-130).  All threads of the CTA; the number of connections written is returned on thread 0.
 // `plane_dead` is called by every thread once the last sample has been read (after a barrier): the streaming kernel starts
 // the next item's plane copy there, under the ordering / greedy tail.
-template <int kLimbThreads, class Smp, class PlaneDead>
+// kChunk: pairs per round of the two-phase path (m.geo / m.vals hold that many); kRankMax: see order_and_link.
+template <int kLimbThreads, int kChunk = kPairChunk, int kRankMax = kRankSortMax, class Smp, class PlaneDead>
 __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem &m, const Smp &smp, int img, int limb, int nA, int nB,
                                               PlaneDead plane_dead) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -330,7 +331,7 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
     // Few pairs (the usual image): split every pair's samples over the threads (phases 0-2 below).  Many pairs (a
     // crowd): one thread per pair does its own samples — enough parallelism already, no staging, fewer barriers.
     const bool direct = npairs > kLimbThreads;
-    const int chunk_size = direct ? kLimbThreads : kPairChunk;
+    const int chunk_size = direct ? kLimbThreads : kChunk;
     const bool fastdiv = a.max_steps <= 32;
     const unsigned rcp_steps = (1u << 20) / (unsigned)a.max_steps + 1u;
     const double half_size = __dmul_rn(0.5, (double)a.min_img_size);
@@ -423,7 +424,7 @@ __device__ __forceinline__ int score_and_link(const LimbArgs &a, const LimbSmem 
     }
     plane_dead();
     limb_stamp(a, img, limb, 2);
-    return order_and_link<kLimbThreads>(a, m, img, limb, nA, nB, ncand);
+    return order_and_link<kLimbThreads, kRankMax>(a, m, img, limb, nA, nB, ncand);
 }
 
 template <typename T, int kLimbThreads>

@@ -1,47 +1,41 @@
-// K3 + K4, the streaming limb kernel with THREE CTAs per SM (device-resident network output).
+// K3 + K4, the streaming limb kernel with THREE CTAs per SM for float32 planes (device-resident network output).
 //
-// Same work queue, same arithmetic and the same publish / grouping protocol as limbs_stream_kernel (k_limbs.cuh); what
-// changes is how much shared memory an item in flight holds.  A limb item is a chain of dependent latencies (claim ->
-// lists -> plane -> fold -> score -> order -> publish) with little arithmetic, so the kernel's rate is items in flight x
-// 1 / chain length; limbs_stream_kernel keeps two items per SM because each carries 36 KB of scratch next to its 64 KB
-// plane.  Here the scratch is 9.3 KB, three CTAs fit an SM, and the chain loses its CTA-wide barriers in the middle:
-//   * the twin rows do not pass through a shared-memory ring: every thread loads 16-byte pieces of the mirrored twin
-//     rows straight into registers (two batches in flight, the first issued before the wait for the upright plane) and
-//     folds them into the plane the bulk copy delivered;
-//   * pairs are scored by warps, not by the CTA: lane q of a warp owns pair 8q + warp (geometry and criteria, one pair
-//     per lane), and the warp walks its pairs with lane i evaluating sample i — the samples of a pair are added in the
-//     reference's order through shuffles (pafprocess.cpp:85), no staging of values in shared memory, no barrier;
-//   * accepted pairs set a bit of a 256-bit map; a candidate's place in pair order is the number of bits below its own;
-//   * the rare cases that need room — more than 256 pairs (a crowd), the introsort emulation — use a per-CTA scratch in
-//     global memory; the grouping tables use the plane's space (no copy is in flight while an image is grouped).
+// Same work queue, same arithmetic, same phases and the same publish / grouping protocol as limbs_stream_kernel
+// (k_limbs.cuh).  What an item costs there is the length of a mostly serial chain (claim -> lists -> plane -> fold ->
+// score -> order -> publish): four warps run it about as fast as eight, and the kernel's rate is items in flight x 1 /
+// chain length.  limbs_stream_kernel keeps two items per SM because each carries 36 KB of scratch next to its 64 KB
+// plane.  Here an item holds 64 KB + 9.6 KB, so three 128-thread CTAs fit an SM:
+//   * the ring the twin rows stream through lies in the rows of the plane buffer the item does NOT use — only the
+//     feature rows [r0, r1) a sample can touch are staged, the larger of [0, r0) and [r1, h) takes the ring (an item that
+//     needs nearly every row falls back to a small ring in the candidate / sample scratch);
+//   * the two-phase scoring takes 24 pairs per round instead of 128 (2.4 KB of geometry and sample values);
+//   * 128 candidates in shared memory — the two-phase path has at most 128 pairs; a crowded limb (one thread per pair) keeps
+//     its candidates in a per-CTA scratch in global memory, and so does the introsort emulation;
+//   * the grouping tables use the plane's space (no copy is in flight while an image is grouped).
 #pragma once
 #include "k_limbs.cuh"
 
 namespace ibp {
 
-constexpr int kL3Threads = 256;
-constexpr int kL3Pairs = 256;  // pairs (and so candidates) of an item scored by the warp path
-constexpr int kL3FoldU = 4;    // 16-byte twin pieces per thread and batch
-constexpr int kL3MaxBands = 8; // bands per plane this kernel keeps the counts of (two sets: the item's and the next item's)
-constexpr int kL3WarpVals = kL3Pairs * 4 / (kL3Threads / 32);  // sample values a warp stages at a time (its share of the candidate arrays)
+constexpr int kL3Threads = 128;
+constexpr int kL3Chunk = 24;  // pairs per round of the two-phase scoring
 
-// shared memory of a CTA beyond the plane: two peak lists with their flags and scores, 256 candidates
-__host__ __device__ inline size_t l3_scratch_bytes(int cap) {
+// shared memory of a CTA beyond the plane: two peak lists with their flags and scores, 128 candidates, one round of pairs
+__host__ __device__ inline size_t l3_scratch_bytes(int cap, int max_steps) {
     size_t off = (size_t)cap * (2 * sizeof(DevPeak) + 2);
     off = (off + 15) & ~(size_t)15;
     off += (size_t)cap * 8;
     off = (off + 15) & ~(size_t)15;
-    return off + (size_t)kL3Pairs * 16;
+    off += (size_t)kL3Threads * 16;
+    off += (size_t)kL3Chunk * (sizeof(PairGeo) + (size_t)max_steps * 4);
+    return (off + 15) & ~(size_t)15;
+}
+// ... of which the ring of last resort (candidates + round scratch)
+__host__ __device__ inline size_t l3_fallback_ring_bytes(int max_steps) {
+    return ((size_t)kL3Threads * 16 + (size_t)kL3Chunk * (sizeof(PairGeo) + (size_t)max_steps * 4)) & ~(size_t)15;
 }
 // global scratch of a CTA: keys, limb scores, pairs of cand_cap candidates + the emulation array
 __host__ __device__ inline size_t l3_global_scratch_bytes(int cand_cap) { return (size_t)cand_cap * 24; }
-
-__device__ __forceinline__ void cp_async4(void *dst_smem, const void *src) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
-}
 
 template <typename T>
 __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a) {
@@ -49,11 +43,11 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
     constexpr int V = 16 / (int)sizeof(T);  // elements per 16-byte vector
     using Vec = typename Vec16<T>::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const int items = a.batch * (kLimbs + 1);
     const size_t hw = (size_t)a.h * a.w;
 
-    // ---- carve shared memory: plane | peak lists | candidates ----
+    // ---- carve shared memory: plane | peak lists | candidates | one round of pairs ----
     T *plane_s = reinterpret_cast<T *>(smem_raw);
     size_t off = (size_t)a.plane_bytes;
     LimbSmem m;
@@ -71,25 +65,32 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
     m.line_b = reinterpret_cast<float *>(smem_raw + off);
     off += (size_t)a.cap * 4;
     off = (off + 15) & ~(size_t)15;
+    const size_t fb_off = off;  // the ring of last resort starts here
     uint64_t *keys_s = reinterpret_cast<uint64_t *>(smem_raw + off);
-    float *cand_limb_s = reinterpret_cast<float *>(smem_raw + off + (size_t)kL3Pairs * 8);
-    uint32_t *cand_pair_s = reinterpret_cast<uint32_t *>(smem_raw + off + (size_t)kL3Pairs * 12);
+    off += (size_t)kLimbThreads * 8;
+    float *cand_limb_s = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)kLimbThreads * 4;
+    uint32_t *cand_pair_s = reinterpret_cast<uint32_t *>(smem_raw + off);
+    off += (size_t)kLimbThreads * 4;
+    m.geo = reinterpret_cast<PairGeo *>(smem_raw + off);
+    off += (size_t)kL3Chunk * sizeof(PairGeo);
+    m.vals = reinterpret_cast<float *>(smem_raw + off);
+    off += (size_t)kL3Chunk * a.max_steps * 4;
+    T *fb_ring = reinterpret_cast<T *>(smem_raw + fb_off);
+    const int row_bytes = a.w * (int)sizeof(T);
+    const int fb_slot_rows = (int)(((off - fb_off) & ~(size_t)15) / kLimbRing) / row_bytes;  // >= 1 (the host checks)
     unsigned char *gs = a.cta_scratch + (size_t)blockIdx.x * a.cta_scratch_bytes;
     uint64_t *keys_g = reinterpret_cast<uint64_t *>(gs);
     float *cand_limb_g = reinterpret_cast<float *>(gs + (size_t)a.cand_cap * 8);
     uint32_t *cand_pair_g = reinterpret_cast<uint32_t *>(gs + (size_t)a.cand_cap * 12);
     m.emu = reinterpret_cast<uint64_t *>(gs + (size_t)a.cand_cap * 16);
-    m.geo = nullptr;
-    m.vals = nullptr;
-    __shared__ uint64_t bar;  // the upright plane of the item
+    __shared__ uint64_t bars[1 + kLimbRing];
     __shared__ int wcnt[kLimbThreads / 32];
     __shared__ int s_last;
     __shared__ float tab4[4][4];
-    __shared__ int s_pbase[2][kParts + 1];          // first id of each part of the image, two sets: see s_bcnt
-    __shared__ int s_bcnt[2][kParts * kL3MaxBands];  // band counts of the image: the item's set and the one the next item's are copied into
-    __shared__ int s_nimg;                           // image of the next item if it is a limb item, else -1
+    __shared__ int s_partbase[kParts + 1];
+    __shared__ int s_bc[kParts * kMaxDeferBands];
     __shared__ int4 s_next;  // {image, nA | nB << 16, limb (30: group the image), r0 | r1 << 16}; image < 0: no more work
-    __shared__ unsigned s_accept[kL3Pairs / 32];
     m.wcnt = wcnt;
 
     auto claim_to_item = [&](unsigned t) {
@@ -108,20 +109,12 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
     auto upright_rows = [&](const int4 &it) {
         if (!has_pairs(it)) return;
         const int r0 = it.w & 0xffff, r1 = it.w >> 16;
-        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, item_limb(it)) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * a.w * (uint32_t)sizeof(T), &bar);
-    };
-    // one thread: ask L2 for the rows of a coming item (its twin rows are read by plain loads, the upright rows by the bulk copy)
-    auto warm_l2 = [&](const int4 &it) {
-        if (!has_pairs(it)) return;
-        const int r0 = it.w & 0xffff, r1 = it.w >> 16;
-        const uint32_t bytes = (uint32_t)(r1 - r0) * a.w * (uint32_t)sizeof(T);
-        bulk_prefetch_l2(twin_of(it.x, item_limb(it)) + (size_t)r0 * a.w, bytes);
-        bulk_prefetch_l2(upright_of(it.x, item_limb(it)) + (size_t)r0 * a.w, bytes);
+        bulk_rows(plane_s + (size_t)r0 * a.w, upright_of(it.x, item_limb(it)) + (size_t)r0 * a.w, (uint32_t)(r1 - r0) * (uint32_t)row_bytes, &bars[0]);
     };
 
     pdl_wait();  // launched as a programmatic dependent: the work queue and the band lists come from the kernels before
     if (tid == 0) {
-        mbar_init(&bar, 1);
+        for (int i = 0; i <= kLimbRing; i++) mbar_init(&bars[i], 1);
         fence_barrier_init();
         const int4 first = a.item_meta[blockIdx.x];  // the grid never exceeds the item count
         upright_rows(first);
@@ -130,10 +123,9 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
     cubic_tab4_init(tab4);
     __syncthreads();
 
-    uint32_t up_uses = 0;  // completed waits on the barrier (one per item with pairs)
-    int bset = 0;          // the set of band counts in use
-    int pre_img = -1;      // image whose counts are on their way into the other set (asynchronous copies), or -1
-    int pending_img = -1;  // image of the limb this CTA finished last and has not published yet (see limbs_stream_kernel)
+    uint32_t up_uses = 0;   // completed waits on bars[0] (one per item with pairs)
+    uint32_t ring_par = 0;  // bit s: parity of the next wait on ring slot s
+    int pending_img = -1;   // image of the limb this CTA finished last and has not published yet (see limbs_stream_kernel)
     auto publish_pending = [&]() {
         if (pending_img >= 0 && tid < 32) {
             __threadfence();  // warp 0 wrote the connections and the count
@@ -153,11 +145,7 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
         auto resolve_next = [&]() {
             if (tid == 0) {
                 const int nitem = claim_to_item(claimed);
-                if (nitem >= 0) {
-                    nmeta = a.item_meta[nitem];
-                    warm_l2(nmeta);
-                }
-                s_nimg = (nitem >= 0 && item_limb(nmeta) < kLimbs) ? nmeta.x : -1;
+                if (nitem >= 0) nmeta = a.item_meta[nitem];
             }
         };
         auto prefetch_next = [&]() {
@@ -190,7 +178,7 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
                 group_image(a.group, img, smem_raw, (size_t)a.smem_bytes, a.timeline ? a.timeline + ((size_t)img * 31 + 30) * 4 + 2 : nullptr);
                 limb_stamp(a, img, 30, 1);
             }
-            if (warp == 0) __syncwarp();  // the chain ran on warp 0: its lanes are done with the tables before a copy may land there
+            if (tid < 32) __syncwarp();  // the chain ran on warp 0: its lanes are done with the tables before a copy may land there
             // claim only now: nothing must wait behind a grouping chain
             if (tid == 0) claimed = atomicAdd(a.work_counter, 1u);
             resolve_next();
@@ -201,19 +189,31 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
         const int pa = c_limb_a[limb], pb = c_limb_b[limb];
         const bool pairs = nA > 0 && nB > 0;
         const T *twin = twin_of(img, limb);
-        if (tid == 0) claimed = atomicAdd(a.work_counter, 1u);  // next claim out now, answer used later
-        if (tid < kL3Pairs / 32) s_accept[tid] = 0;
-        limb_stamp(a, img, limb, 0);
-        const int nbitems = kParts * a.nbands;
-        if (pre_img == img) {  // band counts / first ids of this image: copied under the item before
-            bset ^= 1;
-            asm volatile("cp.async.wait_all;" ::: "memory");
-        } else {
-            for (int i = tid; i < nbitems; i += kLimbThreads) s_bcnt[bset][i] = a.band_count[(size_t)img * nbitems + i];
-            if (tid <= kParts) s_pbase[bset][tid] = a.partbase[img * (kParts + 1) + tid];
+        // the ring of this item: the larger run of plane rows it does not use, or the scratch if that is too small
+        const int free_rows = max(r0, a.h - r1);
+        const bool in_plane = free_rows / kLimbRing >= fb_slot_rows;
+        T *ring = in_plane ? plane_s + (size_t)(r0 >= a.h - r1 ? 0 : r1) * a.w : fb_ring;
+        const int slot_rows = in_plane ? free_rows / kLimbRing : fb_slot_rows;
+        const int nchunks = (r1 - r0 + slot_rows - 1) / slot_rows;
+        auto twin_chunk = [&](int c) {  // one thread: chunk c of the twin rows into its ring slot
+            const int s = c % kLimbRing, first = r0 + c * slot_rows;
+            const int rows = min(slot_rows, r1 - first);
+            bulk_rows(ring + (size_t)s * slot_rows * a.w, twin + (size_t)first * a.w, (uint32_t)rows * (uint32_t)row_bytes, &bars[1 + s]);
+        };
+        // thread 0: next claim out now, answer used later; the ring is free again: first twin chunks out
+        if (tid == 0) {
+            claimed = atomicAdd(a.work_counter, 1u);
+            if (pairs) {
+                fence_proxy_async();  // the previous round's generic-proxy use of the ring region comes first
+                for (int c = 0; c < kLimbRing && c < nchunks; c++) twin_chunk(c);
+            }
         }
-        pre_img = -1;
-        const int *s_bc = s_bcnt[bset], *s_partbase = s_pbase[bset];
+        limb_stamp(a, img, limb, 0);
+        {  // band counts / first ids of this image
+            const int nitems = kParts * a.nbands;
+            for (int i = tid; i < nitems; i += kLimbThreads) s_bc[i] = a.band_count[(size_t)img * nitems + i];
+            if (tid <= kParts) s_partbase[tid] = a.partbase[img * (kParts + 1) + tid];
+        }
         __syncthreads();
         publish_pending();  // the limb this CTA finished before this one
         // k-th peak of part p = entry (band, k - first of band) of the band lists, with its running id
@@ -252,21 +252,6 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
             resolve_next();
             prefetch_next();
         } else {
-            // ---- the twin rows: the first batch of loads is out before anything else of this item waits ----
-            const int wv = a.w / V, total = (r1 - r0) * wv;
-            const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
-            const Vec *t4 = reinterpret_cast<const Vec *>(twin + (size_t)r0 * a.w);
-            auto twin_piece = [&](int i) {  // the piece that mirrors piece i of the rows: same row, column wv - 1 - col
-                if (shift >= 0) return __ldcs(t4 + (i ^ (wv - 1)));
-                const int r = i / wv, col = i - r * wv;
-                return __ldcs(t4 + r * wv + (wv - 1 - col));
-            };
-            Vec tcur[kL3FoldU], tnxt[kL3FoldU];
-#pragma unroll
-            for (int k = 0; k < kL3FoldU; k++) {
-                const int i = tid + k * kLimbThreads;
-                if (i < total) tcur[k] = twin_piece(i);
-            }
             for (int i = tid; i < nA; i += kLimbThreads) {
                 DevPeak p;
                 gather_part(pa, i, p);
@@ -283,40 +268,38 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
             }
             pack_part();
             resolve_next();
-            // ---- fold the twin rows into the upright plane (utils/parse_skeletons.py:91-92) ----
-            mbar_wait(&bar, up_uses & 1u);
+            // ---- fold the twin rows into the upright plane as they land (utils/parse_skeletons.py:91-92) ----
+            mbar_wait(&bars[0], up_uses & 1u);
             up_uses++;
             {
-                Vec *o4 = reinterpret_cast<Vec *>(plane_s) + (size_t)r0 * wv;
-                for (int base = tid; base < total; base += kL3FoldU * kLimbThreads) {
-#pragma unroll
-                    for (int k = 0; k < kL3FoldU; k++) {
-                        const int i = base + (kL3FoldU + k) * kLimbThreads;
-                        if (i < total) tnxt[k] = twin_piece(i);
+                const int wv = a.w / V;
+                const int shift = ((wv & (wv - 1)) == 0) ? (__ffs(wv) - 1) : -1;
+                Vec *d4 = reinterpret_cast<Vec *>(plane_s);
+                for (int c = 0; c < nchunks; c++) {
+                    const int s = c % kLimbRing;
+                    mbar_wait(&bars[1 + s], (ring_par >> s) & 1u);
+                    ring_par ^= 1u << s;
+                    const int first = r0 + c * slot_rows;
+                    const int rows = min(slot_rows, r1 - first);
+                    const Vec *r4 = reinterpret_cast<const Vec *>(ring + (size_t)s * slot_rows * a.w);
+                    Vec *o4 = d4 + (size_t)first * wv;
+                    for (int i = tid; i < rows * wv; i += kLimbThreads) {
+                        const int mi = (shift >= 0) ? (i ^ (wv - 1)) : ((i / wv) * wv + (wv - 1 - (i - (i / wv) * wv)));
+                        Vec v = o4[i];
+                        fold_mirrored(v, r4[mi]);
+                        o4[i] = v;
                     }
-#pragma unroll
-                    for (int k = 0; k < kL3FoldU; k++) {
-                        const int i = base + k * kLimbThreads;
-                        if (i < total) {
-                            Vec v = o4[i];
-                            fold_mirrored(v, tcur[k]);
-                            o4[i] = v;
+                    if (c + kLimbRing < nchunks) {
+                        __syncthreads();  // everybody has read slot s
+                        if (tid == 0) {
+                            fence_proxy_async();
+                            twin_chunk(c + kLimbRing);
                         }
                     }
-#pragma unroll
-                    for (int k = 0; k < kL3FoldU; k++) tcur[k] = tnxt[k];
                 }
+                __syncthreads();
             }
-            __syncthreads();  // the plane and the lists are complete
             limb_stamp(a, img, limb, 1);
-            {  // the next item's band counts, copied asynchronously under the scoring
-                const int nimg = s_nimg;
-                if (nimg >= 0) {
-                    for (int i = tid; i < nbitems; i += kLimbThreads) cp_async4(&s_bcnt[bset ^ 1][i], a.band_count + (size_t)nimg * nbitems + i);
-                    if (tid <= kParts) cp_async4(&s_pbase[bset ^ 1][tid], a.partbase + nimg * (kParts + 1) + tid);
-                }
-                pre_img = nimg;
-            }
             SamplerT<T> smp;
             smp.mode = IBP_LIMB_FEAT_PLANAR;
             smp.limb = limb;
@@ -329,114 +312,17 @@ __global__ void __launch_bounds__(kL3Threads, 3) limbs_stream3_kernel(LimbArgs a
             smp.tab4 = tab4;
             smp.base = reinterpret_cast<const float *>(plane_s);
             smp.plane = plane_s;
-            const int npairs = (a.debug & 2) ? 0 : nA * nB;
-            if (npairs > kL3Pairs) {
+            if (nA * nB > kLimbThreads) {
                 // a crowd: one thread per pair does its own samples (score_and_link's direct path), candidates in global memory
                 m.keys = keys_g;
                 m.cand_limb = cand_limb_g;
                 m.cand_pair = cand_pair_g;
-                n_links = score_and_link<kLimbThreads>(a, m, smp, img, limb, nA, nB, prefetch_next);
+                n_links = score_and_link<kLimbThreads, kL3Chunk, kRankSortMax>(a, m, smp, img, limb, nA, nB, prefetch_next);
             } else {
                 m.keys = keys_s;
                 m.cand_limb = cand_limb_s;
                 m.cand_pair = cand_pair_s;
-                // ---- lane q of warp w owns pair 8q + w: geometry (pafprocess.cpp:66-73) ----
-                const int p_mine = lane * (kLimbThreads / 32) + warp;
-                const bool mine = p_mine < npairs;
-                int ia = 0, ib = 0;
-                DevPeak A, B;
-                PairGeo g;
-                g.steps = 0;
-                g.ax = g.ay = g.sx = g.sy = 0.f;
-                if (mine) {
-                    ia = p_mine / nB;
-                    ib = p_mine - ia * nB;
-                    A = m.sA[ia];
-                    B = m.sB[ib];
-                    g = pair_geometry(A, B, a.max_steps);
-                }
-                // ---- the warp walks its pairs in groups of `gsz`: the (pair, sample) points of a group are spread over the
-                //      lanes (:76-84), the values go through the warp's own 512 bytes of shared memory (the candidate arrays, idle
-                //      until the compaction below), then lane j adds the samples of the group's j-th pair in order (:85-88) ----
-                float my_sum = 0.0f;
-                int my_above = 0;
-                const int nslots = npairs > warp ? (npairs - warp + kLimbThreads / 32 - 1) / (kLimbThreads / 32) : 0;
-                float *wbuf = reinterpret_cast<float *>(keys_s) + warp * kL3WarpVals;
-                const int ms = a.max_steps, gsz = min(32, kL3WarpVals / ms);
-                const unsigned rcp = 65536u / (unsigned)ms + 1u;  // f / ms == (f * rcp) >> 16 for f < 256
-                for (int q0 = 0; q0 < nslots; q0 += gsz) {
-                    const int gp = min(gsz, nslots - q0), nsamp = gp * ms;
-                    for (int fb = 0; fb < nsamp; fb += 32) {
-                        const int f = fb + lane;
-                        const int j = (int)(((unsigned)f * rcp) >> 16), i = f - j * ms;
-                        const int src = min(q0 + j, 31);
-                        PairGeo gq;
-                        gq.ax = __shfl_sync(0xffffffffu, g.ax, src);
-                        gq.ay = __shfl_sync(0xffffffffu, g.ay, src);
-                        gq.sx = __shfl_sync(0xffffffffu, g.sx, src);
-                        gq.sy = __shfl_sync(0xffffffffu, g.sy, src);
-                        gq.steps = __shfl_sync(0xffffffffu, g.steps, src);
-                        if (f < nsamp && i < gq.steps) {
-                            int px, py;
-                            pair_sample_xy(gq, i, px, py);
-                            wbuf[f] = smp.at(px, py);
-                        }
-                    }
-                    __syncwarp();
-                    const int st = __shfl_sync(0xffffffffu, g.steps, min(q0 + lane, 31));
-                    float sum = 0.0f;
-                    int above = 0;
-                    if (lane < gp) {
-                        const float *v = wbuf + lane * ms;
-                        for (int i = 0; i < st; i++) {
-                            const float vi = v[i];
-                            sum = __fadd_rn(sum, vi);  // :85
-                            above += (vi > a.thr);     // :87
-                        }
-                    }
-                    const float t_sum = __shfl_sync(0xffffffffu, sum, (lane - q0) & 31);
-                    const int t_above = __shfl_sync(0xffffffffu, above, (lane - q0) & 31);
-                    if (lane >= q0 && lane < q0 + gp) {
-                        my_sum = t_sum;
-                        my_above = t_above;
-                    }
-                    __syncwarp();  // the next group overwrites the values
-                }
-                // ---- criteria of the lane's own pair (:90-96) ----
-                bool ok = false;
-                float ls = 0.f, rk = 0.f;
-                if (mine && g.steps > 0) {
-                    const float len = limb_length(A, B);
-                    // :90  float + min(0.0, 0.5*min_img_size/len - 1.0) evaluated in double, narrowed on assignment
-                    const double pen_raw = __dsub_rn(__ddiv_rn(__dmul_rn(0.5, (double)a.min_img_size), (double)len), 1.0);
-                    const double pen = (pen_raw < 0.0) ? pen_raw : 0.0;
-                    ls = __double2float_rn(__dadd_rn((double)__fdiv_rn(my_sum, __int2float_rn(g.steps)), pen));
-                    const float need = __fmul_rn(__int2float_rn(g.steps), a.step_ratio);  // :91
-                    if (__int2float_rn(my_above) > need && ls > 0.0f) {                   // :93
-                        ok = true;
-                        rk = __fadd_rn(__fadd_rn(__fmul_rn(a.w_limb, ls), __fmul_rn(a.w_a, A.score)), __fmul_rn(a.w_b, B.score));  // :94-96
-                        atomicOr(&s_accept[p_mine >> 5], 1u << (p_mine & 31));
-                    }
-                }
-                __syncthreads();  // every sample has been read: the plane is dead
-                prefetch_next();
-                limb_stamp(a, img, limb, 2);
-                // ---- a candidate's place in pair order = accepted pairs below its own ----
-                int ncand = 0, idx = 0;
-#pragma unroll
-                for (int wd = 0; wd < kL3Pairs / 32; wd++) {
-                    const unsigned bits = s_accept[wd];
-                    ncand += __popc(bits);
-                    if (wd < (p_mine >> 5)) idx += __popc(bits);
-                    else if (wd == (p_mine >> 5)) idx += __popc(bits & ((1u << (p_mine & 31)) - 1u));
-                }
-                if (ok && idx < a.cand_cap) {
-                    keys_s[idx] = ((uint64_t)float_orderable(rk) << 32) | (uint32_t)idx;
-                    cand_limb_s[idx] = ls;
-                    cand_pair_s[idx] = ((uint32_t)ia << 16) | (uint32_t)ib;
-                }
-                __syncthreads();
-                n_links = order_and_link<kLimbThreads, kL3Pairs>(a, m, img, limb, nA, nB, ncand);
+                n_links = score_and_link<kLimbThreads, kL3Chunk, kLimbThreads>(a, m, smp, img, limb, nA, nB, prefetch_next);
             }
         }
         if (tid == 0) a.link_count[img * kLimbs + limb] = n_links;

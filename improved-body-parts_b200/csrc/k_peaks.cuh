@@ -890,6 +890,7 @@ struct IndexArgs {
     int w;                  // feature width
     int h, up;              // feature rows, up-sampling factor
     uint32_t *status;       // (batch)
+    int group_lag;          // images between the limbs of an image and its "group it" item in the queue (>= 0)
 };
 
 __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
@@ -979,12 +980,12 @@ __global__ void __launch_bounds__(32) index_bands_kernel(IndexArgs a) {
                 if (c1 <= c0 || (a.w & 3) || a.w > 16380) { c0 = 0; c1 = a.w; }
             }
             // queue position: the 30 limbs of rank r follow those of rank r-1 and the "group it" items of ranks < r - lag
-            a.item_meta[rank * kLimbs + lane + max(0, rank - kGroupLag)] = make_int4(img, na | (nb << 16), lane | ((c0 >> 2) << 8) | ((c1 >> 2) << 20), r0 | (r1 << 16));
+            a.item_meta[rank * kLimbs + lane + max(0, rank - a.group_lag)] = make_int4(img, na | (nb << 16), lane | ((c0 >> 2) << 8) | ((c1 >> 2) << 20), r0 | (r1 << 16));
         }
         // "group image of rank q" is queued kGroupLag images later (by then its limbs are finished and whoever claims it
         // does not have to wait), the last ones at the very end
         if (lane == kLimbs) {
-            const int pos = (rank + kGroupLag <= a.batch - 1) ? (rank + kGroupLag + 1) * kLimbs + rank : a.batch * kLimbs + rank;
+            const int pos = (rank + a.group_lag <= a.batch - 1) ? (rank + a.group_lag + 1) * kLimbs + rank : a.batch * kLimbs + rank;
             a.item_meta[pos] = make_int4(img, 0, kLimbs, 0);
         }
     }

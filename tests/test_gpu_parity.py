@@ -224,7 +224,7 @@ def test_bench_workload_exact(oracle):
 
 def test_crowded_limbs_on_default_limits(oracle):
     """Default limits, images with more than 16 people: limbs with more than 256 pairs take the one-thread-per-pair
-    path of the streaming limb kernels (in the three-CTAs-per-SM form of csrc/k_limbs3.cuh: with the candidates in its
+    path of the streaming limb kernels (in limbs_stream3_kernel, csrc/k_limbs3.cuh: with the candidates in its
     global scratch); mixed in one batch with ordinary images, twice (scratch and counters are re-used), against the oracle."""
     from improved_body_parts_b200 import synth
     from improved_body_parts_b200.pipeline import PostProcessor
@@ -262,15 +262,16 @@ def _limb_b():
     return [l[1] for l in config.LIMBS]
 
 
-def test_three_ctas_per_sm_limb_kernel_in_subprocess():
-    """The opt-in form of the streaming limb kernel (csrc/k_limbs3.cuh, IBP_LIMBS_STREAM3=1, read once per process): the
+def test_two_ctas_per_sm_limb_kernel_in_subprocess():
+    """limbs_stream_kernel (two CTAs per SM) serves host sources; with IBP_LIMBS_NO_STREAM3 (read once per process) it
+    takes the device-resident batches as well, which limbs_stream3_kernel (csrc/k_limbs3.cuh) handles by default: the
     streaming tests of this module once more on that kernel, in a process of its own."""
     import os
     import subprocess
     import sys
-    if os.environ.get("IBP_LIMBS_STREAM3"):
-        pytest.skip("already inside the run with the three-CTA kernel")
-    env = dict(os.environ, IBP_LIMBS_STREAM3="1")
+    if os.environ.get("IBP_LIMBS_NO_STREAM3"):
+        pytest.skip("already inside the run without the three-CTA kernel")
+    env = dict(os.environ, IBP_LIMBS_NO_STREAM3="1")
     res = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-m", "gpu", "-q", "-x", "-k",
                           "streaming_kernels or stress or crowded_limbs or bench_workload"],
                          env=env, capture_output=True, text=True, timeout=1500)
