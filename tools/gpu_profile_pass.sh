@@ -20,7 +20,7 @@ for w in $which; do
     case $w in configs1) key=configs1@64 ;; configs3) key=configs3@64 ;; configs2) key=configs2@64 ;; esac
     specs="$specs $rep:$key"
     case $w in
-        configs1) ks="peaks_stream_kernel index_bands_kernel limbs_stream_kernel" ;;
+        configs1) ks="peaks_stream_kernel index_bands_kernel limbs_stream3_kernel" ;;
         configs3) ks="peaks_kernel limbs_kernel" ;;
         configs2) ks="fuse_multiscale fuse_linear gauss_smooth py_connections_kernel py_humans_kernel" ;;
     esac

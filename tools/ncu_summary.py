@@ -12,7 +12,7 @@ import subprocess
 import sys
 
 # bench.py's stage names; checked in this order (first match wins)
-SHORT = [("peaks_stream_kernel", "peaks"), ("index_bands_kernel", "index"), ("limbs_stream_kernel", "limbs"), ("fuse_multiscale_kernel", "fuse"),
+SHORT = [("peaks_stream_kernel", "peaks"), ("index_bands_kernel", "index"), ("limbs_stream3_kernel", "limbs"), ("limbs_stream_kernel", "limbs"), ("fuse_multiscale_kernel", "fuse"),
          ("fuse_strip_kernel", "fuse_strip"), ("fuse_linear_kernel", "fuse_linear"), ("gauss_smooth_kernel", "smooth"),
          ("py_connections_kernel", "py_connections"), ("py_humans_kernel", "py_humans"), ("limbs_kernel", "limbs"), ("peaks_kernel", "peaks")]
 
